@@ -1,0 +1,118 @@
+"""ctypes binding of libarena_gpuacct.so (include/arena_gpuacct.h, arena_top.h).
+
+There is no fallback: if the library is missing, or CUDA is, the calls raise.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libarena_gpuacct.so")
+
+ARENA_NONE = 0xFFFFFFFF
+
+
+class ArenaError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"arena_gpuacct error {code}: {msg}")
+        self.code = code
+
+
+class SnapshotView(C.Structure):
+    """struct arena_snapshot_view"""
+    _fields_ = [
+        ("n_pods", C.c_uint64), ("n_containers", C.c_uint64),
+        ("n_nodes", C.c_uint64), ("n_jobs", C.c_uint64),
+        ("pod_node", C.c_void_p), ("pod_phase", C.c_void_p), ("pod_ctr_begin", C.c_void_p),
+        ("ctr_val", C.c_void_p), ("ctr_scale", C.c_void_p),
+        ("node_cap_val", C.c_void_p), ("node_cap_scale", C.c_void_p),
+        ("pod_job", C.c_void_p), ("pod_role", C.c_void_p), ("pod_created", C.c_void_p),
+    ]
+
+
+class SynthParams(C.Structure):
+    """struct arena_synth_params"""
+    _fields_ = [
+        ("n_pods", C.c_uint64), ("n_nodes", C.c_uint64), ("n_jobs", C.c_uint64), ("seed", C.c_uint64),
+        ("skewed", C.c_int), ("grouped", C.c_int), ("pinned", C.c_int), ("threads", C.c_int),
+    ]
+
+
+_lib = None
+
+# every symbol the two headers declare: (name, restype, argtypes)
+_VP = C.c_void_p
+_SIGS = [
+    ("arena_acct_init", C.c_int, [C.c_int]),
+    ("arena_acct_shutdown", None, []),
+    ("arena_acct_device", C.c_int, []),
+    ("arena_acct_sm_count", C.c_int, []),
+    ("arena_last_error", C.c_char_p, []),
+    ("arena_snapshot_upload", C.c_int, [C.POINTER(SnapshotView), C.POINTER(_VP)]),
+    ("arena_snapshot_wrap_device", C.c_int, [C.POINTER(SnapshotView), C.POINTER(_VP)]),
+    ("arena_snapshot_free", None, [_VP]),
+    ("arena_top_node", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_node_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_node_host", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP]),
+    ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    ("arena_quantity_values", C.c_int, [_VP, _VP, C.c_uint64, _VP]),
+    ("arena_kernel_launches", C.c_uint64, []),
+    ("arena_profile_begin", C.c_int, [C.c_int]),
+    ("arena_profile_end", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
+    # arena_top.h
+    ("arena_host_snapshot_free", None, [_VP]),
+    ("arena_host_snapshot_view", C.c_int, [_VP, C.POINTER(SnapshotView)]),
+    ("arena_load_json", C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
+                                  C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(_VP)]),
+    ("arena_host_pod_order", _VP, [_VP]),
+    ("arena_host_job_name", C.c_char_p, [_VP, C.c_uint32]),
+    ("arena_host_job_trainer", C.c_char_p, [_VP, C.c_uint32]),
+    ("arena_host_node_name", C.c_char_p, [_VP, C.c_uint32]),
+    ("arena_quantity_parse", C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                       C.POINTER(C.c_int32), C.POINTER(C.c_int)]),
+    ("arena_format_top_node", C.c_int, [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
+    ("arena_format_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int64, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
+    ("arena_free_text", None, [_VP]),
+    ("arena_synth_snapshot", C.c_int, [C.POINTER(SynthParams), C.POINTER(_VP)]),
+    ("arena_shard_plan", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.c_int, _VP, _VP]),
+    ("arena_shard_extract", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64,
+                                      C.c_uint64, C.POINTER(_VP)]),
+]
+
+DECLARED_SYMBOLS = [s[0] for s in _SIGS]
+
+
+def lib():
+    """Load the shared library (built in-tree by __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ArenaError(-2, f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                 "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, res, args in _SIGS:
+            fn = getattr(L, name, None)
+            if fn is None:      # TEMPORARY while the loader/printers are being written
+                continue
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise ArenaError(rc, lib().arena_last_error().decode("utf-8", "replace"))
+
+
+_initialised_device = None
+
+
+def init(device: int = 0) -> None:
+    """arena_acct_init: bind this process to one GPU (idempotent)."""
+    global _initialised_device
+    check(lib().arena_acct_init(int(device)))
+    _initialised_device = int(device)

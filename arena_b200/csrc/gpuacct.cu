@@ -1,0 +1,572 @@
+// C ABI of libarena_gpuacct.so (see include/arena_gpuacct.h): device context,
+// snapshot handles and kernel launches.  No torch types, no CPU fallback: if
+// CUDA is unavailable every entry point fails with ARENA_E_CUDA / NOT_INIT.
+#include "../../include/arena_gpuacct.h"
+#include "kernels.cuh"
+#include "host_snapshot.h"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+using namespace arena;
+
+namespace {
+
+using arena_host::fail;
+
+#define CUDA_TRY(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (expr);                                                         \
+        if (e_ != cudaSuccess)                                                           \
+            return fail(ARENA_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                             \
+    } while (0)
+
+struct Context {
+    bool ready = false;
+    int device = -1;
+    int sm_count = 0;
+    int pods_ctas_per_sm = 0;
+    int jobs_ctas_per_sm = 0;
+    cudaStream_t stream = nullptr;
+};
+
+Context g_ctx;
+std::mutex g_mu;
+std::atomic<uint64_t> g_launches{0};
+
+inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// Optional per-kernel timing for bench.py's roofline: CUDA events recorded on
+// the launch stream around the nodes kernel and the pods kernel of every
+// arena_top_node*() call between arena_profile_begin() and arena_profile_end().
+struct Profile {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;     // 3 per call: before nodes, between, after pods
+    size_t used = 0;
+};
+Profile g_prof;
+
+size_t pad16(size_t n) { return (n + 15) & ~(size_t)15; }
+
+}  // namespace
+
+// Device-resident snapshot.  `owned` columns were allocated by upload().
+struct arena_snapshot {
+    arena_snapshot_view v{};     // device pointers
+    bool owns = false;
+    void *block = nullptr;       // single allocation holding all owned columns
+    Scratch *scratch = nullptr;  // per-handle: distinct handles may run concurrently
+    // top job work arrays (allocated on first use)
+    u64 *job_req = nullptr, *job_alloc = nullptr;
+    i64 *job_maxcreated = nullptr;
+    unsigned *job_latest = nullptr;
+    u64 *sort_key = nullptr;
+    unsigned *sort_idx = nullptr;
+    u64 jpad = 0;
+    // device output staging for the host-output entry points
+    i64 *d_out = nullptr;
+    size_t d_out_bytes = 0;
+};
+
+extern "C" {
+
+uint64_t arena_kernel_launches(void) { return g_launches.load(); }
+
+int arena_acct_init(int device)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_ctx.ready) {
+        if (g_ctx.device == device) return ARENA_OK;
+        return fail(ARENA_E_INVALID, "already initialised on device %d", g_ctx.device);
+    }
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(ARENA_E_INVALID, "device %d out of range (have %d)", device, n);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(ARENA_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                    prop.major, prop.minor);
+    g_ctx.device = device;
+    g_ctx.sm_count = prop.multiProcessorCount;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, pods_kernel<false>, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, pods_kernel<true>, kThreads, 0));
+    if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1)
+        return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
+    CUDA_TRY(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    g_ctx.ready = true;
+    return ARENA_OK;
+}
+
+void arena_acct_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx.ready) return;
+    cudaSetDevice(g_ctx.device);
+    cudaStreamSynchronize(g_ctx.stream);
+    cudaStreamDestroy(g_ctx.stream);
+    g_ctx = Context{};
+}
+
+int arena_acct_device(void) { return g_ctx.ready ? g_ctx.device : (int)ARENA_E_NOT_INIT; }
+int arena_acct_sm_count(void) { return g_ctx.ready ? g_ctx.sm_count : (int)ARENA_E_NOT_INIT; }
+
+}  // extern "C"
+
+namespace {
+
+int check_ready()
+{
+    if (!g_ctx.ready) return fail(ARENA_E_NOT_INIT, "arena_acct_init() has not been called");
+    cudaError_t e = cudaSetDevice(g_ctx.device);
+    if (e != cudaSuccess) return fail(ARENA_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return ARENA_OK;
+}
+
+int check_view(const arena_snapshot_view *v, bool device_ptrs)
+{
+    if (!v) return fail(ARENA_E_INVALID, "snapshot view is NULL");
+    if (v->n_pods >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_pods %llu >= 2^32-1", (unsigned long long)v->n_pods);
+    if (v->n_containers > 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_containers exceeds u32 offsets");
+    if (v->n_nodes >= 0xFFFFFFFFull || v->n_jobs >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_nodes / n_jobs >= 2^32-1");
+    if (!v->pod_ctr_begin) return fail(ARENA_E_INVALID, "pod_ctr_begin is NULL (needs P+1 entries even when P == 0)");
+    if (v->n_pods && (!v->pod_node || !v->pod_phase)) return fail(ARENA_E_INVALID, "pod columns are NULL");
+    if (v->n_containers && (!v->ctr_val || !v->ctr_scale)) return fail(ARENA_E_INVALID, "container columns are NULL");
+    if (v->n_nodes && (!v->node_cap_val || !v->node_cap_scale)) return fail(ARENA_E_INVALID, "node columns are NULL");
+    if (v->n_jobs && v->n_pods && (!v->pod_job || !v->pod_role || !v->pod_created))
+        return fail(ARENA_E_INVALID, "n_jobs > 0 but the job columns are NULL");
+    const void *cols[] = {v->pod_node, v->pod_phase, v->pod_ctr_begin, v->ctr_val, v->ctr_scale,
+                          v->node_cap_val, v->node_cap_scale, v->pod_job, v->pod_role, v->pod_created};
+    if (device_ptrs)       // the kernels issue 128-bit loads on these; upload() re-aligns host columns
+        for (const void *p : cols)
+            if (((uintptr_t)p & 15) != 0) return fail(ARENA_E_INVALID, "a device column is not 16-byte aligned");
+    return ARENA_OK;
+}
+
+int alloc_common(arena_snapshot *s)
+{
+    CUDA_TRY(cudaMalloc((void **)&s->scratch, sizeof(Scratch)));
+    CUDA_TRY(cudaMemsetAsync(s->scratch, 0, sizeof(Scratch), g_ctx.stream));
+    return ARENA_OK;
+}
+
+int grid_for(u64 work_items, u64 items_per_cta, int ctas_per_sm)
+{
+    u64 want = (work_items + items_per_cta - 1) / items_per_cta;
+    u64 cap = (u64)g_ctx.sm_count * (u64)ctas_per_sm;      // one resident wave: persistent CTAs
+    if (cap > (u64)kMaxPartials) cap = kMaxPartials;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
+int ensure_out(arena_snapshot *s, size_t bytes)
+{
+    if (s->d_out_bytes >= bytes) return ARENA_OK;
+    if (s->d_out) cudaFree(s->d_out);
+    s->d_out = nullptr;
+    s->d_out_bytes = 0;
+    CUDA_TRY(cudaMalloc((void **)&s->d_out, bytes));
+    s->d_out_bytes = bytes;
+    return ARENA_OK;
+}
+
+int ensure_job_arrays(arena_snapshot *s)
+{
+    if (s->job_req) return ARENA_OK;
+    u64 J = s->v.n_jobs;
+    u64 jpad = kSortTile;
+    while (jpad < J) jpad <<= 1;
+    size_t bytes = pad16(J * 8) * 3 + pad16(J * 4) + pad16(jpad * 8) + pad16(jpad * 4);
+    char *base = nullptr;
+    CUDA_TRY(cudaMalloc((void **)&base, bytes ? bytes : 16));
+    char *p = base;
+    s->job_req = (u64 *)p; p += pad16(J * 8);
+    s->job_alloc = (u64 *)p; p += pad16(J * 8);
+    s->job_maxcreated = (i64 *)p; p += pad16(J * 8);
+    s->sort_key = (u64 *)p; p += pad16(jpad * 8);
+    s->job_latest = (unsigned *)p; p += pad16(J * 4);
+    s->sort_idx = (unsigned *)p;
+    s->jpad = jpad;
+    return ARENA_OK;
+}
+
+int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_cluster, i64 *d_pod_gpu,
+                    cudaStream_t st)
+{
+    const arena_snapshot_view &v = s->v;
+    NodesArgs na;
+    na.N = v.n_nodes;
+    na.cap_val = (const i64 *)v.node_cap_val;
+    na.cap_scale = (const signed char *)v.node_cap_scale;
+    na.node_total = d_total;
+    na.node_alloc = (u64 *)d_alloc;
+    na.cluster_total = d_cluster;
+    na.scratch = s->scratch;
+    const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
+    cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
+    if (prof) { g_prof.used += 3; cudaEventRecord(pe[0], st); }
+    int gn = grid_for(v.n_nodes, kThreads * 4, 8);
+    top_node_nodes_kernel<<<gn, kThreads, 0, st>>>(na);
+    count_launch();
+    if (prof) cudaEventRecord(pe[1], st);
+
+    PodsArgs pa{};
+    pa.P = v.n_pods; pa.C = v.n_containers; pa.K = v.n_nodes;
+    pa.pod_key = v.pod_node;
+    pa.pod_phase = v.pod_phase;
+    pa.pod_ctr_begin = v.pod_ctr_begin;
+    pa.ctr_val = (const i64 *)v.ctr_val;
+    pa.ctr_scale = (const signed char *)v.ctr_scale;
+    pa.key_alloc = (u64 *)d_alloc;
+    pa.pod_gpu = d_pod_gpu;
+    pa.total_alloc = d_cluster + 1;
+    pa.scratch = s->scratch;
+    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
+    pods_kernel<false><<<gp, kThreads, 0, st>>>(pa);
+    count_launch();
+    if (prof) cudaEventRecord(pe[2], st);
+    CUDA_TRY(cudaGetLastError());
+    return ARENA_OK;
+}
+
+int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_order, unsigned *d_latest,
+                   i64 *d_totals, cudaStream_t st)
+{
+    const arena_snapshot_view &v = s->v;
+    int rc = ensure_job_arrays(s);
+    if (rc) return rc;
+    const u64 J = v.n_jobs;
+
+    JobInitArgs ia{J, s->job_req, s->job_alloc, s->job_maxcreated, s->job_latest};
+    job_init_kernel<<<grid_for(J, kThreads * 4, 8), kThreads, 0, st>>>(ia);
+    count_launch();
+
+    PodsArgs pa{};
+    pa.P = v.n_pods; pa.C = v.n_containers; pa.K = J;
+    pa.pod_key = v.pod_job;
+    pa.pod_phase = v.pod_phase;
+    pa.pod_ctr_begin = v.pod_ctr_begin;
+    pa.ctr_val = (const i64 *)v.ctr_val;
+    pa.ctr_scale = (const signed char *)v.ctr_scale;
+    pa.pod_role = v.pod_role;
+    pa.pod_created = (const i64 *)v.pod_created;
+    pa.key_alloc = s->job_alloc;
+    pa.key_req = s->job_req;
+    pa.key_maxcreated = s->job_maxcreated;
+    pa.total_req = d_totals;
+    pa.total_alloc = d_totals + 1;
+    pa.scratch = s->scratch;
+    pods_kernel<true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
+    count_launch();
+
+    if (v.n_pods) {
+        JobLatestArgs la{v.n_pods, J, v.pod_job, v.pod_role, (const i64 *)v.pod_created, s->job_maxcreated,
+                         s->job_latest};
+        job_latest_kernel<<<grid_for(v.n_pods, kThreads * 8, 8), kThreads, 0, st>>>(la);
+        count_launch();
+    }
+
+    JobFinishArgs fa;
+    fa.J = J; fa.Jpad = s->jpad;
+    fa.job_latest = s->job_latest;
+    fa.pod_phase = v.pod_phase;
+    fa.pod_ctr_begin = v.pod_ctr_begin;
+    fa.ctr_val = (const i64 *)v.ctr_val;
+    fa.ctr_scale = (const signed char *)v.ctr_scale;
+    fa.job_req = s->job_req; fa.job_alloc = s->job_alloc;
+    fa.sort_key = s->sort_key; fa.sort_idx = s->sort_idx;
+    fa.totals = d_totals;
+    fa.scratch = s->scratch;
+    job_finish_kernel<<<grid_for(s->jpad, kThreads, 8), kThreads, 0, st>>>(fa);
+    count_launch();
+
+    // sort (requested desc, id asc)
+    const u64 n = s->jpad;
+    const int tiles = (int)(n / kSortTile);
+    bitonic_tile_kernel<<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, 0, 1);
+    count_launch();
+    for (u64 k = 2 * (u64)kSortTile; k <= n; k <<= 1) {
+        for (u64 j = k >> 1; j >= (u64)kSortTile; j >>= 1) {
+            bitonic_global_kernel<<<grid_for(n / 2, kThreads, 8), kThreads, 0, st>>>(s->sort_key, s->sort_idx, n, k, j);
+            count_launch();
+        }
+        bitonic_tile_kernel<<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, k, 0);
+        count_launch();
+    }
+    CUDA_TRY(cudaGetLastError());
+    if (J) {
+        CUDA_TRY(cudaMemcpyAsync(d_req, s->job_req, J * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_alloc, s->job_alloc, J * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_order, s->sort_idx, J * 4, cudaMemcpyDeviceToDevice, st));
+        if (d_latest) CUDA_TRY(cudaMemcpyAsync(d_latest, s->job_latest, J * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return ARENA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    rc = check_view(h, false);
+    if (rc) return rc;
+    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
+    const bool jobs = h->n_jobs > 0 && h->pod_job;
+    arena_snapshot *s = new (std::nothrow) arena_snapshot();
+    if (!s) return fail(ARENA_E_NOMEM, "out of host memory");
+    s->owns = true;
+    s->v = *h;
+    // one allocation, every column padded to 16 bytes (plus one spare vector so
+    // that aligned 128-bit reads never leave the allocation)
+    size_t sizes[10] = {P * 4, P, (P + 1) * 4, C * 8, C, N * 8, N, jobs ? P * 4 : 0, jobs ? P : 0, jobs ? P * 8 : 0};
+    const void *src[10] = {h->pod_node, h->pod_phase, h->pod_ctr_begin, h->ctr_val, h->ctr_scale,
+                           h->node_cap_val, h->node_cap_scale, h->pod_job, h->pod_role, h->pod_created};
+    size_t total = 0;
+    for (size_t z : sizes) total += pad16(z) + 16;
+    cudaError_t e = cudaMalloc(&s->block, total ? total : 16);
+    if (e != cudaSuccess) {
+        delete s;
+        return fail(e == cudaErrorMemoryAllocation ? ARENA_E_NOMEM : ARENA_E_CUDA, "cudaMalloc(%zu): %s", total,
+                    cudaGetErrorString(e));
+    }
+    char *p = (char *)s->block;
+    const void *dst[10];
+    for (int i = 0; i < 10; i++) {
+        dst[i] = p;
+        if (sizes[i]) {
+            e = cudaMemcpyAsync(p, src[i], sizes[i], cudaMemcpyHostToDevice, g_ctx.stream);
+            if (e != cudaSuccess) {
+                cudaFree(s->block);
+                delete s;
+                return fail(ARENA_E_CUDA, "H2D copy of column %d: %s", i, cudaGetErrorString(e));
+            }
+        }
+        p += pad16(sizes[i]) + 16;
+    }
+    s->v.pod_node = (const uint32_t *)dst[0];
+    s->v.pod_phase = (const uint8_t *)dst[1];
+    s->v.pod_ctr_begin = (const uint32_t *)dst[2];
+    s->v.ctr_val = (const int64_t *)dst[3];
+    s->v.ctr_scale = (const int8_t *)dst[4];
+    s->v.node_cap_val = (const int64_t *)dst[5];
+    s->v.node_cap_scale = (const int8_t *)dst[6];
+    s->v.pod_job = jobs ? (const uint32_t *)dst[7] : nullptr;
+    s->v.pod_role = jobs ? (const uint8_t *)dst[8] : nullptr;
+    s->v.pod_created = jobs ? (const int64_t *)dst[9] : nullptr;
+    if (!jobs) s->v.n_jobs = 0;
+    rc = alloc_common(s);
+    if (rc) { arena_snapshot_free(s); return rc; }
+    e = cudaStreamSynchronize(g_ctx.stream);     // host buffers may be reused on return
+    if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "upload: %s", cudaGetErrorString(e)); }
+    *out = s;
+    return ARENA_OK;
+}
+
+int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    rc = check_view(d, true);
+    if (rc) return rc;
+    arena_snapshot *s = new (std::nothrow) arena_snapshot();
+    if (!s) return fail(ARENA_E_NOMEM, "out of host memory");
+    s->v = *d;
+    if (!d->pod_job) s->v.n_jobs = 0;
+    rc = alloc_common(s);
+    if (rc) { arena_snapshot_free(s); return rc; }
+    cudaError_t e = cudaStreamSynchronize(g_ctx.stream);
+    if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "wrap: %s", cudaGetErrorString(e)); }
+    *out = s;
+    return ARENA_OK;
+}
+
+void arena_snapshot_free(arena_snapshot *s)
+{
+    if (!s) return;
+    if (g_ctx.ready) cudaSetDevice(g_ctx.device);
+    if (s->owns && s->block) cudaFree(s->block);
+    if (s->scratch) cudaFree(s->scratch);
+    if (s->job_req) cudaFree(s->job_req);
+    if (s->d_out) cudaFree(s->d_out);
+    delete s;
+}
+
+int arena_top_node_device(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                          int64_t *d_cluster, int64_t *d_pod_gpu, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!s || !d_cluster) return fail(ARENA_E_INVALID, "snapshot or d_cluster is NULL");
+    if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    if (((uintptr_t)d_pod_gpu & 15) != 0) return fail(ARENA_E_INVALID, "d_pod_gpu is not 16-byte aligned");
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, (i64 *)d_pod_gpu, st);
+}
+
+int arena_top_node(const arena_snapshot *cs, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2],
+                   int64_t *pod_gpu)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!cs || !cluster) return fail(ARENA_E_INVALID, "snapshot or cluster is NULL");
+    arena_snapshot *s = const_cast<arena_snapshot *>(cs);
+    const u64 N = s->v.n_nodes, P = s->v.n_pods;
+    if (N && (!node_total || !node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    size_t bytes = 16 + pad16(N * 8) * 2 + (pod_gpu ? pad16(P * 8) : 0);
+    rc = ensure_out(s, bytes);
+    if (rc) return rc;
+    char *base = (char *)s->d_out;
+    i64 *d_cluster = (i64 *)base;
+    i64 *d_total = (i64 *)(base + 16);
+    i64 *d_alloc = (i64 *)(base + 16 + pad16(N * 8));
+    i64 *d_pg = pod_gpu ? (i64 *)(base + 16 + 2 * pad16(N * 8)) : nullptr;
+    cudaStream_t st = g_ctx.stream;
+    rc = launch_top_node(s, d_total, d_alloc, d_cluster, d_pg, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(cluster, d_cluster, 16, cudaMemcpyDeviceToHost, st));
+    if (N) {
+        CUDA_TRY(cudaMemcpyAsync(node_total, d_total, N * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(node_alloc, d_alloc, N * 8, cudaMemcpyDeviceToHost, st));
+    }
+    if (pod_gpu && P) CUDA_TRY(cudaMemcpyAsync(pod_gpu, d_pg, P * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return ARENA_OK;
+}
+
+int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, int64_t *node_alloc,
+                        int64_t cluster[2], int64_t *pod_gpu)
+{
+    arena_snapshot *s = nullptr;
+    arena_snapshot_view v = *host;
+    v.n_jobs = 0; v.pod_job = nullptr; v.pod_role = nullptr; v.pod_created = nullptr;
+    int rc = arena_snapshot_upload(&v, &s);
+    if (rc) return rc;
+    rc = arena_top_node(s, node_total, node_alloc, cluster, pod_gpu);
+    arena_snapshot_free(s);
+    return rc;
+}
+
+int arena_top_job_device(const arena_snapshot *cs, int64_t *d_job_req, int64_t *d_job_alloc,
+                         uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!cs || !d_totals) return fail(ARENA_E_INVALID, "snapshot or d_totals is NULL");
+    arena_snapshot *s = const_cast<arena_snapshot *>(cs);
+    if (s->v.n_pods && !s->v.pod_job) return fail(ARENA_E_INVALID, "snapshot has no job columns");
+    if (s->v.n_jobs && (!d_job_req || !d_job_alloc || !d_job_order)) return fail(ARENA_E_INVALID, "job output buffers are NULL");
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    return launch_top_job(s, (i64 *)d_job_req, (i64 *)d_job_alloc, d_job_order, d_job_latest, (i64 *)d_totals, st);
+}
+
+int arena_top_job(const arena_snapshot *cs, int64_t *job_req, int64_t *job_alloc, uint32_t *job_order,
+                  uint32_t *job_latest, int64_t totals[2])
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!cs || !totals) return fail(ARENA_E_INVALID, "snapshot or totals is NULL");
+    arena_snapshot *s = const_cast<arena_snapshot *>(cs);
+    const u64 J = s->v.n_jobs;
+    if (s->v.n_pods && J && !s->v.pod_job) return fail(ARENA_E_INVALID, "snapshot has no job columns");
+    if (J && (!job_req || !job_alloc || !job_order)) return fail(ARENA_E_INVALID, "job output buffers are NULL");
+    size_t bytes = 16 + pad16(J * 8) * 2 + pad16(J * 4) * 2;
+    rc = ensure_out(s, bytes);
+    if (rc) return rc;
+    char *base = (char *)s->d_out;
+    i64 *d_totals = (i64 *)base;
+    i64 *d_req = (i64 *)(base + 16);
+    i64 *d_alloc = (i64 *)(base + 16 + pad16(J * 8));
+    unsigned *d_order = (unsigned *)(base + 16 + 2 * pad16(J * 8));
+    unsigned *d_latest = (unsigned *)(base + 16 + 2 * pad16(J * 8) + pad16(J * 4));
+    cudaStream_t st = g_ctx.stream;
+    rc = launch_top_job(s, d_req, d_alloc, d_order, d_latest, d_totals, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(totals, d_totals, 16, cudaMemcpyDeviceToHost, st));
+    if (J) {
+        CUDA_TRY(cudaMemcpyAsync(job_req, d_req, J * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(job_alloc, d_alloc, J * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(job_order, d_order, J * 4, cudaMemcpyDeviceToHost, st));
+        if (job_latest) CUDA_TRY(cudaMemcpyAsync(job_latest, d_latest, J * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return ARENA_OK;
+}
+
+int arena_profile_begin(int max_calls)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (max_calls < 1 || max_calls > (1 << 20)) return fail(ARENA_E_INVALID, "max_calls out of range");
+    for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
+    g_prof.ev.assign((size_t)max_calls * 3, nullptr);
+    for (auto &e : g_prof.ev) CUDA_TRY(cudaEventCreate(&e));
+    g_prof.used = 0;
+    g_prof.on = true;
+    return ARENA_OK;
+}
+
+int arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *calls)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    g_prof.on = false;
+    double a = 0, b = 0;
+    uint64_t n = g_prof.used / 3;
+    for (uint64_t i = 0; i < n; i++) {
+        float ms = 0;
+        CUDA_TRY(cudaEventSynchronize(g_prof.ev[3 * i + 2]));
+        CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.ev[3 * i], g_prof.ev[3 * i + 1]));
+        a += ms;
+        CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.ev[3 * i + 1], g_prof.ev[3 * i + 2]));
+        b += ms;
+    }
+    for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
+    g_prof.ev.clear();
+    g_prof.used = 0;
+    if (nodes_ms_sum) *nodes_ms_sum = a;
+    if (pods_ms_sum) *pods_ms_sum = b;
+    if (calls) *calls = n;
+    return ARENA_OK;
+}
+
+int arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, int64_t *out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (n == 0) return ARENA_OK;
+    if (!val || !scale || !out) return fail(ARENA_E_INVALID, "NULL argument");
+    char *d = nullptr;
+    CUDA_TRY(cudaMalloc((void **)&d, pad16(n * 8) * 2 + pad16(n)));
+    i64 *dv = (i64 *)d;
+    i64 *dout = (i64 *)(d + pad16(n * 8));
+    signed char *ds = (signed char *)(d + 2 * pad16(n * 8));
+    cudaStream_t st = g_ctx.stream;
+    cudaError_t e = cudaMemcpyAsync(dv, val, n * 8, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ds, scale, n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        quantity_values_kernel<<<grid_for(n, kThreads, 8), kThreads, 0, st>>>(dv, ds, n, dout);
+        count_launch();
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout, n * 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(ARENA_E_CUDA, "arena_quantity_values: %s", cudaGetErrorString(e));
+    return ARENA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,50 @@
+// Host-resident snapshot shared by the loader, the synthetic generators, the
+// sharder and the printers.
+#pragma once
+#include "../../include/arena_top.h"
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace arena_host {
+
+int fail(int code, const char *fmt, ...);   // sets arena_last_error() text (gpuacct.cu owns the buffer)
+
+// 64-byte aligned (optionally page-locked) raw column storage.
+struct Column {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+    bool pinned = false;
+    Column() = default;
+    Column(const Column &) = delete;
+    Column &operator=(const Column &) = delete;
+    ~Column();
+    int alloc(size_t nbytes, bool want_pinned);
+    template <class T> T *as() { return static_cast<T *>(ptr); }
+};
+
+struct JobMeta {
+    std::string name;          // helm release name
+    std::string ns;            // namespace from `helm list`
+    std::string trainer;       // "mpijob" | "standalonejob" | "tfjob"
+    std::string status;        // GetStatus() of the reference, from the job object
+    std::string chief_host_ip; // status.hostIP of the chief / job pod
+    bool has_start = false;
+    int64_t start_unix = 0;    // job.status.startTime
+};
+
+}  // namespace arena_host
+
+struct arena_host_snapshot {
+    arena_snapshot_view v{};
+    // owned columns (any may be empty when the view borrows from a parent)
+    arena_host::Column c_pod_node, c_pod_phase, c_pod_ctr_begin, c_ctr_val, c_ctr_scale, c_node_cap_val,
+        c_node_cap_scale, c_pod_job, c_pod_role, c_pod_created;
+    // names for the printers; empty for synthetic snapshots ("node-%07u")
+    std::vector<std::string> node_names, node_internal_ip, node_first_addr;
+    std::vector<uint8_t> node_has_addr, node_is_master;
+    std::vector<std::string> pod_names, pod_namespaces;   // in ROW order
+    std::vector<uint32_t> pod_order;                      // row -> PodList index
+    std::vector<arena_host::JobMeta> jobs;
+};

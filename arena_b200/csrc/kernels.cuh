@@ -1,0 +1,603 @@
+// Device code for the GPU accounting path (sm_100a).  HBM-bound integer work:
+// no tensor cores; the design rules are coalesced 128-bit loads, shared-memory
+// staging of prefix sums, warp shuffles, and few, spread-out atomics.
+//
+// Reference semantics (paths relative to /root/reference):
+//   quantity_value   vendor/k8s.io/apimachinery/pkg/api/resource/amount.go:95-101,
+//                    math.go:144-203 (and the dropped `ok`, quantity.go:713-714)
+//   pods kernel      cmd/arena/commands/gpu.go:39-79, pod_helper.go:15-31,
+//                    top_node.go:88-97, 232-242
+//   nodes kernel     gpu.go:18-37, top_node.go:115-118
+//   job kernels      job_info.go:51-70, trainer_mpi.go:241-282,
+//                    trainer_standalone.go:198-221, trainer.go:25-37
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace arena {
+
+typedef unsigned long long u64;
+typedef long long i64;
+
+constexpr unsigned kNone = 0xFFFFFFFFu;
+constexpr int kPhaseSucceeded = 3;
+constexpr int kPhaseFailed = 4;
+
+constexpr int kThreads = 256;              // 8 warps per CTA
+constexpr int kWarps = kThreads / 32;
+constexpr int kPodsPerLane = 4;            // one 128-bit load per u32 column
+constexpr int kWarpPods = 32 * kPodsPerLane;   // 128 pods per warp tile
+constexpr int kRowCtrs = 64;               // containers per row: 2 per lane, one 128-bit load
+constexpr int kRows = 4;                   // rows per chunk held in registers
+constexpr int kChunkCtrs = kRowCtrs * kRows;   // 256 containers -> 2 KB of prefix sums per warp
+constexpr int kMaxPartials = 4096;         // upper bound on CTAs per launch
+
+__device__ __constant__ i64 kPow10[19] = {
+    1ll, 10ll, 100ll, 1000ll, 10000ll, 100000ll, 1000000ll, 10000000ll, 100000000ll,
+    1000000000ll, 10000000000ll, 100000000000ll, 1000000000000ll, 10000000000000ll,
+    100000000000000ll, 1000000000000000ll, 10000000000000000ll, 100000000000000000ll,
+    1000000000000000000ll};
+
+// Quantity.Value() of int64Amount{v, s}.
+//   s < 0: divide by 10^-s, rounding AWAY from zero (negativeScaleInt64: the
+//          digit-by-digit loop is equivalent to one truncating division plus a
+//          +-1 when any remainder was dropped, including the early exit at 0).
+//   s > 0: multiply by 10^s; if the exact product does not fit int64 the
+//          reference returns (0,false) and the caller drops `ok` => 0.
+__device__ __noinline__ i64 quantity_value_slow(i64 v, int s)
+{
+    if (s < 0) {
+        int k = -s;
+        if (k > 18) return v > 0 ? 1 : (v < 0 ? -1 : 0);
+        i64 d = kPow10[k];
+        i64 q, r;
+        if (v >= -2147483647ll && v <= 2147483647ll && k <= 9) {   // cheap 32-bit divide
+            int vi = (int)v, di = (int)d;
+            int qi = vi / di;
+            q = qi;
+            r = vi - qi * di;
+        } else {
+            q = v / d;
+            r = v - q * d;
+        }
+        if (r != 0) q += v > 0 ? 1 : -1;
+        return q;
+    }
+    if (s > 18) return 0;
+    i64 m = kPow10[s];
+    i64 lo = (i64)((u64)v * (u64)m);
+    i64 hi = __mul64hi(v, m);
+    return hi == (lo >> 63) ? lo : 0;
+}
+
+__device__ __forceinline__ i64 quantity_value(i64 v, int s)
+{
+    if (s == 0) return v;
+    return quantity_value_slow(v, s);
+}
+
+__device__ __forceinline__ bool phase_active(unsigned ph)
+{
+    return ph != kPhaseSucceeded && ph != kPhaseFailed;
+}
+
+__device__ __forceinline__ u64 shfl_u64(u64 v, int src)
+{
+    return __shfl_sync(0xffffffffu, v, src);
+}
+
+// Inclusive warp scan of a u64 (wrapping adds).
+__device__ __forceinline__ u64 warp_inclusive_scan(u64 x, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        u64 y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    return x;
+}
+
+__device__ __forceinline__ u64 warp_reduce_sum(u64 x)
+{
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
+    return x;
+}
+
+__device__ __forceinline__ void red_add(u64 *p, u64 v)
+{
+    atomicAdd(p, v);   // result unused -> RED.E.ADD.64
+}
+
+// Streaming loads: read-only path, do not pollute L1 with data touched once.
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ ulonglong2 ldg_stream(const ulonglong2 *p)
+{
+    ulonglong2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
+                 : "=l"(r.x), "=l"(r.y) : "l"(p));
+    return r;
+}
+
+// Scratch shared by the kernels of one device context.  Tickets are left at 0
+// by the CTA that finishes last, so no launch needs a memset first.
+struct Scratch {
+    u64 partial_a[kMaxPartials];   // per-CTA partial of the first total
+    u64 partial_b[kMaxPartials];   // per-CTA partial of the second total
+    unsigned ticket[4];
+};
+
+// Last-CTA-done reduction of per-CTA partial sums into *out (and *out_b).
+// Every CTA calls this once with its partial(s) in thread 0.
+__device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two,
+                                              Scratch *sc, int ticket_id, i64 *out_a, i64 *out_b)
+{
+    __shared__ bool s_last;
+    if (threadIdx.x == 0) {
+        sc->partial_a[blockIdx.x] = block_a;
+        if (two) sc->partial_b[blockIdx.x] = block_b;
+        __threadfence();
+        unsigned t = atomicAdd(&sc->ticket[ticket_id], 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    u64 a = 0, b = 0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+        a += *((volatile u64 *)&sc->partial_a[i]);
+        if (two) b += *((volatile u64 *)&sc->partial_b[i]);
+    }
+    __shared__ u64 s_a[kWarps], s_b[kWarps];
+    a = warp_reduce_sum(a);
+    b = warp_reduce_sum(b);
+    if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u64 ta = 0, tb = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) { ta += s_a[w]; tb += s_b[w]; }
+        *out_a = (i64)ta;
+        if (two) *out_b = (i64)tb;
+        sc->ticket[ticket_id] = 0;      // ready for the next launch
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Nodes kernel: node_total[n] = Value(capacity), node_alloc[n] = 0, and the
+// cluster's total GPUs.  9N bytes read, 16N written.
+// ---------------------------------------------------------------------------
+struct NodesArgs {
+    u64 N;
+    const i64 *cap_val;
+    const signed char *cap_scale;
+    i64 *node_total;
+    u64 *node_alloc;
+    i64 *cluster_total;     // &cluster[0]
+    Scratch *scratch;
+};
+
+__global__ void __launch_bounds__(kThreads) top_node_nodes_kernel(NodesArgs a)
+{
+    u64 sum = 0;
+    for (u64 n = (u64)blockIdx.x * blockDim.x + threadIdx.x; n < a.N; n += (u64)gridDim.x * blockDim.x) {
+        i64 t = quantity_value(a.cap_val[n], a.cap_scale[n]);
+        a.node_total[n] = t;
+        a.node_alloc[n] = 0;
+        sum += (u64)t;
+    }
+    __shared__ u64 s_w[kWarps];
+    sum = warp_reduce_sum(sum);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    u64 block = 0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kWarps; w++) block += s_w[w];
+    finish_totals(block, 0, false, a.scratch, 0, a.cluster_total, nullptr);
+}
+
+// ---------------------------------------------------------------------------
+// Pods kernel.  One warp owns a tile of 128 consecutive pods:
+//
+//  1. 128-bit loads of the pod columns (4 pods per lane).
+//  2. The tile's containers are a contiguous range of the container columns
+//     (CSR).  They are read 64 per row -- one 128-bit load of two int64 values
+//     and one 16-bit load of two scales per lane, fully coalesced -- decoded
+//     with quantity_value, prefix-summed across the warp with shuffles, and the
+//     running EXCLUSIVE prefix sums are parked in the warp's 2 KB of shared
+//     memory.  gpuInPod(p) is then prefix[end(p)] - prefix[begin(p)]: two
+//     shared-memory reads per pod, no per-pod loop, any containers-per-pod.
+//  3. Per-key (node or job) sums use the same telescoping trick one level up:
+//     with S the inclusive prefix sum of the masked pod values over the tile,
+//     every position where the key changes adds +S to the key on the left and
+//     -S to the key on the right (and the tile end adds +S to the last key).
+//     Unsigned arithmetic wraps exactly like Go's int64 `+=`, so the result is
+//     bit-exact whatever the order of the atomics, and it is CORRECT for any
+//     pod order -- grouped input merely makes key changes (hence atomics) rare.
+//
+// kJob == false: key = pod_node, one sum (allocated GPUs), phase-masked.
+// kJob == true : key = pod_job, two sums (requested: unmasked; allocated:
+//                phase-masked); ARENA_ROLE_LATEST pods are left out of the sums
+//                and instead bid for "newest pod of the job" with atomicMax.
+// ---------------------------------------------------------------------------
+struct PodsArgs {
+    u64 P, C, K;                    // pods, containers, number of keys (N or J)
+    const unsigned *pod_key;        // pod_node or pod_job
+    const unsigned char *pod_phase;
+    const unsigned *pod_ctr_begin;
+    const i64 *ctr_val;
+    const signed char *ctr_scale;
+    const unsigned char *pod_role;  // kJob only
+    const i64 *pod_created;         // kJob only
+    u64 *key_alloc;                 // [K] pre-zeroed
+    u64 *key_req;                   // [K] pre-zeroed (kJob only)
+    i64 *key_maxcreated;            // [K] pre-set to INT64_MIN (kJob only)
+    i64 *pod_gpu;                   // [P] or nullptr
+    i64 *total_alloc;               // sum over keys of key_alloc
+    i64 *total_req;                 // kJob only
+    Scratch *scratch;
+};
+
+template <bool kJob>
+__global__ void __launch_bounds__(kThreads) pods_kernel(PodsArgs a)
+{
+    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
+    __shared__ u64 s_wa[kWarps], s_wb[kWarps];
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    u64 *prefix = s_prefix[warp];
+    const unsigned FULL = 0xffffffffu;
+
+    u64 acc_alloc = 0, acc_req = 0;       // lane 31 accumulates the tile totals
+
+    const u64 n_tiles = (a.P + kWarpPods - 1) / kWarpPods;
+    for (u64 tile = (u64)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (u64)gridDim.x * kWarps) {
+        const u64 q = tile * kWarpPods + (u64)lane * kPodsPerLane;
+
+        // ---- 1. pod columns ------------------------------------------------
+        unsigned cb[kPodsPerLane + 1], key[kPodsPerLane], ph[kPodsPerLane];
+        unsigned role[kPodsPerLane];
+        if ((tile + 1) * kWarpPods <= a.P) {                 // full tile: vector loads
+            uint4 c4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_ctr_begin + q));
+            uint4 k4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_key + q));
+            unsigned p4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_phase + q));
+            unsigned last = 0;
+            if (lane == 31) last = __ldg(a.pod_ctr_begin + q + kPodsPerLane);
+            unsigned r4 = 0;
+            if (kJob) r4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_role + q));
+            cb[0] = c4.x; cb[1] = c4.y; cb[2] = c4.z; cb[3] = c4.w;
+            key[0] = k4.x; key[1] = k4.y; key[2] = k4.z; key[3] = k4.w;
+            unsigned nxt = __shfl_down_sync(FULL, c4.x, 1);
+            cb[4] = lane == 31 ? last : nxt;
+#pragma unroll
+            for (int j = 0; j < kPodsPerLane; j++) {
+                ph[j] = (p4 >> (8 * j)) & 0xffu;
+                role[j] = (r4 >> (8 * j)) & 0xffu;
+            }
+        } else {                                             // ragged last tile
+#pragma unroll
+            for (int j = 0; j <= kPodsPerLane; j++) {
+                u64 i = q + j;
+                cb[j] = __ldg(a.pod_ctr_begin + (i < a.P ? i : a.P));
+            }
+#pragma unroll
+            for (int j = 0; j < kPodsPerLane; j++) {
+                u64 i = q + j;
+                bool in = i < a.P;
+                key[j] = in ? __ldg(a.pod_key + i) : kNone;
+                ph[j] = in ? (unsigned)__ldg(a.pod_phase + i) : 0u;
+                role[j] = (kJob && in) ? (unsigned)__ldg(a.pod_role + i) : 0u;
+            }
+        }
+
+        // ---- 2. container prefix sums --------------------------------------
+        const unsigned wc0 = __shfl_sync(FULL, cb[0], 0);
+        const unsigned wc1 = __shfl_sync(FULL, cb[kPodsPerLane], 31);
+        u64 B[kPodsPerLane + 1];
+#pragma unroll
+        for (int j = 0; j <= kPodsPerLane; j++) B[j] = 0;
+
+        if (wc1 > wc0) {
+            u64 carry = 0;
+            for (unsigned chunk_lo = wc0 & ~(unsigned)(kRowCtrs - 1); chunk_lo < wc1; chunk_lo += kChunkCtrs) {
+                ulonglong2 v[kRows];
+                unsigned sc[kRows];
+                // issue every load of the chunk before using any of them
+#pragma unroll
+                for (int r = 0; r < kRows; r++) {
+                    const unsigned rs = chunk_lo + r * kRowCtrs;
+                    const u64 idx = (u64)rs + 2u * lane;
+                    v[r].x = 0; v[r].y = 0; sc[r] = 0;
+                    if (rs < wc1) {
+                        if ((u64)rs + kRowCtrs <= a.C) {
+                            v[r] = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + idx));
+                            sc[r] = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + idx));
+                        } else {                              // row runs past the column end
+                            if (idx < a.C) {
+                                v[r].x = (u64)__ldg(a.ctr_val + idx);
+                                sc[r] = (unsigned char)__ldg(a.ctr_scale + idx);
+                            }
+                            if (idx + 1 < a.C) {
+                                v[r].y = (u64)__ldg(a.ctr_val + idx + 1);
+                                sc[r] |= (unsigned)(unsigned char)__ldg(a.ctr_scale + idx + 1) << 8;
+                            }
+                        }
+                    }
+                }
+                unsigned rows_done = 0;
+#pragma unroll
+                for (int r = 0; r < kRows; r++) {
+                    const unsigned rs = chunk_lo + r * kRowCtrs;
+                    if (rs < wc1) {                            // warp-uniform
+                        u64 x0 = (u64)quantity_value((i64)v[r].x, (int)(signed char)(sc[r] & 0xffu));
+                        u64 x1 = (u64)quantity_value((i64)v[r].y, (int)(signed char)((sc[r] >> 8) & 0xffu));
+                        u64 s = x0 + x1;
+                        u64 inc = warp_inclusive_scan(s, lane);
+                        u64 e0 = carry + inc - s;
+                        ulonglong2 e;
+                        e.x = e0;
+                        e.y = e0 + x0;
+                        *reinterpret_cast<ulonglong2 *>(prefix + r * kRowCtrs + 2 * lane) = e;
+                        carry += shfl_u64(inc, 31);
+                        if (lane == 31) prefix[(r + 1) * kRowCtrs] = carry;   // inclusive end of the row
+                        rows_done = r + 1;
+                    }
+                }
+                __syncwarp();
+                const unsigned n_valid = rows_done * kRowCtrs;
+#pragma unroll
+                for (int j = 0; j <= kPodsPerLane; j++) {
+                    unsigned off = cb[j] - chunk_lo;          // wraps when cb[j] < chunk_lo
+                    if (off <= n_valid) B[j] = prefix[off];
+                }
+                __syncwarp();
+            }
+        }
+
+        // ---- 3. pod values, masks, telescoping sums per key -----------------
+        u64 g[kPodsPerLane];
+#pragma unroll
+        for (int j = 0; j < kPodsPerLane; j++) g[j] = B[j + 1] - B[j];
+
+        if (a.pod_gpu != nullptr) {
+            if ((tile + 1) * kWarpPods <= a.P) {
+                ulonglong2 o0, o1;
+                o0.x = g[0]; o0.y = g[1]; o1.x = g[2]; o1.y = g[3];
+                ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(a.pod_gpu + q);
+                dst[0] = o0;
+                dst[1] = o1;
+            } else {
+#pragma unroll
+                for (int j = 0; j < kPodsPerLane; j++)
+                    if (q + j < a.P) a.pod_gpu[q + j] = (i64)g[j];
+            }
+        }
+
+        u64 S[kPodsPerLane], R[kPodsPerLane];
+        u64 run_a = 0, run_r = 0;
+#pragma unroll
+        for (int j = 0; j < kPodsPerLane; j++) {
+            const bool valid = key[j] < a.K;
+            bool counts = valid;
+            if (kJob) {
+                if (valid && role[j] == 1) {                  // bids for "latest pod of the job"
+                    counts = false;
+                    atomicMax(a.key_maxcreated + key[j], __ldg(a.pod_created + q + j));
+                }
+            }
+            const u64 req = counts ? g[j] : 0;
+            const u64 alc = (counts && phase_active(ph[j])) ? g[j] : 0;
+            run_a += alc;
+            S[j] = run_a;
+            if (kJob) { run_r += req; R[j] = run_r; }
+        }
+        {
+            u64 inc = warp_inclusive_scan(run_a, lane);
+            u64 off = inc - run_a;
+#pragma unroll
+            for (int j = 0; j < kPodsPerLane; j++) S[j] += off;
+            if (lane == 31) acc_alloc += inc;
+        }
+        if (kJob) {
+            u64 inc = warp_inclusive_scan(run_r, lane);
+            u64 off = inc - run_r;
+#pragma unroll
+            for (int j = 0; j < kPodsPerLane; j++) R[j] += off;
+            if (lane == 31) acc_req += inc;
+        }
+        unsigned key_next = __shfl_down_sync(FULL, key[0], 1);
+        if (lane == 31) key_next = kNone;
+#pragma unroll
+        for (int j = 0; j < kPodsPerLane; j++) {
+            const unsigned kl = key[j];
+            const unsigned kr = j + 1 < kPodsPerLane ? key[j + 1] : key_next;
+            const bool tile_end = (lane == 31 && j == kPodsPerLane - 1);
+            if (kl != kr || tile_end) {
+                if (kl < a.K) {
+                    red_add(a.key_alloc + kl, S[j]);
+                    if (kJob) red_add(a.key_req + kl, R[j]);
+                }
+                if (!tile_end && kr < a.K) {
+                    red_add(a.key_alloc + kr, 0ull - S[j]);
+                    if (kJob) red_add(a.key_req + kr, 0ull - R[j]);
+                }
+            }
+        }
+    }
+
+    // ---- totals over all keys: per-CTA partials, last CTA finishes ----------
+    if (lane == 31) { s_wa[warp] = acc_alloc; s_wb[warp] = acc_req; }
+    __syncthreads();
+    u64 block_a = 0, block_b = 0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_b += s_wb[w]; }
+    finish_totals(block_a, block_b, kJob, a.scratch, kJob ? 2 : 1, a.total_alloc, a.total_req);
+}
+
+// ---------------------------------------------------------------------------
+// top job helpers
+// ---------------------------------------------------------------------------
+struct JobInitArgs {
+    u64 J;
+    u64 *job_req, *job_alloc;
+    i64 *job_maxcreated;
+    unsigned *job_latest;
+};
+__global__ void job_init_kernel(JobInitArgs a)
+{
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < a.J; j += (u64)gridDim.x * blockDim.x) {
+        a.job_req[j] = 0;
+        a.job_alloc[j] = 0;
+        a.job_maxcreated[j] = (i64)0x8000000000000000ull;
+        a.job_latest[j] = kNone;
+    }
+}
+
+// Among ARENA_ROLE_LATEST pods whose timestamp equals the job's maximum, the
+// FIRST in list order wins (`latest.Before(current)` is strict,
+// trainer_mpi.go:271): atomicMin on the pod index.
+struct JobLatestArgs {
+    u64 P, J;
+    const unsigned *pod_job;
+    const unsigned char *pod_role;
+    const i64 *pod_created;
+    const i64 *job_maxcreated;
+    unsigned *job_latest;
+};
+__global__ void job_latest_kernel(JobLatestArgs a)
+{
+    for (u64 p = (u64)blockIdx.x * blockDim.x + threadIdx.x; p < a.P; p += (u64)gridDim.x * blockDim.x) {
+        if (a.pod_role[p] != 1) continue;
+        unsigned j = a.pod_job[p];
+        if (j >= a.J) continue;
+        if (a.pod_created[p] == a.job_maxcreated[j]) atomicMin(a.job_latest + j, (unsigned)p);
+    }
+}
+
+// Add the winning pod to its job, emit sort keys, and fold the winners into
+// the totals the pods kernel produced.
+struct JobFinishArgs {
+    u64 J, Jpad;
+    const unsigned *job_latest;
+    const unsigned char *pod_phase;
+    const unsigned *pod_ctr_begin;
+    const i64 *ctr_val;
+    const signed char *ctr_scale;
+    u64 *job_req, *job_alloc;
+    u64 *sort_key;          // [Jpad]
+    unsigned *sort_idx;     // [Jpad]
+    i64 *totals;            // {req, alloc}: in = sums of ROLE_COUNTS pods, out = full totals
+    Scratch *scratch;
+};
+__global__ void __launch_bounds__(kThreads) job_finish_kernel(JobFinishArgs a)
+{
+    u64 add_req = 0, add_alloc = 0;
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < a.Jpad; j += (u64)gridDim.x * blockDim.x) {
+        if (j >= a.J) {                      // padding sorts last
+            a.sort_key[j] = ~0ull;
+            a.sort_idx[j] = kNone;
+            continue;
+        }
+        u64 req = a.job_req[j], alc = a.job_alloc[j];
+        unsigned p = a.job_latest[j];
+        if (p != kNone) {
+            u64 g = 0;
+            for (unsigned c = a.pod_ctr_begin[p]; c < a.pod_ctr_begin[p + 1]; c++)
+                g += (u64)quantity_value(a.ctr_val[c], a.ctr_scale[c]);
+            req += g;
+            add_req += g;
+            if (phase_active(a.pod_phase[p])) { alc += g; add_alloc += g; }
+            a.job_req[j] = req;
+            a.job_alloc[j] = alc;
+        }
+        // requested DESC as an ascending unsigned key: flip sign bit, invert
+        a.sort_key[j] = ~(req ^ 0x8000000000000000ull);
+        a.sort_idx[j] = (unsigned)j;
+    }
+    __shared__ u64 s_a[kWarps], s_b[kWarps];
+    add_req = warp_reduce_sum(add_req);
+    add_alloc = warp_reduce_sum(add_alloc);
+    if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = add_req; s_b[threadIdx.x >> 5] = add_alloc; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u64 r = 0, al = 0;
+        for (int w = 0; w < kWarps; w++) { r += s_a[w]; al += s_b[w]; }
+        if (r) red_add((u64 *)&a.totals[0], r);
+        if (al) red_add((u64 *)&a.totals[1], al);
+    }
+}
+
+// Bitonic sort of (key, idx) pairs, ascending by key then idx: a total order,
+// so the result does not depend on the network being unstable.
+__device__ __forceinline__ bool pair_less(u64 ka, unsigned ia, u64 kb, unsigned ib)
+{
+    return ka < kb || (ka == kb && ia < ib);
+}
+
+constexpr int kSortTile = 2048;    // pairs per CTA in shared memory (24 KB)
+
+// Runs every compare-exchange step with distance < kSortTile of stage `k`
+// (or, when full_sort, all stages k = 2..kSortTile) inside shared memory.
+__global__ void __launch_bounds__(1024) bitonic_tile_kernel(u64 *key, unsigned *idx, u64 n, u64 k_stage, int full_sort)
+{
+    __shared__ u64 s_key[kSortTile];
+    __shared__ unsigned s_idx[kSortTile];
+    const u64 base = (u64)blockIdx.x * kSortTile;
+    for (int t = threadIdx.x; t < kSortTile; t += blockDim.x) {
+        s_key[t] = key[base + t];
+        s_idx[t] = idx[base + t];
+    }
+    __syncthreads();
+    u64 k_first = full_sort ? 2 : k_stage;
+    u64 k_last = full_sort ? (u64)kSortTile : k_stage;
+    for (u64 k = k_first; k <= k_last; k <<= 1) {
+        u64 j0 = k >> 1;
+        if (j0 >= (u64)kSortTile) j0 = kSortTile >> 1;
+        for (u64 j = j0; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < kSortTile / 2; t += blockDim.x) {
+                // t-th compare pair of distance j
+                unsigned lo = (unsigned)(((unsigned)t / (unsigned)j) * 2u * (unsigned)j + ((unsigned)t % (unsigned)j));
+                unsigned hi = lo + (unsigned)j;
+                bool up = (((base + lo) & k) == 0);
+                u64 ka = s_key[lo], kb = s_key[hi];
+                unsigned ia = s_idx[lo], ib = s_idx[hi];
+                bool swap = up ? pair_less(kb, ib, ka, ia) : pair_less(ka, ia, kb, ib);
+                if (swap) { s_key[lo] = kb; s_key[hi] = ka; s_idx[lo] = ib; s_idx[hi] = ia; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int t = threadIdx.x; t < kSortTile; t += blockDim.x) {
+        key[base + t] = s_key[t];
+        idx[base + t] = s_idx[t];
+    }
+}
+
+// One compare-exchange step of distance j >= kSortTile in global memory.
+__global__ void bitonic_global_kernel(u64 *key, unsigned *idx, u64 n, u64 k, u64 j)
+{
+    for (u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x; t < n / 2; t += (u64)gridDim.x * blockDim.x) {
+        u64 lo = (t / j) * 2 * j + (t % j);
+        u64 hi = lo + j;
+        bool up = ((lo & k) == 0);
+        u64 ka = key[lo], kb = key[hi];
+        unsigned ia = idx[lo], ib = idx[hi];
+        bool swap = up ? pair_less(kb, ib, ka, ia) : pair_less(ka, ia, kb, ib);
+        if (swap) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
+    }
+}
+
+// Quantity.Value() probe.
+__global__ void quantity_values_kernel(const i64 *val, const signed char *scale, u64 n, i64 *out)
+{
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        out[i] = quantity_value(val[i], scale[i]);
+}
+
+}  // namespace arena

@@ -1,0 +1,74 @@
+"""Multi-GPU driver: one process per GPU, node-range shards, one all-reduce.
+
+Nodes are independent and a pod only touches its own node, so a snapshot cut
+into contiguous node ranges (arena_shard_plan: about equal pod counts, cuts at
+node boundaries only) needs no data-path exchange: every rank produces a
+disjoint slice of the per-node table.  The only exchange is the pair of
+cluster totals {sum node_total, sum node_alloc} (top_node.go:109-118): one
+int64[2] all-reduce (NCCL over NVLink on GPUs, gloo in the CPU tests).
+Integer sums are order-independent, so any rank count gives identical bits.
+"""
+
+from __future__ import annotations
+
+import os
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def env_rank() -> Tuple[int, int, int]:
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def init_process_group(backend: Optional[str] = None) -> Tuple[int, int, int]:
+    """Initialise torch.distributed from the torchrun environment (idempotent)."""
+    rank, world, local = env_rank()
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kwargs = {}
+        if backend == "nccl":
+            kwargs["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kwargs)
+    return rank, world, local
+
+
+def all_reduce_totals(totals: torch.Tensor) -> torch.Tensor:
+    """Sum an int64[2] (or [4]) totals tensor over all ranks, in place.  With
+    one rank this is a no-op (no collective is issued)."""
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(totals, op=dist.ReduceOp.SUM)
+    return totals
+
+
+def gather_tables(local_total: np.ndarray, local_alloc: np.ndarray, dst: int = 0):
+    """Concatenate the per-rank slices of the node table on rank `dst` (the
+    ranks hold disjoint, ordered node ranges).  Returns (total, alloc) on dst,
+    (None, None) elsewhere."""
+    if not (dist.is_initialized() and dist.get_world_size() > 1):
+        return local_total, local_alloc
+    world, rank = dist.get_world_size(), dist.get_rank()
+    out: Optional[List] = [None] * world if rank == dst else None
+    dist.gather_object((local_total, local_alloc), out, dst=dst)
+    if rank != dst:
+        return None, None
+    return np.concatenate([o[0] for o in out]), np.concatenate([o[1] for o in out])
+
+
+def top_node_sharded(host_shard, details: bool = False):
+    """End-to-end sharded `top node` for this rank's shard (a HostSnapshot):
+    upload + kernels + download through the C ABI, then the totals all-reduce.
+    Returns (TopNodeResult of the shard, global cluster totals int64[2])."""
+    from .top import top_node
+    res = top_node(host_shard, details=details)
+    t = torch.from_numpy(res.cluster.copy())
+    if dist.is_initialized() and dist.get_world_size() > 1 and dist.get_backend() == "nccl":
+        t = t.cuda()
+    all_reduce_totals(t)
+    return res, t.cpu().numpy()

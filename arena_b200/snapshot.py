@@ -1,0 +1,224 @@
+"""Host / device snapshot handles over the C ABI.
+
+`HostSnapshot` is what the reference gets from its two List calls
+(cmd/arena/commands/pod_helper.go:15-43, top_node.go:71), in columnar form;
+`DeviceSnapshot` is the same data resident in HBM.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import numpy as np
+
+from . import _lib
+from ._lib import ArenaError, SnapshotView, SynthParams, check, lib
+
+_COLS = [
+    # name, dtype, length as a function of the view
+    ("pod_node", np.uint32, lambda v: v.n_pods),
+    ("pod_phase", np.uint8, lambda v: v.n_pods),
+    ("pod_ctr_begin", np.uint32, lambda v: v.n_pods + 1),
+    ("ctr_val", np.int64, lambda v: v.n_containers),
+    ("ctr_scale", np.int8, lambda v: v.n_containers),
+    ("node_cap_val", np.int64, lambda v: v.n_nodes),
+    ("node_cap_scale", np.int8, lambda v: v.n_nodes),
+    ("pod_job", np.uint32, lambda v: v.n_pods),
+    ("pod_role", np.uint8, lambda v: v.n_pods),
+    ("pod_created", np.int64, lambda v: v.n_pods),
+]
+
+
+def _np_view(addr: int, dtype, n: int) -> np.ndarray:
+    if n == 0 or not addr:
+        return np.zeros(0, dtype)
+    buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(addr)
+    return np.frombuffer(buf, dtype=dtype, count=n)
+
+
+class HostSnapshot:
+    """Owns an `arena_host_snapshot*` (or keeps numpy arrays alive for a view
+    built from arrays).  `.cols` maps column name -> numpy array (zero-copy)."""
+
+    def __init__(self, handle: Optional[int], view: SnapshotView, keep=None):
+        self._h = handle
+        self.view = view
+        self._keep = keep
+        self.cols: Dict[str, np.ndarray] = {}
+        for name, dt, n in _COLS:
+            self.cols[name] = _np_view(getattr(view, name), dt, int(n(view)))
+
+    # -- constructors -------------------------------------------------------
+    @classmethod
+    def from_handle(cls, handle: int, keep=None) -> "HostSnapshot":
+        v = SnapshotView()
+        check(lib().arena_host_snapshot_view(handle, C.byref(v)))
+        return cls(handle, v, keep)
+
+    @classmethod
+    def from_arrays(cls, cols: Dict[str, np.ndarray], n_jobs: int = 0) -> "HostSnapshot":
+        """Build a view over caller-owned numpy columns (kept alive here)."""
+        keep = {}
+        v = SnapshotView()
+        P = len(cols["pod_node"])
+        for name, dt, _ in _COLS:
+            a = cols.get(name)
+            if a is None:
+                setattr(v, name, None)
+                continue
+            a = np.ascontiguousarray(a, dtype=dt)
+            keep[name] = a
+            setattr(v, name, a.ctypes.data if a.size else None)
+        if "pod_ctr_begin" not in keep or len(keep["pod_ctr_begin"]) != P + 1:
+            raise ValueError("pod_ctr_begin must have P+1 entries")
+        v.n_pods = P
+        v.n_containers = int(keep["pod_ctr_begin"][P])
+        v.n_nodes = len(cols["node_cap_val"])
+        v.n_jobs = n_jobs
+        if v.n_containers != len(cols["ctr_val"]):
+            raise ValueError("pod_ctr_begin[P] != len(ctr_val)")
+        # pod_ctr_begin may be size 1 with P == 0: keep its address
+        v.pod_ctr_begin = keep["pod_ctr_begin"].ctypes.data
+        hs = cls(None, v, keep)
+        return hs
+
+    @classmethod
+    def synth(cls, n_pods: int, n_nodes: int, seed: int = 1, n_jobs: int = 0, skewed: bool = False,
+              grouped: bool = True, pinned: bool = False, threads: int = 0) -> "HostSnapshot":
+        """Seeded synthetic snapshot (arena_synth_snapshot)."""
+        sp = SynthParams(n_pods, n_nodes, n_jobs, seed, int(skewed), int(grouped), int(pinned), threads)
+        h = C.c_void_p()
+        check(lib().arena_synth_snapshot(C.byref(sp), C.byref(h)))
+        return cls.from_handle(h.value)
+
+    @classmethod
+    def from_json(cls, podlist: bytes, nodelist: bytes, joblist: bytes = b"", tfjoblist: bytes = b"",
+                  helm_list: bytes = b"") -> "HostSnapshot":
+        """arena_load_json: PodList/NodeList(/JobList/TFJobList/`helm list`) -> columns."""
+        h = C.c_void_p()
+        check(lib().arena_load_json(podlist, len(podlist), nodelist, len(nodelist),
+                                    joblist or None, len(joblist), tfjoblist or None, len(tfjoblist),
+                                    helm_list or None, len(helm_list), C.byref(h)))
+        return cls.from_handle(h.value)
+
+    # -- properties -----------------------------------------------------------
+    @property
+    def handle(self) -> Optional[int]:
+        return self._h
+
+    @property
+    def n_pods(self) -> int:
+        return int(self.view.n_pods)
+
+    @property
+    def n_containers(self) -> int:
+        return int(self.view.n_containers)
+
+    @property
+    def n_nodes(self) -> int:
+        return int(self.view.n_nodes)
+
+    @property
+    def n_jobs(self) -> int:
+        return int(self.view.n_jobs)
+
+    def algorithmic_bytes_top_node(self, pod_gpu: bool = False) -> int:
+        """B = 9P + 9C + 25N + 20, +8P when pod_gpu is written."""
+        return 9 * self.n_pods + 9 * self.n_containers + 25 * self.n_nodes + 20 + (8 * self.n_pods if pod_gpu else 0)
+
+    def pod_order(self) -> Optional[np.ndarray]:
+        if not self._h:
+            return None
+        p = lib().arena_host_pod_order(self._h)
+        return _np_view(p, np.uint32, self.n_pods).copy() if p else None
+
+    def job_name(self, j: int) -> str:
+        return lib().arena_host_job_name(self._h, j).decode()
+
+    def job_trainer(self, j: int) -> str:
+        return lib().arena_host_job_trainer(self._h, j).decode()
+
+    def node_name(self, n: int) -> str:
+        return lib().arena_host_node_name(self._h, n).decode()
+
+    # -- sharding ---------------------------------------------------------------
+    def shard_plan(self, n_shards: int, by_job: bool = False):
+        key_cut = np.zeros(n_shards + 1, np.uint64)
+        pod_cut = np.zeros(n_shards + 1, np.uint64)
+        check(lib().arena_shard_plan(C.byref(self.view), n_shards, int(by_job), key_cut.ctypes.data,
+                                     pod_cut.ctypes.data))
+        return key_cut, pod_cut
+
+    def shard(self, i: int, n_shards: int, by_job: bool = False) -> "HostSnapshot":
+        key_cut, pod_cut = self.shard_plan(n_shards, by_job)
+        h = C.c_void_p()
+        check(lib().arena_shard_extract(C.byref(self.view), int(by_job), int(key_cut[i]), int(key_cut[i + 1]),
+                                        int(pod_cut[i]), int(pod_cut[i + 1]), C.byref(h)))
+        s = HostSnapshot.from_handle(h.value, keep=self)     # aliases the parent's columns
+        s.key_lo, s.key_hi = int(key_cut[i]), int(key_cut[i + 1])
+        s.pod_lo, s.pod_hi = int(pod_cut[i]), int(pod_cut[i + 1])
+        return s
+
+    def close(self) -> None:
+        if self._h:
+            lib().arena_host_snapshot_free(self._h)
+            self._h = None
+        self.cols = {}
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceSnapshot:
+    """`arena_snapshot*`: columns resident in HBM."""
+
+    def __init__(self, handle: int, host: Optional[HostSnapshot], keep=None):
+        self._h = handle
+        self.host = host
+        self._keep = keep
+        src = host.view if host is not None else keep["view"]
+        self.n_pods, self.n_containers = int(src.n_pods), int(src.n_containers)
+        self.n_nodes, self.n_jobs = int(src.n_nodes), int(src.n_jobs)
+
+    @classmethod
+    def upload(cls, host: HostSnapshot) -> "DeviceSnapshot":
+        h = C.c_void_p()
+        check(lib().arena_snapshot_upload(C.byref(host.view), C.byref(h)))
+        return cls(h.value, host)
+
+    @classmethod
+    def wrap_tensors(cls, tensors: dict, n_jobs: int = 0) -> "DeviceSnapshot":
+        """Wrap CUDA torch tensors (same names / dtypes as the host columns)
+        without copying; the tensors are kept alive by this object."""
+        v = SnapshotView()
+        P = tensors["pod_node"].numel()
+        v.n_pods = P
+        v.n_containers = tensors["ctr_val"].numel()
+        v.n_nodes = tensors["node_cap_val"].numel()
+        v.n_jobs = n_jobs
+        for name, _, _ in _COLS:
+            t = tensors.get(name)
+            setattr(v, name, t.data_ptr() if t is not None and t.numel() else None)
+        v.pod_ctr_begin = tensors["pod_ctr_begin"].data_ptr()
+        h = C.c_void_p()
+        check(lib().arena_snapshot_wrap_device(C.byref(v), C.byref(h)))
+        return cls(h.value, None, keep={"tensors": tensors, "view": v})
+
+    @property
+    def handle(self) -> int:
+        return self._h
+
+    def close(self) -> None:
+        if self._h:
+            lib().arena_snapshot_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

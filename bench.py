@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- pod-records/s and HBM GB/s of `arena top node` GPU accounting.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one pass of the hot path (nodes kernel + pods kernel, plus the
+int64[2] totals all-reduce when N > 1) over one synthetic columnar snapshot
+that is already resident in HBM.  Workload at N = 1: BASELINE.json configs[3]'s
+snapshot (1e8 pods / 1e6 nodes, seed 1; 2.3 GB, larger than the 126 MB L2, so
+no flush is needed between steps) on ONE GPU -- the configuration the >= 70 %
+of HBM bandwidth target is quoted on.  At N > 1 every rank holds a node-range
+shard of the same per-GPU size (weak scaling: N x 1e8 pods over N x 1e6 nodes,
+seed 1 + rank); `--scaling strong` instead cuts ONE 1e8-pod snapshot into N
+node ranges (BASELINE configs[3] as written).
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement".
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "pod-records/sec & HBM GB/s for top-node GPU accounting at 1/2/4/8 B200"
+UNIT = "pod-records/s"
+PODS_FULL = 100_000_000
+NODES_FULL = 1_000_000
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while running."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append((time.time(), ln.strip()))
+
+    def stop(self, t0: float, t1: float):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, ln in self.lines:
+            if ts < t0 - 0.05 or ts > t1 + 0.25:
+                continue
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples in timed region"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------
+# CPU legs (the ONLY place bench.py touches oracle/): bounded samples.
+# --------------------------------------------------------------------------
+def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int):
+    """The reference's CPU algorithm (C restatement, oracle/acct_ref.c) on a
+    bounded sample of the workload: array-of-structs pods with string node
+    names and keyed limits, string-hash join, all host threads."""
+    import numpy as np  # noqa: F401
+    from arena_b200 import HostSnapshot
+    from oracle import cref
+    sample_nodes = max(1, sample_pods // 100)
+    host = HostSnapshot.synth(sample_pods, sample_nodes, seed=1)
+    aos = cref.AoS(host.cols)
+    for _ in range(warmup):
+        aos.run(False, threads)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        total, alloc, cluster = aos.run(False, threads)
+    dt = time.perf_counter() - t0
+    # single-thread columnar pass (B3) and faithful nested loop (B1) for context
+    t1 = time.perf_counter()
+    cref.top_node_columnar(host.cols)
+    b3 = host.n_pods / (time.perf_counter() - t1)
+    small = HostSnapshot.synth(20_000, 200, seed=1)
+    a2 = cref.AoS(small.cols)
+    t2 = time.perf_counter()
+    a2.run(True)
+    b1 = small.n_pods / (time.perf_counter() - t2)
+    a2.close()
+    aos.close()
+    return {
+        "value": host.n_pods * steps / dt, "ms_per_step": dt / steps * 1e3, "sample_pods": host.n_pods,
+        "sample_nodes": sample_nodes, "b3_columnar_1thread": b3, "b1_nested_loop_1thread": b1,
+        "b1_sample": "20000 pods x 200 nodes",
+    }
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    sample = 10_000_000
+    r = cpu_reference_run(args.steps, max(1, min(args.warmup, 2)), sample, threads)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": workload_config(args.gpus, args.scaling),
+        "cpu_baseline": {
+            "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"each step = first {r['sample_pods']} pods / {r['sample_nodes']} nodes of the workload's "
+                      "generator (seed 1) as array-of-structs with string node names and keyed limits, string-hash "
+                      "join (C restatement of gpu.go + top_node.go; the Go reference cannot be built: no toolchain)",
+            "columnar_single_pass_1thread": r["b3_columnar_1thread"],
+            "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
+            "faithful_nested_loop_sample": r["b1_sample"],
+        },
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(n_gpus: int, scaling: str):
+    if scaling == "strong" and n_gpus > 1:
+        wl = (f"BASELINE configs[3]: synthetic snapshot of 1e8 pods / 1e6 nodes (seed 1) cut into {n_gpus} node ranges, "
+              "NCCL totals all-reduce")
+    elif n_gpus > 1:
+        wl = (f"BASELINE configs[3] per GPU: {n_gpus} node-range shards of 1e8 pods / 1e6 nodes each "
+              f"(cluster of {n_gpus}e8 pods / {n_gpus}e6 nodes, seeds 1..{n_gpus}), NCCL totals all-reduce")
+    else:
+        wl = "BASELINE configs[3] on one GPU: synthetic snapshot of 1e8 pods / 1e6 nodes, mixed phases, multi-container pods, seed 1"
+    return {"workload": wl, "command": "arena top node (summary)", "pods_per_gpu": None, "nodes_per_gpu": None,
+            "l2": "inputs (2.3 GB per GPU) exceed the 126 MB L2; no flush between steps",
+            "parallelism": f"node-range shards x{n_gpus}" if n_gpus > 1 else "single GPU"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--pods", type=int, default=PODS_FULL, help="pods per GPU (weak) or in total (strong)")
+    ap.add_argument("--nodes", type=int, default=NODES_FULL)
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3                         # timing rule: W >= 3
+
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # launched directly: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import arena_b200 as ab
+    from arena_b200 import multigpu
+
+    rank, world, local = multigpu.env_rank()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    multigpu.init_process_group("nccl")
+    ab.init(local)
+    n_gpus = world
+
+    # ---- workload ------------------------------------------------------------
+    t_gen = time.time()
+    if args.scaling == "strong" and world > 1:
+        full = ab.HostSnapshot.synth(args.pods, args.nodes, seed=1, pinned=False)
+        host = full.shard(rank, world)
+        # pinned staging of the shard for the e2e leg
+        host = ab.HostSnapshot.from_arrays({k: v.copy() for k, v in host.cols.items() if v.size or k == "pod_ctr_begin"})
+        del full
+    else:
+        host = ab.HostSnapshot.synth(args.pods, args.nodes, seed=1 + rank, pinned=True)
+    P, C, N = host.n_pods, host.n_containers, host.n_nodes
+    log(f"[rank {rank}] snapshot: P={P} C={C} N={N} generated in {time.time() - t_gen:.1f}s")
+    total_pods = torch.tensor([P], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(total_pods)
+    total_pods = int(total_pods.item())
+
+    dev = ab.DeviceSnapshot.upload(host)
+    d_total = torch.empty(N, dtype=torch.int64, device="cuda")
+    d_alloc = torch.empty(N, dtype=torch.int64, device="cuda")
+    d_cluster = torch.empty(2, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step():
+        ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, stream.cuda_stream)
+        multigpu.all_reduce_totals(d_cluster)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+
+    # ---- timed region: exactly K steps, device-timed, max over ranks -----------
+    L0 = ab.lib().arena_kernel_launches()
+    ab._lib.check(ab.lib().arena_profile_begin(args.steps))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    t_wall1 = time.time()
+    ms = ev0.elapsed_time(ev1)
+    launches = int(ab.lib().arena_kernel_launches() - L0)
+    import ctypes as C_
+    nodes_ms, pods_ms, calls = C_.c_double(), C_.c_double(), C_.c_uint64()
+    ab._lib.check(ab.lib().arena_profile_end(C_.byref(nodes_ms), C_.byref(pods_ms), C_.byref(calls)))
+    tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_total = float(tmax.item())
+    ms_per_step = ms_total / args.steps
+    value = total_pods * args.steps / (ms_total / 1e3)
+
+    # sanity: table sums equal the totals this rank contributed (cheap; parity proper is tests/)
+    cl = d_cluster.cpu().numpy()
+    local_alloc_sum = int(d_alloc.sum().item())
+    local_total_sum = int(d_total.sum().item())
+    sums = torch.tensor([local_total_sum, local_alloc_sum], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(sums)
+    if sums.cpu().numpy().tolist() != cl.tolist():
+        raise SystemExit(f"bench.py: cluster totals {cl.tolist()} != table sums {sums.tolist()}")
+
+    # ---- e2e: the public one-shot call with HOST buffers, copies in the timed region
+    e2e_steps = args.e2e_steps or min(args.steps, 10)
+    h_total = np.zeros(N, np.int64)
+    h_alloc = np.zeros(N, np.int64)
+    for _ in range(2):
+        res, gcl = multigpu.top_node_sharded(host)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        res, gcl = multigpu.top_node_sharded(host)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_t.item())
+    if gcl.tolist() != cl.tolist():
+        raise SystemExit(f"bench.py: e2e totals {gcl.tolist()} != device-path totals {cl.tolist()}")
+    t_wall2 = time.time()
+    h2d = 9 * P + 4 + 9 * C + 9 * N          # columns uploaded per step (top node needs no job columns)
+    d2h = 16 * N + 16
+
+    clocks = sampler.stop(t_wall0, t_wall2) if rank == 0 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (pods kernel) ----------------------------
+    peak, peak_src = measured_peak_hbm()
+    pods_bytes = 9 * P + 9 * C + 4           # pod_node+phase+ctr_begin, ctr_val+ctr_scale (SURVEY 8d per-unit sizes)
+    pods_ms_avg = pods_ms.value / max(1, calls.value)
+    achieved = pods_bytes / (pods_ms_avg / 1e3) / 1e9
+    step_bytes = host.algorithmic_bytes_top_node()
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": None, "kernel": "arena::pods_kernel<false>", "kernel_ms": pods_ms_avg,
+        "algorithmic_bytes": pods_bytes, "peak_source": peak_src,
+        "nodes_kernel_ms": nodes_ms.value / max(1, calls.value),
+        "step_algorithmic_bytes": step_bytes,
+        "step_gbs": step_bytes / (ms_per_step / 1e3) / 1e9 * (1 if world == 1 else 1),
+        "frac_of_nominal_8000": achieved / 8000.0,
+    }
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            with open(tr) as f:
+                roofline["traffic"] = json.load(f).get("pods_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
+        "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": dict(workload_config(n_gpus, args.scaling), pods_per_gpu=P, nodes_per_gpu=N, containers_per_gpu=C,
+                       total_pods=total_pods),
+        "clocks": clocks,
+        "e2e": {"value": total_pods * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
+                "call": "arena_top_node_host (upload + kernels + download) + totals all-reduce"},
+        "gpu_launches": launches,
+        "roofline": roofline,
+        "hbm_gbs_step": step_bytes / (ms_per_step / 1e3) / 1e9,
+    }
+
+    if not args.no_cpu and world == 1:
+        threads = os.cpu_count() or 1
+        log("[rank 0] cpu_baseline leg (bounded sample)...")
+        r = cpu_reference_run(steps=5, warmup=1, sample_pods=10_000_000, threads=threads)
+        line["cpu_baseline"] = {
+            "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"5 passes over the first {r['sample_pods']} pods / {r['sample_nodes']} nodes of the generator "
+                      "(seed 1), array-of-structs + string-hash join, all host threads (C restatement of the Go path)",
+            "columnar_single_pass_1thread": r["b3_columnar_1thread"],
+            "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
+            "faithful_nested_loop_sample": r["b1_sample"],
+        }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

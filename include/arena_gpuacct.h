@@ -1,0 +1,172 @@
+/*
+ * arena_gpuacct.h -- C ABI of libarena_gpuacct.so: the GPU resource accounting
+ * behind `arena top node` / `arena top job`, on B200 (sm_100a).
+ *
+ * The reference (a Go CLI, read-only at /root/reference) has no FFI for this
+ * path; its seams are unexported Go functions in package `commands`.  Each
+ * entry point below names the Go seam it stands in for (paths relative to
+ * /root/reference).  INTEGRATION.md shows the cgo binding a maintainer adds.
+ *
+ * Conventions
+ *   - plain C types only; every function returns 0 or a negative arena_status;
+ *     arena_last_error() gives the message for the calling thread.
+ *   - the caller owns every host buffer it passes; the library keeps no host
+ *     pointer after a call returns (cgo pointer-passing rule).
+ *   - one process drives one GPU (one rank per GPU under torchrun / one
+ *     goroutine locked to an OS thread); every entry point makes its device
+ *     current itself.
+ *   - one query in flight per snapshot handle.
+ *   - int64 sums wrap modulo 2^64 exactly like Go's `+=`.
+ *   - all columns must be 16-byte aligned (cudaMalloc / malloc'd arrays are).
+ */
+#ifndef ARENA_GPUACCT_H
+#define ARENA_GPUACCT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum arena_status {
+    ARENA_OK = 0,
+    ARENA_E_INVALID = -1,    /* bad argument (NULL, misaligned, inconsistent counts) */
+    ARENA_E_CUDA = -2,       /* CUDA runtime error; text in arena_last_error() */
+    ARENA_E_NOT_INIT = -3,   /* arena_acct_init() not called for this process */
+    ARENA_E_NOMEM = -4,
+    ARENA_E_TOO_LARGE = -5,  /* a size exceeds what the entry point supports */
+    ARENA_E_PARSE = -6       /* loader: malformed JSON / quantity (arena_top.h) */
+} arena_status;
+
+/* spec.nodeName / job id that matches no row ("" or a node absent from the
+ * NodeList: such pods add to no row and to no total, top_node.go:88-97). */
+#define ARENA_NONE 0xFFFFFFFFu
+
+/* status.phase codes (vendor/k8s.io/api/core/v1/types.go:2339-2358).  Active
+ * <=> code != SUCCEEDED && code != FAILED, the selector of pod_helper.go:18. */
+enum {
+    ARENA_PHASE_EMPTY = 0, ARENA_PHASE_PENDING = 1, ARENA_PHASE_RUNNING = 2,
+    ARENA_PHASE_SUCCEEDED = 3, ARENA_PHASE_FAILED = 4, ARENA_PHASE_UNKNOWN = 5,
+    ARENA_PHASE_OTHER = 255
+};
+
+/* pod_role for `top job` (trainer_mpi.go:241-282, trainer_standalone.go:198-221,
+ * trainer_tensorflow.go:331-344) */
+enum {
+    ARENA_ROLE_COUNTS = 0,   /* always summed (tfjob pods; horovod pods not owned by a Job) */
+    ARENA_ROLE_LATEST = 1    /* only the newest such pod of the job is summed */
+};
+
+/*
+ * Columnar snapshot (struct of arrays).  P pods, C containers, N nodes, J jobs.
+ * A limit / capacity is the reference's int64Amount{value, scale}
+ * (resource/amount.go:57-60) of the SELECTED key: "nvidia.com/gpu" when that
+ * key is present, else "alpha.kubernetes.io/nvidia-gpu", else {0,0}
+ * (gpu.go:18-37, 61-79).  Slow-path quantities (inf.Dec) are resolved by the
+ * loader to {Value(), 0}.  Scale is in [-18, 18] after the loader canonicalises
+ * (scale > 18 can only yield 0).
+ *
+ * Fast when pods that share a node (job) are adjacent; correct in any order.
+ */
+typedef struct arena_snapshot_view {
+    uint64_t n_pods;                 /* P */
+    uint64_t n_containers;           /* C == pod_ctr_begin[P] */
+    uint64_t n_nodes;                /* N */
+    uint64_t n_jobs;                 /* J (0 when the job columns are NULL) */
+    const uint32_t *pod_node;        /* [P]   dictionary id of spec.nodeName, or ARENA_NONE */
+    const uint8_t  *pod_phase;       /* [P]   ARENA_PHASE_* */
+    const uint32_t *pod_ctr_begin;   /* [P+1] CSR offsets into ctr_* (spec.containers only) */
+    const int64_t  *ctr_val;         /* [C]   int64Amount.value */
+    const int8_t   *ctr_scale;       /* [C]   int64Amount.scale */
+    const int64_t  *node_cap_val;    /* [N]   status.capacity, same encoding */
+    const int8_t   *node_cap_scale;  /* [N] */
+    const uint32_t *pod_job;         /* [P]   job id or ARENA_NONE   (top job; may be NULL) */
+    const uint8_t  *pod_role;        /* [P]   ARENA_ROLE_*           (top job; may be NULL) */
+    const int64_t  *pod_created;     /* [P]   creationTimestamp, unix seconds (top job) */
+} arena_snapshot_view;
+
+typedef struct arena_snapshot arena_snapshot;   /* opaque; device-resident columns */
+
+/* Process set-up / tear-down.  Stands in for setupKubeconfig+initKubeClient
+ * (cmd/arena/commands/common.go:29-66): the one-time acquisition of the
+ * backend a `top` command talks to.  Idempotent; `device` is a CUDA ordinal. */
+int  arena_acct_init(int device);
+void arena_acct_shutdown(void);
+int  arena_acct_device(void);                     /* ordinal, or ARENA_E_NOT_INIT */
+int  arena_acct_sm_count(void);
+
+/* Thread-local, static storage; never NULL. */
+const char *arena_last_error(void);
+
+/* Replaces the two List calls that materialise []v1.Pod / []v1.Node
+ * (pod_helper.go:15-43, top_node.go:71): copy host columns to HBM. */
+int  arena_snapshot_upload(const arena_snapshot_view *host, arena_snapshot **out);
+/* Same, but `dev` already holds DEVICE pointers (e.g. torch tensors); nothing
+ * is copied and the caller keeps ownership of the columns. */
+int  arena_snapshot_wrap_device(const arena_snapshot_view *dev, arena_snapshot **out);
+void arena_snapshot_free(arena_snapshot *s);
+
+/*
+ * `arena top node`: NodeDescriber.getAllNodeInfos + caculateNodeGPU + the
+ * cluster roll-up (top_node.go:69-97, 232-242, 109-118), with gpuInNode /
+ * gpuInPod / gpuInContainer (gpu.go:18-79) and Quantity.Value()
+ * (resource/quantity.go:699-718) inside.
+ *   node_total[N], node_alloc[N]  per-node table (HOST buffers)
+ *   cluster[2]                    {sum node_total, sum node_alloc}
+ *   pod_gpu[P] or NULL            gpuInPod of every pod (details view,
+ *                                 top_node.go:186-195; unmasked by phase)
+ */
+int  arena_top_node(const arena_snapshot *s, int64_t *node_total, int64_t *node_alloc,
+                    int64_t cluster[2], int64_t *pod_gpu);
+
+/* Same computation, DEVICE output buffers, enqueued on `stream` (a
+ * cudaStream_t, NULL = the library's own stream) without synchronising.  Used
+ * to time the kernels alone and to feed d_cluster to an NCCL all-reduce. */
+int  arena_top_node_device(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                           int64_t *d_cluster, int64_t *d_pod_gpu, void *stream);
+
+/* One-shot form for callers holding HOST columns: upload, compute, download.
+ * This is the end-to-end call bench.py times as `e2e`. */
+int  arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total,
+                         int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
+
+/*
+ * `arena top job`: TrainingJob.RequestedGPU / AllocatedGPU (job_info.go:51-70,
+ * trainer_tensorflow.go:135-155) for every job, the "latest pod wins" rule of
+ * trainer_mpi.go:263-278 / trainer_standalone.go:198-221, the ordering of
+ * makeTrainingJobOrderdByGPUCount (trainer.go:25-37, 68-75; ties, which
+ * sort.Sort leaves unspecified, broken by ascending job id) and the totals of
+ * list.go:102-103.
+ *   job_req[J], job_alloc[J]   per-job sums (HOST)
+ *   job_order[J]               job ids, requested desc then id asc
+ *   job_latest[J] or NULL      index of the winning ARENA_ROLE_LATEST pod, or ARENA_NONE
+ *   totals[2]                  {sum job_req, sum job_alloc}
+ */
+int  arena_top_job(const arena_snapshot *s, int64_t *job_req, int64_t *job_alloc,
+                   uint32_t *job_order, uint32_t *job_latest, int64_t totals[2]);
+int  arena_top_job_device(const arena_snapshot *s, int64_t *d_job_req, int64_t *d_job_alloc,
+                          uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals,
+                          void *stream);
+
+/* Quantity.Value() of n int64Amount pairs on the GPU (parity probe for
+ * resource/amount.go:95-101 + math.go:144-203); HOST in, HOST out. */
+int  arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, int64_t *out);
+
+/* Per-kernel device timing for the roofline report (no counterpart in the
+ * reference; its only profiler is --pprof, cmd/arena/main.go:14-22).  Between
+ * begin and end, every arena_top_node*() call records CUDA events on its
+ * launch stream around the nodes kernel and the pods kernel (at most
+ * max_calls calls are recorded).  end() waits for them and returns the summed
+ * durations in milliseconds. */
+int  arena_profile_begin(int max_calls);
+int  arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *calls);
+
+/* Number of kernels this library has launched in this process (bench.py's
+ * gpu_launches claim). */
+uint64_t arena_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARENA_GPUACCT_H */

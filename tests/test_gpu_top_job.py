@@ -1,0 +1,56 @@
+"""GPU parity for `top job`: per-job requested/allocated, latest-pod rule,
+ordering and totals, through the C ABI, against oracle/acct_ref.c."""
+
+import numpy as np
+import pytest
+
+from oracle import cref
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_job(gpu, host):
+    J = host.n_jobs
+    dev = gpu.DeviceSnapshot.upload(host)
+    res = gpu.top_job(dev)
+    req, alloc, latest, totals = cref.top_job_columnar(host.cols, J)
+    assert np.array_equal(res.job_req, req)
+    assert np.array_equal(res.job_alloc, alloc)
+    assert np.array_equal(res.job_latest, latest)
+    assert np.array_equal(res.totals, totals)
+    # ordering: requested desc, ties by ascending id (trainer.go:31-33 + documented tie-break)
+    want = np.array(sorted(range(J), key=lambda j: (-int(req[j]), j)), np.uint32)
+    assert np.array_equal(res.job_order, want)
+    res2 = gpu.top_job(dev)          # repeatable on the same handle
+    assert np.array_equal(res2.job_req, req) and np.array_equal(res2.job_order, want)
+    dev.close()
+
+
+@pytest.mark.parametrize("P,N,J,seed", [(10_000, 1_000, 1_000, 20180723), (500, 10, 7, 2), (300_000, 3_000, 5_000, 3),
+                                        (50_000, 100, 1, 4), (2_000, 50, 4_000, 5)])
+def test_top_job_synth(gpu, P, N, J, seed):
+    host = gpu.HostSnapshot.synth(P, N, seed=seed, n_jobs=J)
+    _check_job(gpu, host)
+
+
+def test_top_job_negative_and_ties(gpu):
+    """Many equal requested values (tie-break), negative sums (sort of signed keys)."""
+    rng = np.random.default_rng(5)
+    P, J = 6_000, 300
+    nctr = rng.integers(0, 3, P)
+    cb = np.zeros(P + 1, np.uint32)
+    cb[1:] = np.cumsum(nctr)
+    C = int(cb[-1])
+    cols = dict(pod_node=np.zeros(P, np.uint32), pod_phase=rng.choice(np.array([2, 3, 4, 1], np.uint8), P),
+                pod_ctr_begin=cb, ctr_val=rng.integers(-2, 3, C).astype(np.int64), ctr_scale=np.zeros(C, np.int8),
+                node_cap_val=np.array([8], np.int64), node_cap_scale=np.zeros(1, np.int8),
+                pod_job=rng.integers(0, J + 3, P).astype(np.uint32), pod_role=rng.integers(0, 2, P).astype(np.uint8),
+                pod_created=rng.integers(-5, 5, P).astype(np.int64))
+    host = gpu.HostSnapshot.from_arrays(cols, n_jobs=J)
+    _check_job(gpu, host)
+
+
+def test_top_job_large_sort(gpu):
+    """More jobs than one shared-memory sort tile: exercises the global merge steps."""
+    host = gpu.HostSnapshot.synth(400_000, 1_000, seed=8, n_jobs=70_000)
+    _check_job(gpu, host)

@@ -1,0 +1,167 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the plain-C
+oracle (oracle/acct_ref.c) on the same seeded inputs.  Bit-exact (integers)."""
+
+import numpy as np
+import pytest
+
+from oracle import cref
+
+pytestmark = pytest.mark.gpu
+
+NONE = 0xFFFFFFFF
+
+
+def _check(gpu, host, details=True):
+    from arena_b200 import DeviceSnapshot, top_node
+    dev = DeviceSnapshot.upload(host)
+    res = top_node(dev, details=details)
+    tot, alloc, cl, pg = cref.top_node_columnar(host.cols, details)
+    assert np.array_equal(res.node_total, tot)
+    assert np.array_equal(res.node_alloc, alloc)
+    assert np.array_equal(res.cluster, cl)
+    if details:
+        assert np.array_equal(res.pod_gpu, pg)
+    # a second query on the same handle (scratch tickets must have been reset)
+    res2 = top_node(dev, details=False)
+    assert np.array_equal(res2.node_alloc, alloc) and np.array_equal(res2.cluster, cl)
+    dev.close()
+    return res
+
+
+@pytest.mark.parametrize("P,N,seed", [(200, 16, 1), (1, 1, 2), (127, 3, 3), (128, 3, 4), (129, 7, 5),
+                                      (10_000, 1_000, 6), (100_003, 977, 7), (1_000_000, 100_000, 1)])
+def test_uniform_grouped(gpu, P, N, seed):
+    host = gpu.HostSnapshot.synth(P, N, seed=seed)
+    _check(gpu, host)
+
+
+def test_ungrouped_list_order(gpu):
+    """Pods in arbitrary list order: still exact (only slower)."""
+    host = gpu.HostSnapshot.synth(300_000, 5_000, seed=11, grouped=False)
+    _check(gpu, host)
+
+
+def test_skewed_gpu_sharing(gpu):
+    host = gpu.HostSnapshot.synth(2_000_000, 20_000, seed=5, skewed=True)
+    res = _check(gpu, host)
+    assert (res.node_alloc > res.node_total).any()      # over-subscribed "GPU sharing" nodes
+
+
+def test_empty_inputs(gpu):
+    z = lambda dt, n=0: np.zeros(n, dt)
+    cols = dict(pod_node=z(np.uint32), pod_phase=z(np.uint8), pod_ctr_begin=z(np.uint32, 1), ctr_val=z(np.int64),
+                ctr_scale=z(np.int8), node_cap_val=np.array([8, 4], np.int64), node_cap_scale=z(np.int8, 2))
+    host = gpu.HostSnapshot.from_arrays(cols)
+    res = _check(gpu, host, details=False)
+    assert res.cluster.tolist() == [12, 0]
+    cols["node_cap_val"] = z(np.int64)
+    cols["node_cap_scale"] = z(np.int8)
+    host = gpu.HostSnapshot.from_arrays(cols)
+    res = _check(gpu, host, details=False)
+    assert res.cluster.tolist() == [0, 0]
+
+
+def _ragged(rng, P, N, max_ctr, big=False):
+    nctr = rng.integers(0, max_ctr + 1, P)
+    cb = np.zeros(P + 1, np.uint32)
+    cb[1:] = np.cumsum(nctr)
+    C = int(cb[-1])
+    if big:
+        val = rng.integers(-2**63, 2**63 - 1, C, dtype=np.int64)
+        scale = rng.integers(-18, 19, C).astype(np.int8)
+    else:
+        val = rng.integers(-5, 2000, C).astype(np.int64)
+        scale = rng.choice(np.array([0, 0, 0, -3, -1, 1, 3], np.int8), C)
+    node = np.sort(rng.integers(0, N + 2, P).astype(np.uint32))
+    node[node >= N] = NONE           # ids N, N+1 -> no such node; sorted => they are last
+    return dict(pod_node=node, pod_phase=rng.choice(np.array([0, 1, 2, 3, 4, 5, 255], np.uint8), P),
+                pod_ctr_begin=cb, ctr_val=val, ctr_scale=scale,
+                node_cap_val=rng.integers(-3, 17, N).astype(np.int64),
+                node_cap_scale=rng.choice(np.array([0, 0, -3, 1], np.int8), N))
+
+
+@pytest.mark.parametrize("seed,P,N,max_ctr,big", [(1, 5_000, 40, 6, False), (2, 999, 5, 0, False),
+                                                  (3, 2_000, 11, 700, False), (4, 50_000, 300, 9, True),
+                                                  (5, 130, 2, 3000, True)])
+def test_ragged_and_extreme(gpu, seed, P, N, max_ctr, big):
+    """Pods with zero / hundreds / thousands of containers (multi-chunk path),
+    negative and fractional quantities, every scale in [-18, 18], wrapping sums."""
+    rng = np.random.default_rng(seed)
+    host = gpu.HostSnapshot.from_arrays(_ragged(rng, P, N, max_ctr, big))
+    _check(gpu, host)
+
+
+def test_pod_on_unknown_node_ids(gpu):
+    """Node ids >= N that are not ARENA_NONE are ignored like unknown node names."""
+    rng = np.random.default_rng(9)
+    cols = _ragged(rng, 4_000, 10, 4)
+    cols["pod_node"][::7] = 12345        # also breaks the grouping
+    host = gpu.HostSnapshot.from_arrays(cols)
+    _check(gpu, host)
+
+
+def test_one_shot_host_entry(gpu):
+    """arena_top_node_host: HOST columns in, HOST table out (the e2e call)."""
+    host = gpu.HostSnapshot.synth(200_000, 2_000, seed=21)
+    res = gpu.top_node(host, details=True)
+    tot, alloc, cl, pg = cref.top_node_columnar(host.cols, True)
+    assert np.array_equal(res.node_total, tot) and np.array_equal(res.node_alloc, alloc)
+    assert np.array_equal(res.cluster, cl) and np.array_equal(res.pod_gpu, pg)
+
+
+def test_device_entry_with_torch_tensors(gpu):
+    """arena_snapshot_wrap_device + arena_top_node_device on torch's stream."""
+    import torch
+    host = gpu.HostSnapshot.synth(500_000, 10_000, seed=31)
+    t = {k: torch.from_numpy(v.copy()).cuda() for k, v in host.cols.items() if v.size and not k.startswith("pod_job")
+         and k not in ("pod_role", "pod_created")}
+    dev = gpu.DeviceSnapshot.wrap_tensors(t)
+    d_total = torch.empty(host.n_nodes, dtype=torch.int64, device="cuda")
+    d_alloc = torch.empty_like(d_total)
+    d_cluster = torch.empty(2, dtype=torch.int64, device="cuda")
+    for _ in range(3):
+        gpu.top_node_device(dev, d_total, d_alloc, d_cluster, None, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+    assert np.array_equal(d_total.cpu().numpy(), tot)
+    assert np.array_equal(d_alloc.cpu().numpy(), alloc)
+    assert np.array_equal(d_cluster.cpu().numpy(), cl)
+
+
+def test_full_size_properties(gpu):
+    """BASELINE config 4 size (1e8 pods / 1e6 nodes, one GPU): exact against
+    the C oracle's single pass, plus size-independent properties."""
+    host = gpu.HostSnapshot.synth(100_000_000, 1_000_000, seed=1)
+    dev = gpu.DeviceSnapshot.upload(host)
+    res = gpu.top_node(dev)
+    # checksum of checksums: cluster totals are the sums of the table
+    assert int(res.node_total.sum()) == int(res.cluster[0])
+    assert int(res.node_alloc.sum()) == int(res.cluster[1])
+    # idempotence
+    res2 = gpu.top_node(dev)
+    assert np.array_equal(res.node_alloc, res2.node_alloc) and np.array_equal(res.cluster, res2.cluster)
+    tot, alloc, cl = cref.top_node_columnar_threads(host.cols, 16)
+    assert np.array_equal(res.node_total, tot)
+    assert np.array_equal(res.node_alloc, alloc)
+    assert np.array_equal(res.cluster, cl)
+    # linearity: shards over disjoint node ranges reproduce the table
+    parts = []
+    for i in range(4):
+        sh = host.shard(i, 4)
+        r = gpu.top_node(gpu.DeviceSnapshot.upload(sh))
+        parts.append(r)
+    assert np.array_equal(np.concatenate([p.node_alloc for p in parts]), alloc)
+    assert sum(int(p.cluster[1]) for p in parts) == int(cl[1])
+    dev.close()
+
+
+def test_quantity_values_kernel(gpu):
+    rng = np.random.default_rng(3)
+    val = np.concatenate([rng.integers(-2**63, 2**63 - 1, 20000, dtype=np.int64),
+                          rng.integers(-3000, 3000, 20000).astype(np.int64),
+                          np.array([0, 1, -1, 2**63 - 1, -2**63, 500, -500, 1500, 10, 922337203685477580,
+                                    922337203685477581], np.int64)])
+    scale = rng.integers(-20, 21, len(val)).astype(np.int8)
+    got = gpu.quantity_values(val, scale)
+    want = np.array([cref.quantity_value(int(v), int(s)) for v, s in zip(val, scale)], np.int64)
+    assert np.array_equal(got, want)
