@@ -96,8 +96,8 @@ int arena_acct_init(int device)
                     prop.major, prop.minor);
     g_ctx.device = device;
     g_ctx.sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, pods_kernel<false>, kThreads, 0));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, pods_kernel<true>, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1)
         return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
     CUDA_TRY(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
@@ -229,7 +229,7 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     pa.total_alloc = d_cluster + 1;
     pa.scratch = s->scratch;
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
-    pods_kernel<false><<<gp, kThreads, 0, st>>>(pa);
+    top_node_pods_kernel<<<gp, kThreads, 0, st>>>(pa);
     count_launch();
     if (prof) cudaEventRecord(pe[2], st);
     CUDA_TRY(cudaGetLastError());
@@ -263,7 +263,7 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     pa.total_req = d_totals;
     pa.total_alloc = d_totals + 1;
     pa.scratch = s->scratch;
-    pods_kernel<true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
+    job_pods_kernel<<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
     count_launch();
 
     if (v.n_pods) {

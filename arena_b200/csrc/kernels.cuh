@@ -70,10 +70,32 @@ __device__ __noinline__ i64 quantity_value_slow(i64 v, int s)
     return hi == (lo >> 63) ? lo : 0;
 }
 
+// floor(2^64 / 10^k) + 1: with a < 2^32, umul64hi(a, kRecip10[k]) == a / 10^k exactly
+// (the error term a * (M*d - 2^64) / (d * 2^64) is below 2^-32 < 1/d).
+__device__ __constant__ u64 kRecip10[10] = {
+    0ull, 1844674407370955162ull, 184467440737095517ull, 18446744073709552ull, 1844674407370956ull,
+    184467440737096ull, 18446744073710ull, 1844674407371ull, 184467440738ull, 18446744074ull};
+
+// scale != 0.  The common shape ("500m": scale in [-9,-1], |value| < 2^32) is
+// branch-light: one multiply-high by a reciprocal instead of a 64-bit divide.
+__device__ __forceinline__ i64 quantity_value_nz(i64 v, int s)
+{
+    const u64 a = v < 0 ? 0ull - (u64)v : (u64)v;
+    if (s < 0 && s >= -9 && (a >> 32) == 0) {
+        const unsigned k = (unsigned)(-s);
+        const unsigned d = (unsigned)kPow10[k];
+        unsigned q = (unsigned)__umul64hi(a, kRecip10[k]);
+        const unsigned r = (unsigned)a - q * d;
+        q += (r != 0u);                       // round away from zero
+        return v < 0 ? -(i64)q : (i64)q;
+    }
+    return quantity_value_slow(v, s);
+}
+
 __device__ __forceinline__ i64 quantity_value(i64 v, int s)
 {
     if (s == 0) return v;
-    return quantity_value_slow(v, s);
+    return quantity_value_nz(v, s);
 }
 
 __device__ __forceinline__ bool phase_active(unsigned ph)
@@ -86,15 +108,41 @@ __device__ __forceinline__ u64 shfl_u64(u64 v, int src)
     return __shfl_sync(0xffffffffu, v, src);
 }
 
-// Inclusive warp scan of a u64 (wrapping adds).
-__device__ __forceinline__ u64 warp_inclusive_scan(u64 x, int lane)
+// Inclusive warp scans (wrapping adds).  shfl.up's predicate output says
+// whether the source lane exists, so each step is SHFL + predicated ADD.
+__device__ __forceinline__ unsigned warp_inclusive_scan_u32(unsigned x)
 {
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        u64 y = __shfl_up_sync(0xffffffffu, x, d);
-        if (lane >= d) x += y;
-    }
+    for (int d = 1; d < 32; d <<= 1)
+        asm volatile("{\n\t.reg .u32 y;\n\t.reg .pred p;\n\t"
+                     "shfl.sync.up.b32 y|p, %0, %1, 0, 0xffffffff;\n\t"
+                     "@p add.u32 %0, %0, y;\n\t}"
+                     : "+r"(x) : "r"(d));
     return x;
+}
+
+__device__ __forceinline__ u64 warp_inclusive_scan(u64 x, int lane)
+{
+    unsigned lo = (unsigned)x, hi = (unsigned)(x >> 32);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1)
+        asm volatile("{\n\t.reg .u32 ylo, yhi;\n\t.reg .pred p;\n\t"
+                     "shfl.sync.up.b32 ylo|p, %0, %2, 0, 0xffffffff;\n\t"
+                     "shfl.sync.up.b32 yhi, %1, %2, 0, 0xffffffff;\n\t"
+                     "@p add.cc.u32 %0, %0, ylo;\n\t"
+                     "@p addc.u32 %1, %1, yhi;\n\t}"
+                     : "+r"(lo), "+r"(hi) : "r"(d));
+    (void)lane;
+    return ((u64)hi << 32) | lo;
+}
+
+// Scan of values that are usually tiny: when every lane's value is below 2^26
+// the 32-lane sum fits 32 bits and the cheap scan is exact; otherwise (huge or
+// negative quantities) fall back to the 64-bit one.  Warp-uniform branch.
+__device__ __forceinline__ u64 warp_inclusive_scan_auto(u64 x, int lane)
+{
+    if (!__any_sync(0xffffffffu, (x >> 26) != 0ull)) return (u64)warp_inclusive_scan_u32((unsigned)x);
+    return warp_inclusive_scan(x, lane);
 }
 
 __device__ __forceinline__ u64 warp_reduce_sum(u64 x)
@@ -243,176 +291,188 @@ struct PodsArgs {
     Scratch *scratch;
 };
 
-template <bool kJob>
-__global__ void __launch_bounds__(kThreads) pods_kernel(PodsArgs a)
+// Rare path (a row that runs past the end of the container columns) kept out
+// of line so the hot loop stays small.  Everything by value: no stack traffic.
+struct RowTail { u64 x, y; unsigned sc; };
+__device__ __noinline__ RowTail load_row_tail(const i64 *ctr_val, const signed char *ctr_scale, u64 C, u64 idx)
 {
-    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
-    __shared__ u64 s_wa[kWarps], s_wb[kWarps];
+    RowTail t;
+    t.x = 0; t.y = 0; t.sc = 0;
+    if (idx < C) {
+        t.x = (u64)__ldg(ctr_val + idx);
+        t.sc = (unsigned char)__ldg(ctr_scale + idx);
+    }
+    if (idx + 1 < C) {
+        t.y = (u64)__ldg(ctr_val + idx + 1);
+        t.sc |= (unsigned)(unsigned char)__ldg(ctr_scale + idx + 1) << 8;
+    }
+    return t;
+}
 
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    u64 *prefix = s_prefix[warp];
+struct TileSums { u64 alloc, req; };   // tile totals, valid in lane 31
+
+// Generic tile: any containers-per-pod (multi-chunk), any int64 value, any
+// scale, ragged last tile.  64-bit arithmetic throughout.  This is the whole
+// job kernel; the top-node kernel only falls back to it for tiles its 32-bit
+// fast path cannot take.
+template <bool kJob>
+__device__ __forceinline__ TileSums process_tile_generic(const PodsArgs &a, const unsigned tile, const bool full_tile,
+                                                         const int lane, u64 *prefix)
+{
     const unsigned FULL = 0xffffffffu;
+    const u64 q = (u64)tile * kWarpPods + (u64)lane * kPodsPerLane;
 
-    u64 acc_alloc = 0, acc_req = 0;       // lane 31 accumulates the tile totals
-
-    const u64 n_tiles = (a.P + kWarpPods - 1) / kWarpPods;
-    for (u64 tile = (u64)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (u64)gridDim.x * kWarps) {
-        const u64 q = tile * kWarpPods + (u64)lane * kPodsPerLane;
-
-        // ---- 1. pod columns ------------------------------------------------
-        unsigned cb[kPodsPerLane + 1], key[kPodsPerLane], ph[kPodsPerLane];
-        unsigned role[kPodsPerLane];
-        if ((tile + 1) * kWarpPods <= a.P) {                 // full tile: vector loads
-            uint4 c4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_ctr_begin + q));
-            uint4 k4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_key + q));
-            unsigned p4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_phase + q));
-            unsigned last = 0;
-            if (lane == 31) last = __ldg(a.pod_ctr_begin + q + kPodsPerLane);
-            unsigned r4 = 0;
-            if (kJob) r4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_role + q));
-            cb[0] = c4.x; cb[1] = c4.y; cb[2] = c4.z; cb[3] = c4.w;
-            key[0] = k4.x; key[1] = k4.y; key[2] = k4.z; key[3] = k4.w;
-            unsigned nxt = __shfl_down_sync(FULL, c4.x, 1);
-            cb[4] = lane == 31 ? last : nxt;
+    // ---- 1. pod columns ------------------------------------------------
+    unsigned cb[kPodsPerLane + 1], key[kPodsPerLane];
+    unsigned ph4, r4 = 0;
+    if (full_tile) {                                     // vector loads
+        uint4 c4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_ctr_begin + q));
+        uint4 k4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_key + q));
+        ph4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_phase + q));
+        unsigned last = 0;
+        if (lane == 31) last = __ldg(a.pod_ctr_begin + q + kPodsPerLane);
+        if (kJob) r4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_role + q));
+        cb[0] = c4.x; cb[1] = c4.y; cb[2] = c4.z; cb[3] = c4.w;
+        key[0] = k4.x; key[1] = k4.y; key[2] = k4.z; key[3] = k4.w;
+        unsigned nxt = __shfl_down_sync(FULL, c4.x, 1);
+        cb[4] = lane == 31 ? last : nxt;
+    } else {                                             // ragged last tile
+        ph4 = 0;
 #pragma unroll
-            for (int j = 0; j < kPodsPerLane; j++) {
-                ph[j] = (p4 >> (8 * j)) & 0xffu;
-                role[j] = (r4 >> (8 * j)) & 0xffu;
-            }
-        } else {                                             // ragged last tile
-#pragma unroll
-            for (int j = 0; j <= kPodsPerLane; j++) {
-                u64 i = q + j;
-                cb[j] = __ldg(a.pod_ctr_begin + (i < a.P ? i : a.P));
-            }
-#pragma unroll
-            for (int j = 0; j < kPodsPerLane; j++) {
-                u64 i = q + j;
-                bool in = i < a.P;
-                key[j] = in ? __ldg(a.pod_key + i) : kNone;
-                ph[j] = in ? (unsigned)__ldg(a.pod_phase + i) : 0u;
-                role[j] = (kJob && in) ? (unsigned)__ldg(a.pod_role + i) : 0u;
-            }
+        for (int j = 0; j <= kPodsPerLane; j++) {
+            const u64 i = q + j;
+            cb[j] = __ldg(a.pod_ctr_begin + (i < a.P ? i : a.P));
         }
-
-        // ---- 2. container prefix sums --------------------------------------
-        const unsigned wc0 = __shfl_sync(FULL, cb[0], 0);
-        const unsigned wc1 = __shfl_sync(FULL, cb[kPodsPerLane], 31);
-        u64 B[kPodsPerLane + 1];
-#pragma unroll
-        for (int j = 0; j <= kPodsPerLane; j++) B[j] = 0;
-
-        if (wc1 > wc0) {
-            u64 carry = 0;
-            for (unsigned chunk_lo = wc0 & ~(unsigned)(kRowCtrs - 1); chunk_lo < wc1; chunk_lo += kChunkCtrs) {
-                ulonglong2 v[kRows];
-                unsigned sc[kRows];
-                // issue every load of the chunk before using any of them
-#pragma unroll
-                for (int r = 0; r < kRows; r++) {
-                    const unsigned rs = chunk_lo + r * kRowCtrs;
-                    const u64 idx = (u64)rs + 2u * lane;
-                    v[r].x = 0; v[r].y = 0; sc[r] = 0;
-                    if (rs < wc1) {
-                        if ((u64)rs + kRowCtrs <= a.C) {
-                            v[r] = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + idx));
-                            sc[r] = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + idx));
-                        } else {                              // row runs past the column end
-                            if (idx < a.C) {
-                                v[r].x = (u64)__ldg(a.ctr_val + idx);
-                                sc[r] = (unsigned char)__ldg(a.ctr_scale + idx);
-                            }
-                            if (idx + 1 < a.C) {
-                                v[r].y = (u64)__ldg(a.ctr_val + idx + 1);
-                                sc[r] |= (unsigned)(unsigned char)__ldg(a.ctr_scale + idx + 1) << 8;
-                            }
-                        }
-                    }
-                }
-                unsigned rows_done = 0;
-#pragma unroll
-                for (int r = 0; r < kRows; r++) {
-                    const unsigned rs = chunk_lo + r * kRowCtrs;
-                    if (rs < wc1) {                            // warp-uniform
-                        u64 x0 = (u64)quantity_value((i64)v[r].x, (int)(signed char)(sc[r] & 0xffu));
-                        u64 x1 = (u64)quantity_value((i64)v[r].y, (int)(signed char)((sc[r] >> 8) & 0xffu));
-                        u64 s = x0 + x1;
-                        u64 inc = warp_inclusive_scan(s, lane);
-                        u64 e0 = carry + inc - s;
-                        ulonglong2 e;
-                        e.x = e0;
-                        e.y = e0 + x0;
-                        *reinterpret_cast<ulonglong2 *>(prefix + r * kRowCtrs + 2 * lane) = e;
-                        carry += shfl_u64(inc, 31);
-                        if (lane == 31) prefix[(r + 1) * kRowCtrs] = carry;   // inclusive end of the row
-                        rows_done = r + 1;
-                    }
-                }
-                __syncwarp();
-                const unsigned n_valid = rows_done * kRowCtrs;
-#pragma unroll
-                for (int j = 0; j <= kPodsPerLane; j++) {
-                    unsigned off = cb[j] - chunk_lo;          // wraps when cb[j] < chunk_lo
-                    if (off <= n_valid) B[j] = prefix[off];
-                }
-                __syncwarp();
-            }
-        }
-
-        // ---- 3. pod values, masks, telescoping sums per key -----------------
-        u64 g[kPodsPerLane];
-#pragma unroll
-        for (int j = 0; j < kPodsPerLane; j++) g[j] = B[j + 1] - B[j];
-
-        if (a.pod_gpu != nullptr) {
-            if ((tile + 1) * kWarpPods <= a.P) {
-                ulonglong2 o0, o1;
-                o0.x = g[0]; o0.y = g[1]; o1.x = g[2]; o1.y = g[3];
-                ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(a.pod_gpu + q);
-                dst[0] = o0;
-                dst[1] = o1;
-            } else {
-#pragma unroll
-                for (int j = 0; j < kPodsPerLane; j++)
-                    if (q + j < a.P) a.pod_gpu[q + j] = (i64)g[j];
-            }
-        }
-
-        u64 S[kPodsPerLane], R[kPodsPerLane];
-        u64 run_a = 0, run_r = 0;
 #pragma unroll
         for (int j = 0; j < kPodsPerLane; j++) {
-            const bool valid = key[j] < a.K;
-            bool counts = valid;
-            if (kJob) {
-                if (valid && role[j] == 1) {                  // bids for "latest pod of the job"
-                    counts = false;
-                    atomicMax(a.key_maxcreated + key[j], __ldg(a.pod_created + q + j));
+            const u64 i = q + j;
+            const bool in = i < a.P;
+            key[j] = in ? __ldg(a.pod_key + i) : kNone;
+            ph4 |= (in ? (unsigned)__ldg(a.pod_phase + i) : 0u) << (8 * j);
+            if (kJob) r4 |= (in ? (unsigned)__ldg(a.pod_role + i) : 0u) << (8 * j);
+        }
+    }
+
+    // ---- 2. container prefix sums --------------------------------------
+    const unsigned wc0 = __shfl_sync(FULL, cb[0], 0);
+    const unsigned wc1 = __shfl_sync(FULL, cb[kPodsPerLane], 31);
+    u64 B[kPodsPerLane + 1];
+#pragma unroll
+    for (int j = 0; j <= kPodsPerLane; j++) B[j] = 0;
+
+    u64 carry = 0;
+    for (unsigned chunk_lo = wc0 & ~(unsigned)(kRowCtrs - 1); chunk_lo < wc1; chunk_lo += kChunkCtrs) {
+        ulonglong2 v[kRows];
+        unsigned sc[kRows];
+        // issue every load of the chunk before using any of them
+#pragma unroll
+        for (int r = 0; r < kRows; r++) {
+            const unsigned rs = chunk_lo + r * kRowCtrs;
+            const u64 idx = (u64)rs + 2u * lane;
+            v[r].x = 0; v[r].y = 0; sc[r] = 0;
+            if (rs < wc1) {
+                if ((u64)rs + kRowCtrs <= a.C) {
+                    v[r] = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + idx));
+                    sc[r] = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + idx));
+                } else {
+                    const RowTail t = load_row_tail(a.ctr_val, a.ctr_scale, a.C, idx);
+                    v[r].x = t.x; v[r].y = t.y; sc[r] = t.sc;
                 }
             }
-            const u64 req = counts ? g[j] : 0;
-            const u64 alc = (counts && phase_active(ph[j])) ? g[j] : 0;
-            run_a += alc;
-            S[j] = run_a;
-            if (kJob) { run_r += req; R[j] = run_r; }
         }
-        {
-            u64 inc = warp_inclusive_scan(run_a, lane);
-            u64 off = inc - run_a;
+        unsigned n_valid = 0;
 #pragma unroll
-            for (int j = 0; j < kPodsPerLane; j++) S[j] += off;
-            if (lane == 31) acc_alloc += inc;
+        for (int r = 0; r < kRows; r++) {
+            const unsigned rs = chunk_lo + r * kRowCtrs;
+            if (rs < wc1) {                                // warp-uniform
+                u64 x0 = v[r].x, x1 = v[r].y;
+                if (__any_sync(FULL, sc[r] != 0u)) {       // some quantity in the row has a scale
+                    const int s0 = (int)(signed char)(sc[r] & 0xffu);
+                    const int s1 = (int)(signed char)(sc[r] >> 8);
+                    if (s0 != 0) x0 = (u64)quantity_value_nz((i64)x0, s0);
+                    if (s1 != 0) x1 = (u64)quantity_value_nz((i64)x1, s1);
+                }
+                const u64 s = x0 + x1;
+                const u64 inc = warp_inclusive_scan_auto(s, lane);
+                const u64 e0 = carry + inc - s;
+                ulonglong2 e;
+                e.x = e0;
+                e.y = e0 + x0;
+                *reinterpret_cast<ulonglong2 *>(prefix + r * kRowCtrs + 2 * lane) = e;
+                carry += shfl_u64(inc, 31);
+                if (lane == 31) prefix[(r + 1) * kRowCtrs] = carry;   // inclusive end of the row
+                n_valid = (r + 1) * kRowCtrs;
+            }
         }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j <= kPodsPerLane; j++) {
+            const unsigned off = cb[j] - chunk_lo;         // wraps when cb[j] < chunk_lo
+            if (off <= n_valid) B[j] = prefix[off];
+        }
+        __syncwarp();
+    }
+
+    // ---- 3. pod values, masks, telescoping sums per key -----------------
+    u64 g[kPodsPerLane];
+#pragma unroll
+    for (int j = 0; j < kPodsPerLane; j++) g[j] = B[j + 1] - B[j];
+
+    if (a.pod_gpu != nullptr) {
+        if (full_tile) {
+            ulonglong2 o0, o1;
+            o0.x = g[0]; o0.y = g[1]; o1.x = g[2]; o1.y = g[3];
+            ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(a.pod_gpu + q);
+            dst[0] = o0;
+            dst[1] = o1;
+        } else {
+#pragma unroll
+            for (int j = 0; j < kPodsPerLane; j++)
+                if (q + j < a.P) a.pod_gpu[q + j] = (i64)g[j];
+        }
+    }
+
+    u64 S[kPodsPerLane], R[kPodsPerLane];
+    u64 run_a = 0, run_r = 0;
+#pragma unroll
+    for (int j = 0; j < kPodsPerLane; j++) {
+        const unsigned ph = (ph4 >> (8 * j)) & 0xffu;
+        bool counts = key[j] < a.K;
         if (kJob) {
-            u64 inc = warp_inclusive_scan(run_r, lane);
-            u64 off = inc - run_r;
-#pragma unroll
-            for (int j = 0; j < kPodsPerLane; j++) R[j] += off;
-            if (lane == 31) acc_req += inc;
+            const unsigned role = (r4 >> (8 * j)) & 0xffu;
+            if (counts && role == 1) {                    // bids for "latest pod of the job"
+                counts = false;
+                atomicMax(a.key_maxcreated + key[j], __ldg(a.pod_created + q + j));
+            }
         }
-        unsigned key_next = __shfl_down_sync(FULL, key[0], 1);
-        if (lane == 31) key_next = kNone;
+        const u64 req = counts ? g[j] : 0;
+        const u64 alc = phase_active(ph) ? req : 0;
+        run_a += alc;
+        S[j] = run_a;
+        if (kJob) { run_r += req; R[j] = run_r; }
+    }
+    TileSums out;
+    out.alloc = 0; out.req = 0;
+    {
+        const u64 inc = warp_inclusive_scan_auto(run_a, lane);
+        const u64 off = inc - run_a;
+#pragma unroll
+        for (int j = 0; j < kPodsPerLane; j++) S[j] += off;
+        out.alloc = inc;
+    }
+    if (kJob) {
+        const u64 inc = warp_inclusive_scan_auto(run_r, lane);
+        const u64 off = inc - run_r;
+#pragma unroll
+        for (int j = 0; j < kPodsPerLane; j++) R[j] += off;
+        out.req = inc;
+    }
+    unsigned key_next = __shfl_down_sync(FULL, key[0], 1);
+    if (lane == 31) key_next = kNone;
+    // a lane has work here only where the key changes (rare on grouped input)
+    const bool any_edge = (key[0] != key[1]) | (key[1] != key[2]) | (key[2] != key[3]) |
+                          (key[3] != key_next) | (lane == 31);
+    if (any_edge) {
 #pragma unroll
         for (int j = 0; j < kPodsPerLane; j++) {
             const unsigned kl = key[j];
@@ -430,14 +490,250 @@ __global__ void __launch_bounds__(kThreads) pods_kernel(PodsArgs a)
             }
         }
     }
+    return out;
+}
 
-    // ---- totals over all keys: per-CTA partials, last CTA finishes ----------
+// Out-of-line copy for the top-node kernel's fallback (by-value args: the copy
+// is made at the rare call site, not at kernel entry).
+__device__ __noinline__ TileSums process_tile_fallback(PodsArgs a, unsigned tile, bool full_tile, int lane, u64 *prefix)
+{
+    return process_tile_generic<false>(a, tile, full_tile, lane, prefix);
+}
+
+// Job kernel: generic tiles only.
+__global__ void __launch_bounds__(kThreads) job_pods_kernel(PodsArgs a)
+{
+    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
+    __shared__ u64 s_wa[kWarps], s_wb[kWarps];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    u64 acc_alloc = 0, acc_req = 0;
+    const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
+    const unsigned n_full = (unsigned)(a.P / kWarpPods);
+    for (unsigned tile = blockIdx.x * kWarps + warp; tile < n_tiles; tile += gridDim.x * kWarps) {
+        const TileSums t = process_tile_generic<true>(a, tile, tile < n_full, lane, s_prefix[warp]);
+        acc_alloc += t.alloc;
+        acc_req += t.req;
+    }
     if (lane == 31) { s_wa[warp] = acc_alloc; s_wb[warp] = acc_req; }
     __syncthreads();
     u64 block_a = 0, block_b = 0;
     if (threadIdx.x == 0)
         for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_b += s_wb[w]; }
-    finish_totals(block_a, block_b, kJob, a.scratch, kJob ? 2 : 1, a.total_alloc, a.total_req);
+    finish_totals(block_a, block_b, true, a.scratch, 2, a.total_alloc, a.total_req);
+}
+
+// ---------------------------------------------------------------------------
+// Top-node pods kernel: 32-bit fast path.
+//
+// A tile takes the fast path when (warp-uniform tests)
+//   * it is a full tile of 128 pods,
+//   * its containers fit one chunk: at most 256 container slots from the even
+//     index at or below its first container, all inside the columns,
+//   * every quantity it touches is small and plain: 0 <= value < 2^23 and
+//     scale in [-9, 0].
+// Then every prefix sum fits 32 bits (256 * 2^23 = 2^31), so the whole tile is
+// 32-bit adds, 32-bit shuffles and 32-bit shared-memory words; the container
+// rows are 128 wide (4 per lane: two 128-bit loads of values, two 16-bit loads
+// of scales), so a typical tile is 2 rows = 2 warp scans.  Quantities with a
+// negative scale go through a multiply-by-reciprocal table (exact for these
+// ranges, see kDiv10).  Anything else -- negative or huge values, positive
+// scales, pods with hundreds of containers, the ragged last tile -- is handed
+// to the 64-bit generic tile, so the result is always exact.
+// ---------------------------------------------------------------------------
+constexpr int kFastRow = 128;              // containers per fast-path row
+constexpr unsigned kSmallBits = 23;
+
+// k = -scale in [0, 9]:  x / 10^k == (x * m) >> sh  exactly for x < 2^23
+// (m = floor(2^sh / 10^k) + 1 with sh = 24 + ceil(log2(10^k)): the error term
+// x * (m*d - 2^sh) / (d * 2^sh) < 2^23 * d / (d * 2^sh) <= 1/(2d) < 1/d).
+struct Div10 { unsigned m, sh, d, pad; };
+__device__ __constant__ Div10 kDiv10[10] = {
+    {1u, 0u, 1u, 0u},
+    {26843546u, 28u, 10u, 0u},          // 2^28/10 + 1
+    {21474837u, 31u, 100u, 0u},         // 2^31/100 + 1
+    {17179870u, 34u, 1000u, 0u},        // 2^34/1000 + 1
+    {27487791u, 38u, 10000u, 0u},       // 2^38/1e4 + 1
+    {21990233u, 41u, 100000u, 0u},      // 2^41/1e5 + 1
+    {17592187u, 44u, 1000000u, 0u},     // 2^44/1e6 + 1
+    {28147498u, 48u, 10000000u, 0u},    // 2^48/1e7 + 1
+    {22517999u, 51u, 100000000u, 0u},   // 2^51/1e8 + 1
+    {18014399u, 54u, 1000000000u, 0u},  // 2^54/1e9 + 1
+};
+
+__device__ __forceinline__ unsigned small_value_scaled(unsigned x, unsigned sbyte, const Div10 *tbl)
+{
+    // sbyte = scale as an unsigned byte in {0} U [0xF7, 0xFF]; k = -scale
+    const unsigned k = (0u - sbyte) & 0xffu;
+    const Div10 t = tbl[k];
+    const unsigned q = (unsigned)(((u64)x * t.m) >> t.sh);
+    const unsigned r = x - q * t.d;
+    return q + (r != 0u);                 // round away from zero (x >= 0)
+}
+
+__global__ void __launch_bounds__(kThreads, 4) top_node_pods_kernel(PodsArgs a)
+{
+    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
+    __shared__ u64 s_wa[kWarps];
+    __shared__ Div10 s_div[10];
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const unsigned FULL = 0xffffffffu;
+    if (threadIdx.x < 10) s_div[threadIdx.x] = kDiv10[threadIdx.x];
+    __syncthreads();
+    unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
+
+    u64 acc_alloc = 0;
+    const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
+    const unsigned n_full = (unsigned)(a.P / kWarpPods);
+    const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
+    const unsigned tile_step = gridDim.x * kWarps;
+
+    for (unsigned tile = blockIdx.x * kWarps + warp; tile < n_tiles; tile += tile_step) {
+        bool fast = tile < n_full;
+        u64 tile_alloc = 0;
+        if (fast) {
+            const u64 q = (u64)tile * kWarpPods + (u64)lane * kPodsPerLane;
+            // ---- pod columns -------------------------------------------------
+            const uint4 c4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_ctr_begin + q));
+            const uint4 k4 = ldg_stream(reinterpret_cast<const uint4 *>(a.pod_key + q));
+            const unsigned ph4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_phase + q));
+            unsigned cb4 = 0;
+            if (lane == 31) cb4 = __ldg(a.pod_ctr_begin + q + kPodsPerLane);
+            {
+                const unsigned nxt = __shfl_down_sync(FULL, c4.x, 1);
+                if (lane != 31) cb4 = nxt;
+            }
+            const unsigned wc0 = __shfl_sync(FULL, c4.x, 0);
+            const unsigned wc1 = __shfl_sync(FULL, cb4, 31);
+            const unsigned base = wc0 & ~1u;                  // even: 16-byte aligned value pairs
+            const unsigned span = wc1 - base;
+            fast = span <= (unsigned)kChunkCtrs && (u64)base + kChunkCtrs <= a.C;
+            if (fast) {
+                // ---- container rows: loads first ---------------------------------
+                const unsigned i0 = base + 4u * lane;
+                const bool two = span > (unsigned)kFastRow;       // warp-uniform
+                ulonglong2 va = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0));
+                ulonglong2 vb = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + 2));
+                unsigned sa = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0));
+                unsigned sb = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + 2));
+                ulonglong2 vc, vd;
+                unsigned sc = 0, sd = 0;
+                vc.x = vc.y = vd.x = vd.y = 0;
+                if (two) {
+                    vc = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow));
+                    vd = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow + 2));
+                    sc = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow));
+                    sd = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow + 2));
+                }
+                // ---- eligibility: small non-negative values, scales in [-9, 0] ----
+                const u64 big = (va.x | va.y | vb.x | vb.y | vc.x | vc.y | vd.x | vd.y) >> kSmallBits;
+                const unsigned s4a = sa | (sb << 16), s4b = sc | (sd << 16);
+                bool bad = big != 0ull;
+                if ((s4a | s4b) != 0u) {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const unsigned ba = (s4a >> (8 * i)) & 0xffu, bb = (s4b >> (8 * i)) & 0xffu;
+                        bad |= (ba != 0u && ba < 0xF7u) | (bb != 0u && bb < 0xF7u);
+                    }
+                }
+                fast = !__any_sync(FULL, bad);
+                if (fast) {
+                    // ---- decode + prefix sums, 32-bit ---------------------------------
+                    unsigned x0 = (unsigned)va.x, x1 = (unsigned)va.y, x2 = (unsigned)vb.x, x3 = (unsigned)vb.y;
+                    if (s4a != 0u) {
+                        x0 = small_value_scaled(x0, s4a & 0xffu, s_div);
+                        x1 = small_value_scaled(x1, (s4a >> 8) & 0xffu, s_div);
+                        x2 = small_value_scaled(x2, (s4a >> 16) & 0xffu, s_div);
+                        x3 = small_value_scaled(x3, s4a >> 24, s_div);
+                    }
+                    {
+                        const unsigned p1 = x0, p2 = p1 + x1, p3 = p2 + x2, s = p3 + x3;
+                        const unsigned inc = warp_inclusive_scan_u32(s);
+                        const unsigned ex = inc - s;
+                        *reinterpret_cast<uint4 *>(pre32 + 4 * lane) = make_uint4(ex, ex + p1, ex + p2, ex + p3);
+                        if (lane == 31) pre32[kFastRow] = inc;
+                        if (two) {
+                            const unsigned t0 = __shfl_sync(FULL, inc, 31);
+                            unsigned y0 = (unsigned)vc.x, y1 = (unsigned)vc.y, y2 = (unsigned)vd.x, y3 = (unsigned)vd.y;
+                            if (s4b != 0u) {
+                                y0 = small_value_scaled(y0, s4b & 0xffu, s_div);
+                                y1 = small_value_scaled(y1, (s4b >> 8) & 0xffu, s_div);
+                                y2 = small_value_scaled(y2, (s4b >> 16) & 0xffu, s_div);
+                                y3 = small_value_scaled(y3, s4b >> 24, s_div);
+                            }
+                            const unsigned r1 = y0, r2 = r1 + y1, r3 = r2 + y2, s2 = r3 + y3;
+                            const unsigned inc2 = warp_inclusive_scan_u32(s2);
+                            const unsigned ex2 = t0 + inc2 - s2;
+                            *reinterpret_cast<uint4 *>(pre32 + kFastRow + 4 * lane) =
+                                make_uint4(ex2, ex2 + r1, ex2 + r2, ex2 + r3);
+                            if (lane == 31) pre32[2 * kFastRow] = t0 + inc2;
+                        }
+                    }
+                    __syncwarp();
+                    // ---- gpuInPod = prefix[end] - prefix[begin] -------------------------
+                    const unsigned b0 = pre32[c4.x - base], b1 = pre32[c4.y - base], b2 = pre32[c4.z - base],
+                                   b3 = pre32[c4.w - base], b4 = pre32[cb4 - base];
+                    __syncwarp();
+                    const unsigned g0 = b1 - b0, g1 = b2 - b1, g2 = b3 - b2, g3 = b4 - b3;
+                    if (a.pod_gpu != nullptr) {
+                        ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(a.pod_gpu + q);
+                        ulonglong2 o0, o1;
+                        o0.x = g0; o0.y = g1; o1.x = g2; o1.y = g3;
+                        dst[0] = o0;
+                        dst[1] = o1;
+                    }
+                    // ---- masks: node exists, phase active ------------------------------
+                    // bytes equal to 3 or 4 <=> (byte - 3) < 2; test all four at once
+                    const unsigned a0 = (k4.x < K32 && phase_active(ph4 & 0xffu)) ? g0 : 0u;
+                    const unsigned a1 = (k4.y < K32 && phase_active((ph4 >> 8) & 0xffu)) ? g1 : 0u;
+                    const unsigned a2 = (k4.z < K32 && phase_active((ph4 >> 16) & 0xffu)) ? g2 : 0u;
+                    const unsigned a3 = (k4.w < K32 && phase_active(ph4 >> 24)) ? g3 : 0u;
+                    const unsigned S0 = a0, S1 = S0 + a1, S2 = S1 + a2, S3 = S2 + a3;
+                    const unsigned inc = warp_inclusive_scan_u32(S3);
+                    const unsigned off = inc - S3;
+                    tile_alloc = inc;
+                    // ---- telescoping per-node sums: work only where the node changes ----
+                    unsigned key_next = __shfl_down_sync(FULL, k4.x, 1);
+                    if (lane == 31) key_next = kNone;
+                    const bool e0 = k4.x != k4.y, e1 = k4.y != k4.z, e2 = k4.z != k4.w;
+                    const bool e3 = (k4.w != key_next) | (lane == 31);
+                    if (e0 | e1 | e2 | e3) {
+                        if (e0) {
+                            const u64 v = off + S0;
+                            if (k4.x < K32) red_add(a.key_alloc + k4.x, v);
+                            if (k4.y < K32) red_add(a.key_alloc + k4.y, 0ull - v);
+                        }
+                        if (e1) {
+                            const u64 v = off + S1;
+                            if (k4.y < K32) red_add(a.key_alloc + k4.y, v);
+                            if (k4.z < K32) red_add(a.key_alloc + k4.z, 0ull - v);
+                        }
+                        if (e2) {
+                            const u64 v = off + S2;
+                            if (k4.z < K32) red_add(a.key_alloc + k4.z, v);
+                            if (k4.w < K32) red_add(a.key_alloc + k4.w, 0ull - v);
+                        }
+                        if (e3) {
+                            const u64 v = off + S3;
+                            if (k4.w < K32) red_add(a.key_alloc + k4.w, v);
+                            if (lane != 31 && key_next < K32) red_add(a.key_alloc + key_next, 0ull - v);
+                        }
+                    }
+                }
+            }
+        }
+        if (!fast) tile_alloc = process_tile_fallback(a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+        if (lane == 31) acc_alloc += tile_alloc;
+    }
+
+    if (lane == 31) s_wa[warp] = acc_alloc;
+    __syncthreads();
+    u64 block_a = 0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kWarps; w++) block_a += s_wa[w];
+    finish_totals(block_a, 0, false, a.scratch, 1, a.total_alloc, nullptr);
 }
 
 // ---------------------------------------------------------------------------

@@ -72,15 +72,23 @@ def top_node(snap: Union[DeviceSnapshot, HostSnapshot], details: bool = False) -
     return TopNodeResult(total, alloc, cluster, pod_gpu)
 
 
+def _stream_arg(stream: Optional[int]):
+    """None -> the library's own stream; 0 (torch's default stream handle) ->
+    cudaStreamLegacy, because a NULL stream means "library stream" in the ABI."""
+    if stream is None:
+        return None
+    return C.c_void_p(stream if stream else 1)
+
+
 def top_node_device(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cluster, d_pod_gpu=None,
-                    stream: int = 0) -> None:
+                    stream: Optional[int] = None) -> None:
     """Enqueue the kernels with torch CUDA tensors as outputs; no sync."""
     check(lib().arena_top_node_device(
         snap.handle,
         d_node_total.data_ptr() if d_node_total is not None and d_node_total.numel() else None,
         d_node_alloc.data_ptr() if d_node_alloc is not None and d_node_alloc.numel() else None,
         d_cluster.data_ptr(), d_pod_gpu.data_ptr() if d_pod_gpu is not None else None,
-        C.c_void_p(stream) if stream else None))
+        _stream_arg(stream)))
 
 
 def top_job(snap: DeviceSnapshot) -> TopJobResult:
@@ -94,12 +102,13 @@ def top_job(snap: DeviceSnapshot) -> TopJobResult:
     return TopJobResult(req, alloc, order, latest, totals)
 
 
-def top_job_device(snap: DeviceSnapshot, d_req, d_alloc, d_order, d_latest, d_totals, stream: int = 0) -> None:
+def top_job_device(snap: DeviceSnapshot, d_req, d_alloc, d_order, d_latest, d_totals,
+                   stream: Optional[int] = None) -> None:
     check(lib().arena_top_job_device(
         snap.handle, d_req.data_ptr() if d_req.numel() else None, d_alloc.data_ptr() if d_alloc.numel() else None,
         d_order.data_ptr() if d_order.numel() else None,
         d_latest.data_ptr() if d_latest is not None and d_latest.numel() else None, d_totals.data_ptr(),
-        C.c_void_p(stream) if stream else None))
+        _stream_arg(stream)))
 
 
 def quantity_values(val: np.ndarray, scale: np.ndarray) -> np.ndarray:

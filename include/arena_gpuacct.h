@@ -121,7 +121,8 @@ int  arena_top_node(const arena_snapshot *s, int64_t *node_total, int64_t *node_
                     int64_t cluster[2], int64_t *pod_gpu);
 
 /* Same computation, DEVICE output buffers, enqueued on `stream` (a
- * cudaStream_t, NULL = the library's own stream) without synchronising.  Used
+ * cudaStream_t; NULL = the library's own stream, so pass cudaStreamLegacy to
+ * mean the legacy default stream) without synchronising.  Used
  * to time the kernels alone and to feed d_cluster to an NCCL all-reduce. */
 int  arena_top_node_device(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
                            int64_t *d_cluster, int64_t *d_pod_gpu, void *stream);
