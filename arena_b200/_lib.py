@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libarena_gpuacct.so")
+# ARENA_GPUACCT_LIB: A/B-test another build of the same library (kernel tuning only)
+LIB_PATH = os.environ.get("ARENA_GPUACCT_LIB") or os.path.join(_HERE, "libarena_gpuacct.so")
 
 ARENA_NONE = 0xFFFFFFFF
 

@@ -493,11 +493,11 @@ __device__ __forceinline__ TileSums process_tile_generic(const PodsArgs &a, cons
     return out;
 }
 
-// Out-of-line copy for the top-node kernel's fallback (by-value args: the copy
-// is made at the rare call site, not at kernel entry).
-__device__ __noinline__ TileSums process_tile_fallback(PodsArgs a, unsigned tile, bool full_tile, int lane, u64 *prefix)
+// Out-of-line copy for the top-node kernel's fallback.  The kernel parameter is
+// __grid_constant__, so its address can be passed without a local copy.
+__device__ __noinline__ TileSums process_tile_fallback(const PodsArgs *a, unsigned tile, bool full_tile, int lane, u64 *prefix)
 {
-    return process_tile_generic<false>(a, tile, full_tile, lane, prefix);
+    return process_tile_generic<false>(*a, tile, full_tile, lane, prefix);
 }
 
 // Job kernel: generic tiles only.
@@ -528,59 +528,116 @@ __global__ void __launch_bounds__(kThreads) job_pods_kernel(PodsArgs a)
 //
 // A tile takes the fast path when (warp-uniform tests)
 //   * it is a full tile of 128 pods,
-//   * its containers fit one chunk: at most 256 container slots from the even
-//     index at or below its first container, all inside the columns,
+//   * its containers fit one chunk: at most 256 container slots counted from
+//     the multiple of 16 at or below its first container (128-byte aligned
+//     value rows), all inside the columns,
 //   * every quantity it touches is small and plain: 0 <= value < 2^23 and
 //     scale in [-9, 0].
 // Then every prefix sum fits 32 bits (256 * 2^23 = 2^31), so the whole tile is
-// 32-bit adds, 32-bit shuffles and 32-bit shared-memory words; the container
-// rows are 128 wide (4 per lane: two 128-bit loads of values, two 16-bit loads
-// of scales), so a typical tile is 2 rows = 2 warp scans.  Quantities with a
-// negative scale go through a multiply-by-reciprocal table (exact for these
-// ranges, see kDiv10).  Anything else -- negative or huge values, positive
-// scales, pods with hundreds of containers, the ragged last tile -- is handed
-// to the 64-bit generic tile, so the result is always exact.
+// 32-bit adds, 32-bit shuffles and 32-bit shared-memory words.
+//
+// Row geometry: a row is 128 containers = two halves of 64.  Lane l owns the
+// pair {2l, 2l+1} of each half, so every value load is one fully coalesced
+// 128-bit load per lane (512 contiguous bytes per warp) and every scale load a
+// coalesced 16-bit load.  The two halves need two prefix scans; when the lane
+// sums are below 2^11 (any realistic GPU count) they are packed into the two
+// 16-bit fields of ONE 32-bit scan.  A typical tile is 2 rows = 2 scans.
+// Quantities with a negative scale ("500m") are rounded up with a
+// multiply-by-reciprocal table (kCeilDiv10, exact on this range) in a loop that
+// only runs for the lanes that hold one.  Anything else -- negative or huge
+// values, positive scales, pods with hundreds of containers, the ragged last
+// tile -- is handed to the 64-bit generic tile, so the result is always exact.
 // ---------------------------------------------------------------------------
-constexpr int kFastRow = 128;              // containers per fast-path row
+constexpr int kHalf = 64;                  // containers per half row
+constexpr int kFastRow = 2 * kHalf;        // containers per fast-path row
 constexpr unsigned kSmallBits = 23;
 
-// k = -scale in [0, 9]:  x / 10^k == (x * m) >> sh  exactly for x < 2^23
-// (m = floor(2^sh / 10^k) + 1 with sh = 24 + ceil(log2(10^k)): the error term
-// x * (m*d - 2^sh) / (d * 2^sh) < 2^23 * d / (d * 2^sh) <= 1/(2d) < 1/d).
-struct Div10 { unsigned m, sh, d, pad; };
-__device__ __constant__ Div10 kDiv10[10] = {
-    {1u, 0u, 1u, 0u},
-    {26843546u, 28u, 10u, 0u},          // 2^28/10 + 1
-    {21474837u, 31u, 100u, 0u},         // 2^31/100 + 1
-    {17179870u, 34u, 1000u, 0u},        // 2^34/1000 + 1
-    {27487791u, 38u, 10000u, 0u},       // 2^38/1e4 + 1
-    {21990233u, 41u, 100000u, 0u},      // 2^41/1e5 + 1
-    {17592187u, 44u, 1000000u, 0u},     // 2^44/1e6 + 1
-    {28147498u, 48u, 10000000u, 0u},    // 2^48/1e7 + 1
-    {22517999u, 51u, 100000000u, 0u},   // 2^51/1e8 + 1
-    {18014399u, 54u, 1000000000u, 0u},  // 2^54/1e9 + 1
+// k = -scale in [0, 9]:  ceil(x / 10^k) == ((x + 10^k - 1) * m) >> sh exactly for
+// x < 2^23 (sh = 31 + ceil(log2 10^k), m = floor(2^sh / 10^k) + 1 < 2^32;
+// t = x + 10^k - 1 < 2^31 so t * 10^k < 2^sh, which bounds the error term below
+// 1/10^k).  Checked exhaustively by tests/test_tables.py.
+struct CeilDiv10 { unsigned m, sh, dm1, pad; };
+__device__ __constant__ CeilDiv10 kCeilDiv10[10] = {
+    {1u, 0u, 0u, 0u},
+    {3435973837u, 35u, 9u, 0u},
+    {2748779070u, 38u, 99u, 0u},
+    {2199023256u, 41u, 999u, 0u},
+    {3518437209u, 45u, 9999u, 0u},
+    {2814749768u, 48u, 99999u, 0u},
+    {2251799814u, 51u, 999999u, 0u},
+    {3602879702u, 55u, 9999999u, 0u},
+    {2882303762u, 58u, 99999999u, 0u},
+    {2305843010u, 61u, 999999999u, 0u},
 };
 
-__device__ __forceinline__ unsigned small_value_scaled(unsigned x, unsigned sbyte, const Div10 *tbl)
+__device__ __forceinline__ void red_add_u64(u64 *p, u64 v)
 {
-    // sbyte = scale as an unsigned byte in {0} U [0xF7, 0xFF]; k = -scale
-    const unsigned k = (0u - sbyte) & 0xffu;
-    const Div10 t = tbl[k];
-    const unsigned q = (unsigned)(((u64)x * t.m) >> t.sh);
-    const unsigned r = x - q * t.d;
-    return q + (r != 0u);                 // round away from zero (x >= 0)
+    asm volatile("red.global.add.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(kThreads, 4) top_node_pods_kernel(PodsArgs a)
+// Decode one scaled quantity: sb = scale byte (0, or 0xF7..0xFF for -9..-1).
+// A scale outside [-9, 0] sets `bad` (the tile is then redone by the generic path).
+__device__ __forceinline__ unsigned decode_one(unsigned x, unsigned sb, const CeilDiv10 *tbl, bool &bad)
+{
+    const unsigned k = (0u - sb) & 0xffu;                     // k = -scale
+    bad |= k > 9u;
+    const CeilDiv10 t = tbl[k < 10u ? k : 0u];
+    return (unsigned)(((u64)(x + t.dm1) * t.m) >> t.sh);
+}
+
+// One row: decode, prefix-sum, park exclusive prefixes in pre32[0..128], return
+// the running total after the row.  (xa0,xa1) = lane's pair in the first half,
+// (xb0,xb1) = its pair in the second half.
+__device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigned xb0, unsigned xb1, unsigned sbytes,
+                                             unsigned carry, unsigned *pre32, int lane, const CeilDiv10 *tbl, bool &bad)
+{
+    const unsigned FULL = 0xffffffffu;
+    // scaled quantities are rare: each of the four positions is decoded only by
+    // the lanes that hold one there (divergent, skipped when no lane does)
+    if (sbytes != 0u) {
+        if (sbytes & 0x000000ffu) xa0 = decode_one(xa0, sbytes & 0xffu, tbl, bad);
+        if (sbytes & 0x0000ff00u) xa1 = decode_one(xa1, (sbytes >> 8) & 0xffu, tbl, bad);
+        if (sbytes & 0x00ff0000u) xb0 = decode_one(xb0, (sbytes >> 16) & 0xffu, tbl, bad);
+        if (sbytes & 0xff000000u) xb1 = decode_one(xb1, sbytes >> 24, tbl, bad);
+    }
+    const unsigned sA = xa0 + xa1, sB = xb0 + xb1;
+    unsigned exA, exB, tA, tB;
+    if (!__any_sync(FULL, (sA | sB) >= 2048u)) {             // both scans in one: 16-bit fields
+        const unsigned w = sA | (sB << 16);
+        const unsigned inc = warp_inclusive_scan_u32(w);
+        const unsigned tw = __shfl_sync(FULL, inc, 31);
+        const unsigned ex = inc - w;
+        exA = ex & 0xffffu; exB = ex >> 16;
+        tA = tw & 0xffffu; tB = tw >> 16;
+    } else {
+        const unsigned incA = warp_inclusive_scan_u32(sA);
+        const unsigned incB = warp_inclusive_scan_u32(sB);
+        exA = incA - sA; exB = incB - sB;
+        tA = __shfl_sync(FULL, incA, 31);
+        tB = __shfl_sync(FULL, incB, 31);
+    }
+    exA += carry;
+    exB += carry + tA;
+    *reinterpret_cast<uint2 *>(pre32 + 2 * lane) = make_uint2(exA, exA + xa0);
+    *reinterpret_cast<uint2 *>(pre32 + kHalf + 2 * lane) = make_uint2(exB, exB + xb0);
+    const unsigned total = carry + tA + tB;
+    if (lane == 31) pre32[kFastRow] = total;                  // inclusive end of the row
+    return total;
+}
+
+#ifndef ARENA_MINB
+#define ARENA_MINB 6
+#endif
+__global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
     __shared__ u64 s_wa[kWarps];
-    __shared__ Div10 s_div[10];
+    __shared__ CeilDiv10 s_div[10];
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const unsigned FULL = 0xffffffffu;
-    if (threadIdx.x < 10) s_div[threadIdx.x] = kDiv10[threadIdx.x];
+    if (threadIdx.x < 10) s_div[threadIdx.x] = kCeilDiv10[threadIdx.x];
     __syncthreads();
     unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
 
@@ -607,70 +664,40 @@ __global__ void __launch_bounds__(kThreads, 4) top_node_pods_kernel(PodsArgs a)
             }
             const unsigned wc0 = __shfl_sync(FULL, c4.x, 0);
             const unsigned wc1 = __shfl_sync(FULL, cb4, 31);
-            const unsigned base = wc0 & ~1u;                  // even: 16-byte aligned value pairs
+            const unsigned base = wc0 & ~15u;                 // 16 values = 128 bytes
             const unsigned span = wc1 - base;
             fast = span <= (unsigned)kChunkCtrs && (u64)base + kChunkCtrs <= a.C;
             if (fast) {
-                // ---- container rows: loads first ---------------------------------
-                const unsigned i0 = base + 4u * lane;
+                // ---- container rows: every load first -------------------------------
+                const unsigned i0 = base + 2u * lane;
                 const bool two = span > (unsigned)kFastRow;       // warp-uniform
-                ulonglong2 va = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0));
-                ulonglong2 vb = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + 2));
-                unsigned sa = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0));
-                unsigned sb = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + 2));
-                ulonglong2 vc, vd;
-                unsigned sc = 0, sd = 0;
-                vc.x = vc.y = vd.x = vd.y = 0;
+                const ulonglong2 vA0 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0));
+                const ulonglong2 vB0 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kHalf));
+                unsigned s0 = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0));
+                s0 |= (unsigned)__ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kHalf)) << 16;
+                ulonglong2 vA1, vB1;
+                unsigned s1 = 0;
+                vA1.x = vA1.y = vB1.x = vB1.y = 0;
                 if (two) {
-                    vc = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow));
-                    vd = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow + 2));
-                    sc = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow));
-                    sd = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow + 2));
+                    vA1 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow));
+                    vB1 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow + kHalf));
+                    s1 = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow));
+                    s1 |= (unsigned)__ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow + kHalf)) << 16;
                 }
                 // ---- eligibility: small non-negative values, scales in [-9, 0] ----
-                const u64 big = (va.x | va.y | vb.x | vb.y | vc.x | vc.y | vd.x | vd.y) >> kSmallBits;
-                const unsigned s4a = sa | (sb << 16), s4b = sc | (sd << 16);
-                bool bad = big != 0ull;
-                if ((s4a | s4b) != 0u) {
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const unsigned ba = (s4a >> (8 * i)) & 0xffu, bb = (s4b >> (8 * i)) & 0xffu;
-                        bad |= (ba != 0u && ba < 0xF7u) | (bb != 0u && bb < 0xF7u);
-                    }
-                }
+                bool bad = ((vA0.x | vA0.y | vB0.x | vB0.y | vA1.x | vA1.y | vB1.x | vB1.y) >> kSmallBits) != 0ull;
                 fast = !__any_sync(FULL, bad);
                 if (fast) {
-                    // ---- decode + prefix sums, 32-bit ---------------------------------
-                    unsigned x0 = (unsigned)va.x, x1 = (unsigned)va.y, x2 = (unsigned)vb.x, x3 = (unsigned)vb.y;
-                    if (s4a != 0u) {
-                        x0 = small_value_scaled(x0, s4a & 0xffu, s_div);
-                        x1 = small_value_scaled(x1, (s4a >> 8) & 0xffu, s_div);
-                        x2 = small_value_scaled(x2, (s4a >> 16) & 0xffu, s_div);
-                        x3 = small_value_scaled(x3, s4a >> 24, s_div);
-                    }
-                    {
-                        const unsigned p1 = x0, p2 = p1 + x1, p3 = p2 + x2, s = p3 + x3;
-                        const unsigned inc = warp_inclusive_scan_u32(s);
-                        const unsigned ex = inc - s;
-                        *reinterpret_cast<uint4 *>(pre32 + 4 * lane) = make_uint4(ex, ex + p1, ex + p2, ex + p3);
-                        if (lane == 31) pre32[kFastRow] = inc;
-                        if (two) {
-                            const unsigned t0 = __shfl_sync(FULL, inc, 31);
-                            unsigned y0 = (unsigned)vc.x, y1 = (unsigned)vc.y, y2 = (unsigned)vd.x, y3 = (unsigned)vd.y;
-                            if (s4b != 0u) {
-                                y0 = small_value_scaled(y0, s4b & 0xffu, s_div);
-                                y1 = small_value_scaled(y1, (s4b >> 8) & 0xffu, s_div);
-                                y2 = small_value_scaled(y2, (s4b >> 16) & 0xffu, s_div);
-                                y3 = small_value_scaled(y3, s4b >> 24, s_div);
-                            }
-                            const unsigned r1 = y0, r2 = r1 + y1, r3 = r2 + y2, s2 = r3 + y3;
-                            const unsigned inc2 = warp_inclusive_scan_u32(s2);
-                            const unsigned ex2 = t0 + inc2 - s2;
-                            *reinterpret_cast<uint4 *>(pre32 + kFastRow + 4 * lane) =
-                                make_uint4(ex2, ex2 + r1, ex2 + r2, ex2 + r3);
-                            if (lane == 31) pre32[2 * kFastRow] = t0 + inc2;
-                        }
-                    }
+                    unsigned total = fast_row((unsigned)vA0.x, (unsigned)vA0.y, (unsigned)vB0.x, (unsigned)vB0.y, s0,
+                                              0u, pre32, lane, s_div, bad);
+                    if (two)
+                        total = fast_row((unsigned)vA1.x, (unsigned)vA1.y, (unsigned)vB1.x, (unsigned)vB1.y, s1,
+                                         total, pre32 + kFastRow, lane, s_div, bad);
+                    // a scale outside [-9, 0] turned up while decoding: redo the tile generically
+                    // (nothing has been published yet: shared memory is scratch, atomics come later)
+                    fast = !__any_sync(FULL, bad);
+                }
+                if (fast) {
                     __syncwarp();
                     // ---- gpuInPod = prefix[end] - prefix[begin] -------------------------
                     const unsigned b0 = pre32[c4.x - base], b1 = pre32[c4.y - base], b2 = pre32[c4.z - base],
@@ -685,7 +712,6 @@ __global__ void __launch_bounds__(kThreads, 4) top_node_pods_kernel(PodsArgs a)
                         dst[1] = o1;
                     }
                     // ---- masks: node exists, phase active ------------------------------
-                    // bytes equal to 3 or 4 <=> (byte - 3) < 2; test all four at once
                     const unsigned a0 = (k4.x < K32 && phase_active(ph4 & 0xffu)) ? g0 : 0u;
                     const unsigned a1 = (k4.y < K32 && phase_active((ph4 >> 8) & 0xffu)) ? g1 : 0u;
                     const unsigned a2 = (k4.z < K32 && phase_active((ph4 >> 16) & 0xffu)) ? g2 : 0u;
@@ -702,29 +728,29 @@ __global__ void __launch_bounds__(kThreads, 4) top_node_pods_kernel(PodsArgs a)
                     if (e0 | e1 | e2 | e3) {
                         if (e0) {
                             const u64 v = off + S0;
-                            if (k4.x < K32) red_add(a.key_alloc + k4.x, v);
-                            if (k4.y < K32) red_add(a.key_alloc + k4.y, 0ull - v);
+                            if (k4.x < K32) red_add_u64(a.key_alloc + k4.x, v);
+                            if (k4.y < K32) red_add_u64(a.key_alloc + k4.y, 0ull - v);
                         }
                         if (e1) {
                             const u64 v = off + S1;
-                            if (k4.y < K32) red_add(a.key_alloc + k4.y, v);
-                            if (k4.z < K32) red_add(a.key_alloc + k4.z, 0ull - v);
+                            if (k4.y < K32) red_add_u64(a.key_alloc + k4.y, v);
+                            if (k4.z < K32) red_add_u64(a.key_alloc + k4.z, 0ull - v);
                         }
                         if (e2) {
                             const u64 v = off + S2;
-                            if (k4.z < K32) red_add(a.key_alloc + k4.z, v);
-                            if (k4.w < K32) red_add(a.key_alloc + k4.w, 0ull - v);
+                            if (k4.z < K32) red_add_u64(a.key_alloc + k4.z, v);
+                            if (k4.w < K32) red_add_u64(a.key_alloc + k4.w, 0ull - v);
                         }
                         if (e3) {
                             const u64 v = off + S3;
-                            if (k4.w < K32) red_add(a.key_alloc + k4.w, v);
-                            if (lane != 31 && key_next < K32) red_add(a.key_alloc + key_next, 0ull - v);
+                            if (k4.w < K32) red_add_u64(a.key_alloc + k4.w, v);
+                            if (lane != 31 && key_next < K32) red_add_u64(a.key_alloc + key_next, 0ull - v);
                         }
                     }
                 }
             }
         }
-        if (!fast) tile_alloc = process_tile_fallback(a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+        if (!fast) tile_alloc = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
         if (lane == 31) acc_alloc += tile_alloc;
     }
 
