@@ -59,6 +59,7 @@ _SIGS = [
     ("arena_top_node_host", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP]),
     ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_job_device_noalloc", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_quantity_values", C.c_int, [_VP, _VP, C.c_uint64, _VP]),
     ("arena_kernel_launches", C.c_uint64, []),
     ("arena_profile_begin", C.c_int, [C.c_int]),

@@ -543,6 +543,147 @@ int arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *calls
     return ARENA_OK;
 }
 
+}  // extern "C" (reopened below)
+
+// ---------------------------------------------------------------------------
+// arena_top_job_device_noalloc: `top job` for callers that must not allocate.
+//
+// Some hosts of this library may not call cudaMalloc on the query path: a
+// monitoring agent that polls `top job` on a fixed device-memory budget next to
+// training jobs, a caller whose CUDA context has allocation hooked or forbidden
+// after start-up, a caller in the middle of building a launch sequence where an
+// allocation would synchronise the device.  The regular entry points allocate
+// per-handle work arrays (per-job accumulators, sort buffers, the CTA-partials
+// block) with cudaMalloc; this one keeps the same work arrays in ONE file-scope
+// device array that is part of the loaded module, so nothing is allocated or
+// freed here -- not by us, not by a library on our behalf.
+//
+//   * Size: kNoAllocMaxJobs jobs at most (the array is ~105 KiB and every GPU
+//     that loads the library carries it until the process exits).  More jobs
+//     are refused with ARENA_E_TOO_LARGE; use arena_top_job_device for those.
+//   * The array's name is only a host-side handle for the symbol, not a device
+//     address, so the device address is looked up with cudaGetSymbolAddress
+//     once per device, with that device current.  The FIRST call on a device
+//     performs that look-up: make it before starting any stream capture.
+//   * Every call uses the same array and finds the previous call's contents in
+//     it.  What has to start from a known value (the last-CTA tickets, the
+//     per-job maxima, the sort padding) is re-initialised on the stream by
+//     each call.  Two calls that overlap on the GPU (different streams, or
+//     different host threads) would race on it: serialise them.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr unsigned kNoAllocMaxJobs = 2048;     // == kSortTile: one shared-memory sort tile
+
+struct NoAllocWork {
+    Scratch scratch;                            // CTA partials + tickets
+    i64 maxcreated[kNoAllocMaxJobs];
+    u64 sort_key[kNoAllocMaxJobs];
+    unsigned sort_idx[kNoAllocMaxJobs];
+};
+
+static __device__ __align__(256) unsigned char g_noalloc_work[sizeof(NoAllocWork)];
+
+constexpr int kMaxDevices = 64;
+NoAllocWork *g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_work, per device
+
+// One-time, per device: resolve the symbol to a device address.  Passing
+// g_noalloc_work itself to a kernel from host code would hand it the host
+// shadow of the symbol.
+int noalloc_work(NoAllocWork **out)
+{
+    const int dev = g_ctx.device;
+    if (dev < 0 || dev >= kMaxDevices) return fail(ARENA_E_INVALID, "device ordinal %d not supported by the no-alloc path", dev);
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_work);     // current device == dev (check_ready)
+        if (e != cudaSuccess || !p)
+            return fail(ARENA_E_CUDA, "cudaGetSymbolAddress(g_noalloc_work): %s", cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = static_cast<NoAllocWork *>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return ARENA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_req, int64_t *d_job_alloc,
+                                 uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    rc = check_view(dev, true);
+    if (rc) return rc;
+    const u64 J = dev->n_jobs, P = dev->n_pods;
+    if (J > kNoAllocMaxJobs)
+        return fail(ARENA_E_TOO_LARGE,
+                    "arena_top_job_device_noalloc handles at most %u jobs (got %llu): its work arrays live in a "
+                    "fixed device array; use arena_top_job_device for larger inputs",
+                    kNoAllocMaxJobs, (unsigned long long)J);
+    if (P && !dev->pod_job) return fail(ARENA_E_INVALID, "snapshot view has no job columns");
+    if (!d_totals) return fail(ARENA_E_INVALID, "d_totals is NULL");
+    if (J && (!d_job_req || !d_job_alloc || !d_job_order || !d_job_latest))
+        return fail(ARENA_E_INVALID, "job output buffers are NULL (d_job_latest is required here: it doubles as a work array)");
+    NoAllocWork *w = nullptr;
+    rc = noalloc_work(&w);
+    if (rc) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+
+    // leftovers of an earlier (possibly interrupted) call must not leak into this one
+    CUDA_TRY(cudaMemsetAsync(w->scratch.ticket, 0, sizeof(w->scratch.ticket), st));
+
+    // the per-job accumulators are the caller's output buffers themselves
+    JobInitArgs ia{J, (u64 *)d_job_req, (u64 *)d_job_alloc, w->maxcreated, d_job_latest};
+    job_init_kernel<<<grid_for(J, kThreads * 4, 8), kThreads, 0, st>>>(ia);
+    count_launch();
+
+    PodsArgs pa{};
+    pa.P = P; pa.C = dev->n_containers; pa.K = J;
+    pa.pod_key = dev->pod_job;
+    pa.pod_phase = dev->pod_phase;
+    pa.pod_ctr_begin = dev->pod_ctr_begin;
+    pa.ctr_val = (const i64 *)dev->ctr_val;
+    pa.ctr_scale = (const signed char *)dev->ctr_scale;
+    pa.pod_role = dev->pod_role;
+    pa.pod_created = (const i64 *)dev->pod_created;
+    pa.key_alloc = (u64 *)d_job_alloc;
+    pa.key_req = (u64 *)d_job_req;
+    pa.key_maxcreated = w->maxcreated;
+    pa.total_req = (i64 *)d_totals;
+    pa.total_alloc = (i64 *)d_totals + 1;
+    pa.scratch = &w->scratch;
+    job_pods_kernel<<<grid_for(P, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
+    count_launch();
+
+    if (P) {
+        JobLatestArgs la{P, J, dev->pod_job, dev->pod_role, (const i64 *)dev->pod_created, w->maxcreated, d_job_latest};
+        job_latest_kernel<<<grid_for(P, kThreads * 8, 8), kThreads, 0, st>>>(la);
+        count_launch();
+    }
+
+    JobFinishArgs fa;
+    fa.J = J; fa.Jpad = kNoAllocMaxJobs;
+    fa.job_latest = d_job_latest;
+    fa.pod_phase = dev->pod_phase;
+    fa.pod_ctr_begin = dev->pod_ctr_begin;
+    fa.ctr_val = (const i64 *)dev->ctr_val;
+    fa.ctr_scale = (const signed char *)dev->ctr_scale;
+    fa.job_req = (u64 *)d_job_req; fa.job_alloc = (u64 *)d_job_alloc;
+    fa.sort_key = w->sort_key; fa.sort_idx = w->sort_idx;
+    fa.totals = (i64 *)d_totals;
+    fa.scratch = &w->scratch;
+    job_finish_kernel<<<grid_for(kNoAllocMaxJobs, kThreads, 8), kThreads, 0, st>>>(fa);
+    count_launch();
+
+    bitonic_tile_kernel<<<1, 1024, 0, st>>>(w->sort_key, w->sort_idx, kNoAllocMaxJobs, 0, 1);
+    count_launch();
+    CUDA_TRY(cudaGetLastError());
+    if (J) CUDA_TRY(cudaMemcpyAsync(d_job_order, w->sort_idx, J * 4, cudaMemcpyDeviceToDevice, st));
+    return ARENA_OK;
+}
+
 int arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, int64_t *out)
 {
     int rc = check_ready();

@@ -139,3 +139,28 @@ def format_top_job(host: HostSnapshot, res: TopJobResult, now_unix: int) -> str:
     check(lib().arena_format_top_job(host.handle, _ptr(res.job_req), _ptr(res.job_alloc), _ptr(res.job_order),
                                      _ptr(res.job_latest), now_unix, C.byref(p), C.byref(n)))
     return _take_text(p, n)
+
+
+def top_job_device_noalloc(tensors: dict, n_jobs: int, d_req, d_alloc, d_order, d_latest, d_totals,
+                           stream: Optional[int] = None) -> None:
+    """arena_top_job_device_noalloc: `top job` over CUDA tensors holding the
+    columns, for callers that must not allocate device memory on the query
+    path (the library keeps the work arrays in a fixed device array instead of
+    cudaMalloc'ing them).  At most ARENA_NOALLOC_MAX_JOBS (2048) jobs; calls
+    share that one array, so do not overlap them on the GPU; make the first
+    call on a device before starting any stream capture.  Enqueues only."""
+    from ._lib import SnapshotView
+    from .snapshot import _COLS
+    v = SnapshotView()
+    v.n_pods = tensors["pod_node"].numel()
+    v.n_containers = tensors["ctr_val"].numel()
+    v.n_nodes = tensors["node_cap_val"].numel()
+    v.n_jobs = n_jobs
+    for name, _, _ in _COLS:
+        t = tensors.get(name)
+        setattr(v, name, t.data_ptr() if t is not None and t.numel() else None)
+    v.pod_ctr_begin = tensors["pod_ctr_begin"].data_ptr()
+    check(lib().arena_top_job_device_noalloc(
+        C.byref(v), d_req.data_ptr() if d_req.numel() else None, d_alloc.data_ptr() if d_alloc.numel() else None,
+        d_order.data_ptr() if d_order.numel() else None, d_latest.data_ptr() if d_latest.numel() else None,
+        d_totals.data_ptr(), _stream_arg(stream)))

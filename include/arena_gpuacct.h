@@ -150,6 +150,26 @@ int  arena_top_job_device(const arena_snapshot *s, int64_t *d_job_req, int64_t *
                           uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals,
                           void *stream);
 
+/*
+ * `top job` without any allocation.  (No counterpart in the reference: a Go
+ * program never manages device memory.)  For callers that cannot call
+ * cudaMalloc on the query path -- an agent polling next to training jobs on a
+ * fixed device-memory budget, a host whose CUDA context forbids or hooks
+ * allocation after start-up, a caller for whom an allocation's implicit device
+ * synchronisation is unacceptable.  Same results as arena_top_job_device, but:
+ *   - `dev` holds DEVICE column pointers (no snapshot handle: making one allocates);
+ *   - the work arrays live in a fixed ~105 KiB device array inside the library,
+ *     so at most ARENA_NOALLOC_MAX_JOBS jobs; more -> ARENA_E_TOO_LARGE;
+ *   - d_job_latest is required (it doubles as a work array);
+ *   - the first call on a device resolves the array's device address: make
+ *     that call before beginning any stream capture;
+ *   - all calls share the one array: calls that overlap on the GPU race.
+ */
+#define ARENA_NOALLOC_MAX_JOBS 2048
+int  arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_req, int64_t *d_job_alloc,
+                                  uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals,
+                                  void *stream);
+
 /* Quantity.Value() of n int64Amount pairs on the GPU (parity probe for
  * resource/amount.go:95-101 + math.go:144-203); HOST in, HOST out. */
 int  arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, int64_t *out);
