@@ -68,7 +68,7 @@ _SIGS = [
     ("arena_host_snapshot_free", None, [_VP]),
     ("arena_host_snapshot_view", C.c_int, [_VP, C.POINTER(SnapshotView)]),
     ("arena_load_json", C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
-                                  C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(_VP)]),
+                                  C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_VP)]),
     ("arena_host_pod_order", _VP, [_VP]),
     ("arena_host_job_name", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_host_job_trainer", C.c_char_p, [_VP, C.c_uint32]),
@@ -96,9 +96,7 @@ def lib():
                                  "(there is no CPU fallback)")
         L = C.CDLL(LIB_PATH)
         for name, res, args in _SIGS:
-            fn = getattr(L, name, None)
-            if fn is None:      # TEMPORARY while the loader/printers are being written
-                continue
+            fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
         _lib = L

@@ -1,0 +1,124 @@
+// arena-top: the `top` command surface of the reference CLI
+// (cmd/arena/commands/top.go:17-32, top_node.go:26-55, top_job.go:13-84) over
+// fixture files instead of an API server, computing on the GPU through the C ABI.
+//
+//   arena-top node [-d|--details] --pods PODLIST.json --nodes NODELIST.json
+//   arena-top job  --pods PODLIST.json --nodes NODELIST.json --jobs JOBLIST.json
+//                  [--tfjobs TFJOBLIST.json] --releases HELM_LIST.txt [--now UNIX_SECONDS]
+// Common: [--device N] [--time]
+// Errors are printed to stdout and the exit status is 1, as in the reference
+// (`fmt.Println(err); os.Exit(1)`, top_node.go:34-48).
+#include "../../include/arena_top.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+static const char kTopLong[] =
+    "Display Resource (GPU) usage.\n\nAvailable Commands:\n  node        Display Resource (GPU) usage of nodes\n"
+    "  job         Display Resource (GPU) usage of pods\n    \n\nUsage:\n  arena-top [command]\n";
+
+static bool slurp(const char *path, std::string &out)
+{
+    std::ifstream f(path, std::ios::binary);
+    if (!f) return false;
+    std::ostringstream ss;
+    ss << f.rdbuf();
+    out = ss.str();
+    return true;
+}
+
+static int die(const std::string &msg)
+{
+    printf("%s\n", msg.c_str());
+    return 1;
+}
+
+static int die_arena() { return die(arena_last_error()); }
+
+int main(int argc, char **argv)
+{
+    if (argc < 2 || (strcmp(argv[1], "node") != 0 && strcmp(argv[1], "job") != 0)) {
+        fputs(kTopLong, stdout);
+        return argc < 2 ? 0 : 1;
+    }
+    const bool is_node = strcmp(argv[1], "node") == 0;
+    bool details = false, timing = false;
+    int device = 0;
+    long long now = (long long)time(nullptr);
+    const char *pods_path = nullptr, *nodes_path = nullptr, *jobs_path = nullptr, *tfjobs_path = nullptr,
+               *releases_path = nullptr;
+    for (int i = 2; i < argc; i++) {
+        const std::string a = argv[i];
+        auto need = [&](const char **dst) { if (i + 1 >= argc) return false; *dst = argv[++i]; return true; };
+        const char *tmp = nullptr;
+        if (a == "-d" || a == "--details") details = true;
+        else if (a == "--time") timing = true;
+        else if (a == "--pods") { if (!need(&pods_path)) return die("flag needs an argument: --pods"); }
+        else if (a == "--nodes") { if (!need(&nodes_path)) return die("flag needs an argument: --nodes"); }
+        else if (a == "--jobs") { if (!need(&jobs_path)) return die("flag needs an argument: --jobs"); }
+        else if (a == "--tfjobs") { if (!need(&tfjobs_path)) return die("flag needs an argument: --tfjobs"); }
+        else if (a == "--releases") { if (!need(&releases_path)) return die("flag needs an argument: --releases"); }
+        else if (a == "--device") { if (!need(&tmp)) return die("flag needs an argument: --device"); device = atoi(tmp); }
+        else if (a == "--now") { if (!need(&tmp)) return die("flag needs an argument: --now"); now = atoll(tmp); }
+        else return die("unknown flag: " + a);
+    }
+    if (!pods_path || !nodes_path) return die("--pods and --nodes are required");
+    if (!is_node && !releases_path) return die("top job needs --releases (the output of `helm list`)");
+    std::string pods, nodes, jobs, tfjobs, releases;
+    if (!slurp(pods_path, pods)) return die(std::string("open ") + pods_path + ": no such file or directory");
+    if (!slurp(nodes_path, nodes)) return die(std::string("open ") + nodes_path + ": no such file or directory");
+    if (jobs_path && !slurp(jobs_path, jobs)) return die(std::string("open ") + jobs_path + ": no such file or directory");
+    if (tfjobs_path && !slurp(tfjobs_path, tfjobs)) return die(std::string("open ") + tfjobs_path + ": no such file or directory");
+    if (releases_path && !slurp(releases_path, releases)) return die(std::string("open ") + releases_path + ": no such file or directory");
+
+    auto t0 = std::chrono::steady_clock::now();
+    arena_host_snapshot *host = nullptr;
+    if (arena_load_json(pods.data(), pods.size(), nodes.data(), nodes.size(), jobs_path ? jobs.data() : nullptr, jobs.size(),
+                        tfjobs_path ? tfjobs.data() : nullptr, tfjobs.size(),
+                        (!is_node && releases_path) ? releases.data() : nullptr, releases.size(), is_node ? 0 : 1, &host))
+        return die_arena();
+    auto t1 = std::chrono::steady_clock::now();
+    if (arena_acct_init(device)) return die_arena();
+    arena_snapshot_view view;
+    arena_host_snapshot_view(host, &view);
+    arena_snapshot *dev = nullptr;
+    if (arena_snapshot_upload(&view, &dev)) return die_arena();
+    auto t2 = std::chrono::steady_clock::now();
+
+    char *text = nullptr;
+    size_t len = 0;
+    if (is_node) {
+        std::vector<int64_t> total(view.n_nodes + 1), alloc(view.n_nodes + 1), pod_gpu(details ? view.n_pods + 1 : 1);
+        int64_t cluster[2];
+        if (arena_top_node(dev, total.data(), alloc.data(), cluster, details ? pod_gpu.data() : nullptr)) return die_arena();
+        if (arena_format_top_node(host, total.data(), alloc.data(), details ? pod_gpu.data() : nullptr, details ? 1 : 0, &text, &len))
+            return die_arena();
+    } else {
+        const size_t J = view.n_jobs;
+        std::vector<int64_t> req(J + 1), alloc(J + 1);
+        std::vector<uint32_t> order(J + 1), latest(J + 1);
+        int64_t totals[2];
+        if (arena_top_job(dev, req.data(), alloc.data(), order.data(), latest.data(), totals)) return die_arena();
+        if (arena_format_top_job(host, req.data(), alloc.data(), order.data(), latest.data(), now, &text, &len)) return die_arena();
+    }
+    auto t3 = std::chrono::steady_clock::now();
+    fwrite(text, 1, len, stdout);
+    arena_free_text(text);
+    if (timing) {
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[arena-top] pods=%llu nodes=%llu jobs=%llu  load %.2f ms, init+upload %.2f ms, query+format %.2f ms\n",
+                (unsigned long long)view.n_pods, (unsigned long long)view.n_nodes, (unsigned long long)view.n_jobs,
+                ms(t0, t1), ms(t1, t2), ms(t2, t3));
+    }
+    arena_snapshot_free(dev);
+    arena_host_snapshot_free(host);
+    arena_acct_shutdown();
+    return 0;
+}

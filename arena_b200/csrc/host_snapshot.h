@@ -28,10 +28,14 @@ struct JobMeta {
     std::string name;          // helm release name
     std::string ns;            // namespace from `helm list`
     std::string trainer;       // "mpijob" | "standalonejob" | "tfjob"
-    std::string status;        // GetStatus() of the reference, from the job object
-    std::string chief_host_ip; // status.hostIP of the chief / job pod
-    bool has_start = false;
-    int64_t start_unix = 0;    // job.status.startTime
+    // batch/v1 Job (mpijob, standalonejob): status.active / succeeded / failed
+    int64_t active = 0, succeeded = 0, failed = 0;
+    // TFJob: GetStatus() resolved from status.conditions at load time
+    bool tf_found = false;
+    std::string tf_status;     // "SUCCEEDED" | "FAILED" | "PENDING" | "RUNNING"
+    uint32_t tf_chief_row = 0xFFFFFFFFu;   // row of the chief pod (worker index 0), or none
+    bool has_start = false;    // status.startTime present and not the zero time
+    int64_t start_unix = 0;
 };
 
 }  // namespace arena_host
@@ -44,7 +48,7 @@ struct arena_host_snapshot {
     // names for the printers; empty for synthetic snapshots ("node-%07u")
     std::vector<std::string> node_names, node_internal_ip, node_first_addr;
     std::vector<uint8_t> node_has_addr, node_is_master;
-    std::vector<std::string> pod_names, pod_namespaces;   // in ROW order
+    std::vector<std::string> pod_names, pod_namespaces, pod_host_ip;   // in ROW order
     std::vector<uint32_t> pod_order;                      // row -> PodList index
     std::vector<arena_host::JobMeta> jobs;
 };

@@ -42,8 +42,11 @@ __device__ __constant__ i64 kPow10[19] = {
 //   s < 0: divide by 10^-s, rounding AWAY from zero (negativeScaleInt64: the
 //          digit-by-digit loop is equivalent to one truncating division plus a
 //          +-1 when any remainder was dropped, including the early exit at 0).
-//   s > 0: multiply by 10^s; if the exact product does not fit int64 the
-//          reference returns (0,false) and the caller drops `ok` => 0.
+//   s > 0: multiply by 10^s.  The caller drops `ok` and keeps the value, and the
+//          value on overflow depends on the scale (math.go:144-168): scales
+//          1, 2, 3, 6, 9 are ONE checked multiply that returns the WRAPPED
+//          product (math.go:118-140); every other scale is a loop of x10 steps
+//          that returns 0 once a step overflows.  INT64_MIN gives 0 for any s >= 1.
 __device__ __noinline__ i64 quantity_value_slow(i64 v, int s)
 {
     if (s < 0) {
@@ -64,8 +67,10 @@ __device__ __noinline__ i64 quantity_value_slow(i64 v, int s)
         return q;
     }
     if (s > 18) return 0;
+    if (v == (i64)0x8000000000000000ull) return 0;
     i64 m = kPow10[s];
     i64 lo = (i64)((u64)v * (u64)m);
+    if (s == 1 || s == 2 || s == 3 || s == 6 || s == 9) return lo;
     i64 hi = __mul64hi(v, m);
     return hi == (lo >> 63) ? lo : 0;
 }

@@ -1,0 +1,535 @@
+// JSON fixtures -> columnar snapshot.  Replaces, for fixture-driven runs, the
+// List calls and the client-side decoding the reference does before its
+// accounting (paths relative to /root/reference):
+//   pods / nodes     cmd/arena/commands/pod_helper.go:15-43, top_node.go:71
+//   jobs / tfjobs    pod_helper.go:45-55, trainer_tensorflow.go:176-208
+//   helm releases    util/helm/helm.go:164-195
+//   job membership   trainer_mpi.go:91-119, 222-332; trainer_standalone.go:71-99,
+//                    182-273; trainer_tensorflow.go:215-245, 315-418; trainer.go:10-23
+//   key selection    gpu.go:18-37, 61-79 (presence decides, not positivity)
+//   schema           vendor/k8s.io/api/core/v1/types.go (field names only)
+#include "host_snapshot.h"
+#include "json.h"
+#include "quantity.h"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <numeric>
+#include <unordered_map>
+
+using arena_json::Value;
+using namespace arena_host;
+
+namespace {
+
+const char kPrimary[] = "nvidia.com/gpu";                        // const.go:7
+const char kDeprecated[] = "alpha.kubernetes.io/nvidia-gpu";     // const.go:9
+const char kMasterLabel[] = "node-role.kubernetes.io/master";    // const.go:11
+
+struct LoadError {
+    std::string msg;
+};
+
+[[noreturn]] void bad(const std::string &m) { throw LoadError{m}; }
+
+const Value *child(const Value *v, const char *key)
+{
+    if (!v || v->is_null()) return nullptr;
+    if (!v->is_object()) bad(std::string("expected an object around \"") + key + "\"");
+    const Value *c = v->get(key);
+    if (c && c->is_null()) return nullptr;
+    return c;
+}
+
+std::string str_field(const Value *v, const char *key)
+{
+    const Value *c = child(v, key);
+    if (!c) return std::string();
+    if (!c->is_string()) bad(std::string("field \"") + key + "\" is not a string");
+    return c->str();
+}
+
+int64_t int_field(const Value *v, const char *key)
+{
+    const Value *c = child(v, key);
+    if (!c) return 0;
+    if (c->type != arena_json::Type::Number) bad(std::string("field \"") + key + "\" is not a number");
+    int64_t x = 0;
+    bool neg = false;
+    for (char ch : c->raw) {
+        if (ch == '-') { neg = true; continue; }
+        if (ch < '0' || ch > '9') bad(std::string("field \"") + key + "\" is not an integer");
+        x = x * 10 + (ch - '0');
+    }
+    return neg ? -x : x;
+}
+
+// map[string]string lookup: (found, value)
+bool label(const Value *labels, const char *key, std::string &out)
+{
+    if (!labels) return false;
+    if (!labels->is_object()) bad("labels is not an object");
+    const Value *c = labels->get(key);
+    if (!c) return false;
+    if (c->is_null()) { out.clear(); return true; }       // null decodes to "" with the key present
+    if (!c->is_string()) bad("label value is not a string");
+    out = c->str();
+    return true;
+}
+
+bool label_is(const Value *labels, const char *key, const char *want)
+{
+    std::string v;
+    return label(labels, key, v) && v == want;
+}
+
+// Decode every entry of a ResourceList (a bad quantity anywhere fails the List
+// decode in the reference) and return the selected GPU quantity.
+void resource_list(const Value *rl, const char *what, bool select, int64_t &val, int8_t &scale)
+{
+    val = 0;
+    scale = 0;
+    if (!rl) return;
+    if (!rl->is_object()) bad(std::string(what) + " is not an object");
+    const Value *primary = nullptr, *deprecated = nullptr;
+    for (const auto &m : rl->members) {
+        ParsedQuantity q;
+        if (!unmarshal_quantity_json(m.second.raw, q))
+            bad(std::string("invalid quantity ") + std::string(m.second.raw) + " for \"" + m.first + "\" in " + what);
+        if (m.first == kPrimary) primary = &m.second;           // duplicates: last wins
+        else if (m.first == kDeprecated) deprecated = &m.second;
+    }
+    if (!select) return;
+    const Value *pick = primary ? primary : deprecated;          // gpu.go:61-79: key PRESENCE
+    if (!pick) return;
+    ParsedQuantity q;
+    unmarshal_quantity_json(pick->raw, q);
+    column_encoding(q, val, scale);
+}
+
+int64_t days_from_civil(int64_t y, unsigned m, unsigned d)
+{
+    y -= m <= 2;
+    const int64_t era = (y >= 0 ? y : y - 399) / 400;
+    const unsigned yoe = (unsigned)(y - era * 400);
+    const unsigned doy = (153 * (m + (m > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+    const unsigned doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+    return era * 146097 + (int64_t)doe - 719468;
+}
+
+const int64_t kZeroTimeUnix = -62135596800ll;      // Go's time.Time{} (0001-01-01T00:00:00Z)
+
+// metav1.Time.UnmarshalJSON: null -> zero time, else time.Parse(RFC3339)
+// (vendor/k8s.io/apimachinery/pkg/apis/meta/v1/time.go:105-121).  Sub-second
+// digits are accepted and dropped (the API server writes whole seconds).
+int64_t parse_time(const Value *v, const char *what)
+{
+    if (!v) return kZeroTimeUnix;
+    if (!v->is_string()) bad(std::string(what) + " is not a string");
+    const std::string s = v->str();
+    auto num = [&](size_t at, size_t n) -> int {
+        if (at + n > s.size()) bad(std::string("bad RFC3339 time \"") + s + "\"");
+        int x = 0;
+        for (size_t i = at; i < at + n; i++) {
+            if (s[i] < '0' || s[i] > '9') bad(std::string("bad RFC3339 time \"") + s + "\"");
+            x = x * 10 + (s[i] - '0');
+        }
+        return x;
+    };
+    if (s.size() < 20 || s[4] != '-' || s[7] != '-' || (s[10] != 'T' && s[10] != 't') || s[13] != ':' || s[16] != ':')
+        bad(std::string("bad RFC3339 time \"") + s + "\"");
+    const int Y = num(0, 4), M = num(5, 2), D = num(8, 2), h = num(11, 2), mi = num(14, 2), sec = num(17, 2);
+    if (M < 1 || M > 12 || D < 1 || D > 31 || h > 23 || mi > 59 || sec > 59) bad(std::string("bad RFC3339 time \"") + s + "\"");
+    size_t i = 19;
+    if (i < s.size() && s[i] == '.') {
+        i++;
+        size_t st = i;
+        while (i < s.size() && s[i] >= '0' && s[i] <= '9') i++;
+        if (i == st) bad(std::string("bad RFC3339 time \"") + s + "\"");
+    }
+    int64_t off = 0;
+    if (i < s.size() && (s[i] == 'Z' || s[i] == 'z')) i++;
+    else if (i < s.size() && (s[i] == '+' || s[i] == '-')) {
+        const int sign = s[i] == '-' ? -1 : 1;
+        if (i + 6 > s.size() || s[i + 3] != ':') bad(std::string("bad RFC3339 time \"") + s + "\"");
+        off = sign * (num(i + 1, 2) * 3600 + num(i + 4, 2) * 60);
+        i += 6;
+    } else bad(std::string("bad RFC3339 time \"") + s + "\"");
+    if (i != s.size()) bad(std::string("bad RFC3339 time \"") + s + "\"");
+    return days_from_civil(Y, (unsigned)M, (unsigned)D) * 86400 + h * 3600 + mi * 60 + sec - off;
+}
+
+uint8_t phase_code(const std::string &p)
+{
+    if (p.empty()) return ARENA_PHASE_EMPTY;
+    if (p == "Pending") return ARENA_PHASE_PENDING;
+    if (p == "Running") return ARENA_PHASE_RUNNING;
+    if (p == "Succeeded") return ARENA_PHASE_SUCCEEDED;
+    if (p == "Failed") return ARENA_PHASE_FAILED;
+    if (p == "Unknown") return ARENA_PHASE_UNKNOWN;
+    return ARENA_PHASE_OTHER;
+}
+
+struct PodRec {
+    std::string name, ns, node_name, host_ip;
+    uint8_t phase = 0;
+    std::vector<int64_t> ctr_val;
+    std::vector<int8_t> ctr_scale;
+    int64_t created = kZeroTimeUnix;
+    bool owner_is_job = false;
+    const Value *labels = nullptr;
+    uint32_t node = ARENA_NONE, job = ARENA_NONE;
+    uint8_t role = ARENA_ROLE_COUNTS;
+};
+
+struct ObjRec {                 // batch/v1 Job or TFJob: what membership and the printer need
+    std::string ns;
+    const Value *labels = nullptr;
+    const Value *status = nullptr;
+};
+
+const Value *items_of(const Value &doc, const char *what)
+{
+    if (!doc.is_object()) bad(std::string(what) + " is not a JSON object");
+    const Value *items = doc.get("items");
+    if (!items || items->is_null()) return nullptr;
+    if (!items->is_array()) bad(std::string(what) + ".items is not an array");
+    return items;
+}
+
+void parse_doc(const char *text, size_t len, const char *what, Value &doc)
+{
+    arena_json::ParseError e;
+    if (!arena_json::parse(std::string_view(text, len), doc, e))
+        bad(std::string(what) + ": JSON syntax error at byte " + std::to_string(e.offset) + ": " + e.message);
+}
+
+// hasCondition / isSucceeded / isFailed / isPending: trainer_tensorflow.go:420-439
+bool tf_condition(const Value *status, const char *type)
+{
+    const Value *conds = child(status, "conditions");
+    if (!conds) return false;
+    if (!conds->is_array()) bad("tfjob status.conditions is not an array");
+    for (const Value &c : conds->items)
+        if (str_field(&c, "type") == type && str_field(&c, "status") == "True") return true;
+    return false;
+}
+
+int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodelen, const char *joblist, size_t joblen,
+         const char *tfjoblist, size_t tflen, const char *helm, size_t helmlen, bool group_by_job,
+         arena_host_snapshot *h)
+{
+    Value pod_doc, node_doc, job_doc, tf_doc;
+    parse_doc(nodelist, nodelen, "NodeList", node_doc);
+    parse_doc(podlist, podlen, "PodList", pod_doc);
+
+    // ---- nodes -------------------------------------------------------------------
+    const Value *nitems = items_of(node_doc, "NodeList");
+    const size_t N = nitems ? nitems->items.size() : 0;
+    std::vector<int64_t> cap_val(N);
+    std::vector<int8_t> cap_scale(N);
+    std::unordered_map<std::string, uint32_t> node_id;
+    h->node_names.resize(N); h->node_internal_ip.resize(N); h->node_first_addr.resize(N);
+    h->node_has_addr.assign(N, 0); h->node_is_master.assign(N, 0);
+    for (size_t n = 0; n < N; n++) {
+        const Value &node = nitems->items[n];
+        if (!node.is_object()) bad("NodeList item is not an object");
+        const Value *meta = child(&node, "metadata");
+        const Value *status = child(&node, "status");
+        h->node_names[n] = str_field(meta, "name");
+        if (!node_id.emplace(h->node_names[n], (uint32_t)n).second)
+            bad("duplicate node name \"" + h->node_names[n] + "\" (the API server guarantees unique node names)");
+        const Value *labels = child(meta, "labels");
+        std::string tmp;
+        h->node_is_master[n] = label(labels, kMasterLabel, tmp) ? 1 : 0;       // top_node.go:244-250: key presence
+        int64_t v; int8_t s;
+        resource_list(child(status, "allocatable"), "node status.allocatable", false, v, s);
+        resource_list(child(status, "capacity"), "node status.capacity", true, cap_val[n], cap_scale[n]);
+        const Value *addrs = child(status, "addresses");
+        if (addrs) {
+            if (!addrs->is_array()) bad("node status.addresses is not an array");
+            bool have_internal = false;
+            for (size_t i = 0; i < addrs->items.size(); i++) {
+                const Value &a = addrs->items[i];
+                const std::string type = str_field(&a, "type"), addr = str_field(&a, "address");
+                if (i == 0) { h->node_first_addr[n] = addr; h->node_has_addr[n] = 1; }     // top_node.go:173-175
+                if (!have_internal && type == "InternalIP") { h->node_internal_ip[n] = addr; have_internal = true; }
+            }
+            if (!have_internal) h->node_internal_ip[n] = "unknown";                     // top_node.go:120-129
+        } else {
+            h->node_internal_ip[n] = "unknown";
+        }
+    }
+
+    // ---- pods --------------------------------------------------------------------
+    const Value *pitems = items_of(pod_doc, "PodList");
+    const size_t P = pitems ? pitems->items.size() : 0;
+    std::vector<PodRec> pods(P);
+    for (size_t p = 0; p < P; p++) {
+        const Value &pod = pitems->items[p];
+        if (!pod.is_object()) bad("PodList item is not an object");
+        PodRec &r = pods[p];
+        const Value *meta = child(&pod, "metadata");
+        const Value *spec = child(&pod, "spec");
+        const Value *status = child(&pod, "status");
+        r.name = str_field(meta, "name");
+        r.ns = str_field(meta, "namespace");
+        r.labels = child(meta, "labels");
+        r.created = parse_time(child(meta, "creationTimestamp"), "metadata.creationTimestamp");
+        if (const Value *owners = child(meta, "ownerReferences")) {
+            if (!owners->is_array()) bad("metadata.ownerReferences is not an array");
+            for (const Value &o : owners->items)
+                if (str_field(&o, "kind") == "Job") { r.owner_is_job = true; break; }
+        }
+        r.node_name = str_field(spec, "nodeName");
+        r.phase = phase_code(str_field(status, "phase"));
+        r.host_ip = str_field(status, "hostIP");
+        for (const char *list : {"initContainers", "containers"}) {
+            const Value *cs = child(spec, list);
+            if (!cs) continue;
+            if (!cs->is_array()) bad(std::string("spec.") + list + " is not an array");
+            const bool counted = std::strcmp(list, "containers") == 0;         // gpu.go:40: spec.containers only
+            for (const Value &c : cs->items) {
+                if (!c.is_object()) bad("container is not an object");
+                const Value *res = child(&c, "resources");
+                int64_t v; int8_t s;
+                resource_list(child(res, "requests"), "resources.requests", false, v, s);
+                resource_list(child(res, "limits"), "resources.limits", counted, v, s);   // gpu.go:61-69: LIMITS
+                if (counted) { r.ctr_val.push_back(v); r.ctr_scale.push_back(s); }
+            }
+        }
+        if (!r.node_name.empty()) {
+            auto it = node_id.find(r.node_name);
+            if (it != node_id.end()) r.node = it->second;
+        }
+    }
+
+    // ---- jobs (only when a `helm list` text is given) -------------------------------
+    if (helm) {
+        // util/helm/helm.go:180-192: name = first field, namespace = last field,
+        // lines containing "NAME" are skipped, later lines overwrite earlier ones.
+        std::map<std::string, std::string> releases;                  // sorted by name => job ids
+        std::string_view text(helm, helmlen);
+        size_t pos = 0;
+        while (pos <= text.size()) {
+            size_t nl = text.find('\n', pos);
+            std::string_view line = text.substr(pos, nl == std::string_view::npos ? std::string_view::npos : nl - pos);
+            pos = nl == std::string_view::npos ? text.size() + 1 : nl + 1;
+            if (line.find("NAME") != std::string_view::npos) continue;
+            std::vector<std::string_view> cols;
+            size_t i = 0;
+            auto is_sp = [](char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; };
+            while (i < line.size()) {
+                while (i < line.size() && is_sp(line[i])) i++;
+                size_t st = i;
+                while (i < line.size() && !is_sp(line[i])) i++;
+                if (i > st) cols.push_back(line.substr(st, i - st));
+            }
+            if (cols.size() > 1) releases[std::string(cols.front())] = std::string(cols.back());
+        }
+
+        std::vector<ObjRec> jobs, tfjobs;
+        if (joblist) {
+            parse_doc(joblist, joblen, "JobList", job_doc);
+            if (const Value *it = items_of(job_doc, "JobList"))
+                for (const Value &j : it->items) {
+                    const Value *meta = child(&j, "metadata");
+                    jobs.push_back({str_field(meta, "namespace"), child(meta, "labels"), child(&j, "status")});
+                }
+        }
+        // NewTensorFlowJobTrainer lists TFJobs only when allPods is non-empty
+        // (trainer_tensorflow.go:188-202); without a TFJobList the trainer is disabled.
+        const bool tf_enabled = tfjoblist != nullptr;
+        if (tfjoblist && P > 0) {
+            parse_doc(tfjoblist, tflen, "TFJobList", tf_doc);
+            if (const Value *it = items_of(tf_doc, "TFJobList"))
+                for (const Value &j : it->items) {
+                    const Value *meta = child(&j, "metadata");
+                    tfjobs.push_back({str_field(meta, "namespace"), child(meta, "labels"), child(&j, "status")});
+                }
+        }
+        auto find_obj = [&](const std::vector<ObjRec> &objs, const std::string &name, const std::string &ns,
+                            const char *app) -> const ObjRec * {
+            for (const ObjRec &o : objs)                                 // first match in list order
+                if (label_is(o.labels, "release", name.c_str()) && label_is(o.labels, "app", app) && o.ns == ns) return &o;
+            return nullptr;
+        };
+        std::unordered_map<std::string, uint32_t> job_of_release;
+        for (const auto &rel : releases) {
+            const std::string &name = rel.first, &ns = rel.second;
+            JobMeta jm;
+            jm.name = name;
+            jm.ns = ns;
+            const ObjRec *obj = nullptr;
+            // trainer precedence: MPI, Standalone, TensorFlow (trainer.go:10-23); with an
+            // empty Job list the reference would fall back to API calls: not supported here.
+            if ((obj = find_obj(jobs, name, ns, "tf-horovod"))) jm.trainer = "mpijob";
+            else if ((obj = find_obj(jobs, name, ns, "training"))) jm.trainer = "standalonejob";
+            else if (tf_enabled && (obj = find_obj(tfjobs, name, ns, "tfjob"))) jm.trainer = "tfjob";
+            else continue;                                               // "Unkown chart": no row
+            const Value *st = obj->status;
+            if (jm.trainer == "tfjob") {
+                jm.tf_found = true;
+                if (tf_condition(st, "Succeeded")) jm.tf_status = "SUCCEEDED";
+                else if (tf_condition(st, "Failed")) jm.tf_status = "FAILED";
+                else if (tf_condition(st, "Created") || tf_condition(st, "Restarting")) jm.tf_status = "PENDING";
+                else jm.tf_status = "RUNNING";
+            } else {
+                jm.active = int_field(st, "active");
+                jm.succeeded = int_field(st, "succeeded");
+                jm.failed = int_field(st, "failed");
+            }
+            if (const Value *t = child(st, "startTime")) {
+                jm.start_unix = parse_time(t, "status.startTime");
+                jm.has_start = jm.start_unix != kZeroTimeUnix;
+            }
+            job_of_release.emplace(name, (uint32_t)h->jobs.size());
+            h->jobs.push_back(std::move(jm));
+        }
+        // pod -> job: the release label names the job, the trainer's own predicate decides
+        for (PodRec &r : pods) {
+            std::string rel;
+            if (!label(r.labels, "release", rel)) continue;
+            auto it = job_of_release.find(rel);
+            if (it == job_of_release.end()) continue;
+            const JobMeta &jm = h->jobs[it->second];
+            if (r.ns != jm.ns) continue;
+            if (jm.trainer == "mpijob") {                                // trainer_mpi.go:315-332, 247-279
+                if (!label_is(r.labels, "app", "tf-horovod")) continue;
+                r.role = r.owner_is_job ? ARENA_ROLE_LATEST : ARENA_ROLE_COUNTS;
+            } else if (jm.trainer == "standalonejob") {                  // trainer_standalone.go:198-221, 257-273
+                if (!label_is(r.labels, "app", "training")) continue;
+                r.role = ARENA_ROLE_LATEST;
+            } else {                                                     // trainer_tensorflow.go:394-418
+                if (!label_is(r.labels, "app", "tfjob") || !label_is(r.labels, "group_name", "kubeflow.org")) continue;
+                r.role = ARENA_ROLE_COUNTS;
+            }
+            r.job = it->second;
+        }
+    }
+    const size_t J = h->jobs.size();
+
+    // ---- row order: stable grouping by node (or by job) --------------------------------
+    std::vector<uint32_t> order(P);
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+        return group_by_job ? pods[a].job < pods[b].job : pods[a].node < pods[b].node;     // ARENA_NONE sorts last
+    });
+    h->pod_order = order;
+
+    size_t C = 0;
+    for (const PodRec &r : pods) C += r.ctr_val.size();
+    if (C > 0xFFFFFFFFull || P >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
+    int rc;
+    if ((rc = h->c_pod_node.alloc(P * 4, false))) return rc;
+    if ((rc = h->c_pod_phase.alloc(P, false))) return rc;
+    if ((rc = h->c_pod_ctr_begin.alloc((P + 1) * 4, false))) return rc;
+    if ((rc = h->c_ctr_val.alloc(C * 8, false))) return rc;
+    if ((rc = h->c_ctr_scale.alloc(C, false))) return rc;
+    if ((rc = h->c_node_cap_val.alloc(N * 8, false))) return rc;
+    if ((rc = h->c_node_cap_scale.alloc(N, false))) return rc;
+    if ((rc = h->c_pod_job.alloc(P * 4, false))) return rc;
+    if ((rc = h->c_pod_role.alloc(P, false))) return rc;
+    if ((rc = h->c_pod_created.alloc(P * 8, false))) return rc;
+    uint32_t *pod_node = h->c_pod_node.as<uint32_t>();
+    uint8_t *pod_phase = h->c_pod_phase.as<uint8_t>();
+    uint32_t *cb = h->c_pod_ctr_begin.as<uint32_t>();
+    int64_t *ctr_val = h->c_ctr_val.as<int64_t>();
+    int8_t *ctr_scale = h->c_ctr_scale.as<int8_t>();
+    uint32_t *pod_job = h->c_pod_job.as<uint32_t>();
+    uint8_t *pod_role = h->c_pod_role.as<uint8_t>();
+    int64_t *pod_created = h->c_pod_created.as<int64_t>();
+    std::memcpy(h->c_node_cap_val.ptr, cap_val.data(), N * 8);
+    std::memcpy(h->c_node_cap_scale.ptr, cap_scale.data(), N);
+    h->pod_names.resize(P); h->pod_namespaces.resize(P); h->pod_host_ip.resize(P);
+    std::vector<uint32_t> row_of(P);
+    size_t c = 0;
+    for (size_t row = 0; row < P; row++) {
+        PodRec &r = pods[order[row]];
+        row_of[order[row]] = (uint32_t)row;
+        pod_node[row] = r.node;
+        pod_phase[row] = r.phase;
+        cb[row] = (uint32_t)c;
+        for (size_t k = 0; k < r.ctr_val.size(); k++, c++) { ctr_val[c] = r.ctr_val[k]; ctr_scale[c] = r.ctr_scale[k]; }
+        pod_job[row] = r.job;
+        pod_role[row] = r.role;
+        pod_created[row] = r.created;
+        h->pod_names[row] = std::move(r.name);
+        h->pod_namespaces[row] = std::move(r.ns);
+        h->pod_host_ip[row] = std::move(r.host_ip);
+    }
+    cb[P] = (uint32_t)c;
+
+    // chief pod of a tfjob: worker index 0; the LAST match in list order is kept
+    // (trainer_tensorflow.go:336-338, 357-372)
+    for (size_t p = 0; p < P; p++) {
+        const PodRec &r = pods[p];
+        if (r.job == ARENA_NONE || h->jobs[r.job].trainer != "tfjob") continue;
+        if (label_is(r.labels, "tf-replica-type", "worker") && label_is(r.labels, "tf-replica-index", "0"))
+            h->jobs[r.job].tf_chief_row = row_of[p];
+    }
+
+    arena_snapshot_view &v = h->v;
+    v.n_pods = P; v.n_containers = C; v.n_nodes = N; v.n_jobs = J;
+    v.pod_node = pod_node; v.pod_phase = pod_phase; v.pod_ctr_begin = cb;
+    v.ctr_val = ctr_val; v.ctr_scale = ctr_scale;
+    v.node_cap_val = h->c_node_cap_val.as<int64_t>(); v.node_cap_scale = h->c_node_cap_scale.as<int8_t>();
+    v.pod_job = pod_job; v.pod_role = pod_role; v.pod_created = pod_created;
+    return ARENA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int arena_load_json(const char *podlist_json, size_t podlist_len, const char *nodelist_json, size_t nodelist_len,
+                    const char *joblist_json, size_t joblist_len, const char *tfjoblist_json, size_t tfjoblist_len,
+                    const char *helm_list_text, size_t helm_len, int group_by_job, arena_host_snapshot **out)
+{
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    if (!podlist_json || !nodelist_json) return fail(ARENA_E_INVALID, "PodList and NodeList are required");
+    arena_host_snapshot *h = new arena_host_snapshot();
+    int rc;
+    try {
+        rc = load(podlist_json, podlist_len, nodelist_json, nodelist_len, joblist_json, joblist_len, tfjoblist_json,
+                  tfjoblist_len, helm_list_text, helm_len, group_by_job != 0, h);
+    } catch (const LoadError &e) {
+        rc = fail(ARENA_E_PARSE, "%s", e.msg.c_str());
+    } catch (const std::bad_alloc &) {
+        rc = fail(ARENA_E_NOMEM, "out of host memory while loading");
+    }
+    if (rc) { delete h; return rc; }
+    *out = h;
+    return ARENA_OK;
+}
+
+const char *arena_host_job_name(const arena_host_snapshot *h, uint32_t job)
+{
+    return (h && job < h->jobs.size()) ? h->jobs[job].name.c_str() : "";
+}
+const char *arena_host_job_trainer(const arena_host_snapshot *h, uint32_t job)
+{
+    return (h && job < h->jobs.size()) ? h->jobs[job].trainer.c_str() : "";
+}
+const char *arena_host_node_name(const arena_host_snapshot *h, uint32_t node)
+{
+    return (h && node < h->node_names.size()) ? h->node_names[node].c_str() : "";
+}
+
+int arena_quantity_parse(const char *raw, size_t len, int64_t *value_out, int64_t *amount_val_out,
+                         int32_t *amount_scale_out, int *slow_path_out)
+{
+    if (!raw) return fail(ARENA_E_INVALID, "raw is NULL");
+    ParsedQuantity q;
+    if (!unmarshal_quantity_json(std::string_view(raw, len), q))
+        return fail(ARENA_E_PARSE, "invalid quantity: %.*s", (int)(len > 200 ? 200 : len), raw);
+    if (value_out) *value_out = q.value;
+    if (amount_val_out) *amount_val_out = q.amount;
+    if (amount_scale_out) *amount_scale_out = q.scale;
+    if (slow_path_out) *slow_path_out = q.slow ? 1 : 0;
+    return ARENA_OK;
+}
+
+}  // extern "C"

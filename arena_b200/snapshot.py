@@ -93,13 +93,15 @@ class HostSnapshot:
         return cls.from_handle(h.value)
 
     @classmethod
-    def from_json(cls, podlist: bytes, nodelist: bytes, joblist: bytes = b"", tfjoblist: bytes = b"",
-                  helm_list: bytes = b"") -> "HostSnapshot":
+    def from_json(cls, podlist: bytes, nodelist: bytes, joblist: Optional[bytes] = None,
+                  tfjoblist: Optional[bytes] = None, helm_list: Optional[bytes] = None,
+                  group_by_job: bool = False) -> "HostSnapshot":
         """arena_load_json: PodList/NodeList(/JobList/TFJobList/`helm list`) -> columns."""
         h = C.c_void_p()
-        check(lib().arena_load_json(podlist, len(podlist), nodelist, len(nodelist),
-                                    joblist or None, len(joblist), tfjoblist or None, len(tfjoblist),
-                                    helm_list or None, len(helm_list), C.byref(h)))
+        n = lambda b: len(b) if b is not None else 0
+        check(lib().arena_load_json(podlist, len(podlist), nodelist, len(nodelist), joblist, n(joblist),
+                                    tfjoblist, n(tfjoblist), helm_list, n(helm_list), int(group_by_job),
+                                    C.byref(h)))
         return cls.from_handle(h.value)
 
     # -- properties -----------------------------------------------------------

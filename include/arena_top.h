@@ -45,7 +45,10 @@ int  arena_host_snapshot_view(const arena_host_snapshot *h, arena_snapshot_view 
  * Pods are re-ordered so that pods of one node are adjacent (stable: list
  * order is kept inside a node; pods that match no node go last), which is the
  * grouping the kernels are fastest on; arena_host_pod_order() gives the
- * original list index of each row.  A malformed quantity fails the whole load
+ * original list index of each row.  With group_by_job != 0 (use it for `top
+ * job`) the rows are grouped by job instead, again stably, so that "first pod
+ * in list order wins a timestamp tie" (trainer_mpi.go:263-278) is "lowest row
+ * wins" inside every job.  A malformed quantity fails the whole load
  * with ARENA_E_PARSE, as a failed List decode does in the reference
  * (top_node.go:39-42).
  */
@@ -54,7 +57,7 @@ int  arena_load_json(const char *podlist_json, size_t podlist_len,
                      const char *joblist_json, size_t joblist_len,
                      const char *tfjoblist_json, size_t tfjoblist_len,
                      const char *helm_list_text, size_t helm_len,
-                     arena_host_snapshot **out);
+                     int group_by_job, arena_host_snapshot **out);
 
 /* Row -> original PodList index ([P]); job id -> name / trainer type. */
 const uint32_t *arena_host_pod_order(const arena_host_snapshot *h);

@@ -100,7 +100,10 @@ int64_t oracle_quantity_value(int64_t value, int32_t scale)
 {
     if (scale < 0) return negative_scale_int64(value, -scale);
     int64_t r;
-    if (!positive_scale_int64(value, scale, &r)) return 0;   /* (0,false): ok dropped */
+    /* `i, _ := q.i.AsScaledInt64(scale)`: the result is used whatever `ok` says.
+     * The looped scales return (0,false) on overflow, but the single-multiply
+     * scales 1,2,3,6,9 return the WRAPPED product with ok=false (math.go:118-140). */
+    (void)positive_scale_int64(value, scale, &r);
     return r;
 }
 

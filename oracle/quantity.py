@@ -290,7 +290,7 @@ def _dec_set_string(value: str) -> Tuple[int, int]:
     one '.', as produced by parse_quantity_string."""
     body = value
     neg = False
-    if body[:1] in "+-":
+    if body[:1] in ("+", "-"):
         neg = body[0] == "-"
         body = body[1:]
     if body.count(".") > 1:

@@ -1,0 +1,56 @@
+"""The C ABI: the library loads and exports every symbol the two headers
+declare (no compute calls: no GPU needed), and fails loudly without CUDA."""
+
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_functions(path):
+    text = open(path).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return set(re.findall(r"\b(arena_[a-z0-9_]+)\s*\(", text))
+
+
+def test_every_declared_symbol_is_exported(built):
+    from arena_b200 import _lib
+    declared = header_functions(os.path.join(ROOT, "include", "arena_gpuacct.h")) | \
+        header_functions(os.path.join(ROOT, "include", "arena_top.h"))
+    assert len(declared) >= 30
+    L = C.CDLL(_lib.LIB_PATH)
+    missing = [s for s in sorted(declared) if not hasattr(L, s)]
+    assert not missing, f"not exported: {missing}"
+    # and the Python binding table covers the headers exactly
+    assert set(_lib.DECLARED_SYMBOLS) == declared
+
+
+def test_no_torch_types_and_no_oracle_in_the_product():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "arena_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src, f"{f} mentions the oracle: the product must not route through it"
+    for h in ("arena_gpuacct.h", "arena_top.h"):
+        src = open(os.path.join(ROOT, "include", h)).read()
+        assert "torch" not in src.replace("torchrun", "").replace("torch tensors", "")
+
+
+def test_calls_fail_loudly_without_init_or_gpu(built):
+    """No CPU fallback: without arena_acct_init (or without a GPU) compute entry
+    points return an error instead of computing on the host."""
+    import torch
+    from arena_b200 import _lib
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the -m gpu tests")
+    L = _lib.lib()
+    rc = L.arena_acct_init(0)
+    assert rc != 0
+    assert L.arena_last_error()
+    cluster = (C.c_int64 * 2)()
+    assert L.arena_top_node(None, None, None, cluster, None) == -3      # ARENA_E_NOT_INIT
+    v = _lib.SnapshotView()
+    assert L.arena_top_node_host(C.byref(v), None, None, cluster, None) == -3

@@ -1,0 +1,95 @@
+"""GPU: the JSON fixtures end to end through the C ABI and through the
+arena-top CLI, against the expected texts the oracle produced."""
+
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import top_ref
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+D = os.path.join(HERE, "golden", "config1")
+CLI = os.path.join(ROOT, "arena_b200", "arena-top")
+sys.path.insert(0, os.path.join(HERE, "golden"))
+import make_fixtures as MF  # noqa: E402
+
+
+def rd(name, mode="rb"):
+    with open(os.path.join(D, name), mode) as f:
+        return f.read()
+
+
+def test_config1_top_node_text(gpu):
+    h = gpu.HostSnapshot.from_json(rd("pods.json"), rd("nodes.json"))
+    dev = gpu.DeviceSnapshot.upload(h)
+    res = gpu.top_node(dev, details=True)
+    assert gpu.format_top_node(h, res) == rd("expected_top_node.txt", "r")
+    assert gpu.format_top_node(h, res, details=True) == rd("expected_top_node_details.txt", "r")
+    table = [[h.node_name(n), int(res.node_total[n]), int(res.node_alloc[n])] for n in range(h.n_nodes)]
+    assert table == json.loads(rd("expected_node_table.json"))
+    got = {r[0]: (r[1], r[2]) for r in table}
+    for name, want in MF.HAND_NODE_TABLE_EDGE.items():
+        assert got[name] == want
+
+
+def test_config1_top_job_text(gpu):
+    h = gpu.HostSnapshot.from_json(rd("pods.json"), rd("nodes.json"), rd("jobs.json"), rd("tfjobs.json"),
+                                   rd("helm_list.txt"), group_by_job=True)
+    res = gpu.top_job(gpu.DeviceSnapshot.upload(h))
+    assert gpu.format_top_job(h, res, MF.NOW) == rd("expected_top_job.txt", "r")
+    got = {h.job_name(j): (h.job_trainer(j), int(res.job_req[j]), int(res.job_alloc[j])) for j in range(h.n_jobs)}
+    assert got == MF.HAND_JOB_TABLE
+
+
+def test_config2_top_job_full_size(gpu):
+    """BASELINE configs[1]: top job over 1e4 TFJob/Horovod pods on 1000 nodes."""
+    podlist, nodelist, joblist, tfjoblist, helm = MF.config2()
+    P, N, Jl, T = (json.dumps(x).encode() for x in (podlist, nodelist, joblist, tfjoblist))
+    assert len(podlist["items"]) >= 10_000 and len(nodelist["items"]) == 1000
+    text, rows = top_ref.top_job(P, Jl, T, helm, MF.NOW)
+    h = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=True)
+    res = gpu.top_job(gpu.DeviceSnapshot.upload(h))
+    assert gpu.format_top_job(h, res, MF.NOW) == text
+    # node-grouped rows give the same job table (the kernels do not need grouping)
+    h2 = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=False)
+    res2 = gpu.top_job(gpu.DeviceSnapshot.upload(h2))
+    assert np.array_equal(res2.job_req, res.job_req) and np.array_equal(res2.job_alloc, res.job_alloc)
+    ntext, _ = top_ref.top_node(P, N)
+    r = gpu.top_node(gpu.DeviceSnapshot.upload(h2))
+    assert gpu.format_top_node(h2, r) == ntext
+
+
+def run_cli(*args):
+    p = subprocess.run([CLI, *args], capture_output=True, text=True, timeout=120)
+    return p.returncode, p.stdout, p.stderr
+
+
+def test_cli_matches_expected_output(gpu):
+    pods, nodes = os.path.join(D, "pods.json"), os.path.join(D, "nodes.json")
+    rc, out, _ = run_cli("node", "--pods", pods, "--nodes", nodes)
+    assert rc == 0 and out == rd("expected_top_node.txt", "r")
+    rc, out, _ = run_cli("node", "-d", "--pods", pods, "--nodes", nodes)
+    assert rc == 0 and out == rd("expected_top_node_details.txt", "r")
+    rc, out, err = run_cli("job", "--pods", pods, "--nodes", nodes, "--jobs", os.path.join(D, "jobs.json"), "--tfjobs",
+                           os.path.join(D, "tfjobs.json"), "--releases", os.path.join(D, "helm_list.txt"), "--now",
+                           str(MF.NOW), "--time")
+    assert rc == 0 and out == rd("expected_top_job.txt", "r") and "[arena-top]" in err
+
+
+def test_cli_error_behaviour(gpu, tmp_path):
+    """Errors go to stdout and the exit status is 1 (top_node.go:34-48)."""
+    bad = tmp_path / "pods.json"
+    bad.write_text('{"items":[{"spec":{"containers":[{"resources":{"limits":{"nvidia.com/gpu":"1x"}}}]}}]}')
+    rc, out, _ = run_cli("node", "--pods", str(bad), "--nodes", os.path.join(D, "nodes.json"))
+    assert rc == 1 and "invalid quantity" in out
+    rc, out, _ = run_cli("node", "--pods", "/nonexistent.json", "--nodes", os.path.join(D, "nodes.json"))
+    assert rc == 1 and "no such file" in out
+    rc, out, _ = run_cli()
+    assert rc == 0 and "Display Resource (GPU) usage." in out

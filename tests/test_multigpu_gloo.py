@@ -1,0 +1,87 @@
+"""The N > 1 path on CPU: world_size-2 `gloo` processes run the sharding plan,
+the totals all-reduce and the table gather of arena_b200.multigpu.  There is no
+GPU here, so each rank's per-shard table comes from the C oracle -- the test is
+about the plumbing: disjoint node ranges, no pod crossing ranks, one int64[2]
+exchange, identical bits at any rank count."""
+
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, P, N, seed, skewed, out_dir):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    from arena_b200 import HostSnapshot, multigpu
+    from oracle import cref
+    r, w, _ = multigpu.init_process_group("gloo")
+    assert (r, w) == (rank, world)
+    host = HostSnapshot.synth(P, N, seed=seed, skewed=skewed)        # every rank sees the same snapshot
+    shard = host.shard(rank, world)
+    tot, alloc, cl, _ = cref.top_node_columnar(shard.cols)
+    g = multigpu.all_reduce_totals(torch.from_numpy(cl.copy()))
+    full_total, full_alloc = multigpu.gather_tables(tot, alloc, dst=0)
+    if rank == 0:
+        np.savez(os.path.join(out_dir, "r0.npz"), cluster=g.numpy(), total=full_total, alloc=full_alloc,
+                 pods=np.array([shard.n_pods]), nodes=np.array([shard.n_nodes]))
+    else:
+        assert full_total is None and full_alloc is None
+        np.savez(os.path.join(out_dir, f"r{rank}.npz"), cluster=g.numpy(), pods=np.array([shard.n_pods]),
+                 nodes=np.array([shard.n_nodes]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("P,N,seed,skewed", [(200_000, 2_000, 1, False), (300_000, 500, 5, True)])
+def test_two_rank_sharded_top_node(built, tmp_path, P, N, seed, skewed):
+    from arena_b200 import HostSnapshot
+    from oracle import cref
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), P, N, seed, skewed, str(tmp_path)), nprocs=world, join=True)
+    host = HostSnapshot.synth(P, N, seed=seed, skewed=skewed)
+    tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+    r0 = np.load(tmp_path / "r0.npz")
+    r1 = np.load(tmp_path / "r1.npz")
+    assert np.array_equal(r0["cluster"], cl) and np.array_equal(r1["cluster"], cl)     # every rank has the totals
+    assert np.array_equal(r0["total"], tot) and np.array_equal(r0["alloc"], alloc)     # gathered table == unsharded
+    assert int(r0["pods"][0] + r1["pods"][0]) == P and int(r0["nodes"][0] + r1["nodes"][0]) == N
+
+
+def test_shard_plan_properties(built):
+    from arena_b200 import HostSnapshot
+    host = HostSnapshot.synth(500_000, 3_000, seed=9, skewed=True)
+    pn = host.cols["pod_node"]
+    for G in (1, 2, 3, 4, 8):
+        key_cut, pod_cut = host.shard_plan(G)
+        assert key_cut[0] == 0 and key_cut[-1] == host.n_nodes and pod_cut[0] == 0 and pod_cut[-1] == host.n_pods
+        assert np.all(np.diff(key_cut.astype(np.int64)) >= 0) and np.all(np.diff(pod_cut.astype(np.int64)) >= 0)
+        for i in range(G):
+            lo, hi = int(pod_cut[i]), int(pod_cut[i + 1])
+            seg = pn[lo:hi]
+            real = seg[seg != 0xFFFFFFFF]
+            if len(real):                                  # no pod crosses a shard boundary
+                assert real.min() >= key_cut[i] and real.max() < key_cut[i + 1]
+            if i < G - 1:
+                assert not np.any(seg == 0xFFFFFFFF)       # unmatched pods ride with the last shard
+        # balance: no shard exceeds the ideal share by more than the largest node
+        counts = np.bincount(pn[pn != 0xFFFFFFFF], minlength=host.n_nodes)
+        sizes = np.diff(pod_cut.astype(np.int64))
+        assert sizes[:-1].max(initial=0) <= host.n_pods / G + counts.max()
+
+
+def test_shard_plan_rejects_ungrouped_input(built):
+    from arena_b200 import ArenaError, HostSnapshot
+    host = HostSnapshot.synth(100_000, 100, seed=3, grouped=False)
+    with pytest.raises(ArenaError):
+        host.shard_plan(2)
