@@ -37,7 +37,7 @@ struct Context {
 };
 
 Context g_ctx;
-std::mutex g_mu;
+std::mutex g_mu, g_host_mu;
 std::atomic<uint64_t> g_launches{0};
 
 inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
@@ -61,6 +61,7 @@ struct arena_snapshot {
     arena_snapshot_view v{};     // device pointers
     bool owns = false;
     void *block = nullptr;       // single allocation holding all owned columns
+    size_t block_bytes = 0;
     Scratch *scratch = nullptr;  // per-handle: distinct handles may run concurrently
     // top job work arrays (allocated on first use)
     u64 *job_req = nullptr, *job_alloc = nullptr;
@@ -73,6 +74,8 @@ struct arena_snapshot {
     i64 *d_out = nullptr;
     size_t d_out_bytes = 0;
 };
+
+static arena_snapshot *g_host_snap = nullptr;    // staging snapshot of arena_top_node_host
 
 extern "C" {
 
@@ -111,6 +114,7 @@ void arena_acct_shutdown(void)
     if (!g_ctx.ready) return;
     cudaSetDevice(g_ctx.device);
     cudaStreamSynchronize(g_ctx.stream);
+    if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
     cudaStreamDestroy(g_ctx.stream);
     g_ctx = Context{};
 }
@@ -314,47 +318,41 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
 
 extern "C" {
 
-int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
+// Copy host columns into s->block (grown when too small; one allocation, every
+// column padded to 16 bytes plus a spare vector so aligned 128-bit reads stay
+// inside it) and point s->v at the device copies.  Asynchronous on the
+// library stream.
+static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool jobs)
 {
-    int rc = check_ready();
-    if (rc) return rc;
-    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
-    *out = nullptr;
-    rc = check_view(h, false);
-    if (rc) return rc;
     const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
-    const bool jobs = h->n_jobs > 0 && h->pod_job;
-    arena_snapshot *s = new (std::nothrow) arena_snapshot();
-    if (!s) return fail(ARENA_E_NOMEM, "out of host memory");
-    s->owns = true;
-    s->v = *h;
-    // one allocation, every column padded to 16 bytes (plus one spare vector so
-    // that aligned 128-bit reads never leave the allocation)
     size_t sizes[10] = {P * 4, P, (P + 1) * 4, C * 8, C, N * 8, N, jobs ? P * 4 : 0, jobs ? P : 0, jobs ? P * 8 : 0};
     const void *src[10] = {h->pod_node, h->pod_phase, h->pod_ctr_begin, h->ctr_val, h->ctr_scale,
                            h->node_cap_val, h->node_cap_scale, h->pod_job, h->pod_role, h->pod_created};
     size_t total = 0;
     for (size_t z : sizes) total += pad16(z) + 16;
-    cudaError_t e = cudaMalloc(&s->block, total ? total : 16);
-    if (e != cudaSuccess) {
-        delete s;
-        return fail(e == cudaErrorMemoryAllocation ? ARENA_E_NOMEM : ARENA_E_CUDA, "cudaMalloc(%zu): %s", total,
-                    cudaGetErrorString(e));
+    if (total < 16) total = 16;
+    if (s->block_bytes < total) {
+        if (s->block) cudaFree(s->block);
+        s->block = nullptr;
+        s->block_bytes = 0;
+        cudaError_t e = cudaMalloc(&s->block, total);
+        if (e != cudaSuccess)
+            return fail(e == cudaErrorMemoryAllocation ? ARENA_E_NOMEM : ARENA_E_CUDA, "cudaMalloc(%zu): %s", total,
+                        cudaGetErrorString(e));
+        s->block_bytes = total;
     }
+    s->owns = true;
     char *p = (char *)s->block;
     const void *dst[10];
     for (int i = 0; i < 10; i++) {
         dst[i] = p;
         if (sizes[i]) {
-            e = cudaMemcpyAsync(p, src[i], sizes[i], cudaMemcpyHostToDevice, g_ctx.stream);
-            if (e != cudaSuccess) {
-                cudaFree(s->block);
-                delete s;
-                return fail(ARENA_E_CUDA, "H2D copy of column %d: %s", i, cudaGetErrorString(e));
-            }
+            cudaError_t e = cudaMemcpyAsync(p, src[i], sizes[i], cudaMemcpyHostToDevice, g_ctx.stream);
+            if (e != cudaSuccess) return fail(ARENA_E_CUDA, "H2D copy of column %d: %s", i, cudaGetErrorString(e));
         }
         p += pad16(sizes[i]) + 16;
     }
+    s->v = *h;
     s->v.pod_node = (const uint32_t *)dst[0];
     s->v.pod_phase = (const uint8_t *)dst[1];
     s->v.pod_ctr_begin = (const uint32_t *)dst[2];
@@ -366,9 +364,23 @@ int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
     s->v.pod_role = jobs ? (const uint8_t *)dst[8] : nullptr;
     s->v.pod_created = jobs ? (const int64_t *)dst[9] : nullptr;
     if (!jobs) s->v.n_jobs = 0;
-    rc = alloc_common(s);
+    return ARENA_OK;
+}
+
+int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    rc = check_view(h, false);
+    if (rc) return rc;
+    arena_snapshot *s = new (std::nothrow) arena_snapshot();
+    if (!s) return fail(ARENA_E_NOMEM, "out of host memory");
+    rc = fill_snapshot(s, h, h->n_jobs > 0 && h->pod_job);
+    if (!rc) rc = alloc_common(s);
     if (rc) { arena_snapshot_free(s); return rc; }
-    e = cudaStreamSynchronize(g_ctx.stream);     // host buffers may be reused on return
+    cudaError_t e = cudaStreamSynchronize(g_ctx.stream);     // host buffers may be reused on return
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "upload: %s", cudaGetErrorString(e)); }
     *out = s;
     return ARENA_OK;
@@ -450,14 +462,22 @@ int arena_top_node(const arena_snapshot *cs, int64_t *node_total, int64_t *node_
 int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, int64_t *node_alloc,
                         int64_t cluster[2], int64_t *pod_gpu)
 {
-    arena_snapshot *s = nullptr;
-    arena_snapshot_view v = *host;
-    v.n_jobs = 0; v.pod_job = nullptr; v.pod_role = nullptr; v.pod_created = nullptr;
-    int rc = arena_snapshot_upload(&v, &s);
+    int rc = check_ready();
     if (rc) return rc;
-    rc = arena_top_node(s, node_total, node_alloc, cluster, pod_gpu);
-    arena_snapshot_free(s);
-    return rc;
+    rc = check_view(host, false);
+    if (rc) return rc;
+    // One staging snapshot per process, kept between calls: a polling caller
+    // pays for cudaMalloc only when its snapshot grows.  Calls are serialised.
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    if (!g_host_snap) {
+        g_host_snap = new (std::nothrow) arena_snapshot();
+        if (!g_host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
+        rc = alloc_common(g_host_snap);
+        if (rc) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; return rc; }
+    }
+    rc = fill_snapshot(g_host_snap, host, false);            // async H2D on the library stream ...
+    if (rc) return rc;
+    return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
 }
 
 int arena_top_job_device(const arena_snapshot *cs, int64_t *d_job_req, int64_t *d_job_alloc,

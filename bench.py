@@ -339,7 +339,7 @@ def main():
     step_bytes = host.algorithmic_bytes_top_node()
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None, "kernel": "arena::pods_kernel<false>", "kernel_ms": pods_ms_avg,
+        "traffic": None, "kernel": "arena::top_node_pods_kernel", "kernel_ms": pods_ms_avg,
         "algorithmic_bytes": pods_bytes, "peak_source": peak_src,
         "nodes_kernel_ms": nodes_ms.value / max(1, calls.value),
         "step_algorithmic_bytes": step_bytes,
