@@ -321,7 +321,9 @@ int arena_shard_plan(const arena_snapshot_view *v, int n_shards, int by_job, uin
     uint64_t Pk = std::lower_bound(key, key + P, (uint32_t)std::min<uint64_t>(K, 0xFFFFFFFFull)) - key;
     key_cut[0] = 0; pod_cut[0] = 0;
     for (int s = 1; s < n_shards; s++) {
-        uint64_t target = Pk * (uint64_t)s / (uint64_t)n_shards;
+        // equal shares of ALL pods: the unmatched ones sit at the end, so they
+        // count towards the last shard's share
+        uint64_t target = P * (uint64_t)s / (uint64_t)n_shards;
         uint64_t k;
         if (target >= Pk) k = K;
         else {
