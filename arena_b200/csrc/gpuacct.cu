@@ -526,6 +526,37 @@ int arena_top_job(const arena_snapshot *cs, int64_t *job_req, int64_t *job_alloc
     return ARENA_OK;
 }
 
+int arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!s || iters < 1 || !gbs_out) return fail(ARENA_E_INVALID, "bad argument");
+    const arena_snapshot_view &v = s->v;
+    StreamReadArgs a;
+    const void *cols[5] = {v.pod_ctr_begin, v.pod_node, v.pod_phase, v.ctr_val, v.ctr_scale};
+    const u64 bytes[5] = {v.n_pods * 4, v.n_pods * 4, v.n_pods, v.n_containers * 8, v.n_containers};
+    u64 total = 0;
+    for (int i = 0; i < 5; i++) { a.col[i] = (const uint4 *)cols[i]; a.n16[i] = bytes[i] / 16; total += a.n16[i] * 16; }
+    a.sink = (u64 *)s->scratch;
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    const int grid = g_ctx.sm_count * 8;
+    cudaStream_t st = g_ctx.stream;
+    stream_read_kernel<<<grid, kThreads, 0, st>>>(a);           // warm-up
+    CUDA_TRY(cudaEventRecord(e0, st));
+    for (int i = 0; i < iters; i++) { stream_read_kernel<<<grid, kThreads, 0, st>>>(a); count_launch(); }
+    CUDA_TRY(cudaEventRecord(e1, st));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *gbs_out = (double)total * iters / (ms / 1e3) / 1e9;
+    if (ms_out) *ms_out = ms / iters;
+    return ARENA_OK;
+}
+
 int arena_profile_begin(int max_calls)
 {
     int rc = check_ready();

@@ -920,6 +920,33 @@ __global__ void bitonic_global_kernel(u64 *key, unsigned *idx, u64 n, u64 k, u64
     }
 }
 
+// Calibration: how fast can this GPU merely READ the columns the pods kernel
+// reads (no arithmetic to speak of)?  One 128-bit load per lane, grid-stride,
+// over the five columns back to back.  bench.py reports it beside the roofline.
+struct StreamReadArgs {
+    const uint4 *col[5];
+    u64 n16[5];               // 16-byte vectors per column
+    u64 *sink;
+};
+__global__ void __launch_bounds__(kThreads) stream_read_kernel(StreamReadArgs a)
+{
+    u64 acc = 0;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+#pragma unroll 1
+    for (int c = 0; c < 5; c++) {
+        const uint4 *p = a.col[c];
+        const u64 n = a.n16[c];
+        u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < n; i += 4 * stride) {          // 4 loads in flight per thread
+            const uint4 v0 = ldg_stream(p + i), v1 = ldg_stream(p + i + stride), v2 = ldg_stream(p + i + 2 * stride),
+                        v3 = ldg_stream(p + i + 3 * stride);
+            acc += v0.x ^ v0.w ^ v1.y ^ v1.z ^ v2.x ^ v2.w ^ v3.y ^ v3.z;
+        }
+        for (; i < n; i += stride) { const uint4 v = ldg_stream(p + i); acc += v.x ^ v.w; }
+    }
+    if (acc == 0x9E3779B97F4A7C15ull) *a.sink = acc;            // never true in practice; defeats dead-code removal
+}
+
 // Quantity.Value() probe.
 __global__ void quantity_values_kernel(const i64 *val, const signed char *scale, u64 n, i64 *out)
 {

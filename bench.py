@@ -346,6 +346,11 @@ def main():
         "step_gbs": step_bytes / (ms_per_step / 1e3) / 1e9 * (1 if world == 1 else 1),
         "frac_of_nominal_8000": achieved / 8000.0,
     }
+    # calibration: the same five columns read with plain coalesced loads, no arithmetic
+    cal_gbs, cal_ms = C_.c_double(), C_.c_double()
+    ab._lib.check(ab.lib().arena_calibrate_stream_read(dev.handle, 20, C_.byref(cal_gbs), C_.byref(cal_ms)))
+    roofline["read_only_stream_gbs"] = cal_gbs.value
+    roofline["frac_of_read_only_stream"] = achieved / cal_gbs.value
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:

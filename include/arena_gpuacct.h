@@ -183,6 +183,12 @@ int  arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, 
 int  arena_profile_begin(int max_calls);
 int  arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *calls);
 
+/* Calibration (no counterpart in the reference): read the five columns the
+ * pods kernel reads with plain coalesced 128-bit loads and no arithmetic,
+ * `iters` times; *gbs_out = bytes read / time.  The ceiling a read-only
+ * streaming kernel reaches on this GPU, reported next to the roofline. */
+int  arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out);
+
 /* Number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim). */
 uint64_t arena_kernel_launches(void);

@@ -4,5 +4,5 @@ cd /root/repo
 while [ $# -gt 1 ]; do
   name=$1; flags=$2; shift 2
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC $flags -Xptxas -v -c arena_b200/csrc/gpuacct.cu -o /tmp/gpuacct_$name.o 2>&1 | grep -A2 "top_node_pods" | grep -E "Used" | sed "s/^/$name: /"
-  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/lib_$name.so /tmp/gpuacct_$name.o arena_b200/_obj/errors.o arena_b200/_obj/synth.o -lcudart
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/lib_$name.so /tmp/gpuacct_$name.o $(ls arena_b200/_obj/*.o | grep -v gpuacct.o) -lcudart
 done
