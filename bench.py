@@ -110,7 +110,7 @@ class ClockSampler:
 # --------------------------------------------------------------------------
 # CPU legs (the ONLY place bench.py touches oracle/): bounded samples.
 # --------------------------------------------------------------------------
-def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int):
+def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int, min_seconds: float = 0.0):
     """The reference's CPU algorithm (C restatement, oracle/acct_ref.c) on a
     bounded sample of the workload: array-of-structs pods with string node
     names and keyed limits, string-hash join, all host threads."""
@@ -123,8 +123,11 @@ def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int):
     for _ in range(warmup):
         aos.run(False, threads)
     t0 = time.perf_counter()
-    for _ in range(steps):
+    done = 0
+    while done < steps or (time.perf_counter() - t0) < min_seconds:
         total, alloc, cluster = aos.run(False, threads)
+        done += 1
+    steps = done
     dt = time.perf_counter() - t0
     # single-thread columnar pass (B3) and faithful nested loop (B1) for context
     t1 = time.perf_counter()
@@ -138,7 +141,8 @@ def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int):
     a2.close()
     aos.close()
     return {
-        "value": host.n_pods * steps / dt, "ms_per_step": dt / steps * 1e3, "sample_pods": host.n_pods,
+        "value": host.n_pods * steps / dt, "ms_per_step": dt / steps * 1e3, "sample_pods": host.n_pods, "passes": steps,
+        "seconds": dt,
         "sample_nodes": sample_nodes, "b3_columnar_1thread": b3, "b1_nested_loop_1thread": b1,
         "b1_sample": "20000 pods x 200 nodes",
     }
@@ -155,7 +159,8 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": workload_config(args.gpus, args.scaling),
+        "config": dict(workload_config(args.gpus, args.scaling), pods_per_gpu=PODS_FULL, nodes_per_gpu=NODES_FULL,
+                       total_pods=PODS_FULL * (args.gpus if args.scaling == "weak" else 1)),
         "cpu_baseline": {
             "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"each step = first {r['sample_pods']} pods / {r['sample_nodes']} nodes of the workload's "
@@ -377,11 +382,12 @@ def main():
     if not args.no_cpu and world == 1:
         threads = os.cpu_count() or 1
         log("[rank 0] cpu_baseline leg (bounded sample)...")
-        r = cpu_reference_run(steps=5, warmup=1, sample_pods=10_000_000, threads=threads)
+        r = cpu_reference_run(steps=5, warmup=1, sample_pods=10_000_000, threads=threads, min_seconds=10.0)
         line["cpu_baseline"] = {
             "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"5 passes over the first {r['sample_pods']} pods / {r['sample_nodes']} nodes of the generator "
-                      "(seed 1), array-of-structs + string-hash join, all host threads (C restatement of the Go path)",
+            "sample": f"{r['passes']} passes ({r['seconds']:.1f} s) over the first {r['sample_pods']} pods / "
+                      f"{r['sample_nodes']} nodes of the generator (seed 1), array-of-structs + string-hash join, all "
+                      "host threads (C restatement of the Go path; the Go reference cannot be built here)",
             "columnar_single_pass_1thread": r["b3_columnar_1thread"],
             "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
             "faithful_nested_loop_sample": r["b1_sample"],
