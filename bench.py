@@ -153,8 +153,7 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     threads = os.cpu_count() or 1
-    sample = 10_000_000
-    r = cpu_reference_run(args.steps, max(1, min(args.warmup, 2)), sample, threads)
+    r = cpu_reference_run(args.steps, max(1, min(args.warmup, 2)), args.sample_pods, threads)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
@@ -201,6 +200,7 @@ def main():
     ap.add_argument("--nodes", type=int, default=NODES_FULL)
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3                         # timing rule: W >= 3
@@ -215,6 +215,11 @@ def main():
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"),
                os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
+
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's
+    # version banner) are sent to stderr for the duration of the run
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
 
     import numpy as np
     import torch
@@ -382,7 +387,7 @@ def main():
     if not args.no_cpu and world == 1:
         threads = os.cpu_count() or 1
         log("[rank 0] cpu_baseline leg (bounded sample)...")
-        r = cpu_reference_run(steps=5, warmup=1, sample_pods=10_000_000, threads=threads, min_seconds=10.0)
+        r = cpu_reference_run(steps=5, warmup=1, sample_pods=args.sample_pods, threads=threads, min_seconds=10.0)
         line["cpu_baseline"] = {
             "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"{r['passes']} passes ({r['seconds']:.1f} s) over the first {r['sample_pods']} pods / "
@@ -392,7 +397,8 @@ def main():
             "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
             "faithful_nested_loop_sample": r["b1_sample"],
         }
-    print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
