@@ -691,6 +691,10 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                 }
                 // ---- eligibility: small non-negative values, scales in [-9, 0] ----
                 bool bad = ((vA0.x | vA0.y | vB0.x | vB0.y | vA1.x | vA1.y | vB1.x | vB1.y) >> kSmallBits) != 0ull;
+                // offsets must be non-decreasing through the tile (lane chains to lane via cb4), which
+                // keeps every shared-memory index below inside [0, span]: a corrupt CSR column is
+                // summed by the generic path, whose lookups are range-checked, instead of faulting
+                bad |= (c4.x > c4.y) | (c4.y > c4.z) | (c4.z > c4.w) | (c4.w > cb4);
                 fast = !__any_sync(FULL, bad);
                 if (fast) {
                     unsigned total = fast_row((unsigned)vA0.x, (unsigned)vA0.y, (unsigned)vB0.x, (unsigned)vB0.y, s0,

@@ -165,3 +165,25 @@ def test_quantity_values_kernel(gpu):
     got = gpu.quantity_values(val, scale)
     want = np.array([cref.quantity_value(int(v), int(s)) for v, s in zip(val, scale)], np.int64)
     assert np.array_equal(got, want)
+
+
+def test_corrupt_csr_offsets_do_not_fault(gpu):
+    """Garbage in pod_ctr_begin (non-monotonic offsets) must not crash the process:
+    the fast path hands such tiles to the range-checked generic path.  The sums are
+    then meaningless; only memory safety and a clean return are checked."""
+    rng = np.random.default_rng(12)
+    host = gpu.HostSnapshot.synth(50_000, 500, seed=12)
+    cols = {k: v.copy() for k, v in host.cols.items() if v.size}
+    cb = cols["pod_ctr_begin"]
+    idx = rng.integers(1, len(cb) - 1, 2_000)
+    cb[idx] = rng.integers(0, cb[-1] + 1, len(idx)).astype(np.uint32)      # keep them inside [0, C]
+    bad = gpu.HostSnapshot.from_arrays({k: v for k, v in cols.items() if not k.startswith("pod_job")
+                                        and k not in ("pod_role", "pod_created")})
+    dev = gpu.DeviceSnapshot.upload(bad)
+    res = gpu.top_node(dev, details=True)
+    assert res.node_alloc.shape == (500,)
+    # the library is still healthy afterwards
+    good = gpu.DeviceSnapshot.upload(host)
+    r2 = gpu.top_node(good)
+    tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+    assert np.array_equal(r2.node_alloc, alloc)
