@@ -85,3 +85,32 @@ def test_shard_plan_rejects_ungrouped_input(built):
     host = HostSnapshot.synth(100_000, 100, seed=3, grouped=False)
     with pytest.raises(ArenaError):
         host.shard_plan(2)
+
+
+def test_job_range_shards_reproduce_top_job(built):
+    """`top job` shards by job-id range (jobs span nodes): per-shard sums concatenate to the
+    unsharded table and the totals add up."""
+    from arena_b200 import HostSnapshot
+    from oracle import cref
+    J = 400
+    host = HostSnapshot.synth(120_000, 800, seed=4, n_jobs=J)
+    # group rows by job (stable) so that job ranges are contiguous pod ranges
+    order = np.argsort(host.cols["pod_job"], kind="stable")
+    cb = host.cols["pod_ctr_begin"]
+    lens = (cb[1:] - cb[:-1])[order]
+    new_cb = np.zeros(len(order) + 1, np.uint32)
+    new_cb[1:] = np.cumsum(lens)
+    idx = np.concatenate([np.arange(cb[p], cb[p + 1]) for p in order]) if len(order) else np.zeros(0, np.int64)
+    cols = {k: host.cols[k][order] for k in ("pod_node", "pod_phase", "pod_job", "pod_role", "pod_created")}
+    cols.update(pod_ctr_begin=new_cb, ctr_val=host.cols["ctr_val"][idx], ctr_scale=host.cols["ctr_scale"][idx],
+                node_cap_val=host.cols["node_cap_val"], node_cap_scale=host.cols["node_cap_scale"])
+    grouped = HostSnapshot.from_arrays(cols, n_jobs=J)
+    req, alloc, latest, totals = cref.top_job_columnar(grouped.cols, J)
+    parts = []
+    for i in range(3):
+        sh = grouped.shard(i, 3, by_job=True)
+        r, a, l, t = cref.top_job_columnar(sh.cols, sh.n_jobs)
+        parts.append((r, a, t))
+    assert np.array_equal(np.concatenate([p[0] for p in parts]), req)
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), alloc)
+    assert (sum(int(p[2][0]) for p in parts), sum(int(p[2][1]) for p in parts)) == (int(totals[0]), int(totals[1]))
