@@ -557,6 +557,37 @@ int arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_
     return ARENA_OK;
 }
 
+int arena_calibrate_stream_pattern(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!s || iters < 1 || !gbs_out) return fail(ARENA_E_INVALID, "bad argument");
+    const arena_snapshot_view &v = s->v;
+    PodsArgs pa{};
+    pa.P = v.n_pods; pa.C = v.n_containers; pa.K = v.n_nodes;
+    pa.pod_key = v.pod_node; pa.pod_phase = v.pod_phase; pa.pod_ctr_begin = v.pod_ctr_begin;
+    pa.ctr_val = (const i64 *)v.ctr_val; pa.ctr_scale = (const signed char *)v.ctr_scale;
+    const u64 n_full = v.n_pods / kWarpPods;
+    const double total = (double)n_full * (kWarpPods * 9.0 + kChunkCtrs * 9.0);     // bytes requested per pass
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    const int grid = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
+    cudaStream_t st = g_ctx.stream;
+    stream_pattern_kernel<<<grid, kThreads, 0, st>>>(pa, (u64 *)s->scratch);
+    CUDA_TRY(cudaEventRecord(e0, st));
+    for (int i = 0; i < iters; i++) { stream_pattern_kernel<<<grid, kThreads, 0, st>>>(pa, (u64 *)s->scratch); count_launch(); }
+    CUDA_TRY(cudaEventRecord(e1, st));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *gbs_out = total * iters / (ms / 1e3) / 1e9;
+    if (ms_out) *ms_out = ms / iters;
+    return ARENA_OK;
+}
+
 int arena_profile_begin(int max_calls)
 {
     int rc = check_ready();

@@ -361,6 +361,9 @@ def main():
     ab._lib.check(ab.lib().arena_calibrate_stream_read(dev.handle, 20, C_.byref(cal_gbs), C_.byref(cal_ms)))
     roofline["read_only_stream_gbs"] = cal_gbs.value
     roofline["frac_of_read_only_stream"] = achieved / cal_gbs.value
+    pat_gbs, pat_ms = C_.c_double(), C_.c_double()
+    ab._lib.check(ab.lib().arena_calibrate_stream_pattern(dev.handle, 20, C_.byref(pat_gbs), C_.byref(pat_ms)))
+    roofline["tile_pattern_only_ms"] = pat_ms.value       # same access pattern, no arithmetic, no dependent loads
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:

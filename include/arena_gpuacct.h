@@ -188,6 +188,10 @@ int  arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *call
  * `iters` times; *gbs_out = bytes read / time.  The ceiling a read-only
  * streaming kernel reaches on this GPU, reported next to the roofline. */
 int  arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out);
+/* Same, but with the pods kernel's access pattern (five columns at once, per
+ * 128-pod tile, grid-stride) and no dependent loads: what that pattern can
+ * reach before any arithmetic.  *gbs_out counts the bytes requested. */
+int  arena_calibrate_stream_pattern(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out);
 
 /* Number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim). */

@@ -55,3 +55,5 @@ print(f"P={P} pods_kernel {pods_ms*1e3:.1f} us  {byts/pods_ms/1e6:.0f} GB/s  fra
 g, m = C.c_double(), C.c_double()
 ab._lib.check(ab.lib().arena_calibrate_stream_read(dev.handle, 20, C.byref(g), C.byref(m)))
 print(f"stream-read calibration: {m.value*1e3:.1f} us  {g.value:.0f} GB/s  frac_of_6538.9={g.value/6538.9:.3f}", flush=True)
+ab._lib.check(ab.lib().arena_calibrate_stream_pattern(dev.handle, 20, C.byref(g), C.byref(m)))
+print(f"tile-pattern calibration: {m.value*1e3:.1f} us  {g.value:.0f} GB/s requested", flush=True)
