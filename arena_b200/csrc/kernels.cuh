@@ -578,37 +578,47 @@ __device__ __constant__ CeilDiv10 kCeilDiv10[10] = {
     {2305843010u, 61u, 999999999u, 0u},
 };
 
+// {m, 10^k - 1} of kCeilDiv10, padded to 16 entries so that any nibble is a
+// valid index (entries 0 and 10..15 are never used for valid scales).
+__device__ __constant__ uint2 kCeilDiv10Packed[16] = {
+    {0u, 0u}, {3435973837u, 9u}, {2748779070u, 99u}, {2199023256u, 999u}, {3518437209u, 9999u},
+    {2814749768u, 99999u}, {2251799814u, 999999u}, {3602879702u, 9999999u}, {2882303762u, 99999999u},
+    {2305843010u, 999999999u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};
+
 __device__ __forceinline__ void red_add_u64(u64 *p, u64 v)
 {
     asm volatile("red.global.add.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
-// Decode one scaled quantity: sb = scale byte (0xF7..0xFF for -9..-1; never 0 here).
-// A scale outside [-9, -1] sets `bad` (the tile is then redone by the generic path).
-// Every table shift is >= 35, so ((x + d - 1) * m) >> sh is the HIGH word of the
-// 32x32 product shifted by sh - 32: one IMAD.HI and one shift.
-__device__ __forceinline__ unsigned decode_one(unsigned x, unsigned sb, const CeilDiv10 *tbl, bool &bad)
+// Decode one scaled quantity: sb = scale byte, already validated to be 0xF7..0xFF
+// (-9..-1), so k = -scale is the low nibble of -sb.  ceil(x / 10^k) is the HIGH
+// word of (x + 10^k - 1) * m shifted by sh - 32 (every table shift is >= 35, and
+// sh - 32 == (k * 3402) >> 10 for k = 1..9); m and 10^k - 1 come from constant
+// memory with one 64-bit load (kCeilDiv10Packed, indexable by any nibble).
+__device__ __forceinline__ unsigned decode_one(unsigned x, unsigned sb)
 {
-    const unsigned k = (0u - sb) & 0xffu;                     // k = -scale
-    bad |= k > 9u;
-    const CeilDiv10 t = tbl[k < 10u ? k : 1u];
-    return __umulhi(x + t.dm1, t.m) >> (t.sh - 32u);
+    const unsigned k = (0u - sb) & 0xfu;
+    const uint2 t = kCeilDiv10Packed[k];                      // {m, 10^k - 1}
+    return __umulhi(x + t.y, t.x) >> ((k * 3402u) >> 10);
 }
 
 // One row: decode, prefix-sum, park exclusive prefixes in pre32[0..128], return
 // the running total after the row.  (xa0,xa1) = lane's pair in the first half,
 // (xb0,xb1) = its pair in the second half.
 __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigned xb0, unsigned xb1, unsigned sbytes,
-                                             unsigned carry, unsigned *pre32, int lane, const CeilDiv10 *tbl, bool &bad)
+                                             unsigned carry, unsigned *pre32, int lane, bool &bad)
 {
     const unsigned FULL = 0xffffffffu;
     // scaled quantities are rare: each of the four positions is decoded only by
     // the lanes that hold one there (divergent, skipped when no lane does)
     if (sbytes != 0u) {
-        if (sbytes & 0x000000ffu) xa0 = decode_one(xa0, sbytes & 0xffu, tbl, bad);
-        if (sbytes & 0x0000ff00u) xa1 = decode_one(xa1, (sbytes >> 8) & 0xffu, tbl, bad);
-        if (sbytes & 0x00ff0000u) xb0 = decode_one(xb0, (sbytes >> 16) & 0xffu, tbl, bad);
-        if (sbytes & 0xff000000u) xb1 = decode_one(xb1, sbytes >> 24, tbl, bad);
+        // every byte must be 0 or in [0xF7, 0xFF] (scale 0 or -9..-1); anything else sends the
+        // tile to the generic path (the values decoded below are then thrown away)
+        bad |= (__vcmpgeu4(sbytes, 0xF7F7F7F7u) | __vcmpeq4(sbytes, 0u)) != 0xFFFFFFFFu;
+        if (sbytes & 0x000000ffu) xa0 = decode_one(xa0, sbytes & 0xffu);
+        if (sbytes & 0x0000ff00u) xa1 = decode_one(xa1, (sbytes >> 8) & 0xffu);
+        if (sbytes & 0x00ff0000u) xb0 = decode_one(xb0, (sbytes >> 16) & 0xffu);
+        if (sbytes & 0xff000000u) xb1 = decode_one(xb1, sbytes >> 24);
     }
     const unsigned sA = xa0 + xa1, sB = xb0 + xb1;
     unsigned exA, exB, tA, tB;
@@ -642,13 +652,10 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
     __shared__ u64 s_wa[kWarps];
-    __shared__ CeilDiv10 s_div[10];
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const unsigned FULL = 0xffffffffu;
-    if (threadIdx.x < 10) s_div[threadIdx.x] = kCeilDiv10[threadIdx.x];
-    __syncthreads();
     unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
 
     u64 acc_alloc = 0;
@@ -703,10 +710,10 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                 fast = !__any_sync(FULL, bad);
                 if (fast) {
                     unsigned total = fast_row((unsigned)vA0.x, (unsigned)vA0.y, (unsigned)vB0.x, (unsigned)vB0.y, s0,
-                                              0u, pre32, lane, s_div, bad);
+                                              0u, pre32, lane, bad);
                     if (two)
                         total = fast_row((unsigned)vA1.x, (unsigned)vA1.y, (unsigned)vB1.x, (unsigned)vB1.y, s1,
-                                         total, pre32 + kFastRow, lane, s_div, bad);
+                                         total, pre32 + kFastRow, lane, bad);
                     // a scale outside [-9, 0] turned up while decoding: redo the tile generically
                     // (nothing has been published yet: shared memory is scratch, atomics come later)
                     fast = !__any_sync(FULL, bad);

@@ -30,6 +30,20 @@ def test_ceil_div10_table_is_exact_on_its_whole_domain():
         assert np.array_equal(got, (x + np.uint64(d - 1)) // np.uint64(d)), k
 
 
+def test_packed_table_matches_and_shift_formula():
+    src = open(os.path.join(ROOT, "arena_b200", "csrc", "kernels.cuh")).read()
+    body = src[src.index("kCeilDiv10Packed[16] = {"):]
+    pairs = re.findall(r"\{(\d+)u, (\d+)u\}", body[:body.index("};")])
+    assert len(pairs) == 16
+    full = _table("kCeilDiv10")
+    for k in range(1, 10):
+        m, sh, dm1 = full[k]
+        assert (int(pairs[k][0]), int(pairs[k][1])) == (m, dm1)
+        assert sh >= 35 and sh - 32 == (k * 3402) >> 10          # the kernel derives the shift from k
+    # (x + dm1) * m >> sh == umulhi(x + dm1, m) >> (sh - 32) needs x + dm1 < 2^32
+    assert (1 << 23) + 999_999_999 < 2 ** 32
+
+
 def test_recip10_table():
     src = open(os.path.join(ROOT, "arena_b200", "csrc", "kernels.cuh")).read()
     body = src[src.index("kRecip10[10] = {"):]
