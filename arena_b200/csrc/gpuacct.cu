@@ -205,20 +205,11 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
                     cudaStream_t st)
 {
     const arena_snapshot_view &v = s->v;
-    NodesArgs na;
-    na.N = v.n_nodes;
-    na.cap_val = (const i64 *)v.node_cap_val;
-    na.cap_scale = (const signed char *)v.node_cap_scale;
-    na.node_total = d_total;
-    na.node_alloc = (u64 *)d_alloc;
-    na.cluster_total = d_cluster;
-    na.scratch = s->scratch;
     const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
     cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
     if (prof) { g_prof.used += 3; cudaEventRecord(pe[0], st); }
-    int gn = grid_for(v.n_nodes, kThreads * 4, 8);
-    top_node_nodes_kernel<<<gn, kThreads, 0, st>>>(na);
-    count_launch();
+    // node_alloc is accumulated with atomics: it starts from zero
+    if (v.n_nodes) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
     if (prof) cudaEventRecord(pe[1], st);
 
     PodsArgs pa{};
@@ -232,7 +223,14 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     pa.pod_gpu = d_pod_gpu;
     pa.total_alloc = d_cluster + 1;
     pa.scratch = s->scratch;
+    pa.n_nodes = v.n_nodes;
+    pa.cap_val = (const i64 *)v.node_cap_val;
+    pa.cap_scale = (const signed char *)v.node_cap_scale;
+    pa.node_total = d_total;
+    pa.total_capacity = d_cluster;
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
+    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
+    if (gn > gp) gp = gn;
     top_node_pods_kernel<<<gp, kThreads, 0, st>>>(pa);
     count_launch();
     if (prof) cudaEventRecord(pe[2], st);

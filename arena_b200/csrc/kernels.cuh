@@ -7,7 +7,7 @@
 //                    math.go:144-203 (and the dropped `ok`, quantity.go:713-714)
 //   pods kernel      cmd/arena/commands/gpu.go:39-79, pod_helper.go:15-31,
 //                    top_node.go:88-97, 232-242
-//   nodes kernel     gpu.go:18-37, top_node.go:115-118
+//   (same kernel)    gpu.go:18-37, top_node.go:115-118 (node capacities, cluster total)
 //   job kernels      job_info.go:51-70, trainer_mpi.go:241-282,
 //                    trainer_standalone.go:198-221, trainer.go:25-37
 #pragma once
@@ -225,39 +225,6 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
 }
 
 // ---------------------------------------------------------------------------
-// Nodes kernel: node_total[n] = Value(capacity), node_alloc[n] = 0, and the
-// cluster's total GPUs.  9N bytes read, 16N written.
-// ---------------------------------------------------------------------------
-struct NodesArgs {
-    u64 N;
-    const i64 *cap_val;
-    const signed char *cap_scale;
-    i64 *node_total;
-    u64 *node_alloc;
-    i64 *cluster_total;     // &cluster[0]
-    Scratch *scratch;
-};
-
-__global__ void __launch_bounds__(kThreads) top_node_nodes_kernel(NodesArgs a)
-{
-    u64 sum = 0;
-    for (u64 n = (u64)blockIdx.x * blockDim.x + threadIdx.x; n < a.N; n += (u64)gridDim.x * blockDim.x) {
-        i64 t = quantity_value(a.cap_val[n], a.cap_scale[n]);
-        a.node_total[n] = t;
-        a.node_alloc[n] = 0;
-        sum += (u64)t;
-    }
-    __shared__ u64 s_w[kWarps];
-    sum = warp_reduce_sum(sum);
-    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
-    __syncthreads();
-    u64 block = 0;
-    if (threadIdx.x == 0)
-        for (int w = 0; w < kWarps; w++) block += s_w[w];
-    finish_totals(block, 0, false, a.scratch, 0, a.cluster_total, nullptr);
-}
-
-// ---------------------------------------------------------------------------
 // Pods kernel.  One warp owns a tile of 128 consecutive pods:
 //
 //  1. 128-bit loads of the pod columns (4 pods per lane).
@@ -297,6 +264,12 @@ struct PodsArgs {
     i64 *total_alloc;               // sum over keys of key_alloc
     i64 *total_req;                 // kJob only
     Scratch *scratch;
+    // top node only: the per-node capacities, decoded by the same launch
+    u64 n_nodes;
+    const i64 *cap_val;
+    const signed char *cap_scale;
+    i64 *node_total;                // [N] Value(capacity)
+    i64 *total_capacity;            // sum of node_total
 };
 
 // Rare path (a row that runs past the end of the container columns) kept out
@@ -775,12 +748,25 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
         if (lane == 31) acc_alloc += tile_alloc;
     }
 
+    // ---- node capacities (gpuInNode, gpu.go:18-37): 9N bytes in, 8N out.  Done by the same
+    // launch, after the pod tiles, where it fills the tail of the grid instead of costing a
+    // second launch (node_alloc was zeroed by a memset before this kernel).
+    u64 cap_sum = 0;
+    for (u64 n = (u64)blockIdx.x * blockDim.x + threadIdx.x; n < a.n_nodes; n += (u64)gridDim.x * blockDim.x) {
+        const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
+        a.node_total[n] = t;
+        cap_sum += (u64)t;
+    }
+    cap_sum = warp_reduce_sum(cap_sum);
+
+    __shared__ u64 s_wc[kWarps];
     if (lane == 31) s_wa[warp] = acc_alloc;
+    if (lane == 0) s_wc[warp] = cap_sum;
     __syncthreads();
-    u64 block_a = 0;
+    u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
-        for (int w = 0; w < kWarps; w++) block_a += s_wa[w];
-    finish_totals(block_a, 0, false, a.scratch, 1, a.total_alloc, nullptr);
+        for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
+    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity);
 }
 
 // ---------------------------------------------------------------------------

@@ -177,11 +177,11 @@ int  arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, 
 /* Per-kernel device timing for the roofline report (no counterpart in the
  * reference; its only profiler is --pprof, cmd/arena/main.go:14-22).  Between
  * begin and end, every arena_top_node*() call records CUDA events on its
- * launch stream around the nodes kernel and the pods kernel (at most
+ * launch stream around the node_alloc memset and the top-node kernel (at most
  * max_calls calls are recorded).  end() waits for them and returns the summed
  * durations in milliseconds. */
 int  arena_profile_begin(int max_calls);
-int  arena_profile_end(double *nodes_ms_sum, double *pods_ms_sum, uint64_t *calls);
+int  arena_profile_end(double *memset_ms_sum, double *kernel_ms_sum, uint64_t *calls);
 
 /* Calibration (no counterpart in the reference): read the five columns the
  * pods kernel reads with plain coalesced 128-bit loads and no arithmetic,
