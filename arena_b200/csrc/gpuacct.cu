@@ -63,6 +63,7 @@ struct arena_snapshot {
     void *block = nullptr;       // single allocation holding all owned columns
     size_t block_bytes = 0;
     Scratch *scratch = nullptr;  // per-handle: distinct handles may run concurrently
+    bool direct = false;         // pods not grouped by node: per-pod adds instead of telescoping
     // top job work arrays (allocated on first use)
     u64 *job_req = nullptr, *job_alloc = nullptr;
     i64 *job_maxcreated = nullptr;
@@ -99,7 +100,7 @@ int arena_acct_init(int device)
                     prop.major, prop.minor);
     g_ctx.device = device;
     g_ctx.sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false>, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1)
         return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
@@ -158,6 +159,27 @@ int alloc_common(arena_snapshot *s)
 {
     CUDA_TRY(cudaMalloc((void **)&s->scratch, sizeof(Scratch)));
     CUDA_TRY(cudaMemsetAsync(s->scratch, 0, sizeof(Scratch), g_ctx.stream));
+    return ARENA_OK;
+}
+
+// Are the pods grouped by node?  Sample 4096 adjacent pairs of the DEVICE pod_node column; when
+// more than a quarter of them change node the snapshot uses the per-pod-add kernel.  Either
+// kernel is exact for any order, so this only picks the faster one.  Synchronises the stream.
+int probe_grouping(arena_snapshot *s)
+{
+    s->direct = false;
+    const u64 P = s->v.n_pods;
+    if (P < 2 || !s->scratch) return ARENA_OK;
+    const unsigned n = P - 1 < 4096 ? (unsigned)(P - 1) : 4096u;
+    unsigned *flag = &s->scratch->ticket[3];
+    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), g_ctx.stream));
+    probe_grouping_kernel<<<16, 256, 0, g_ctx.stream>>>(s->v.pod_node, P, n, flag);
+    count_launch();
+    unsigned diff = 0;
+    CUDA_TRY(cudaMemcpyAsync(&diff, flag, sizeof(unsigned), cudaMemcpyDeviceToHost, g_ctx.stream));
+    CUDA_TRY(cudaStreamSynchronize(g_ctx.stream));
+    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), g_ctx.stream));
+    s->direct = diff * 4u > n;
     return ARENA_OK;
 }
 
@@ -231,7 +253,8 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
     const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
     if (gn > gp) gp = gn;
-    top_node_pods_kernel<<<gp, kThreads, 0, st>>>(pa);
+    if (s->direct) top_node_pods_kernel<true><<<gp, kThreads, 0, st>>>(pa);
+    else top_node_pods_kernel<false><<<gp, kThreads, 0, st>>>(pa);
     count_launch();
     if (prof) cudaEventRecord(pe[2], st);
     CUDA_TRY(cudaGetLastError());
@@ -377,6 +400,7 @@ int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
     if (!s) return fail(ARENA_E_NOMEM, "out of host memory");
     rc = fill_snapshot(s, h, h->n_jobs > 0 && h->pod_job);
     if (!rc) rc = alloc_common(s);
+    if (!rc) rc = probe_grouping(s);
     if (rc) { arena_snapshot_free(s); return rc; }
     cudaError_t e = cudaStreamSynchronize(g_ctx.stream);     // host buffers may be reused on return
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "upload: %s", cudaGetErrorString(e)); }
@@ -397,6 +421,7 @@ int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **ou
     s->v = *d;
     if (!d->pod_job) s->v.n_jobs = 0;
     rc = alloc_common(s);
+    if (!rc) rc = probe_grouping(s);
     if (rc) { arena_snapshot_free(s); return rc; }
     cudaError_t e = cudaStreamSynchronize(g_ctx.stream);
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "wrap: %s", cudaGetErrorString(e)); }
@@ -475,6 +500,18 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
     }
     rc = fill_snapshot(g_host_snap, host, false);            // async H2D on the library stream ...
     if (rc) return rc;
+    {   // grouping probe on the HOST column (no extra device round trip on this path)
+        const u64 P = host->n_pods;
+        unsigned diff = 0, n = 0;
+        if (P >= 2) {
+            n = P - 1 < 4096 ? (unsigned)(P - 1) : 4096u;
+            for (unsigned i = 0; i < n; i++) {
+                const u64 p = (u64)i * (P - 1) / n;
+                diff += host->pod_node[p] != host->pod_node[p + 1];
+            }
+        }
+        g_host_snap->direct = diff * 4u > n;
+    }
     return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
 }
 

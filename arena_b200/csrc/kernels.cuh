@@ -621,6 +621,11 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
 #ifndef ARENA_MINB
 #define ARENA_MINB 6
 #endif
+// kDirect: pods are NOT grouped by node (almost every position would be an edge and telescoping
+// would cost two atomics per pod): each pod's own value is added to its node instead, one atomic
+// per pod that contributes anything.  Both instantiations are exact for any order; the host picks
+// one from a sample of the pod_node column (probe_grouping / arena_snapshot_upload).
+template <bool kDirect>
 __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
@@ -719,7 +724,12 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                     if (lane == 31) key_next = kNone;
                     const bool e0 = k4.x != k4.y, e1 = k4.y != k4.z, e2 = k4.z != k4.w;
                     const bool e3 = (k4.w != key_next) | (lane == 31);
-                    if (e0 | e1 | e2 | e3) {
+                    if (kDirect) {
+                        if (a0) red_add_u64(a.key_alloc + k4.x, a0);
+                        if (a1) red_add_u64(a.key_alloc + k4.y, a1);
+                        if (a2) red_add_u64(a.key_alloc + k4.z, a2);
+                        if (a3) red_add_u64(a.key_alloc + k4.w, a3);
+                    } else if (e0 | e1 | e2 | e3) {
                         if (e0) {
                             const u64 v = off + S0;
                             if (k4.x < K32) red_add_u64(a.key_alloc + k4.x, v);
@@ -920,6 +930,18 @@ __global__ void bitonic_global_kernel(u64 *key, unsigned *idx, u64 n, u64 k, u64
         bool swap = up ? pair_less(kb, ib, ka, ia) : pair_less(ka, ia, kb, ib);
         if (swap) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
     }
+}
+
+// Samples adjacent pairs of the key column: *out = number of sampled pairs whose keys differ.
+__global__ void probe_grouping_kernel(const unsigned *key, u64 P, unsigned n_samples, unsigned *out)
+{
+    unsigned diff = 0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_samples; i += gridDim.x * blockDim.x) {
+        const u64 p = (u64)i * (P - 1) / n_samples;
+        diff += key[p] != key[p + 1];
+    }
+    diff = __reduce_add_sync(0xffffffffu, diff);
+    if ((threadIdx.x & 31) == 0 && diff) atomicAdd(out, diff);
 }
 
 // Calibration: how fast can this GPU merely READ the columns the pods kernel
