@@ -100,7 +100,7 @@ int arena_acct_init(int device)
                     prop.major, prop.minor);
     g_ctx.device = device;
     g_ctx.sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false>, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1)
         return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
@@ -253,8 +253,13 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
     const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
     if (gn > gp) gp = gn;
-    if (s->direct) top_node_pods_kernel<true><<<gp, kThreads, 0, st>>>(pa);
-    else top_node_pods_kernel<false><<<gp, kThreads, 0, st>>>(pa);
+    if (d_pod_gpu) {
+        if (s->direct) top_node_pods_kernel<true, true><<<gp, kThreads, 0, st>>>(pa);
+        else top_node_pods_kernel<false, true><<<gp, kThreads, 0, st>>>(pa);
+    } else {
+        if (s->direct) top_node_pods_kernel<true, false><<<gp, kThreads, 0, st>>>(pa);
+        else top_node_pods_kernel<false, false><<<gp, kThreads, 0, st>>>(pa);
+    }
     count_launch();
     if (prof) cudaEventRecord(pe[2], st);
     CUDA_TRY(cudaGetLastError());

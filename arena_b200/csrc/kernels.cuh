@@ -625,7 +625,8 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
 // would cost two atomics per pod): each pod's own value is added to its node instead, one atomic
 // per pod that contributes anything.  Both instantiations are exact for any order; the host picks
 // one from a sample of the pod_node column (probe_grouping / arena_snapshot_upload).
-template <bool kDirect>
+// kDetails: also write gpuInPod of every pod (the details view); kept out of the summary kernel.
+template <bool kDirect, bool kDetails>
 __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
@@ -703,7 +704,7 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                                    b3 = pre32[c4.w - base], b4 = pre32[cb4 - base];
                     __syncwarp();
                     const unsigned g0 = b1 - b0, g1 = b2 - b1, g2 = b3 - b2, g3 = b4 - b3;
-                    if (a.pod_gpu != nullptr) {
+                    if (kDetails) {
                         ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(a.pod_gpu + q);
                         ulonglong2 o0, o1;
                         o0.x = g0; o0.y = g1; o1.x = g2; o1.y = g3;
