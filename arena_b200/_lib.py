@@ -75,6 +75,7 @@ _SIGS = [
     ("arena_host_job_name", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_host_job_trainer", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_host_node_name", C.c_char_p, [_VP, C.c_uint32]),
+    ("arena_host_pod_name", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_quantity_parse", C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                        C.POINTER(C.c_int32), C.POINTER(C.c_int)]),
     ("arena_format_top_node", C.c_int, [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),

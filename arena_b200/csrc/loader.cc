@@ -13,9 +13,14 @@
 #include "quantity.h"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <numeric>
+#include <thread>
 #include <unordered_map>
 
 using arena_json::Value;
@@ -78,12 +83,6 @@ bool label(const Value *labels, const char *key, std::string &out)
     return true;
 }
 
-bool label_is(const Value *labels, const char *key, const char *want)
-{
-    std::string v;
-    return label(labels, key, v) && v == want;
-}
-
 // Decode every entry of a ResourceList (a bad quantity anywhere fails the List
 // decode in the reference) and return the selected GPU quantity.
 void resource_list(const Value *rl, const char *what, bool select, int64_t &val, int8_t &scale)
@@ -93,12 +92,12 @@ void resource_list(const Value *rl, const char *what, bool select, int64_t &val,
     if (!rl) return;
     if (!rl->is_object()) bad(std::string(what) + " is not an object");
     const Value *primary = nullptr, *deprecated = nullptr;
-    for (const auto &m : rl->members) {
+    for (const Value &m : rl->children()) {
         ParsedQuantity q;
-        if (!unmarshal_quantity_json(m.second.raw, q))
-            bad(std::string("invalid quantity ") + std::string(m.second.raw) + " for \"" + m.first + "\" in " + what);
-        if (m.first == kPrimary) primary = &m.second;           // duplicates: last wins
-        else if (m.first == kDeprecated) deprecated = &m.second;
+        if (!unmarshal_quantity_json(m.raw, q))
+            bad(std::string("invalid quantity ") + std::string(m.raw) + " for \"" + std::string(m.key) + "\" in " + what);
+        if (m.key == kPrimary) primary = &m;                    // duplicates: last wins
+        else if (m.key == kDeprecated) deprecated = &m;
     }
     if (!select) return;
     const Value *pick = primary ? primary : deprecated;          // gpu.go:61-79: key PRESENCE
@@ -171,6 +170,15 @@ uint8_t phase_code(const std::string &p)
     return ARENA_PHASE_OTHER;
 }
 
+// The labels the job-membership rules read, copied out so a pod record does not
+// point into its (per-item, short-lived) JSON tree.
+enum : uint8_t { kHasRelease = 1, kHasApp = 2, kHasGroup = 4, kHasReplicaType = 8, kHasReplicaIndex = 16 };
+struct PodLabels {
+    uint8_t has = 0;
+    std::string release, app, group_name, replica_type, replica_index;
+    bool is(uint8_t bit, const std::string &field, const char *want) const { return (has & bit) && field == want; }
+};
+
 struct PodRec {
     std::string name, ns, node_name, host_ip;
     uint8_t phase = 0;
@@ -178,9 +186,16 @@ struct PodRec {
     std::vector<int8_t> ctr_scale;
     int64_t created = kZeroTimeUnix;
     bool owner_is_job = false;
-    const Value *labels = nullptr;
+    PodLabels labels;
     uint32_t node = ARENA_NONE, job = ARENA_NONE;
     uint8_t role = ARENA_ROLE_COUNTS;
+};
+
+struct NodeRec {
+    std::string name, internal_ip, first_addr;
+    uint8_t has_addr = 0, is_master = 0;
+    int64_t cap_val = 0;
+    int8_t cap_scale = 0;
 };
 
 struct ObjRec {                 // batch/v1 Job or TFJob: what membership and the printer need
@@ -198,11 +213,274 @@ const Value *items_of(const Value &doc, const char *what)
     return items;
 }
 
-void parse_doc(const char *text, size_t len, const char *what, Value &doc)
+// Which members the loader ever reads.  Everything else (a real PodList is mostly
+// managedFields, volumes, env, containerStatuses ...) is validated and dropped by the
+// parser without building nodes.  Inside the string->string / string->Quantity maps
+// every key is kept: a bad quantity under ANY resource name fails the decode.
+bool is_map_parent(std::string_view k)
+{
+    return k == "labels" || k == "limits" || k == "requests" || k == "capacity" || k == "allocatable";
+}
+
+bool one_of(std::string_view key, std::initializer_list<std::string_view> set)
+{
+    for (std::string_view s : set)
+        if (key == s) return true;
+    return false;
+}
+
+bool keep_core(std::string_view parent, std::string_view key)      // PodList, NodeList
+{
+    if (is_map_parent(parent)) return true;
+    switch (key.size()) {
+    case 4: return one_of(key, {"spec", "name", "kind", "type"});
+    case 5: return one_of(key, {"items", "phase"});
+    case 6: return one_of(key, {"status", "labels", "limits", "hostIP"});
+    case 7: return one_of(key, {"address"});
+    case 8: return one_of(key, {"metadata", "nodeName", "requests", "capacity"});
+    case 9: return one_of(key, {"namespace", "resources", "addresses"});
+    case 10: return one_of(key, {"containers"});
+    case 11: return one_of(key, {"allocatable"});
+    case 14: return one_of(key, {"initContainers"});
+    case 15: return one_of(key, {"ownerReferences"});
+    case 17: return one_of(key, {"creationTimestamp"});
+    default: return false;
+    }
+}
+
+bool keep_job(std::string_view parent, std::string_view key)       // JobList, TFJobList
+{
+    if (is_map_parent(parent)) return true;
+    switch (key.size()) {
+    case 4: return one_of(key, {"type"});
+    case 5: return one_of(key, {"items"});
+    case 6: return one_of(key, {"status", "labels", "active", "failed"});
+    case 8: return one_of(key, {"metadata"});
+    case 9: return one_of(key, {"namespace", "succeeded", "startTime"});
+    case 10: return one_of(key, {"conditions"});
+    default: return false;
+    }
+}
+
+struct Doc {
+    arena_json::Tree tree;
+    std::vector<arena_json::Range> item_ranges; // elements of .items when `split`
+    bool split = false;
+};
+
+struct SyntaxError {
+    size_t offset;
+    std::string message;
+};
+
+[[noreturn]] void bad_syntax(const char *what, size_t offset, const std::string &message)
+{
+    bad(std::string(what) + ": JSON syntax error at byte " + std::to_string(offset) + ": " + message);
+}
+
+// Parses the list envelope.  With `split` the elements of the root "items" array are
+// left as byte ranges (doc.split says whether that happened) for for_each_item.
+void parse_doc(const char *text, size_t len, const char *what, Doc &doc, arena_json::KeyFilter filter, bool split)
 {
     arena_json::ParseError e;
-    if (!arena_json::parse(std::string_view(text, len), doc, e))
-        bad(std::string(what) + ": JSON syntax error at byte " + std::to_string(e.offset) + ": " + e.message);
+    arena_json::ParseOptions opt;
+    opt.filter = filter;
+    if (split) {
+        opt.split_key = "items";
+        opt.split_out = &doc.item_ranges;
+        opt.split_done = &doc.split;
+    }
+    if (!arena_json::parse(std::string_view(text, len), doc.tree, e, opt)) bad_syntax(what, e.offset, e.message);
+}
+
+// ARENA_LOADER_TRACE=1: per-phase wall times on stderr (tools/loader_timing.py reads them)
+struct PhaseTrace {
+    bool on = std::getenv("ARENA_LOADER_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void mark(const char *phase)
+    {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[arena loader] %-22s %8.2f ms\n", phase, std::chrono::duration<double, std::milli>(now - t).count());
+        t = now;
+    }
+};
+
+unsigned loader_threads(size_t n_items)
+{
+    unsigned t = std::thread::hardware_concurrency();
+    if (const char *env = std::getenv("ARENA_LOADER_THREADS")) {
+        const long v = std::strtol(env, nullptr, 10);
+        if (v > 0) t = (unsigned)v;
+    }
+    if (t < 1) t = 1;
+    if (t > 64) t = 64;
+    const size_t by_work = n_items / 256 + 1;                    // a thread is not worth starting for fewer items
+    return (unsigned)std::min<size_t>(t, by_work);
+}
+
+// Runs extract(item, rec) over every element of doc's "items", in parallel over the
+// byte ranges when the envelope was split.  Error precedence is that of a sequential
+// pass: the syntax error at the lowest byte offset, else the extraction error of the
+// lowest item index.
+template <class Rec, class Extract>
+void for_each_item(const char *text, size_t len, const char *what, Doc &doc, arena_json::KeyFilter filter,
+                   std::vector<Rec> &recs, Extract extract)
+{
+    const Value *items = items_of(doc.tree.root(), what);
+    if (!items) { recs.clear(); return; }
+    if (!doc.split) {
+        recs.resize(items->size());
+        size_t k = 0;
+        for (const Value &item : items->children()) extract(item, recs[k++]);
+        return;
+    }
+    const std::vector<arena_json::Range> &ranges = doc.item_ranges;
+    const size_t n = ranges.size();
+    recs.resize(n);
+    const unsigned T = loader_threads(n);
+    struct Outcome {
+        bool syntax = false, extraction = false, nomem = false;
+        size_t syntax_offset = 0, item = 0;
+        std::string syntax_message, message;
+    };
+    std::vector<Outcome> outcomes(T);
+    std::atomic<size_t> next{0};
+    const size_t kChunk = 64;
+    const std::string_view doc_text(text, len);
+    auto work = [&](unsigned tid) {
+        Outcome &o = outcomes[tid];
+        arena_json::ParseOptions opt;
+        opt.filter = filter;
+        arena_json::Tree item;                                   // reused: its node pool stops growing after a few items
+        for (;;) {
+            const size_t lo = next.fetch_add(kChunk);
+            if (lo >= n) break;
+            const size_t hi = std::min(n, lo + kChunk);
+            for (size_t k = lo; k < hi; k++) {
+                try {
+                    arena_json::ParseError e;
+                    if (!arena_json::parse_range(doc_text, ranges[k], 2, "items", item, e, opt)) {
+                        if (!o.syntax || e.offset < o.syntax_offset) {
+                            o.syntax = true; o.syntax_offset = e.offset; o.syntax_message = e.message;
+                        }
+                        continue;
+                    }
+                    extract(item.root(), recs[k]);
+                } catch (const LoadError &e) {
+                    if (!o.extraction || k < o.item) { o.extraction = true; o.item = k; o.message = e.msg; }
+                } catch (const std::bad_alloc &) {
+                    o.nomem = true;
+                    return;
+                }
+            }
+        }
+    };
+    if (T <= 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> pool;
+        pool.reserve(T - 1);
+        for (unsigned t = 1; t < T; t++) pool.emplace_back(work, t);
+        work(0);
+        for (std::thread &th : pool) th.join();
+    }
+    const Outcome *first_syntax = nullptr, *first_extract = nullptr;
+    for (const Outcome &o : outcomes) {
+        if (o.nomem) throw std::bad_alloc();
+        if (o.syntax && (!first_syntax || o.syntax_offset < first_syntax->syntax_offset)) first_syntax = &o;
+        if (o.extraction && (!first_extract || o.item < first_extract->item)) first_extract = &o;
+    }
+    if (first_syntax) bad_syntax(what, first_syntax->syntax_offset, first_syntax->syntax_message);
+    if (first_extract) bad(first_extract->message);
+}
+
+void pod_labels(const Value *labels, PodLabels &out)
+{
+    if (!labels) return;
+    if (label(labels, "release", out.release)) out.has |= kHasRelease;
+    if (label(labels, "app", out.app)) out.has |= kHasApp;
+    if (label(labels, "group_name", out.group_name)) out.has |= kHasGroup;
+    if (label(labels, "tf-replica-type", out.replica_type)) out.has |= kHasReplicaType;
+    if (label(labels, "tf-replica-index", out.replica_index)) out.has |= kHasReplicaIndex;
+}
+
+void extract_node(const Value &node, NodeRec &r)
+{
+    if (!node.is_object()) bad("NodeList item is not an object");
+    const Value *meta = child(&node, "metadata");
+    const Value *status = child(&node, "status");
+    r.name = str_field(meta, "name");
+    const Value *labels = child(meta, "labels");
+    std::string tmp;
+    r.is_master = label(labels, kMasterLabel, tmp) ? 1 : 0;               // top_node.go:244-250: key presence
+    int64_t v; int8_t s;
+    resource_list(child(status, "allocatable"), "node status.allocatable", false, v, s);
+    resource_list(child(status, "capacity"), "node status.capacity", true, r.cap_val, r.cap_scale);
+    r.internal_ip = "unknown";                                            // top_node.go:120-129
+    const Value *addrs = child(status, "addresses");
+    if (!addrs) return;
+    if (!addrs->is_array()) bad("node status.addresses is not an array");
+    bool have_internal = false;
+    size_t i = 0;
+    for (const Value &a : addrs->children()) {
+        std::string type = str_field(&a, "type"), addr = str_field(&a, "address");
+        if (!have_internal && type == "InternalIP") { r.internal_ip = addr; have_internal = true; }
+        if (i++ == 0) { r.first_addr = std::move(addr); r.has_addr = 1; }   // top_node.go:173-175
+    }
+}
+
+void extract_pod(const Value &pod, PodRec &r, const std::unordered_map<std::string, uint32_t> &node_id)
+{
+    if (!pod.is_object()) bad("PodList item is not an object");
+    const Value *meta = child(&pod, "metadata");
+    const Value *spec = child(&pod, "spec");
+    const Value *status = child(&pod, "status");
+    r.name = str_field(meta, "name");
+    r.ns = str_field(meta, "namespace");
+    pod_labels(child(meta, "labels"), r.labels);
+    r.created = parse_time(child(meta, "creationTimestamp"), "metadata.creationTimestamp");
+    if (const Value *owners = child(meta, "ownerReferences")) {
+        if (!owners->is_array()) bad("metadata.ownerReferences is not an array");
+        for (const Value &o : owners->children())
+            if (str_field(&o, "kind") == "Job") { r.owner_is_job = true; break; }
+    }
+    r.node_name = str_field(spec, "nodeName");
+    r.phase = phase_code(str_field(status, "phase"));
+    r.host_ip = str_field(status, "hostIP");
+    for (const char *list : {"initContainers", "containers"}) {
+        const Value *cs = child(spec, list);
+        if (!cs) continue;
+        if (!cs->is_array()) bad(std::string("spec.") + list + " is not an array");
+        const bool counted = std::strcmp(list, "containers") == 0;             // gpu.go:40: spec.containers only
+        for (const Value &c : cs->children()) {
+            if (!c.is_object()) bad("container is not an object");
+            const Value *res = child(&c, "resources");
+            int64_t v; int8_t s;
+            resource_list(child(res, "requests"), "resources.requests", false, v, s);
+            resource_list(child(res, "limits"), "resources.limits", counted, v, s);   // gpu.go:61-69: LIMITS
+            if (counted) { r.ctr_val.push_back(v); r.ctr_scale.push_back(s); }
+        }
+    }
+    if (!r.node_name.empty()) {
+        auto it = node_id.find(r.node_name);
+        if (it != node_id.end()) r.node = it->second;
+    }
+}
+
+// Stable grouping of rows by key (node or job id; ARENA_NONE last): a counting sort.
+std::vector<uint32_t> group_rows(const std::vector<PodRec> &pods, size_t n_keys, bool by_job)
+{
+    auto key_of = [&](const PodRec &r) -> size_t {
+        const uint32_t k = by_job ? r.job : r.node;
+        return k == ARENA_NONE ? n_keys : (size_t)k;
+    };
+    std::vector<size_t> start(n_keys + 2, 0);
+    for (const PodRec &r : pods) start[key_of(r) + 1]++;
+    for (size_t k = 1; k < start.size(); k++) start[k] += start[k - 1];
+    std::vector<uint32_t> order(pods.size());
+    for (size_t p = 0; p < pods.size(); p++) order[start[key_of(pods[p])]++] = (uint32_t)p;
+    return order;
 }
 
 // hasCondition / isSucceeded / isFailed / isPending: trainer_tensorflow.go:420-439
@@ -211,7 +489,7 @@ bool tf_condition(const Value *status, const char *type)
     const Value *conds = child(status, "conditions");
     if (!conds) return false;
     if (!conds->is_array()) bad("tfjob status.conditions is not an array");
-    for (const Value &c : conds->items)
+    for (const Value &c : conds->children())
         if (str_field(&c, "type") == type && str_field(&c, "status") == "True") return true;
     return false;
 }
@@ -220,90 +498,55 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
          const char *tfjoblist, size_t tflen, const char *helm, size_t helmlen, bool group_by_job,
          arena_host_snapshot *h)
 {
-    Value pod_doc, node_doc, job_doc, tf_doc;
-    parse_doc(nodelist, nodelen, "NodeList", node_doc);
-    parse_doc(podlist, podlen, "PodList", pod_doc);
+    PhaseTrace trace;
+    Doc pod_doc, node_doc, job_doc, tf_doc;
+    parse_doc(nodelist, nodelen, "NodeList", node_doc, keep_core, true);
+    parse_doc(podlist, podlen, "PodList", pod_doc, keep_core, true);
+    trace.mark("envelopes + item scan");
 
     // ---- nodes -------------------------------------------------------------------
-    const Value *nitems = items_of(node_doc, "NodeList");
-    const size_t N = nitems ? nitems->items.size() : 0;
-    std::vector<int64_t> cap_val(N);
-    std::vector<int8_t> cap_scale(N);
+    std::vector<NodeRec> nodes;
+    try {
+        for_each_item(nodelist, nodelen, "NodeList", node_doc, keep_core, nodes, extract_node);
+    } catch (const LoadError &e) {
+        // a sequential decode reads BOTH documents before looking at any field, so a syntax
+        // error inside a pod outranks a bad field in a node
+        if (pod_doc.split && e.msg.find("JSON syntax error") == std::string::npos) {
+            Doc whole;
+            parse_doc(podlist, podlen, "PodList", whole, [](std::string_view, std::string_view) { return false; }, false);
+        }
+        throw;
+    }
+    const size_t N = nodes.size();
     std::unordered_map<std::string, uint32_t> node_id;
+    node_id.reserve(N * 2);
     h->node_names.resize(N); h->node_internal_ip.resize(N); h->node_first_addr.resize(N);
     h->node_has_addr.assign(N, 0); h->node_is_master.assign(N, 0);
+    std::vector<int64_t> cap_val(N);
+    std::vector<int8_t> cap_scale(N);
+    std::string dup_node;
     for (size_t n = 0; n < N; n++) {
-        const Value &node = nitems->items[n];
-        if (!node.is_object()) bad("NodeList item is not an object");
-        const Value *meta = child(&node, "metadata");
-        const Value *status = child(&node, "status");
-        h->node_names[n] = str_field(meta, "name");
-        if (!node_id.emplace(h->node_names[n], (uint32_t)n).second)
-            bad("duplicate node name \"" + h->node_names[n] + "\" (the API server guarantees unique node names)");
-        const Value *labels = child(meta, "labels");
-        std::string tmp;
-        h->node_is_master[n] = label(labels, kMasterLabel, tmp) ? 1 : 0;       // top_node.go:244-250: key presence
-        int64_t v; int8_t s;
-        resource_list(child(status, "allocatable"), "node status.allocatable", false, v, s);
-        resource_list(child(status, "capacity"), "node status.capacity", true, cap_val[n], cap_scale[n]);
-        const Value *addrs = child(status, "addresses");
-        if (addrs) {
-            if (!addrs->is_array()) bad("node status.addresses is not an array");
-            bool have_internal = false;
-            for (size_t i = 0; i < addrs->items.size(); i++) {
-                const Value &a = addrs->items[i];
-                const std::string type = str_field(&a, "type"), addr = str_field(&a, "address");
-                if (i == 0) { h->node_first_addr[n] = addr; h->node_has_addr[n] = 1; }     // top_node.go:173-175
-                if (!have_internal && type == "InternalIP") { h->node_internal_ip[n] = addr; have_internal = true; }
-            }
-            if (!have_internal) h->node_internal_ip[n] = "unknown";                     // top_node.go:120-129
-        } else {
-            h->node_internal_ip[n] = "unknown";
-        }
+        NodeRec &r = nodes[n];
+        if (!node_id.emplace(r.name, (uint32_t)n).second && dup_node.empty()) dup_node = r.name;
+        h->node_names[n] = std::move(r.name);
+        h->node_internal_ip[n] = std::move(r.internal_ip);
+        h->node_first_addr[n] = std::move(r.first_addr);
+        h->node_has_addr[n] = r.has_addr;
+        h->node_is_master[n] = r.is_master;
+        cap_val[n] = r.cap_val;
+        cap_scale[n] = r.cap_scale;
     }
+    if (!dup_node.empty())
+        bad("duplicate node name \"" + dup_node + "\" (the API server guarantees unique node names)");
+
+    trace.mark("nodes");
 
     // ---- pods --------------------------------------------------------------------
-    const Value *pitems = items_of(pod_doc, "PodList");
-    const size_t P = pitems ? pitems->items.size() : 0;
-    std::vector<PodRec> pods(P);
-    for (size_t p = 0; p < P; p++) {
-        const Value &pod = pitems->items[p];
-        if (!pod.is_object()) bad("PodList item is not an object");
-        PodRec &r = pods[p];
-        const Value *meta = child(&pod, "metadata");
-        const Value *spec = child(&pod, "spec");
-        const Value *status = child(&pod, "status");
-        r.name = str_field(meta, "name");
-        r.ns = str_field(meta, "namespace");
-        r.labels = child(meta, "labels");
-        r.created = parse_time(child(meta, "creationTimestamp"), "metadata.creationTimestamp");
-        if (const Value *owners = child(meta, "ownerReferences")) {
-            if (!owners->is_array()) bad("metadata.ownerReferences is not an array");
-            for (const Value &o : owners->items)
-                if (str_field(&o, "kind") == "Job") { r.owner_is_job = true; break; }
-        }
-        r.node_name = str_field(spec, "nodeName");
-        r.phase = phase_code(str_field(status, "phase"));
-        r.host_ip = str_field(status, "hostIP");
-        for (const char *list : {"initContainers", "containers"}) {
-            const Value *cs = child(spec, list);
-            if (!cs) continue;
-            if (!cs->is_array()) bad(std::string("spec.") + list + " is not an array");
-            const bool counted = std::strcmp(list, "containers") == 0;         // gpu.go:40: spec.containers only
-            for (const Value &c : cs->items) {
-                if (!c.is_object()) bad("container is not an object");
-                const Value *res = child(&c, "resources");
-                int64_t v; int8_t s;
-                resource_list(child(res, "requests"), "resources.requests", false, v, s);
-                resource_list(child(res, "limits"), "resources.limits", counted, v, s);   // gpu.go:61-69: LIMITS
-                if (counted) { r.ctr_val.push_back(v); r.ctr_scale.push_back(s); }
-            }
-        }
-        if (!r.node_name.empty()) {
-            auto it = node_id.find(r.node_name);
-            if (it != node_id.end()) r.node = it->second;
-        }
-    }
+    std::vector<PodRec> pods;
+    for_each_item(podlist, podlen, "PodList", pod_doc, keep_core, pods,
+                  [&](const Value &item, PodRec &r) { extract_pod(item, r, node_id); });
+    const size_t P = pods.size();
+    trace.mark("pods");
 
     // ---- jobs (only when a `helm list` text is given) -------------------------------
     if (helm) {
@@ -331,9 +574,9 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
 
         std::vector<ObjRec> jobs, tfjobs;
         if (joblist) {
-            parse_doc(joblist, joblen, "JobList", job_doc);
-            if (const Value *it = items_of(job_doc, "JobList"))
-                for (const Value &j : it->items) {
+            parse_doc(joblist, joblen, "JobList", job_doc, keep_job, false);
+            if (const Value *it = items_of(job_doc.tree.root(), "JobList"))
+                for (const Value &j : it->children()) {
                     const Value *meta = child(&j, "metadata");
                     jobs.push_back({str_field(meta, "namespace"), child(meta, "labels"), child(&j, "status")});
                 }
@@ -342,9 +585,9 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
         // (trainer_tensorflow.go:188-202); without a TFJobList the trainer is disabled.
         const bool tf_enabled = tfjoblist != nullptr;
         if (tfjoblist && P > 0) {
-            parse_doc(tfjoblist, tflen, "TFJobList", tf_doc);
-            if (const Value *it = items_of(tf_doc, "TFJobList"))
-                for (const Value &j : it->items) {
+            parse_doc(tfjoblist, tflen, "TFJobList", tf_doc, keep_job, false);
+            if (const Value *it = items_of(tf_doc.tree.root(), "TFJobList"))
+                for (const Value &j : it->children()) {
                     const Value *meta = child(&j, "metadata");
                     tfjobs.push_back({str_field(meta, "namespace"), child(meta, "labels"), child(&j, "status")});
                 }
@@ -404,33 +647,29 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
         }
         // pod -> job: the release label names the job, the trainer's own predicate decides
         for (PodRec &r : pods) {
-            std::string rel;
-            if (!label(r.labels, "release", rel)) continue;
-            auto it = job_of_release.find(rel);
+            if (!(r.labels.has & kHasRelease)) continue;
+            auto it = job_of_release.find(r.labels.release);
             if (it == job_of_release.end()) continue;
             const JobMeta &jm = h->jobs[it->second];
             if (r.ns != jm.ns) continue;
             if (jm.trainer == "mpijob") {                                // trainer_mpi.go:315-332, 247-279
-                if (!label_is(r.labels, "app", "tf-horovod")) continue;
+                if (!r.labels.is(kHasApp, r.labels.app, "tf-horovod")) continue;
                 r.role = r.owner_is_job ? ARENA_ROLE_LATEST : ARENA_ROLE_COUNTS;
             } else if (jm.trainer == "standalonejob") {                  // trainer_standalone.go:198-221, 257-273
-                if (!label_is(r.labels, "app", "training")) continue;
+                if (!r.labels.is(kHasApp, r.labels.app, "training")) continue;
                 r.role = ARENA_ROLE_LATEST;
             } else {                                                     // trainer_tensorflow.go:394-418
-                if (!label_is(r.labels, "app", "tfjob") || !label_is(r.labels, "group_name", "kubeflow.org")) continue;
+                if (!r.labels.is(kHasApp, r.labels.app, "tfjob") || !r.labels.is(kHasGroup, r.labels.group_name, "kubeflow.org")) continue;
                 r.role = ARENA_ROLE_COUNTS;
             }
             r.job = it->second;
         }
     }
     const size_t J = h->jobs.size();
+    trace.mark("jobs");
 
     // ---- row order: stable grouping by node (or by job) --------------------------------
-    std::vector<uint32_t> order(P);
-    std::iota(order.begin(), order.end(), 0u);
-    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-        return group_by_job ? pods[a].job < pods[b].job : pods[a].node < pods[b].node;     // ARENA_NONE sorts last
-    });
+    const std::vector<uint32_t> order = group_rows(pods, group_by_job ? J : N, group_by_job);
     h->pod_order = order;
 
     size_t C = 0;
@@ -481,10 +720,11 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
     for (size_t p = 0; p < P; p++) {
         const PodRec &r = pods[p];
         if (r.job == ARENA_NONE || h->jobs[r.job].trainer != "tfjob") continue;
-        if (label_is(r.labels, "tf-replica-type", "worker") && label_is(r.labels, "tf-replica-index", "0"))
+        if (r.labels.is(kHasReplicaType, r.labels.replica_type, "worker") && r.labels.is(kHasReplicaIndex, r.labels.replica_index, "0"))
             h->jobs[r.job].tf_chief_row = row_of[p];
     }
 
+    trace.mark("columns");
     arena_snapshot_view &v = h->v;
     v.n_pods = P; v.n_containers = C; v.n_nodes = N; v.n_jobs = J;
     v.pod_node = pod_node; v.pod_phase = pod_phase; v.pod_ctr_begin = cb;
@@ -531,6 +771,10 @@ const char *arena_host_job_trainer(const arena_host_snapshot *h, uint32_t job)
 const char *arena_host_node_name(const arena_host_snapshot *h, uint32_t node)
 {
     return (h && node < h->node_names.size()) ? h->node_names[node].c_str() : "";
+}
+const char *arena_host_pod_name(const arena_host_snapshot *h, uint32_t row)
+{
+    return (h && row < h->pod_names.size()) ? h->pod_names[row].c_str() : "";
 }
 
 int arena_quantity_parse(const char *raw, size_t len, int64_t *value_out, int64_t *amount_val_out,

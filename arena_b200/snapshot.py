@@ -144,6 +144,9 @@ class HostSnapshot:
     def node_name(self, n: int) -> str:
         return lib().arena_host_node_name(self._h, n).decode()
 
+    def pod_name(self, row: int) -> str:
+        return lib().arena_host_pod_name(self._h, row).decode()
+
     # -- sharding ---------------------------------------------------------------
     def shard_plan(self, n_shards: int, by_job: bool = False):
         key_cut = np.zeros(n_shards + 1, np.uint64)

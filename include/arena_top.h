@@ -59,11 +59,13 @@ int  arena_load_json(const char *podlist_json, size_t podlist_len,
                      const char *helm_list_text, size_t helm_len,
                      int group_by_job, arena_host_snapshot **out);
 
-/* Row -> original PodList index ([P]); job id -> name / trainer type. */
+/* Row -> original PodList index ([P]); job id -> name / trainer type; node id and
+ * row -> metadata.name ("" for synthetic snapshots, which carry no names). */
 const uint32_t *arena_host_pod_order(const arena_host_snapshot *h);
 const char *arena_host_job_name(const arena_host_snapshot *h, uint32_t job);
 const char *arena_host_job_trainer(const arena_host_snapshot *h, uint32_t job);
 const char *arena_host_node_name(const arena_host_snapshot *h, uint32_t node);
+const char *arena_host_pod_name(const arena_host_snapshot *h, uint32_t row);
 
 /* Quantity.UnmarshalJSON + Value() of one raw JSON token (quotes included for
  * strings), on the host.  Returns ARENA_E_PARSE for what the reference rejects. */
