@@ -33,6 +33,14 @@ class SnapshotView(C.Structure):
     ]
 
 
+class LoadDeviceStats(C.Structure):
+    """struct arena_load_device_stats"""
+    _fields_ = [
+        ("n_items", C.c_uint64), ("flagged_item", C.c_uint64), ("flag_reason", C.c_uint32), ("fell_back", C.c_uint32),
+        ("ms_h2d", C.c_double), ("ms_structure", C.c_double), ("ms_items", C.c_double), ("ms_device", C.c_double),
+    ]
+
+
 class SynthParams(C.Structure):
     """struct arena_synth_params"""
     _fields_ = [
@@ -54,6 +62,8 @@ _SIGS = [
     ("arena_snapshot_upload", C.c_int, [C.POINTER(SnapshotView), C.POINTER(_VP)]),
     ("arena_snapshot_wrap_device", C.c_int, [C.POINTER(SnapshotView), C.POINTER(_VP)]),
     ("arena_snapshot_free", None, [_VP]),
+    ("arena_snapshot_counts", C.c_int, [_VP, C.POINTER(C.c_uint64)]),
+    ("arena_snapshot_download", C.c_int, [_VP, C.POINTER(SnapshotView)]),
     ("arena_top_node", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_host", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP]),
@@ -71,6 +81,12 @@ _SIGS = [
     ("arena_host_snapshot_view", C.c_int, [_VP, C.POINTER(SnapshotView)]),
     ("arena_load_json", C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
                                   C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_VP)]),
+    ("arena_pinned_alloc", C.c_int, [C.c_size_t, C.POINTER(_VP)]),
+    ("arena_pinned_free", None, [_VP]),
+    ("arena_load_json_device", C.c_int, [_VP, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(_VP), C.POINTER(_VP),
+                                         C.POINTER(LoadDeviceStats)]),
+    ("arena_scan_podlist_host", C.c_int, [C.c_char_p, C.c_size_t, _VP, C.c_uint64, C.POINTER(C.c_uint64), _VP, _VP, _VP,
+                                          _VP, _VP]),
     ("arena_host_pod_order", _VP, [_VP]),
     ("arena_host_job_name", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_host_job_trainer", C.c_char_p, [_VP, C.c_uint32]),

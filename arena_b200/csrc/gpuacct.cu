@@ -4,6 +4,7 @@
 #include "../../include/arena_gpuacct.h"
 #include "kernels.cuh"
 #include "host_snapshot.h"
+#include "gpuacct_internal.h"
 
 #include <atomic>
 #include <cstdarg>
@@ -116,6 +117,7 @@ void arena_acct_shutdown(void)
     cudaSetDevice(g_ctx.device);
     cudaStreamSynchronize(g_ctx.stream);
     if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
+    arena_internal::free_loader_workspace();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx = Context{};
 }
@@ -431,6 +433,73 @@ int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **ou
     cudaError_t e = cudaStreamSynchronize(g_ctx.stream);
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "wrap: %s", cudaGetErrorString(e)); }
     *out = s;
+    return ARENA_OK;
+}
+
+}  // extern "C"
+
+namespace arena_internal {
+
+int ready(cudaStream_t *stream, int *sm_count)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (stream) *stream = g_ctx.stream;
+    if (sm_count) *sm_count = g_ctx.sm_count;
+    return ARENA_OK;
+}
+
+void add_launches(unsigned long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int adopt_device_block(void *block, size_t block_bytes, const arena_snapshot_view &device_view, arena_snapshot **out)
+{
+    *out = nullptr;
+    int rc = check_ready();
+    if (!rc) rc = check_view(&device_view, true);
+    arena_snapshot *s = rc ? nullptr : new (std::nothrow) arena_snapshot();
+    if (!rc && !s) rc = fail(ARENA_E_NOMEM, "out of host memory");
+    if (rc) { cudaFree(block); return rc; }
+    s->v = device_view;
+    s->v.n_jobs = 0;
+    s->owns = true;
+    s->block = block;
+    s->block_bytes = block_bytes;
+    rc = alloc_common(s);
+    if (!rc) rc = probe_grouping(s);
+    if (rc) { arena_snapshot_free(s); return rc; }
+    *out = s;
+    return ARENA_OK;
+}
+
+}  // namespace arena_internal
+
+extern "C" {
+
+int arena_snapshot_counts(const arena_snapshot *s, uint64_t counts_out[4])
+{
+    if (!s || !counts_out) return fail(ARENA_E_INVALID, "snapshot or counts_out is NULL");
+    counts_out[0] = s->v.n_pods; counts_out[1] = s->v.n_containers;
+    counts_out[2] = s->v.n_nodes; counts_out[3] = s->v.n_jobs;
+    return ARENA_OK;
+}
+
+int arena_snapshot_download(const arena_snapshot *s, const arena_snapshot_view *o)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!s || !o) return fail(ARENA_E_INVALID, "snapshot or host_out is NULL");
+    const arena_snapshot_view &v = s->v;
+    const u64 P = v.n_pods, C = v.n_containers, N = v.n_nodes;
+    struct Col { const void *src; const void *dst; size_t bytes; };
+    const Col cols[] = {
+        {v.pod_node, o->pod_node, P * 4}, {v.pod_phase, o->pod_phase, P}, {v.pod_ctr_begin, o->pod_ctr_begin, (P + 1) * 4},
+        {v.ctr_val, o->ctr_val, C * 8}, {v.ctr_scale, o->ctr_scale, C}, {v.node_cap_val, o->node_cap_val, N * 8},
+        {v.node_cap_scale, o->node_cap_scale, N}, {v.pod_job, o->pod_job, P * 4}, {v.pod_role, o->pod_role, P},
+        {v.pod_created, o->pod_created, P * 8}};
+    for (const Col &c : cols)
+        if (c.src && c.dst && c.bytes)
+            CUDA_TRY(cudaMemcpyAsync(const_cast<void *>(c.dst), c.src, c.bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
+    CUDA_TRY(cudaStreamSynchronize(g_ctx.stream));
     return ARENA_OK;
 }
 

@@ -139,7 +139,10 @@ struct Parser {
         if (split_seen) { split_conflict = true; return false; }      // duplicate key: parse() starts over without splitting
         size_t end = 0;
         std::vector<Range> ranges;
-        if (!split_array(t, j, ranges, end)) return false;
+        if (opt->split_hook) {
+            if (!opt->split_hook(opt->split_user, j, &end) || end <= j + 1 || end > t.size() || t[end - 1] != ']') return false;
+            ranges.push_back({j, end});
+        } else if (!split_array(t, j, ranges, end)) return false;
         split_seen = true;
         *opt->split_out = std::move(ranges);
         if (opt->split_done) *opt->split_done = true;

@@ -94,6 +94,12 @@ struct ParseOptions {
     std::string_view split_key;
     std::vector<Range> *split_out = nullptr;
     bool *split_done = nullptr;
+    // Someone else (the GPU structural scan) already knows where containers end: when set,
+    // this is asked for the end of the array opening at `open` instead of scanning for it,
+    // and `split_out` receives ONE range, the array itself; its elements are the caller's
+    // business (it must validate them).
+    bool (*split_hook)(void *user, size_t open, size_t *end) = nullptr;
+    void *split_user = nullptr;
 };
 
 // Parses exactly one JSON document (surrounding whitespace allowed) into `out`

@@ -1,0 +1,721 @@
+// One PodList item -> the `top node` columns, as straight-line code that runs the
+// same on the host and on the device (one GPU thread per pod).
+//
+// This is the device half of the wire-format step: it replaces,
+// for the fields the accounting reads, the json-iterator decode of a v1.Pod
+// (/root/reference: cmd/arena/commands/pod_helper.go:15-43,
+// vendor/k8s.io/apimachinery/pkg/runtime/serializer/json/json.go:104-113, 171) and
+// Quantity.UnmarshalJSON (vendor/k8s.io/apimachinery/pkg/api/resource/quantity.go:648-667).
+//
+// Contract: the scanner VALIDATES the item's JSON and extracts
+//     spec.nodeName, status.phase, spec.containers[*].resources.limits[GPU key]
+// exactly as the host loader (loader.cc extract_pod) does, or it FLAGS the item.
+// A flag means "not handled here", never "invalid": the caller then runs the host
+// loader, which is the authority for every error message and every exotic but legal
+// spelling (escaped keys, duplicate keys, quantities with suffixes on a GPU key,
+// RFC 3339 times with offsets, more than kInlineCtrs containers ...).  So the only
+// thing this file must guarantee is: flag == 0  =>  the outputs equal the host's.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <type_traits>
+
+#if defined(__CUDACC__)
+#define ARENA_HD __host__ __device__
+#else
+#define ARENA_HD
+#endif
+
+namespace arena_scan {
+
+constexpr int kInlineCtrs = 8;        // containers per pod handled without the host
+constexpr int kMaxLevels = 40;        // nesting inside one item handled without the host
+constexpr uint32_t kNoNode = 0xFFFFFFFFu;
+
+// why an item was handed back to the host (diagnostics only; any non-zero value means the same)
+enum Flag : uint32_t {
+    kOk = 0,
+    kFlagSyntax = 1,          // not well-formed here: the host reports the exact error
+    kFlagShape = 2,           // a field has a type the host rejects or treats specially
+    kFlagEscapedKey = 3,      // a key with a backslash in a place where key names matter
+    kFlagDuplicateKey = 4,    // last-wins is left to the host
+    kFlagQuantity = 5,        // a quantity outside the plain grammar, or a GPU quantity that is not plain digits
+    kFlagTime = 6,            // creationTimestamp not in the API server's canonical form
+    kFlagTooDeep = 7,
+    kFlagTooManyContainers = 8,
+    kFlagEscapedValue = 9,    // nodeName / phase with a backslash
+    kFlagSeparator = 10,      // something other than one comma between two items
+    kFlagKeyHash = 11,        // a key with the length and hash of a known one but other bytes
+    kFlagTooManyFields = 12,  // more deferred checks than the per-item list holds
+};
+
+// ---- node name -> id: open addressing, exact (bytes are compared) ----------------------
+struct NodeSlot {
+    uint64_t hash;            // 0 = empty
+    uint32_t id;
+    uint32_t name_len;
+    uint64_t name_off;        // into NodeTable::names
+};
+
+struct NodeTable {
+    const NodeSlot *slots;
+    uint64_t mask;            // slot count - 1 (a power of two)
+    const unsigned char *names;
+};
+
+ARENA_HD inline uint64_t hash_bytes(const unsigned char *p, size_t n)
+{
+    uint64_t h = 0xcbf29ce484222325ull;                 // FNV-1a
+    for (size_t k = 0; k < n; k++) { h ^= p[k]; h *= 0x100000001b3ull; }
+    return h | 0x8000000000000000ull;                   // never 0
+}
+
+ARENA_HD inline uint32_t find_node(const NodeTable &nt, const unsigned char *p, size_t n)
+{
+    const uint64_t h = hash_bytes(p, n);
+    for (uint64_t idx = h & nt.mask;; idx = (idx + 1) & nt.mask) {
+        const NodeSlot s = nt.slots[idx];
+        if (s.hash == 0) return kNoNode;
+        if (s.hash == h && s.name_len == n) {
+            const unsigned char *q = nt.names + s.name_off;
+            size_t k = 0;
+            while (k < n && q[k] == p[k]) k++;
+            if (k == n) return s.id;
+        }
+    }
+}
+
+struct PodOut {
+    uint32_t flag;
+    uint32_t node;                    // node id or kNoNode
+    uint32_t n_ctrs;
+    uint8_t phase;                    // ARENA_PHASE_*
+    int64_t ctr_val[kInlineCtrs];     // column encoding with scale 0
+};
+
+namespace detail {
+
+enum Role : uint8_t {
+    R_SKIP_OBJ, R_SKIP_ARR, R_ITEM, R_META, R_LABELS, R_OWNERS, R_OWNER, R_SPEC, R_CTRS, R_CTR, R_RES, R_LIMITS,
+    R_QMAP, R_ICTRS, R_ICTR, R_IRES, R_STATUS, R_COUNT
+};
+
+ARENA_HD inline bool role_is_array(uint8_t r) { return r == R_SKIP_ARR || r == R_OWNERS || r == R_CTRS || r == R_ICTRS; }
+
+// key ids: bit positions in the per-role "seen" mask (0 = a key nobody looks at)
+enum Key : uint8_t {
+    K_OTHER = 0, K_METADATA, K_SPEC, K_STATUS,                                  // item
+    K_NAME, K_NAMESPACE, K_LABELS, K_CREATED, K_OWNERS,                         // metadata
+    K_L_RELEASE, K_L_APP, K_L_GROUP, K_L_RTYPE, K_L_RINDEX,                     // labels
+    K_KIND,                                                                     // ownerReference
+    K_NODENAME, K_CONTAINERS, K_INITCONTAINERS,                                 // spec
+    K_RESOURCES,                                                                // container
+    K_LIMITS, K_REQUESTS,                                                       // resources
+    K_GPU, K_GPU_DEPRECATED, K_QUANTITY,                                        // resource maps
+    K_PHASE, K_HOSTIP,                                                          // status
+    K_ELEMENT                                                                   // array element
+};
+
+ARENA_HD inline bool bytes_are(const unsigned char *p, size_t n, const char *lit)
+{
+    size_t k = 0;
+    for (; k < n; k++)
+        if (lit[k] == 0 || (unsigned char)lit[k] != p[k]) return false;
+    return lit[k] == 0;
+}
+
+// Keys are recognised by (length, FNV-1a of the bytes), both gathered while the lexer walks
+// the string, so the hot loop never goes back to memory; every recognised key is then
+// compared byte for byte (key_text) before its value is trusted.
+ARENA_HD constexpr uint32_t fnv32(const char *s)
+{
+    uint32_t h = 2166136261u;
+    for (int k = 0; s[k]; k++) h = (h ^ (uint8_t)s[k]) * 16777619u;
+    return h;
+}
+ARENA_HD constexpr uint32_t lit_len(const char *s)
+{
+    uint32_t n = 0;
+    while (s[n]) n++;
+    return n;
+}
+
+ARENA_HD inline const char *key_text(uint8_t key)
+{
+    switch (key) {
+    case K_METADATA: return "metadata";
+    case K_SPEC: return "spec";
+    case K_STATUS: return "status";
+    case K_NAME: return "name";
+    case K_NAMESPACE: return "namespace";
+    case K_LABELS: return "labels";
+    case K_CREATED: return "creationTimestamp";
+    case K_OWNERS: return "ownerReferences";
+    case K_L_RELEASE: return "release";
+    case K_L_APP: return "app";
+    case K_L_GROUP: return "group_name";
+    case K_L_RTYPE: return "tf-replica-type";
+    case K_L_RINDEX: return "tf-replica-index";
+    case K_KIND: return "kind";
+    case K_NODENAME: return "nodeName";
+    case K_CONTAINERS: return "containers";
+    case K_INITCONTAINERS: return "initContainers";
+    case K_RESOURCES: return "resources";
+    case K_LIMITS: return "limits";
+    case K_REQUESTS: return "requests";
+    case K_GPU: return "nvidia.com/gpu";                               // const.go:7
+    case K_GPU_DEPRECATED: return "alpha.kubernetes.io/nvidia-gpu";    // const.go:9
+    case K_PHASE: return "phase";
+    case K_HOSTIP: return "hostIP";
+    default: return "";
+    }
+}
+
+#define ARENA_KEY_IS(lit) \
+    (n == std::integral_constant<uint32_t, lit_len(lit)>::value && h == std::integral_constant<uint32_t, fnv32(lit)>::value)
+ARENA_HD inline uint8_t key_id_hashed(uint8_t role, uint32_t n, uint32_t h)
+{
+    switch (role) {
+    case R_ITEM:
+        if (ARENA_KEY_IS("metadata")) return K_METADATA;
+        if (ARENA_KEY_IS("spec")) return K_SPEC;
+        if (ARENA_KEY_IS("status")) return K_STATUS;
+        return K_OTHER;
+    case R_META:
+        if (ARENA_KEY_IS("name")) return K_NAME;
+        if (ARENA_KEY_IS("namespace")) return K_NAMESPACE;
+        if (ARENA_KEY_IS("labels")) return K_LABELS;
+        if (ARENA_KEY_IS("creationTimestamp")) return K_CREATED;
+        if (ARENA_KEY_IS("ownerReferences")) return K_OWNERS;
+        return K_OTHER;
+    case R_LABELS:
+        if (ARENA_KEY_IS("release")) return K_L_RELEASE;
+        if (ARENA_KEY_IS("app")) return K_L_APP;
+        if (ARENA_KEY_IS("group_name")) return K_L_GROUP;
+        if (ARENA_KEY_IS("tf-replica-type")) return K_L_RTYPE;
+        if (ARENA_KEY_IS("tf-replica-index")) return K_L_RINDEX;
+        return K_OTHER;
+    case R_OWNER:
+        return ARENA_KEY_IS("kind") ? K_KIND : K_OTHER;
+    case R_SPEC:
+        if (ARENA_KEY_IS("nodeName")) return K_NODENAME;
+        if (ARENA_KEY_IS("containers")) return K_CONTAINERS;
+        if (ARENA_KEY_IS("initContainers")) return K_INITCONTAINERS;
+        return K_OTHER;
+    case R_CTR:
+    case R_ICTR:
+        return ARENA_KEY_IS("resources") ? K_RESOURCES : K_OTHER;
+    case R_RES:
+    case R_IRES:
+        if (ARENA_KEY_IS("limits")) return K_LIMITS;
+        if (ARENA_KEY_IS("requests")) return K_REQUESTS;
+        return K_OTHER;
+    case R_LIMITS:
+        if (ARENA_KEY_IS("nvidia.com/gpu")) return K_GPU;
+        if (ARENA_KEY_IS("alpha.kubernetes.io/nvidia-gpu")) return K_GPU_DEPRECATED;
+        return K_QUANTITY;
+    case R_QMAP:
+        return K_QUANTITY;
+    case R_STATUS:
+        if (ARENA_KEY_IS("phase")) return K_PHASE;
+        if (ARENA_KEY_IS("hostIP")) return K_HOSTIP;
+        return K_OTHER;
+    default:
+        return K_OTHER;
+    }
+}
+#undef ARENA_KEY_IS
+
+ARENA_HD inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
+ARENA_HD inline bool is_ws(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+
+// A SUFFICIENT condition for ParseQuantity (quantity.go:159-390) to succeed:
+//   [+-]? digits+ ( '.' digits* )? ( "" | n u m k M G T P E | Ki Mi Gi Ti Pi Ei | [eE][+-]?digits{1,9} )
+ARENA_HD inline bool quantity_plain(const unsigned char *p, size_t n)
+{
+    if (n == 0 || n > 64) return false;
+    size_t i = 0;
+    if (p[0] == '+' || p[0] == '-') i++;
+    size_t d0 = i;
+    while (i < n && is_digit(p[i])) i++;
+    if (i == d0) return false;
+    if (i < n && p[i] == '.') {
+        i++;
+        while (i < n && is_digit(p[i])) i++;
+    }
+    const size_t left = n - i;
+    if (left == 0) return true;
+    const unsigned char a = p[i];
+    if (left == 1) return a == 'n' || a == 'u' || a == 'm' || a == 'k' || a == 'M' || a == 'G' || a == 'T' || a == 'P' || a == 'E';
+    if (left == 2 && p[i + 1] == 'i') return a == 'K' || a == 'M' || a == 'G' || a == 'T' || a == 'P' || a == 'E';
+    if (a != 'e' && a != 'E') return false;
+    size_t j = i + 1;
+    if (p[j] == '+' || p[j] == '-') j++;
+    const size_t e0 = j;
+    while (j < n && is_digit(p[j])) j++;
+    return j == n && j > e0 && j - e0 <= 9;
+}
+
+// The API server's creationTimestamp: "YYYY-MM-DDTHH:MM:SSZ" with the field ranges
+// time.Parse(RFC3339) checks first; everything else goes to the host.
+ARENA_HD inline bool time_canonical(const unsigned char *p, size_t n)
+{
+    if (n != 20) return false;
+    if (p[4] != '-' || p[7] != '-' || p[10] != 'T' || p[13] != ':' || p[16] != ':' || p[19] != 'Z') return false;
+    const int at[] = {0, 1, 2, 3, 5, 6, 8, 9, 11, 12, 14, 15, 17, 18};
+    for (int k : at)
+        if (!is_digit(p[k])) return false;
+    const int Y = (p[0] - '0') * 1000 + (p[1] - '0') * 100 + (p[2] - '0') * 10 + (p[3] - '0');
+    const int M = (p[5] - '0') * 10 + (p[6] - '0'), D = (p[8] - '0') * 10 + (p[9] - '0');
+    const int h = (p[11] - '0') * 10 + (p[12] - '0'), mi = (p[14] - '0') * 10 + (p[15] - '0');
+    const int s = (p[17] - '0') * 10 + (p[18] - '0');
+    if (M < 1 || M > 12 || D < 1 || h > 23 || mi > 59 || s > 59) return false;
+    const bool leap = (Y % 4 == 0 && Y % 100 != 0) || Y % 400 == 0;
+    const int dim = M == 2 ? (leap ? 29 : 28) : (M == 4 || M == 6 || M == 9 || M == 11) ? 30 : 31;
+    return D <= dim;                                       // Go rejects "day out of range": leave those to the host
+}
+
+ARENA_HD inline uint8_t phase_code(const unsigned char *p, size_t n)
+{
+    if (n == 0) return 0;                                  // ARENA_PHASE_EMPTY
+    if (bytes_are(p, n, "Pending")) return 1;
+    if (bytes_are(p, n, "Running")) return 2;
+    if (bytes_are(p, n, "Succeeded")) return 3;
+    if (bytes_are(p, n, "Failed")) return 4;
+    if (bytes_are(p, n, "Unknown")) return 5;
+    return 255;                                            // ARENA_PHASE_OTHER
+}
+
+// ---- the lexer: a table-driven automaton, one byte per step ---------------------------------
+// Every thread of a warp runs the SAME few instructions per byte (class lookup, transition
+// lookup), whatever token it is in; only token boundaries take a (short) divergent path.
+// Acceptance is that of json.cc's recursive parser.
+enum Class : uint8_t {
+    C_SPACE, C_WHITE, C_LCURB, C_RCURB, C_LSQRB, C_RSQRB, C_COLON, C_COMMA, C_QUOTE, C_BACKS, C_SLASH, C_PLUS, C_MINUS,
+    C_POINT, C_ZERO, C_DIGIT, C_B, C_F, C_N, C_R, C_T, C_U, C_HEXLET, C_E, C_ETC, C_CTRL, C_COUNT
+};
+
+enum LexState : uint8_t {
+    S_VAL, S_ARR0, S_OBJ0, S_KEY, S_COLON, S_AFTER, S_STR, S_ESC, S_U1, S_U2, S_U3, S_U4, S_MINUS, S_ZERO, S_INT,
+    S_FRAC0, S_FRAC, S_EXP0, S_EXPS, S_EXP, S_COUNT
+};
+
+enum Action : uint8_t {
+    A_NONE, A_ERR, A_OPEN, A_CLOSE, A_COMMA, A_KEY_BEGIN, A_STR_BEGIN, A_STR_END, A_NUM_BEGIN, A_NUM_END, A_LITERAL
+};
+
+struct LexTables {
+    uint8_t cls[256];
+    uint16_t next[S_COUNT * C_COUNT];          // action << 8 | next state
+};
+
+constexpr uint16_t lex_entry(uint8_t action, uint8_t state) { return (uint16_t)((uint16_t)action << 8 | state); }
+
+constexpr LexTables make_lex_tables()
+{
+    LexTables t{};
+    for (int c = 0; c < 256; c++) t.cls[c] = c < 0x20 ? C_CTRL : C_ETC;
+    t.cls[' '] = C_SPACE; t.cls['\t'] = C_WHITE; t.cls['\n'] = C_WHITE; t.cls['\r'] = C_WHITE;
+    t.cls['{'] = C_LCURB; t.cls['}'] = C_RCURB; t.cls['['] = C_LSQRB; t.cls[']'] = C_RSQRB;
+    t.cls[':'] = C_COLON; t.cls[','] = C_COMMA; t.cls['"'] = C_QUOTE; t.cls['\\'] = C_BACKS; t.cls['/'] = C_SLASH;
+    t.cls['+'] = C_PLUS; t.cls['-'] = C_MINUS; t.cls['.'] = C_POINT; t.cls['0'] = C_ZERO;
+    for (int c = '1'; c <= '9'; c++) t.cls[c] = C_DIGIT;
+    t.cls['b'] = C_B; t.cls['f'] = C_F; t.cls['n'] = C_N; t.cls['r'] = C_R; t.cls['t'] = C_T; t.cls['u'] = C_U;
+    t.cls['a'] = C_HEXLET; t.cls['c'] = C_HEXLET; t.cls['d'] = C_HEXLET;
+    t.cls['A'] = C_HEXLET; t.cls['B'] = C_HEXLET; t.cls['C'] = C_HEXLET; t.cls['D'] = C_HEXLET; t.cls['F'] = C_HEXLET;
+    t.cls['e'] = C_E; t.cls['E'] = C_E;
+
+    for (int k = 0; k < S_COUNT * C_COUNT; k++) t.next[k] = lex_entry(A_ERR, S_AFTER);
+    auto at = [&](int st, int c) -> uint16_t & { return t.next[st * C_COUNT + c]; };
+    // between tokens
+    const int gaps[] = {S_VAL, S_ARR0, S_OBJ0, S_KEY, S_COLON, S_AFTER};
+    for (int st : gaps) { at(st, C_SPACE) = lex_entry(A_NONE, (uint8_t)st); at(st, C_WHITE) = lex_entry(A_NONE, (uint8_t)st); }
+    const int value_starts[] = {S_VAL, S_ARR0};
+    for (int st : value_starts) {
+        at(st, C_LCURB) = lex_entry(A_OPEN, S_OBJ0);
+        at(st, C_LSQRB) = lex_entry(A_OPEN, S_ARR0);
+        at(st, C_QUOTE) = lex_entry(A_STR_BEGIN, S_STR);
+        at(st, C_MINUS) = lex_entry(A_NUM_BEGIN, S_MINUS);
+        at(st, C_ZERO) = lex_entry(A_NUM_BEGIN, S_ZERO);
+        at(st, C_DIGIT) = lex_entry(A_NUM_BEGIN, S_INT);
+        at(st, C_T) = lex_entry(A_LITERAL, S_AFTER);
+        at(st, C_F) = lex_entry(A_LITERAL, S_AFTER);
+        at(st, C_N) = lex_entry(A_LITERAL, S_AFTER);
+    }
+    at(S_ARR0, C_RSQRB) = lex_entry(A_CLOSE, S_AFTER);
+    at(S_OBJ0, C_RCURB) = lex_entry(A_CLOSE, S_AFTER);
+    at(S_OBJ0, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_STR);
+    at(S_KEY, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_STR);
+    at(S_COLON, C_COLON) = lex_entry(A_NONE, S_VAL);
+    at(S_AFTER, C_COMMA) = lex_entry(A_COMMA, S_VAL);
+    at(S_AFTER, C_RCURB) = lex_entry(A_CLOSE, S_AFTER);
+    at(S_AFTER, C_RSQRB) = lex_entry(A_CLOSE, S_AFTER);
+    // strings
+    for (int c = 0; c < C_COUNT; c++) at(S_STR, c) = lex_entry(A_NONE, S_STR);
+    at(S_STR, C_WHITE) = lex_entry(A_ERR, S_AFTER);                    // \t \n \r are control characters
+    at(S_STR, C_CTRL) = lex_entry(A_ERR, S_AFTER);
+    at(S_STR, C_QUOTE) = lex_entry(A_STR_END, S_AFTER);
+    at(S_STR, C_BACKS) = lex_entry(A_NONE, S_ESC);
+    const int escapes[] = {C_QUOTE, C_BACKS, C_SLASH, C_B, C_F, C_N, C_R, C_T};
+    for (int c : escapes) at(S_ESC, c) = lex_entry(A_NONE, S_STR);
+    at(S_ESC, C_U) = lex_entry(A_NONE, S_U1);
+    const int hex[] = {C_ZERO, C_DIGIT, C_B, C_F, C_HEXLET, C_E};
+    for (int c : hex) {
+        at(S_U1, c) = lex_entry(A_NONE, S_U2);
+        at(S_U2, c) = lex_entry(A_NONE, S_U3);
+        at(S_U3, c) = lex_entry(A_NONE, S_U4);
+        at(S_U4, c) = lex_entry(A_NONE, S_STR);
+    }
+    // numbers: -? (0 | [1-9][0-9]*) (\.[0-9]+)? ([eE][+-]?[0-9]+)?
+    at(S_MINUS, C_ZERO) = lex_entry(A_NONE, S_ZERO);
+    at(S_MINUS, C_DIGIT) = lex_entry(A_NONE, S_INT);
+    at(S_INT, C_ZERO) = lex_entry(A_NONE, S_INT);
+    at(S_INT, C_DIGIT) = lex_entry(A_NONE, S_INT);
+    const int int_ends[] = {S_ZERO, S_INT};
+    for (int st : int_ends) { at(st, C_POINT) = lex_entry(A_NONE, S_FRAC0); at(st, C_E) = lex_entry(A_NONE, S_EXP0); }
+    at(S_FRAC0, C_ZERO) = lex_entry(A_NONE, S_FRAC);
+    at(S_FRAC0, C_DIGIT) = lex_entry(A_NONE, S_FRAC);
+    at(S_FRAC, C_ZERO) = lex_entry(A_NONE, S_FRAC);
+    at(S_FRAC, C_DIGIT) = lex_entry(A_NONE, S_FRAC);
+    at(S_FRAC, C_E) = lex_entry(A_NONE, S_EXP0);
+    at(S_EXP0, C_PLUS) = lex_entry(A_NONE, S_EXPS);
+    at(S_EXP0, C_MINUS) = lex_entry(A_NONE, S_EXPS);
+    const int exp_digits[] = {S_EXP0, S_EXPS, S_EXP};
+    for (int st : exp_digits) { at(st, C_ZERO) = lex_entry(A_NONE, S_EXP); at(st, C_DIGIT) = lex_entry(A_NONE, S_EXP); }
+    // a number ends at the first byte that can follow a value; that byte is then handled as in S_AFTER
+    const int num_ends[] = {S_ZERO, S_INT, S_FRAC, S_EXP};
+    const int followers[] = {C_SPACE, C_WHITE, C_COMMA, C_RCURB, C_RSQRB};
+    for (int st : num_ends)
+        for (int c : followers) at(st, c) = lex_entry(A_NUM_END, S_AFTER);
+    return t;
+}
+
+}  // namespace detail
+
+// The tables as data.  The scanner indexes ONE fused table, [state][byte] -> action << 8 | next
+// state (10 KB: json_device.cu builds it in shared memory from kLexTables, the host keeps a
+// static copy).
+static constexpr detail::LexTables kLexTables = detail::make_lex_tables();
+constexpr int kFusedEntries = detail::S_COUNT * 256;
+
+ARENA_HD inline uint16_t fused_entry(const detail::LexTables &lt, int k)
+{
+    return lt.next[(k >> 8) * detail::C_COUNT + lt.cls[k & 255]];
+}
+
+// Scans the item in t[begin, end) (which must be exactly one JSON value).  See the contract
+// at the top.  `fused` is the [state][byte] table; on the device `t` must be 16-byte aligned and
+// readable in whole 16-byte words up to 16 bytes past `end` (the device buffer is padded).
+//
+// The walk itself never re-reads the text: keys are recognised by length + hash, and whatever
+// needs the bytes of a token (confirming a recognised key, checking a quantity or a timestamp,
+// decoding the phase, the GPU digits, the node name) is put on a short per-item list and
+// done after the walk, where the lanes of a warp work through their lists side by side.
+constexpr int kMaxTodo = 96;
+
+ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t end, const NodeTable &nodes,
+                                   const uint16_t *fused, PodOut &out)
+{
+    using namespace detail;
+    enum What : uint8_t { W_KEY, W_QUANTITY, W_GPU, W_TIME, W_PHASE };
+    struct Todo {
+        uint32_t pos;                    // relative to `begin`
+        uint16_t len;
+        uint8_t what, arg;               // W_KEY: key id; W_GPU: index into gpu_slot[]
+    };
+    Todo todo[kMaxTodo];
+    int n_todo = 0;
+    uint8_t stack[kMaxLevels];           // role of every open container
+    uint32_t seen[kMaxLevels];           // key ids already met in the object at that level
+    stack[0] = R_SKIP_ARR;
+    seen[0] = 0;
+    int depth = 0;
+    uint32_t flag = kOk;
+
+    // GPU quantities wait on the list; a container points at the one that counts for it
+    constexpr int16_t kAbsent = -1, kNull = -2;                         // no GPU key / "key": null => 0
+    int16_t ctr_ref[kInlineCtrs];
+    int64_t gpu_value[2 * kInlineCtrs + 2];                              // evaluated W_GPU entries
+    int n_gpu = 0;
+    int16_t cur_ref = kAbsent, gpu_ref = kAbsent, dep_ref = kAbsent;
+    bool gpu_present = false, dep_present = false;
+
+    size_t node_off = 0, node_len = 0;
+    int phase_todo = -1;                 // W_PHASE entry of the status that counts, or -1 (=> "")
+    uint32_t n_ctrs = 0;
+
+    uint8_t key = K_ELEMENT;             // key id of the value being read, in its parent
+    size_t tok = 0;                      // start of the current string body / number
+    bool is_key = false, escaped = false, done = false;
+    uint8_t st = S_VAL;
+    uint32_t hash = 0;                   // FNV-1a of the bytes since `tok`
+
+    auto defer = [&](uint8_t what, uint8_t arg, size_t body, size_t len) -> int {
+        if (n_todo >= kMaxTodo || len > 0xFFFFu) { flag = kFlagTooManyFields; return -1; }
+        todo[n_todo] = Todo{(uint32_t)(body - begin), (uint16_t)len, what, arg};
+        return n_todo++;
+    };
+
+    // one finished scalar in context (parent role, key): the host loader's field rules
+    auto scalar = [&](bool is_string, bool is_number, bool is_null, size_t body, size_t len) {
+        const uint8_t parent = depth ? stack[depth - 1] : (uint8_t)R_SKIP_ARR;
+        if (depth == 0) { flag = kFlagShape; return; }                 // "PodList item is not an object"
+        switch (key) {
+        case K_OTHER: break;
+        case K_ELEMENT:
+            if (parent == R_CTRS || parent == R_ICTRS) flag = kFlagShape;          // "container is not an object"
+            else if (parent == R_OWNERS && !is_null) flag = kFlagShape;
+            break;
+        case K_METADATA: case K_LABELS: case K_OWNERS: case K_INITCONTAINERS: case K_REQUESTS:
+            if (!is_null) flag = kFlagShape;
+            break;
+        case K_SPEC: if (!is_null) flag = kFlagShape; node_len = 0; n_ctrs = 0; break;
+        case K_STATUS: if (!is_null) flag = kFlagShape; phase_todo = -1; break;
+        case K_CONTAINERS: if (!is_null) flag = kFlagShape; n_ctrs = 0; break;
+        case K_RESOURCES: if (!is_null) flag = kFlagShape; cur_ref = kAbsent; break;
+        case K_LIMITS: if (!is_null) flag = kFlagShape; cur_ref = kAbsent; break;
+        case K_NAME: case K_NAMESPACE: case K_HOSTIP: case K_KIND:
+        case K_L_RELEASE: case K_L_APP: case K_L_GROUP: case K_L_RTYPE: case K_L_RINDEX:
+            if (!is_string && !is_null) flag = kFlagShape;
+            break;
+        case K_CREATED:
+            if (is_null) break;
+            if (!is_string) flag = kFlagShape;
+            else if (escaped) flag = kFlagTime;
+            else defer(W_TIME, 0, body, len);
+            break;
+        case K_NODENAME:
+            node_len = 0;
+            if (is_null) break;
+            if (!is_string) flag = kFlagShape;
+            else if (escaped) flag = kFlagEscapedValue;
+            else { node_off = body; node_len = len; }
+            break;
+        case K_PHASE:
+            phase_todo = -1;
+            if (is_null) break;
+            if (!is_string) flag = kFlagShape;
+            else if (escaped) flag = kFlagEscapedValue;
+            else phase_todo = defer(W_PHASE, 0, body, len);
+            break;
+        case K_QUANTITY:
+            // Quantity.UnmarshalJSON: null, or the raw token with its quotes dropped
+            if (is_null) break;
+            if (!(is_string || is_number)) flag = kFlagQuantity;
+            else defer(W_QUANTITY, 0, body, len);
+            break;
+        case K_GPU: case K_GPU_DEPRECATED: {
+            int16_t ref = kNull;
+            if (!is_null) {
+                if (!(is_string || is_number) || n_gpu >= 2 * kInlineCtrs + 2) { flag = kFlagQuantity; break; }
+                if (defer(W_GPU, (uint8_t)n_gpu, body, len) < 0) break;
+                ref = (int16_t)n_gpu++;
+            }
+            if (key == K_GPU) { gpu_present = true; gpu_ref = ref; }
+            else { dep_present = true; dep_ref = ref; }
+            break;
+        }
+        default: break;
+        }
+    };
+
+    size_t done_at = end;
+    unsigned skip = 0;                   // bytes of a literal already checked
+    // one byte
+    auto step = [&](const unsigned char c, const size_t i) {
+        if (skip) { skip--; return; }
+        uint16_t e = fused[st * 256 + c];
+        uint8_t act = (uint8_t)(e >> 8);
+        uint8_t ns = (uint8_t)e;
+        if (ns == S_ESC) escaped = true;
+        if (act == A_NONE) { hash = (hash ^ c) * 16777619u; st = ns; return; }
+
+        // ---- token boundary ---------------------------------------------------------------
+        if (act == A_NUM_END) {
+            scalar(false, true, false, tok, i - tok);
+            e = fused[S_AFTER * 256 + c];                              // the same byte, as the follower of a value
+            act = (uint8_t)(e >> 8);
+            ns = (uint8_t)e;
+        }
+        switch (act) {
+        case A_NONE: break;
+        case A_OPEN: {
+            const bool obj = c == '{';
+            uint8_t role = obj ? R_SKIP_OBJ : R_SKIP_ARR;
+            const uint8_t parent = depth ? stack[depth - 1] : (uint8_t)R_SKIP_ARR;
+            if (depth == 0) {
+                if (!obj) flag = kFlagShape;                           // "PodList item is not an object"
+                role = R_ITEM;
+            } else if (obj) {
+                switch (key) {
+                case K_METADATA: role = R_META; break;
+                case K_SPEC: role = R_SPEC; node_len = 0; n_ctrs = 0; break;
+                case K_STATUS: role = R_STATUS; phase_todo = -1; break;
+                case K_LABELS: role = R_LABELS; break;
+                case K_RESOURCES: role = parent == R_CTR ? R_RES : R_IRES; cur_ref = kAbsent; break;
+                case K_LIMITS:
+                    if (parent == R_RES) { role = R_LIMITS; cur_ref = kAbsent; gpu_present = dep_present = false; }
+                    else role = R_QMAP;
+                    break;
+                case K_REQUESTS: role = R_QMAP; break;
+                case K_ELEMENT:
+                    if (parent == R_CTRS) { role = R_CTR; cur_ref = kAbsent; }
+                    else if (parent == R_ICTRS) role = R_ICTR;
+                    else if (parent == R_OWNERS) role = R_OWNER;
+                    break;
+                case K_OTHER: break;
+                default: flag = kFlagShape; break;                     // an object where the host wants a scalar or a list
+                }
+            } else {
+                switch (key) {
+                case K_OWNERS: role = R_OWNERS; break;
+                case K_CONTAINERS: role = R_CTRS; n_ctrs = 0; break;
+                case K_INITCONTAINERS: role = R_ICTRS; break;
+                case K_ELEMENT:
+                    if (parent == R_CTRS || parent == R_ICTRS || parent == R_OWNERS) flag = kFlagShape;
+                    break;
+                case K_OTHER: break;
+                default: flag = kFlagShape; break;                     // a list where the host wants an object or a scalar
+                }
+            }
+            if (depth >= kMaxLevels) { flag = kFlagTooDeep; break; }
+            stack[depth] = role;
+            seen[depth] = 0;
+            depth++;
+            key = K_ELEMENT;                                           // (arrays; objects set it at every key)
+            break;
+        }
+        case A_CLOSE: {
+            if (depth == 0) { flag = kFlagSyntax; break; }
+            const uint8_t role = stack[depth - 1];
+            if (role_is_array(role) != (c == ']')) { flag = kFlagSyntax; break; }
+            if (role == R_LIMITS) cur_ref = gpu_present ? gpu_ref : dep_present ? dep_ref : kAbsent;   // gpu.go:61-79: key presence
+            else if (role == R_CTR) {
+                if (n_ctrs < (uint32_t)kInlineCtrs) ctr_ref[n_ctrs] = cur_ref;
+                else flag = kFlagTooManyContainers;
+                n_ctrs++;
+            }
+            depth--;
+            if (depth == 0) { done = true; done_at = i; }
+            break;
+        }
+        case A_COMMA:
+            if (depth == 0) { flag = kFlagSyntax; break; }
+            if (role_is_array(stack[depth - 1])) { ns = S_VAL; key = K_ELEMENT; }
+            else ns = S_KEY;
+            break;
+        case A_KEY_BEGIN: tok = i + 1; is_key = true; escaped = false; hash = 2166136261u; break;
+        case A_STR_BEGIN: tok = i + 1; is_key = false; escaped = false; break;
+        case A_STR_END:
+            if (is_key) {
+                const uint8_t role = stack[depth - 1];
+                if (role == R_SKIP_OBJ) key = K_OTHER;
+                else {
+                    if (escaped) flag = kFlagEscapedKey;
+                    key = key_id_hashed(role, (uint32_t)(i - tok), hash);
+                    if (key != K_OTHER && key != K_QUANTITY) {
+                        const uint32_t bit = 1u << key;
+                        if (seen[depth - 1] & bit) flag = kFlagDuplicateKey;
+                        seen[depth - 1] |= bit;
+                        defer(W_KEY, key, tok, i - tok);               // confirmed byte for byte after the walk
+                    }
+                }
+                ns = S_COLON;
+            } else {
+                scalar(true, false, false, tok, i - tok);
+                ns = S_AFTER;
+            }
+            break;
+        case A_NUM_BEGIN: tok = i; break;
+        case A_LITERAL: {
+            const char *w = c == 't' ? "true" : c == 'f' ? "false" : "null";
+            const size_t n = c == 'f' ? 5 : 4;
+            bool ok = end - i >= n;
+            for (size_t k = 1; ok && k < n; k++) ok = t[i + k] == (unsigned char)w[k];
+            if (!ok) { flag = kFlagSyntax; break; }
+            scalar(false, false, c == 'n', i, n);
+            skip = (unsigned)n - 1;
+            break;
+        }
+        default: flag = kFlagSyntax; break;                            // A_ERR
+        }
+        st = ns;
+    };
+#if defined(__CUDA_ARCH__)
+    // Lock step: every lane of the warp consumes one 16-byte word per outer iteration (lanes
+    // whose item starts inside the word idle through the first bytes), and the next word is
+    // requested before the current one is processed, so the load latency overlaps the work.
+    size_t base = begin & ~(size_t)15;
+    uint4 cur = *reinterpret_cast<const uint4 *>(t + base);
+    for (; base < end && !flag && !done; base += 16) {
+        const uint4 nxt = *reinterpret_cast<const uint4 *>(t + base + 16);
+        const uint64_t lo = (uint64_t)cur.x | ((uint64_t)cur.y << 32), hi = (uint64_t)cur.z | ((uint64_t)cur.w << 32);
+        for (int k = 0; k < 16; k++) {
+            const size_t i = base + k;
+            const unsigned char c = (unsigned char)((k < 8 ? lo : hi) >> ((k & 7) * 8));
+            if (i >= begin && i < end && !flag && !done) step(c, i);
+        }
+        cur = nxt;
+    }
+#else
+    for (size_t i = begin; i < end && !flag && !done; i++) step(t[i], i);
+#endif
+    if (!flag && !done) flag = kFlagSyntax;                            // ran out of bytes inside the item
+    if (!flag)
+        for (size_t i = done_at + 1; i < end; i++)
+            if (!is_ws(t[i])) { flag = kFlagSyntax; break; }
+
+    // ---- the deferred checks: the only place that goes back to the text ---------------------
+    uint8_t phase = 0;
+    for (int k = 0; k < n_todo && !flag; k++) {
+        const Todo d = todo[k];
+        const unsigned char *p = t + begin + d.pos;
+        switch (d.what) {
+        case W_KEY:
+            if (!bytes_are(p, d.len, key_text(d.arg))) flag = kFlagKeyHash;
+            break;
+        case W_QUANTITY:
+            if (!quantity_plain(p, d.len)) flag = kFlagQuantity;
+            break;
+        case W_GPU: {
+            // plain digits only: every other spelling of a GPU count is the host's business
+            int64_t v = 0;
+            bool digits = d.len >= 1 && d.len <= 15;
+            for (uint32_t q = 0; digits && q < d.len; q++) {
+                if (!is_digit(p[q])) digits = false;
+                else v = v * 10 + (p[q] - '0');
+            }
+            if (!digits) flag = kFlagQuantity;
+            gpu_value[d.arg] = v;
+            break;
+        }
+        case W_TIME:
+            if (!time_canonical(p, d.len)) flag = kFlagTime;
+            break;
+        default:                                                       // W_PHASE
+            if (k == phase_todo) phase = phase_code(p, d.len);
+            break;
+        }
+    }
+    if (!flag)
+        for (uint32_t k = 0; k < n_ctrs && k < (uint32_t)kInlineCtrs; k++)
+            out.ctr_val[k] = ctr_ref[k] >= 0 ? gpu_value[ctr_ref[k]] : 0;
+    out.flag = flag;
+    out.phase = phase;
+    out.n_ctrs = n_ctrs;
+    out.node = (!flag && node_len) ? find_node(nodes, t + node_off, node_len) : kNoNode;     // loader.cc: "" joins nothing
+}
+
+// What must sit between two items (or between '[' and the first one): whitespace and,
+// unless `first`, exactly one comma.
+ARENA_HD inline bool gap_ok(const unsigned char *t, size_t from, size_t to, bool first)
+{
+    int commas = 0;
+    for (size_t k = from; k < to; k++) {
+        if (t[k] == ',') commas++;
+        else if (!detail::is_ws(t[k])) return false;
+    }
+    return commas == (first ? 0 : 1);
+}
+
+}  // namespace arena_scan

@@ -13,7 +13,7 @@ from typing import Dict, Optional
 import numpy as np
 
 from . import _lib
-from ._lib import ArenaError, SnapshotView, SynthParams, check, lib
+from ._lib import ArenaError, LoadDeviceStats, SnapshotView, SynthParams, check, lib
 
 _COLS = [
     # name, dtype, length as a function of the view
@@ -165,11 +165,52 @@ class HostSnapshot:
         s.pod_lo, s.pod_hi = int(pod_cut[i]), int(pod_cut[i + 1])
         return s
 
+    def scan_podlist(self, podlist: bytes, capacity: int):
+        """arena_scan_podlist_host: the DEVICE loader's per-item scanner run on the
+        host against this (NodeList) snapshot.  Returns numpy arrays."""
+        n = C.c_uint64()
+        node = np.zeros(capacity, np.uint32)
+        phase = np.zeros(capacity, np.uint8)
+        nctr = np.zeros(capacity, np.uint32)
+        vals = np.zeros((capacity, 8), np.int64)
+        flag = np.zeros(capacity, np.uint8)
+        check(lib().arena_scan_podlist_host(podlist, len(podlist), self._h, capacity, C.byref(n), node.ctypes.data,
+                                            phase.ctypes.data, nctr.ctypes.data, vals.ctypes.data, flag.ctypes.data))
+        k = int(n.value)
+        return {"n": k, "node": node[:k], "phase": phase[:k], "n_ctrs": nctr[:k], "ctr_val": vals[:k], "flag": flag[:k]}
+
     def close(self) -> None:
         if self._h:
             lib().arena_host_snapshot_free(self._h)
             self._h = None
         self.cols = {}
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PinnedBuffer:
+    """arena_pinned_alloc: page-locked host bytes (read a PodList into one of these and the
+    copy to the device runs at PCIe speed)."""
+
+    def __init__(self, nbytes: int):
+        p = C.c_void_p()
+        check(lib().arena_pinned_alloc(int(nbytes), C.byref(p)))
+        self.ptr, self.capacity, self.nbytes = p.value, int(nbytes), 0
+
+    def fill(self, data: bytes) -> "PinnedBuffer":
+        assert len(data) <= self.capacity
+        C.memmove(self.ptr, data, len(data))
+        self.nbytes = len(data)
+        return self
+
+    def close(self) -> None:
+        if self.ptr:
+            lib().arena_pinned_free(self.ptr)
+            self.ptr = None
 
     def __del__(self):
         try:
@@ -212,6 +253,40 @@ class DeviceSnapshot:
         h = C.c_void_p()
         check(lib().arena_snapshot_wrap_device(C.byref(v), C.byref(h)))
         return cls(h.value, None, keep={"tensors": tensors, "view": v})
+
+    @classmethod
+    def from_json_device(cls, podlist, nodelist: bytes):
+        """arena_load_json_device: the PodList (bytes or a PinnedBuffer) is parsed on the
+        GPU.  Returns (DeviceSnapshot, stats dict); .host is the NodeList's host snapshot
+        (zero pods unless the host loader had to take over)."""
+        nodes, dev, st = C.c_void_p(), C.c_void_p(), LoadDeviceStats()
+        if isinstance(podlist, PinnedBuffer):
+            ptr, n = C.c_void_p(podlist.ptr), podlist.nbytes
+        else:
+            ptr, n = podlist, len(podlist)
+        check(lib().arena_load_json_device(ptr, n, nodelist, len(nodelist), C.byref(nodes), C.byref(dev), C.byref(st)))
+        host = HostSnapshot.from_handle(nodes.value)
+        counts = (C.c_uint64 * 4)()
+        check(lib().arena_snapshot_counts(dev, counts))
+        v = SnapshotView()
+        v.n_pods, v.n_containers, v.n_nodes, v.n_jobs = counts[0], counts[1], counts[2], counts[3]
+        out = cls(dev.value, None, keep={"view": v})
+        out.host = host
+        stats = {k: getattr(st, k) for k, _ in LoadDeviceStats._fields_}
+        return out, stats
+
+    def download(self) -> dict:
+        """Device columns copied back to numpy arrays (tests / inspection)."""
+        P, Cn, N = self.n_pods, self.n_containers, self.n_nodes
+        cols = {"pod_node": np.zeros(P, np.uint32), "pod_phase": np.zeros(P, np.uint8),
+                "pod_ctr_begin": np.zeros(P + 1, np.uint32), "ctr_val": np.zeros(Cn, np.int64),
+                "ctr_scale": np.zeros(Cn, np.int8), "node_cap_val": np.zeros(N, np.int64),
+                "node_cap_scale": np.zeros(N, np.int8)}
+        v = SnapshotView()
+        for k, a in cols.items():
+            setattr(v, k, a.ctypes.data)
+        check(lib().arena_snapshot_download(self._h, C.byref(v)))
+        return cols
 
     @property
     def handle(self) -> int:

@@ -106,6 +106,12 @@ int  arena_snapshot_upload(const arena_snapshot_view *host, arena_snapshot **out
  * is copied and the caller keeps ownership of the columns. */
 int  arena_snapshot_wrap_device(const arena_snapshot_view *dev, arena_snapshot **out);
 void arena_snapshot_free(arena_snapshot *s);
+/* counts_out = { n_pods, n_containers, n_nodes, n_jobs } of a device snapshot. */
+int  arena_snapshot_counts(const arena_snapshot *s, uint64_t counts_out[4]);
+/* Copies the device columns back into the HOST buffers `host_out` points to (sized from
+ * arena_snapshot_counts; NULL pointers are skipped).  For inspection and tests: no
+ * reference counterpart. */
+int  arena_snapshot_download(const arena_snapshot *s, const arena_snapshot_view *host_out);
 
 /*
  * `arena top node`: NodeDescriber.getAllNodeInfos + caculateNodeGPU + the

@@ -59,6 +59,63 @@ int  arena_load_json(const char *podlist_json, size_t podlist_len,
                      const char *helm_list_text, size_t helm_len,
                      int group_by_job, arena_host_snapshot **out);
 
+/*
+ * The same wire-format step with the PodList parsed ON THE GPU (`top node` columns only).
+ * The document is copied to the device; a structural scan there (quote / bracket bitmasks,
+ * 64 bytes per thread, prefix-composed across the grid) finds every element of .items, and
+ * one thread per pod validates its item and extracts spec.nodeName (joined to the NodeList
+ * by an exact hash lookup), status.phase and the GPU limit of every container.  Replaces the
+ * same reference code as arena_load_json (pod_helper.go:15-43, json.go:171,
+ * quantity.go:648-667) for the fields A1 of SURVEY.md section 8 names.
+ *
+ *   nodes_out      host snapshot of the NodeList (names, addresses, capacities: what the
+ *                  printers need); it has ZERO pods unless the host loader had to take over
+ *   snapshot_out   device snapshot, rows in PodList order (the accounting kernels are exact
+ *                  for any order and pick the ungrouped variant when it is faster)
+ *
+ * Anything a pod item contains that the device scanner does not decide itself -- escaped or
+ * duplicate keys, a GPU quantity that is not plain digits, a timestamp that is not in the API
+ * server's canonical form, more than 8 containers, any malformed text -- makes the whole
+ * document go through arena_load_json + arena_snapshot_upload instead: the columns, the
+ * results and the error messages are those of the host loader either way, and
+ * stats->fell_back says which path ran.  Needs arena_acct_init(); there is no CPU stand-in
+ * for the device (ARENA_E_NOT_INIT / ARENA_E_CUDA).  PodLists of 4 GiB and more take the
+ * host path.
+ */
+typedef struct arena_load_device_stats {
+    uint64_t n_items;         /* pods found by the device scan */
+    uint64_t flagged_item;    /* first item the device handed back (when fell_back) */
+    uint32_t flag_reason;     /* arena_scan::Flag of that item (diagnostic) */
+    uint32_t fell_back;       /* 1 = the host loader produced the snapshot */
+    /* host clock since the call started, at the points where the host waits for the device */
+    double   ms_h2d;          /* document copied to the device */
+    double   ms_structure;    /* + structural scan (3 kernels) */
+    double   ms_items;        /* + envelope on the host, item ranges, one thread per pod, CSR offsets */
+    double   ms_device;       /* + final columns: the whole device path */
+} arena_load_device_stats;
+
+/* Page-locked host memory for documents: reading the API server's response straight into
+ * such a buffer lets the copy to the device run at full PCIe speed (a pageable buffer is
+ * staged by the driver at roughly a third of it). */
+int  arena_pinned_alloc(size_t bytes, void **out);
+void arena_pinned_free(void *p);
+
+int  arena_load_json_device(const char *podlist_json, size_t podlist_len,
+                            const char *nodelist_json, size_t nodelist_len,
+                            arena_host_snapshot **nodes_out, arena_snapshot **snapshot_out,
+                            arena_load_device_stats *stats /* may be NULL */);
+
+/*
+ * Diagnostic: the per-item scanner of arena_load_json_device (csrc/pod_scan.cuh, the same
+ * source compiled for the host) over every element of .items, in PodList order.  `nodes`
+ * is a snapshot loaded from the NodeList.  Arrays hold `capacity` pods (ctr_val: 8 values
+ * per pod); pod_flag[k] != 0 means item k would be handed to the host loader.  Used by the
+ * CPU test-suite to compare the device code with the host loader without a GPU.
+ */
+int  arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const arena_host_snapshot *nodes,
+                             uint64_t capacity, uint64_t *n_items_out, uint32_t *pod_node, uint8_t *pod_phase,
+                             uint32_t *pod_n_ctrs, int64_t *ctr_val, uint8_t *pod_flag);
+
 /* Row -> original PodList index ([P]); job id -> name / trainer type; node id and
  * row -> metadata.name ("" for synthetic snapshots, which carry no names). */
 const uint32_t *arena_host_pod_order(const arena_host_snapshot *h);

@@ -4,9 +4,10 @@ The synthetic documents carry the bulk a real `kubectl get pods -o json` has
 (managedFields, volumes, env, probes, containerStatuses: about 3 KB per pod), of
 which the accounting path reads a few dozen bytes.
 
-    python tools/loader_timing.py [--pods 10000] [--nodes 100] [--reps 5]
+    python tools/loader_timing.py [--pods 10000] [--nodes 100] [--reps 5] [--device]
 
-Prints MB/s and pods/s of arena_load_json (no GPU needed).
+Prints MB/s and pods/s of arena_load_json (no GPU needed); with --device also of
+arena_load_json_device (PodList parsed on the GPU) followed by one `top node`.
 """
 import argparse
 import json
@@ -113,6 +114,7 @@ def main():
     ap.add_argument("--pods", type=int, default=10000)
     ap.add_argument("--nodes", type=int, default=100)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--device", action="store_true")
     args = ap.parse_args()
     import os
     import sys
@@ -126,8 +128,29 @@ def main():
         snap = HostSnapshot.from_json(pods, nodes)
         best = min(best, time.perf_counter() - t0)
         del snap
-    print(json.dumps({"podlist_bytes": len(pods), "bytes_per_pod": len(pods) / args.pods, "pods": args.pods,
-                      "load_ms": best * 1e3, "MB_per_s": len(pods) / best / 1e6, "pods_per_s": args.pods / best}))
+    line = {"podlist_bytes": len(pods), "bytes_per_pod": len(pods) / args.pods, "pods": args.pods,
+            "host_threads": os.cpu_count(), "load_ms": best * 1e3, "MB_per_s": len(pods) / best / 1e6,
+            "pods_per_s": args.pods / best}
+    if args.device:
+        import arena_b200
+        from arena_b200 import DeviceSnapshot
+        arena_b200.init(0)
+        pinned = arena_b200.PinnedBuffer(len(pods)).fill(pods)
+        for label, src in (("device", pods), ("device_pinned", pinned)):
+            dbest, stats = float("inf"), None
+            for _ in range(args.reps + 2):
+                t0 = time.perf_counter()
+                dev, st = DeviceSnapshot.from_json_device(src, nodes)
+                dt = time.perf_counter() - t0
+                if dt < dbest:
+                    dbest, stats = dt, st
+                t0 = time.perf_counter()
+                arena_b200.top_node(dev)
+                top_ms = (time.perf_counter() - t0) * 1e3
+                dev.close()
+            line.update({label + "_load_ms": dbest * 1e3, label + "_MB_per_s": len(pods) / dbest / 1e6,
+                         label + "_pods_per_s": args.pods / dbest, label + "_stats": stats, "top_node_ms": top_ms})
+    print(json.dumps(line))
 
 
 if __name__ == "__main__":
