@@ -553,7 +553,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     int2 *d_cta_state;
     int *d_word_state;
     ScanResult *d_res;
-    CUDA_TRY(bufs.alloc(&d_text, n_words * kWordBytes + 64));
+    CUDA_TRY(bufs.alloc(&d_text, n_words * kWordBytes + 512));      // the per-pod kernel reads and prefetches past the end
     CUDA_TRY(bufs.alloc(&d_quote, n_words * 8));
     CUDA_TRY(bufs.alloc(&d_open, n_words * 8));
     CUDA_TRY(bufs.alloc(&d_close, n_words * 8));

@@ -292,16 +292,16 @@ ARENA_HD inline uint8_t phase_code(const unsigned char *p, size_t n)
 // Acceptance is that of json.cc's recursive parser.
 enum Class : uint8_t {
     C_SPACE, C_WHITE, C_LCURB, C_RCURB, C_LSQRB, C_RSQRB, C_COLON, C_COMMA, C_QUOTE, C_BACKS, C_SLASH, C_PLUS, C_MINUS,
-    C_POINT, C_ZERO, C_DIGIT, C_B, C_F, C_N, C_R, C_T, C_U, C_HEXLET, C_E, C_ETC, C_CTRL, C_COUNT
+    C_POINT, C_ZERO, C_DIGIT, C_A, C_B, C_LOW_E, C_F, C_L, C_N, C_R, C_S, C_T, C_U, C_HEXLET, C_E, C_ETC, C_CTRL, C_COUNT
 };
 
 enum LexState : uint8_t {
     S_VAL, S_ARR0, S_OBJ0, S_KEY, S_COLON, S_AFTER, S_STR, S_ESC, S_U1, S_U2, S_U3, S_U4, S_MINUS, S_ZERO, S_INT,
-    S_FRAC0, S_FRAC, S_EXP0, S_EXPS, S_EXP, S_COUNT
+    S_FRAC0, S_FRAC, S_EXP0, S_EXPS, S_EXP, S_T1, S_T2, S_T3, S_F1, S_F2, S_F3, S_F4, S_N1, S_N2, S_N3, S_COUNT
 };
 
 enum Action : uint8_t {
-    A_NONE, A_ERR, A_OPEN, A_CLOSE, A_COMMA, A_KEY_BEGIN, A_STR_BEGIN, A_STR_END, A_NUM_BEGIN, A_NUM_END, A_LITERAL
+    A_NONE, A_ERR, A_OPEN, A_CLOSE, A_COMMA, A_KEY_BEGIN, A_STR_BEGIN, A_STR_END, A_NUM_BEGIN, A_NUM_END, A_LIT_END
 };
 
 struct LexTables {
@@ -321,9 +321,9 @@ constexpr LexTables make_lex_tables()
     t.cls['+'] = C_PLUS; t.cls['-'] = C_MINUS; t.cls['.'] = C_POINT; t.cls['0'] = C_ZERO;
     for (int c = '1'; c <= '9'; c++) t.cls[c] = C_DIGIT;
     t.cls['b'] = C_B; t.cls['f'] = C_F; t.cls['n'] = C_N; t.cls['r'] = C_R; t.cls['t'] = C_T; t.cls['u'] = C_U;
-    t.cls['a'] = C_HEXLET; t.cls['c'] = C_HEXLET; t.cls['d'] = C_HEXLET;
+    t.cls['a'] = C_A; t.cls['c'] = C_HEXLET; t.cls['d'] = C_HEXLET; t.cls['l'] = C_L; t.cls['s'] = C_S;
     t.cls['A'] = C_HEXLET; t.cls['B'] = C_HEXLET; t.cls['C'] = C_HEXLET; t.cls['D'] = C_HEXLET; t.cls['F'] = C_HEXLET;
-    t.cls['e'] = C_E; t.cls['E'] = C_E;
+    t.cls['e'] = C_LOW_E; t.cls['E'] = C_E;
 
     for (int k = 0; k < S_COUNT * C_COUNT; k++) t.next[k] = lex_entry(A_ERR, S_AFTER);
     auto at = [&](int st, int c) -> uint16_t & { return t.next[st * C_COUNT + c]; };
@@ -338,10 +338,15 @@ constexpr LexTables make_lex_tables()
         at(st, C_MINUS) = lex_entry(A_NUM_BEGIN, S_MINUS);
         at(st, C_ZERO) = lex_entry(A_NUM_BEGIN, S_ZERO);
         at(st, C_DIGIT) = lex_entry(A_NUM_BEGIN, S_INT);
-        at(st, C_T) = lex_entry(A_LITERAL, S_AFTER);
-        at(st, C_F) = lex_entry(A_LITERAL, S_AFTER);
-        at(st, C_N) = lex_entry(A_LITERAL, S_AFTER);
+        at(st, C_T) = lex_entry(A_NONE, S_T1);
+        at(st, C_F) = lex_entry(A_NONE, S_F1);
+        at(st, C_N) = lex_entry(A_NONE, S_N1);
     }
+    // true / false / null: the last letter ends the value
+    at(S_T1, C_R) = lex_entry(A_NONE, S_T2); at(S_T2, C_U) = lex_entry(A_NONE, S_T3); at(S_T3, C_LOW_E) = lex_entry(A_LIT_END, S_AFTER);
+    at(S_F1, C_A) = lex_entry(A_NONE, S_F2); at(S_F2, C_L) = lex_entry(A_NONE, S_F3); at(S_F3, C_S) = lex_entry(A_NONE, S_F4);
+    at(S_F4, C_LOW_E) = lex_entry(A_LIT_END, S_AFTER);
+    at(S_N1, C_U) = lex_entry(A_NONE, S_N2); at(S_N2, C_L) = lex_entry(A_NONE, S_N3); at(S_N3, C_L) = lex_entry(A_LIT_END, S_AFTER);
     at(S_ARR0, C_RSQRB) = lex_entry(A_CLOSE, S_AFTER);
     at(S_OBJ0, C_RCURB) = lex_entry(A_CLOSE, S_AFTER);
     at(S_OBJ0, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_STR);
@@ -359,7 +364,7 @@ constexpr LexTables make_lex_tables()
     const int escapes[] = {C_QUOTE, C_BACKS, C_SLASH, C_B, C_F, C_N, C_R, C_T};
     for (int c : escapes) at(S_ESC, c) = lex_entry(A_NONE, S_STR);
     at(S_ESC, C_U) = lex_entry(A_NONE, S_U1);
-    const int hex[] = {C_ZERO, C_DIGIT, C_B, C_F, C_HEXLET, C_E};
+    const int hex[] = {C_ZERO, C_DIGIT, C_A, C_B, C_LOW_E, C_F, C_HEXLET, C_E};
     for (int c : hex) {
         at(S_U1, c) = lex_entry(A_NONE, S_U2);
         at(S_U2, c) = lex_entry(A_NONE, S_U3);
@@ -372,12 +377,17 @@ constexpr LexTables make_lex_tables()
     at(S_INT, C_ZERO) = lex_entry(A_NONE, S_INT);
     at(S_INT, C_DIGIT) = lex_entry(A_NONE, S_INT);
     const int int_ends[] = {S_ZERO, S_INT};
-    for (int st : int_ends) { at(st, C_POINT) = lex_entry(A_NONE, S_FRAC0); at(st, C_E) = lex_entry(A_NONE, S_EXP0); }
+    for (int st : int_ends) {
+        at(st, C_POINT) = lex_entry(A_NONE, S_FRAC0);
+        at(st, C_E) = lex_entry(A_NONE, S_EXP0);
+        at(st, C_LOW_E) = lex_entry(A_NONE, S_EXP0);
+    }
     at(S_FRAC0, C_ZERO) = lex_entry(A_NONE, S_FRAC);
     at(S_FRAC0, C_DIGIT) = lex_entry(A_NONE, S_FRAC);
     at(S_FRAC, C_ZERO) = lex_entry(A_NONE, S_FRAC);
     at(S_FRAC, C_DIGIT) = lex_entry(A_NONE, S_FRAC);
     at(S_FRAC, C_E) = lex_entry(A_NONE, S_EXP0);
+    at(S_FRAC, C_LOW_E) = lex_entry(A_NONE, S_EXP0);
     at(S_EXP0, C_PLUS) = lex_entry(A_NONE, S_EXPS);
     at(S_EXP0, C_MINUS) = lex_entry(A_NONE, S_EXPS);
     const int exp_digits[] = {S_EXP0, S_EXPS, S_EXP};
@@ -404,16 +414,26 @@ ARENA_HD inline uint16_t fused_entry(const detail::LexTables &lt, int k)
 }
 
 // Scans the item in t[begin, end) (which must be exactly one JSON value).  See the contract
-// at the top.  `fused` is the [state][byte] table; on the device `t` must be 16-byte aligned and
-// readable in whole 16-byte words up to 16 bytes past `end` (the device buffer is padded).
+// at the top.  `fused` is the [state][byte] table; on the device `t` must be 8-byte aligned and
+// readable in whole 8-byte words up to 16 bytes past `end` (the device buffer is padded).
 //
-// The walk itself never re-reads the text: keys are recognised by length + hash, and whatever
-// needs the bytes of a token (confirming a recognised key, checking a quantity or a timestamp,
-// decoding the phase, the GPU digits, the node name) is put on a short per-item list and
-// done after the walk, where the lanes of a warp work through their lists side by side.
+// Shape of the walk (what keeps a warp of 32 different pods together):
+//   * the FAST loop eats bytes with one table lookup each.  Token boundaries inside a subtree
+//     nobody reads ("quiet": managedFields, env, volumes, conditions ... most of a pod) are
+//     settled right there with a bit stack of container types -- no role stack, no switch;
+//   * a boundary that matters (a key or a value under metadata / spec / status / containers /
+//     resources / limits) ends the fast loop.  The lanes of a warp meet again after it, and
+//     pods of one schema reach their k-th such boundary together, so the SLOW handler runs
+//     once per boundary, not once per lane;
+//   * the walk never re-reads the text: keys are recognised by length + hash, and whatever
+//     needs the bytes of a token (confirming a recognised key, checking a quantity or a
+//     timestamp, decoding the phase, the GPU digits, the node name) goes on a short list
+//     worked off after the walk, again side by side.
 constexpr int kMaxTodo = 96;
+constexpr int kRoleLevels = 8;           // ITEM > SPEC > CTRS > CTR > RES > LIMITS is the deepest path with a role
+constexpr int kMaxBitDepth = 62;         // container types live in a 64-bit stack
 
-ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t end, const NodeTable &nodes,
+ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t end_, const NodeTable &nodes,
                                    const uint16_t *fused, PodOut &out)
 {
     using namespace detail;
@@ -421,16 +441,21 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
     struct Todo {
         uint32_t pos;                    // relative to `begin`
         uint16_t len;
-        uint8_t what, arg;               // W_KEY: key id; W_GPU: index into gpu_slot[]
+        uint8_t what, arg;               // W_KEY: key id; W_GPU: index into gpu_value[]
     };
     Todo todo[kMaxTodo];
     int n_todo = 0;
-    uint8_t stack[kMaxLevels];           // role of every open container
-    uint32_t seen[kMaxLevels];           // key ids already met in the object at that level
+    uint8_t stack[kRoleLevels];          // role of the open containers that have one (never the quiet ones)
+    uint32_t seen[kRoleLevels];          // key ids already met in the object at that level
     stack[0] = R_SKIP_ARR;
     seen[0] = 0;
-    int depth = 0;
+    const uint32_t begin = (uint32_t)begin_, end = (uint32_t)end_;       // the caller keeps documents below 4 GiB
     uint32_t flag = kOk;
+
+    uint64_t bits = 0;                   // bit 0 = the innermost open container is an array
+    int depth = 0;
+    constexpr int kNotQuiet = 1 << 30;
+    int quiet_base = kNotQuiet;          // quiet <=> depth > quiet_base
 
     // GPU quantities wait on the list; a container points at the one that counts for it
     constexpr int16_t kAbsent = -1, kNull = -2;                         // no GPU key / "key": null => 0
@@ -440,26 +465,26 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
     int16_t cur_ref = kAbsent, gpu_ref = kAbsent, dep_ref = kAbsent;
     bool gpu_present = false, dep_present = false;
 
-    size_t node_off = 0, node_len = 0;
+    uint32_t node_off = 0, node_len = 0;
     int phase_todo = -1;                 // W_PHASE entry of the status that counts, or -1 (=> "")
     uint32_t n_ctrs = 0;
 
     uint8_t key = K_ELEMENT;             // key id of the value being read, in its parent
-    size_t tok = 0;                      // start of the current string body / number
+    uint32_t tok = 0;                    // start of the current string body / number
     bool is_key = false, escaped = false, done = false;
     uint8_t st = S_VAL;
-    uint32_t hash = 0;                   // FNV-1a of the bytes since `tok`
+    uint32_t hash = 0;                   // FNV-1a of the bytes since the last key's opening quote
 
-    auto defer = [&](uint8_t what, uint8_t arg, size_t body, size_t len) -> int {
+    auto defer = [&](uint8_t what, uint8_t arg, uint32_t body, uint32_t len) -> int {
         if (n_todo >= kMaxTodo || len > 0xFFFFu) { flag = kFlagTooManyFields; return -1; }
-        todo[n_todo] = Todo{(uint32_t)(body - begin), (uint16_t)len, what, arg};
+        todo[n_todo] = Todo{body - begin, (uint16_t)len, what, arg};
         return n_todo++;
     };
 
     // one finished scalar in context (parent role, key): the host loader's field rules
-    auto scalar = [&](bool is_string, bool is_number, bool is_null, size_t body, size_t len) {
-        const uint8_t parent = depth ? stack[depth - 1] : (uint8_t)R_SKIP_ARR;
+    auto scalar = [&](bool is_string, bool is_number, bool is_null, uint32_t body, uint32_t len) {
         if (depth == 0) { flag = kFlagShape; return; }                 // "PodList item is not an object"
+        const uint8_t parent = stack[depth - 1];
         switch (key) {
         case K_OTHER: break;
         case K_ELEMENT:
@@ -519,21 +544,11 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
         }
     };
 
-    size_t done_at = end;
-    unsigned skip = 0;                   // bytes of a literal already checked
-    // one byte
-    auto step = [&](const unsigned char c, const size_t i) {
-        if (skip) { skip--; return; }
-        uint16_t e = fused[st * 256 + c];
-        uint8_t act = (uint8_t)(e >> 8);
-        uint8_t ns = (uint8_t)e;
-        if (ns == S_ESC) escaped = true;
-        if (act == A_NONE) { hash = (hash ^ c) * 16777619u; st = ns; return; }
-
-        // ---- token boundary ---------------------------------------------------------------
+    // a boundary where roles matter (never called while quiet)
+    auto slow = [&](uint8_t act, uint8_t ns, const unsigned char c, const uint32_t i) {
         if (act == A_NUM_END) {
             scalar(false, true, false, tok, i - tok);
-            e = fused[S_AFTER * 256 + c];                              // the same byte, as the follower of a value
+            const uint16_t e = fused[S_AFTER * 256 + c];               // the same byte, as the follower of a value
             act = (uint8_t)(e >> 8);
             ns = (uint8_t)e;
         }
@@ -578,9 +593,10 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
                 default: flag = kFlagShape; break;                     // a list where the host wants an object or a scalar
                 }
             }
-            if (depth >= kMaxLevels) { flag = kFlagTooDeep; break; }
-            stack[depth] = role;
-            seen[depth] = 0;
+            if (role == R_SKIP_OBJ || role == R_SKIP_ARR) quiet_base = depth;      // nobody reads this subtree
+            else if (depth >= kRoleLevels) { flag = kFlagTooDeep; break; }
+            else { stack[depth] = role; seen[depth] = 0; }
+            bits = (bits << 1) | (obj ? 0u : 1u);
             depth++;
             key = K_ELEMENT;                                           // (arrays; objects set it at every key)
             break;
@@ -588,20 +604,21 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
         case A_CLOSE: {
             if (depth == 0) { flag = kFlagSyntax; break; }
             const uint8_t role = stack[depth - 1];
-            if (role_is_array(role) != (c == ']')) { flag = kFlagSyntax; break; }
+            if ((bool)(bits & 1) != (c == ']')) { flag = kFlagSyntax; break; }
             if (role == R_LIMITS) cur_ref = gpu_present ? gpu_ref : dep_present ? dep_ref : kAbsent;   // gpu.go:61-79: key presence
             else if (role == R_CTR) {
                 if (n_ctrs < (uint32_t)kInlineCtrs) ctr_ref[n_ctrs] = cur_ref;
                 else flag = kFlagTooManyContainers;
                 n_ctrs++;
             }
+            bits >>= 1;
             depth--;
-            if (depth == 0) { done = true; done_at = i; }
+            if (depth == 0) done = true;
             break;
         }
         case A_COMMA:
             if (depth == 0) { flag = kFlagSyntax; break; }
-            if (role_is_array(stack[depth - 1])) { ns = S_VAL; key = K_ELEMENT; }
+            if (bits & 1) { ns = S_VAL; key = K_ELEMENT; }
             else ns = S_KEY;
             break;
         case A_KEY_BEGIN: tok = i + 1; is_key = true; escaped = false; hash = 2166136261u; break;
@@ -609,16 +626,13 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
         case A_STR_END:
             if (is_key) {
                 const uint8_t role = stack[depth - 1];
-                if (role == R_SKIP_OBJ) key = K_OTHER;
-                else {
-                    if (escaped) flag = kFlagEscapedKey;
-                    key = key_id_hashed(role, (uint32_t)(i - tok), hash);
-                    if (key != K_OTHER && key != K_QUANTITY) {
-                        const uint32_t bit = 1u << key;
-                        if (seen[depth - 1] & bit) flag = kFlagDuplicateKey;
-                        seen[depth - 1] |= bit;
-                        defer(W_KEY, key, tok, i - tok);               // confirmed byte for byte after the walk
-                    }
+                if (escaped) flag = kFlagEscapedKey;
+                key = key_id_hashed(role, i - tok, hash);
+                if (key != K_OTHER && key != K_QUANTITY) {
+                    const uint32_t bit = 1u << key;
+                    if (seen[depth - 1] & bit) flag = kFlagDuplicateKey;
+                    seen[depth - 1] |= bit;
+                    defer(W_KEY, key, tok, i - tok);                   // confirmed byte for byte after the walk
                 }
                 ns = S_COLON;
             } else {
@@ -627,42 +641,94 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin, size_t 
             }
             break;
         case A_NUM_BEGIN: tok = i; break;
-        case A_LITERAL: {
-            const char *w = c == 't' ? "true" : c == 'f' ? "false" : "null";
-            const size_t n = c == 'f' ? 5 : 4;
-            bool ok = end - i >= n;
-            for (size_t k = 1; ok && k < n; k++) ok = t[i + k] == (unsigned char)w[k];
-            if (!ok) { flag = kFlagSyntax; break; }
-            scalar(false, false, c == 'n', i, n);
-            skip = (unsigned)n - 1;
-            break;
-        }
+        case A_LIT_END: scalar(false, false, c == 'l', i, 1); break;   // ...l = null
         default: flag = kFlagSyntax; break;                            // A_ERR
         }
         st = ns;
     };
+
+    // ---- the walk ------------------------------------------------------------------------------
+    uint32_t pos = begin;
 #if defined(__CUDA_ARCH__)
-    // Lock step: every lane of the warp consumes one 16-byte word per outer iteration (lanes
-    // whose item starts inside the word idle through the first bytes), and the next word is
-    // requested before the current one is processed, so the load latency overlaps the work.
-    size_t base = begin & ~(size_t)15;
-    uint4 cur = *reinterpret_cast<const uint4 *>(t + base);
-    for (; base < end && !flag && !done; base += 16) {
-        const uint4 nxt = *reinterpret_cast<const uint4 *>(t + base + 16);
-        const uint64_t lo = (uint64_t)cur.x | ((uint64_t)cur.y << 32), hi = (uint64_t)cur.z | ((uint64_t)cur.w << 32);
-        for (int k = 0; k < 16; k++) {
-            const size_t i = base + k;
-            const unsigned char c = (unsigned char)((k < 8 ? lo : hi) >> ((k & 7) * 8));
-            if (i >= begin && i < end && !flag && !done) step(c, i);
-        }
-        cur = nxt;
-    }
-#else
-    for (size_t i = begin; i < end && !flag && !done; i++) step(t[i], i);
+    // bytes come from two 8-byte registers: `buf` is being eaten, `ahead` was requested eight
+    // bytes earlier, so the load has had time to land
+    // (a scoreboard covers a register for the whole warp, so every lane's refill makes all 32
+    // wait for it: the line is asked for 256 bytes early to make that wait an L1 hit)
+    uint64_t buf = *reinterpret_cast<const uint64_t *>(t + (pos & ~7u)) >> ((pos & 7u) * 8);
+    uint64_t ahead = *reinterpret_cast<const uint64_t *>(t + (pos & ~7u) + 8);
+    for (uint32_t k = 0; k < 256; k += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(t + (pos & ~127u) + k));
+    auto refill = [&]() {
+        buf = ahead;
+        ahead = *reinterpret_cast<const uint64_t *>(t + pos + 8);
+        if ((pos & 127u) == 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(t + pos + 256));
+    };
 #endif
+    while (pos < end && !flag && !done) {
+        uint8_t act = A_NONE, ns = st;
+        unsigned char c = 0;
+        // FAST: until a boundary that needs the slow handler
+        while (pos < end) {
+#if defined(__CUDA_ARCH__)
+            c = (unsigned char)buf;
+#else
+            c = t[pos];
+#endif
+            const uint16_t e = fused[st * 256 + c];
+            act = (uint8_t)(e >> 8);
+            ns = (uint8_t)e;
+            if (act != A_NONE) {
+                if (depth <= quiet_base) break;                        // roles matter here
+                // quiet: container types are all that is needed
+                if (act == A_NUM_END) {
+                    const uint16_t e2 = fused[S_AFTER * 256 + c];
+                    act = (uint8_t)(e2 >> 8);
+                    ns = (uint8_t)e2;
+                }
+                if (act == A_OPEN) {
+                    if (depth >= kMaxBitDepth) { flag = kFlagTooDeep; break; }
+                    bits = (bits << 1) | (c == '[' ? 1u : 0u);
+                    depth++;
+                } else if (act == A_CLOSE) {
+                    if ((bool)(bits & 1) != (c == ']')) { flag = kFlagSyntax; break; }
+                    bits >>= 1;
+                    depth--;
+                    if (depth == quiet_base) quiet_base = kNotQuiet;   // the subtree is over; its value needed no handling
+                } else if (act == A_COMMA) {
+                    ns = (bits & 1) ? S_VAL : S_KEY;
+                } else if (act == A_KEY_BEGIN) {
+                    is_key = true;
+                } else if (act == A_STR_BEGIN) {
+                    is_key = false;
+                } else if (act == A_STR_END) {
+                    ns = is_key ? S_COLON : S_AFTER;
+                } else if (act == A_ERR) {
+                    flag = kFlagSyntax;
+                    break;
+                }
+                act = A_NONE;
+            } else {
+                hash = (hash ^ c) * 16777619u;
+                if (ns == S_ESC) escaped = true;
+            }
+            st = ns;
+            pos++;
+#if defined(__CUDA_ARCH__)
+            buf >>= 8;
+            if ((pos & 7u) == 0) refill();
+#endif
+        }
+        if (act == A_NONE || flag) continue;                           // ran out of bytes, or flagged while quiet
+        // SLOW: the lanes of a warp arrive here together
+        slow(act, ns, c, pos);
+        pos++;
+#if defined(__CUDA_ARCH__)
+        buf >>= 8;
+        if ((pos & 7u) == 0) refill();
+#endif
+    }
     if (!flag && !done) flag = kFlagSyntax;                            // ran out of bytes inside the item
     if (!flag)
-        for (size_t i = done_at + 1; i < end; i++)
+        for (uint32_t i = pos; i < end; i++)
             if (!is_ws(t[i])) { flag = kFlagSyntax; break; }
 
     // ---- the deferred checks: the only place that goes back to the text ---------------------
