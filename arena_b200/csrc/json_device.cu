@@ -30,6 +30,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -361,6 +362,7 @@ struct ItemArgs {
     const unsigned char *text;
     const u32 *item_begin, *item_end;
     u64 n_items, A, B;
+    unsigned lanes;                // pods per warp
     NodeTable nodes;
     u32 *pod_node;
     unsigned char *pod_phase, *pod_flag;
@@ -369,12 +371,25 @@ struct ItemArgs {
     ScanResult *res;
 };
 
-__global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const __grid_constant__ detail::LexTables tables)
+__global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const uint4 *__restrict__ fused_table)
 {
-    __shared__ uint16_t s_fused[kFusedEntries];            // every lane indexes it with its own state: shared, not constant
-    for (int k = threadIdx.x; k < kFusedEntries; k += blockDim.x) s_fused[k] = fused_entry(tables, k);
+    // every lane indexes the table with its own state: shared memory, not constant
+    __shared__ __align__(16) uint32_t s_fused[kFusedEntries];
+    __shared__ __align__(128) unsigned char s_ring[128 * 64];          // [thread][4 windows of 16 bytes]
+    const uint32_t fused_base = (uint32_t)__cvta_generic_to_shared(s_fused);
+    for (int k = threadIdx.x; k < kFusedEntries / 4; k += blockDim.x) {
+        uint4 v = __ldg(fused_table + k);                              // row offsets -> shared-memory addresses
+        v.x += fused_base; v.y += fused_base; v.z += fused_base; v.w += fused_base;
+        reinterpret_cast<uint4 *>(s_fused)[k] = v;
+    }
     __syncthreads();
-    const u64 p = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    // With few pods only the first `lanes` lanes of every warp take one: the walk is a long
+    // dependent chain per lane, so a small job finishes sooner spread over many thin warps
+    // (more warps per scheduler to switch between, fewer lanes dragging each other through
+    // their rare paths) than packed into a few full ones.
+    const unsigned lane = threadIdx.x & 31u;
+    if (lane >= a.lanes) return;
+    const u64 p = ((u64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * a.lanes + lane;
     if (p >= a.n_items) return;
     const u64 begin = a.item_begin[p], end = a.item_end[p];
     PodOut out;
@@ -382,7 +397,7 @@ __global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const
     const u64 prev_end = p == 0 ? a.A + 1 : (u64)a.item_end[p - 1];
     if (end <= begin || prev_end > begin || !gap_ok(a.text, prev_end, begin, p == 0)) out.flag = kFlagSeparator;
     else if (p + 1 == a.n_items && !gap_ok(a.text, end, a.B - 1, true)) out.flag = kFlagSeparator;
-    else scan_pod_item(a.text, begin, end, a.nodes, s_fused, out);
+    else scan_pod_item(a.text, begin, end, a.nodes, SharedLex{fused_base}, RingFeed(a.text, s_ring + threadIdx.x * 64), out);
     if (out.flag) {
         atomicOr(&a.res->any_flag, 1u);
         const u32 old = atomicMin(&a.res->first_flag_item, (u32)p);
@@ -537,7 +552,8 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
 {
     *handled = false;
     cudaStream_t st;
-    int rc = arena_internal::ready(&st, nullptr);
+    int sm_count = 0;
+    int rc = arena_internal::ready(&st, &sm_count);
     if (rc) return rc;
     if (len == 0 || len >= 0xFFFFFF00ull) return ARENA_OK;              // byte offsets are u32 on the device
     const auto t_start = std::chrono::steady_clock::now();
@@ -652,6 +668,11 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     arena_scan_host::build_node_table(nodes->node_names, slots, blob);
     NodeSlot *d_slots;
     unsigned char *d_blob;
+    uint32_t *d_fused;
+    std::vector<uint32_t> fused(kFusedEntries);
+    build_fused(fused.data());
+    CUDA_TRY(bufs.alloc(&d_fused, fused.size() * 4));
+    CUDA_TRY(cudaMemcpyAsync(d_fused, fused.data(), fused.size() * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(bufs.alloc(&d_slots, slots.size() * sizeof(NodeSlot)));
     CUDA_TRY(bufs.alloc(&d_blob, blob.size()));
     CUDA_TRY(cudaMemcpyAsync(d_slots, slots.data(), slots.size() * sizeof(NodeSlot), cudaMemcpyHostToDevice, st));
@@ -679,7 +700,17 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         ia.nodes = NodeTable{d_slots, (uint64_t)slots.size() - 1, d_blob};
         ia.pod_node = d_pod_node_tmp; ia.pod_phase = d_pod_phase_tmp; ia.pod_flag = d_pod_flag;
         ia.pod_nctr = d_nctr; ia.ctr_tmp = d_ctr_tmp; ia.res = d_res;
-        scan_items_kernel<<<(unsigned)((P + 127) / 128), 128, 0, st>>>(ia, kLexTables);
+        // aim at >= 4 warps per SM sub-partition before filling the warps up
+        const u64 warps_wanted = (u64)sm_count * 16;
+        unsigned lanes = 32;
+        while (lanes > 4 && (P + lanes - 1) / lanes < warps_wanted) lanes >>= 1;
+        if (const char *env = std::getenv("ARENA_LOADER_LANES")) {     // tuning aid
+            const long v = std::strtol(env, nullptr, 10);
+            if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) lanes = (unsigned)v;
+        }
+        ia.lanes = lanes;
+        const u64 n_warps = (P + lanes - 1) / lanes;
+        scan_items_kernel<<<(unsigned)((n_warps + 3) / 4), 128, 0, st>>>(ia, (const uint4 *)d_fused);
         arena_internal::add_launches(1);
         CUDA_TRY(cudaGetLastError());
         rc = exclusive_scan(d_nctr, P, d_ctr_begin64, d_tile_sums2, &d_res->n_containers, st);
@@ -820,11 +851,12 @@ int arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const 
     std::vector<unsigned char> blob;
     arena_scan_host::build_node_table(nodes->node_names, slots, blob);
     const NodeTable nt{slots.data(), (uint64_t)slots.size() - 1, blob.data()};
-    std::vector<uint16_t> fused(kFusedEntries);
-    for (int k = 0; k < kFusedEntries; k++) fused[k] = fused_entry(kLexTables, k);
+    std::vector<uint32_t> fused(kFusedEntries);
+    build_fused(fused.data());
     for (size_t k = 0; k < ranges.size(); k++) {
         PodOut out;
-        scan_pod_item((const unsigned char *)podlist_json, ranges[k].begin, ranges[k].end, nt, fused.data(), out);
+        scan_pod_item((const unsigned char *)podlist_json, ranges[k].begin, ranges[k].end, nt, DirectLex{fused.data()},
+                      DirectFeed{(const unsigned char *)podlist_json}, out);
         if (pod_flag) pod_flag[k] = (uint8_t)out.flag;
         if (pod_node) pod_node[k] = out.node;
         if (pod_phase) pod_phase[k] = out.phase;

@@ -297,11 +297,14 @@ enum Class : uint8_t {
 
 enum LexState : uint8_t {
     S_VAL, S_ARR0, S_OBJ0, S_KEY, S_COLON, S_AFTER, S_STR, S_ESC, S_U1, S_U2, S_U3, S_U4, S_MINUS, S_ZERO, S_INT,
-    S_FRAC0, S_FRAC, S_EXP0, S_EXPS, S_EXP, S_T1, S_T2, S_T3, S_F1, S_F2, S_F3, S_F4, S_N1, S_N2, S_N3, S_COUNT
+    S_FRAC0, S_FRAC, S_EXP0, S_EXPS, S_EXP, S_T1, S_T2, S_T3, S_F1, S_F2, S_F3, S_F4, S_N1, S_N2, S_N3,
+    S_KSTR, S_KESC, S_KU1, S_KU2, S_KU3, S_KU4,                          // a KEY string: same rules as S_STR, other exits
+    S_COUNT
 };
 
 enum Action : uint8_t {
-    A_NONE, A_ERR, A_OPEN, A_CLOSE, A_COMMA, A_KEY_BEGIN, A_STR_BEGIN, A_STR_END, A_NUM_BEGIN, A_NUM_END, A_LIT_END
+    A_NONE, A_ERR, A_OPEN, A_CLOSE, A_COMMA, A_KEY_BEGIN, A_KEY_END, A_STR_BEGIN, A_STR_END, A_ESCAPE, A_NUM_BEGIN, A_LIT_END,
+    A_NUM_ENDED = 0x80                   // flag on the action of the byte that follows a number
 };
 
 struct LexTables {
@@ -349,27 +352,30 @@ constexpr LexTables make_lex_tables()
     at(S_N1, C_U) = lex_entry(A_NONE, S_N2); at(S_N2, C_L) = lex_entry(A_NONE, S_N3); at(S_N3, C_L) = lex_entry(A_LIT_END, S_AFTER);
     at(S_ARR0, C_RSQRB) = lex_entry(A_CLOSE, S_AFTER);
     at(S_OBJ0, C_RCURB) = lex_entry(A_CLOSE, S_AFTER);
-    at(S_OBJ0, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_STR);
-    at(S_KEY, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_STR);
+    at(S_OBJ0, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_KSTR);
+    at(S_KEY, C_QUOTE) = lex_entry(A_KEY_BEGIN, S_KSTR);
     at(S_COLON, C_COLON) = lex_entry(A_NONE, S_VAL);
     at(S_AFTER, C_COMMA) = lex_entry(A_COMMA, S_VAL);
     at(S_AFTER, C_RCURB) = lex_entry(A_CLOSE, S_AFTER);
     at(S_AFTER, C_RSQRB) = lex_entry(A_CLOSE, S_AFTER);
-    // strings
-    for (int c = 0; c < C_COUNT; c++) at(S_STR, c) = lex_entry(A_NONE, S_STR);
-    at(S_STR, C_WHITE) = lex_entry(A_ERR, S_AFTER);                    // \t \n \r are control characters
-    at(S_STR, C_CTRL) = lex_entry(A_ERR, S_AFTER);
-    at(S_STR, C_QUOTE) = lex_entry(A_STR_END, S_AFTER);
-    at(S_STR, C_BACKS) = lex_entry(A_NONE, S_ESC);
-    const int escapes[] = {C_QUOTE, C_BACKS, C_SLASH, C_B, C_F, C_N, C_R, C_T};
-    for (int c : escapes) at(S_ESC, c) = lex_entry(A_NONE, S_STR);
-    at(S_ESC, C_U) = lex_entry(A_NONE, S_U1);
-    const int hex[] = {C_ZERO, C_DIGIT, C_A, C_B, C_LOW_E, C_F, C_HEXLET, C_E};
-    for (int c : hex) {
-        at(S_U1, c) = lex_entry(A_NONE, S_U2);
-        at(S_U2, c) = lex_entry(A_NONE, S_U3);
-        at(S_U3, c) = lex_entry(A_NONE, S_U4);
-        at(S_U4, c) = lex_entry(A_NONE, S_STR);
+    // strings (value strings: S_STR..S_U4, key strings: S_KSTR..S_KU4)
+    for (int fam = 0; fam < 2; fam++) {
+        const int str = fam ? S_KSTR : S_STR, esc = fam ? S_KESC : S_ESC, u1 = fam ? S_KU1 : S_U1;
+        for (int c = 0; c < C_COUNT; c++) at(str, c) = lex_entry(A_NONE, (uint8_t)str);
+        at(str, C_WHITE) = lex_entry(A_ERR, S_AFTER);                  // \t \n \r are control characters
+        at(str, C_CTRL) = lex_entry(A_ERR, S_AFTER);
+        at(str, C_QUOTE) = fam ? lex_entry(A_KEY_END, S_COLON) : lex_entry(A_STR_END, S_AFTER);
+        at(str, C_BACKS) = lex_entry(A_ESCAPE, (uint8_t)esc);
+        const int escapes[] = {C_QUOTE, C_BACKS, C_SLASH, C_B, C_F, C_N, C_R, C_T};
+        for (int c : escapes) at(esc, c) = lex_entry(A_NONE, (uint8_t)str);
+        at(esc, C_U) = lex_entry(A_NONE, (uint8_t)u1);
+        const int hex[] = {C_ZERO, C_DIGIT, C_A, C_B, C_LOW_E, C_F, C_HEXLET, C_E};
+        for (int c : hex) {
+            at(u1, c) = lex_entry(A_NONE, (uint8_t)(u1 + 1));
+            at(u1 + 1, c) = lex_entry(A_NONE, (uint8_t)(u1 + 2));
+            at(u1 + 2, c) = lex_entry(A_NONE, (uint8_t)(u1 + 3));
+            at(u1 + 3, c) = lex_entry(A_NONE, (uint8_t)str);
+        }
     }
     // numbers: -? (0 | [1-9][0-9]*) (\.[0-9]+)? ([eE][+-]?[0-9]+)?
     at(S_MINUS, C_ZERO) = lex_entry(A_NONE, S_ZERO);
@@ -396,26 +402,95 @@ constexpr LexTables make_lex_tables()
     const int num_ends[] = {S_ZERO, S_INT, S_FRAC, S_EXP};
     const int followers[] = {C_SPACE, C_WHITE, C_COMMA, C_RCURB, C_RSQRB};
     for (int st : num_ends)
-        for (int c : followers) at(st, c) = lex_entry(A_NUM_END, S_AFTER);
+        for (int c : followers) at(st, c) = (uint16_t)(at(S_AFTER, c) | (A_NUM_ENDED << 8));
     return t;
 }
 
 }  // namespace detail
 
-// The tables as data.  The scanner indexes ONE fused table, [state][byte] -> action << 8 | next
-// state (10 KB: json_device.cu builds it in shared memory from kLexTables, the host keeps a
-// static copy).
+// The tables as data.  The scanner indexes ONE fused table of 32-bit entries, [state][byte]:
+//     bits 24..31  action (0 on the common path)
+//     bits  0..23  where the next state's row starts -- a byte offset from the table's base here;
+//                  the device copy adds its shared-memory address, so that there the next
+//                  lookup address is just  entry + 4 * byte.
 static constexpr detail::LexTables kLexTables = detail::make_lex_tables();
 constexpr int kFusedEntries = detail::S_COUNT * 256;
+constexpr uint32_t kRowBytes = 256 * 4;
 
-ARENA_HD inline uint16_t fused_entry(const detail::LexTables &lt, int k)
+inline void build_fused(uint32_t *out)
 {
-    return lt.next[(k >> 8) * detail::C_COUNT + lt.cls[k & 255]];
+    for (int k = 0; k < kFusedEntries; k++) {
+        const uint16_t e = kLexTables.next[(k >> 8) * detail::C_COUNT + kLexTables.cls[k & 255]];
+        out[k] = (uint32_t)(e >> 8) << 24 | (uint32_t)(e & 0xff) * kRowBytes;
+    }
 }
 
+struct DirectLex {                       // host
+    const uint32_t *table;
+    ARENA_HD uint32_t row(unsigned state) const { return state * kRowBytes; }
+    ARENA_HD uint32_t next(uint32_t row, unsigned c) const { return table[(row >> 2) + c]; }
+};
+
+#if defined(__CUDACC__)
+struct SharedLex {                       // device: rows are shared-memory addresses
+    uint32_t base;
+    __device__ uint32_t row(unsigned state) const { return base + state * kRowBytes; }
+    __device__ uint32_t next(uint32_t row, unsigned c) const
+    {
+        uint32_t e;
+        asm("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(row + (c << 2)));
+        return e;
+    }
+};
+#endif
+
+// ---- where the walk gets its bytes from ------------------------------------------------------
+struct DirectFeed {                      // host: straight from the document
+    const unsigned char *t;
+    ARENA_HD unsigned get(uint32_t pos) const { return t[pos]; }
+    ARENA_HD void start(uint32_t) {}
+    ARENA_HD void entered_window(uint32_t) {}
+};
+
+#if defined(__CUDACC__)
+// Device: every lane owns a 64-byte ring in shared memory (4 windows of 16 bytes) that
+// cp.async fills two windows ahead of the walk.  The hot loop then depends on shared-memory
+// loads only: a global load in it would stall all 32 lanes of the warp whenever any one of
+// them refills, because a scoreboard covers a register for the whole warp.
+struct RingFeed {
+    const unsigned char *t;              // 16-byte aligned, readable 64 bytes past the item
+    uint32_t ring_shared;                // this lane's 64 bytes (64-byte aligned), as a shared-window address
+    __device__ RingFeed(const unsigned char *text, unsigned char *lane_ring)
+        : t(text), ring_shared((uint32_t)__cvta_generic_to_shared(lane_ring)) {}
+    __device__ void request(uint32_t window) const
+    {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n"
+                     "cp.async.commit_group;" ::"r"(ring_shared + (window & 3u) * 16u), "l"(t + (size_t)window * 16));
+    }
+    __device__ void start(uint32_t pos) const
+    {
+        const uint32_t w = pos >> 4;
+        request(w); request(w + 1); request(w + 2);
+        asm volatile("cp.async.wait_group 2;" ::: "memory");            // window w has landed
+    }
+    // the walk stepped onto the first byte of a window: ask for the one two ahead
+    __device__ void entered_window(uint32_t pos) const
+    {
+        request((pos >> 4) + 2);
+        asm volatile("cp.async.wait_group 2;" ::: "memory");            // all but the last two requests: this window is in
+    }
+    __device__ unsigned get(uint32_t pos) const
+    {
+        unsigned c;
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(ring_shared | (pos & 63u)));
+        return c;
+    }
+};
+#endif
+
 // Scans the item in t[begin, end) (which must be exactly one JSON value).  See the contract
-// at the top.  `fused` is the [state][byte] table; on the device `t` must be 8-byte aligned and
-// readable in whole 8-byte words up to 16 bytes past `end` (the device buffer is padded).
+// at the top.  `lex` looks up the [state][byte] table, `feed` hands out the bytes (DirectLex /
+// DirectFeed on the host, SharedLex / RingFeed on the device).
 //
 // Shape of the walk (what keeps a warp of 32 different pods together):
 //   * the FAST loop eats bytes with one table lookup each.  Token boundaries inside a subtree
@@ -433,8 +508,9 @@ constexpr int kMaxTodo = 96;
 constexpr int kRoleLevels = 8;           // ITEM > SPEC > CTRS > CTR > RES > LIMITS is the deepest path with a role
 constexpr int kMaxBitDepth = 62;         // container types live in a 64-bit stack
 
+template <class Lex, class Feed>
 ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t end_, const NodeTable &nodes,
-                                   const uint16_t *fused, PodOut &out)
+                                   const Lex lex, Feed feed, PodOut &out)
 {
     using namespace detail;
     enum What : uint8_t { W_KEY, W_QUANTITY, W_GPU, W_TIME, W_PHASE };
@@ -471,8 +547,8 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
 
     uint8_t key = K_ELEMENT;             // key id of the value being read, in its parent
     uint32_t tok = 0;                    // start of the current string body / number
-    bool is_key = false, escaped = false, done = false;
-    uint8_t st = S_VAL;
+    bool escaped = false, done = false;
+    uint32_t row = lex.row(S_VAL);       // the lexer state, as the start of its table row
     uint32_t hash = 0;                   // FNV-1a of the bytes since the last key's opening quote
 
     auto defer = [&](uint8_t what, uint8_t arg, uint32_t body, uint32_t len) -> int {
@@ -545,12 +621,10 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
     };
 
     // a boundary where roles matter (never called while quiet)
-    auto slow = [&](uint8_t act, uint8_t ns, const unsigned char c, const uint32_t i) {
-        if (act == A_NUM_END) {
+    auto slow = [&](unsigned act, uint32_t ns, const unsigned c, const uint32_t i) {
+        if (act & A_NUM_ENDED) {                                       // this byte follows a number
             scalar(false, true, false, tok, i - tok);
-            const uint16_t e = fused[S_AFTER * 256 + c];               // the same byte, as the follower of a value
-            act = (uint8_t)(e >> 8);
-            ns = (uint8_t)e;
+            act &= 0x7fu;
         }
         switch (act) {
         case A_NONE: break;
@@ -618,72 +692,50 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
         }
         case A_COMMA:
             if (depth == 0) { flag = kFlagSyntax; break; }
-            if (bits & 1) { ns = S_VAL; key = K_ELEMENT; }
-            else ns = S_KEY;
+            if (bits & 1) { ns = lex.row(S_VAL); key = K_ELEMENT; }
+            else ns = lex.row(S_KEY);
             break;
-        case A_KEY_BEGIN: tok = i + 1; is_key = true; escaped = false; hash = 2166136261u; break;
-        case A_STR_BEGIN: tok = i + 1; is_key = false; escaped = false; break;
-        case A_STR_END:
-            if (is_key) {
-                const uint8_t role = stack[depth - 1];
-                if (escaped) flag = kFlagEscapedKey;
-                key = key_id_hashed(role, i - tok, hash);
-                if (key != K_OTHER && key != K_QUANTITY) {
-                    const uint32_t bit = 1u << key;
-                    if (seen[depth - 1] & bit) flag = kFlagDuplicateKey;
-                    seen[depth - 1] |= bit;
-                    defer(W_KEY, key, tok, i - tok);                   // confirmed byte for byte after the walk
-                }
-                ns = S_COLON;
-            } else {
-                scalar(true, false, false, tok, i - tok);
-                ns = S_AFTER;
+        case A_KEY_BEGIN: tok = i + 1; escaped = false; hash = 2166136261u; break;
+        case A_STR_BEGIN: tok = i + 1; escaped = false; break;
+        case A_ESCAPE: escaped = true; break;
+        case A_KEY_END: {
+            const uint8_t role = stack[depth - 1];
+            if (escaped) flag = kFlagEscapedKey;
+            key = key_id_hashed(role, i - tok, hash);
+            if (key != K_OTHER && key != K_QUANTITY) {
+                const uint32_t bit = 1u << key;
+                if (seen[depth - 1] & bit) flag = kFlagDuplicateKey;
+                seen[depth - 1] |= bit;
+                defer(W_KEY, key, tok, i - tok);                       // confirmed byte for byte after the walk
             }
             break;
+        }
+        case A_STR_END: scalar(true, false, false, tok, i - tok); break;
         case A_NUM_BEGIN: tok = i; break;
         case A_LIT_END: scalar(false, false, c == 'l', i, 1); break;   // ...l = null
         default: flag = kFlagSyntax; break;                            // A_ERR
         }
-        st = ns;
+        row = ns;
     };
 
     // ---- the walk ------------------------------------------------------------------------------
+    // (ONE loop, one byte per trip, short ifs inside: each `if` ends where the lanes of a warp
+    // meet again.  Nested loops here make the compiler put that meeting point after the whole
+    // nest, and 32 lanes then drift apart and run one at a time.)
     uint32_t pos = begin;
-#if defined(__CUDA_ARCH__)
-    // bytes come from two 8-byte registers: `buf` is being eaten, `ahead` was requested eight
-    // bytes earlier, so the load has had time to land
-    // (a scoreboard covers a register for the whole warp, so every lane's refill makes all 32
-    // wait for it: the line is asked for 256 bytes early to make that wait an L1 hit)
-    uint64_t buf = *reinterpret_cast<const uint64_t *>(t + (pos & ~7u)) >> ((pos & 7u) * 8);
-    uint64_t ahead = *reinterpret_cast<const uint64_t *>(t + (pos & ~7u) + 8);
-    for (uint32_t k = 0; k < 256; k += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(t + (pos & ~127u) + k));
-    auto refill = [&]() {
-        buf = ahead;
-        ahead = *reinterpret_cast<const uint64_t *>(t + pos + 8);
-        if ((pos & 127u) == 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(t + pos + 256));
-    };
-#endif
+    feed.start(pos);
     while (pos < end && !flag && !done) {
-        uint8_t act = A_NONE, ns = st;
-        unsigned char c = 0;
+        unsigned e = 0, c = 0;
+        bool pending = false;
         // FAST: until a boundary that needs the slow handler
         while (pos < end) {
-#if defined(__CUDA_ARCH__)
-            c = (unsigned char)buf;
-#else
-            c = t[pos];
-#endif
-            const uint16_t e = fused[st * 256 + c];
-            act = (uint8_t)(e >> 8);
-            ns = (uint8_t)e;
-            if (act != A_NONE) {
-                if (depth <= quiet_base) break;                        // roles matter here
+            c = feed.get(pos);
+            e = lex.next(row, c);
+            if (e >> 24) {                                             // some action
+                if (depth <= quiet_base) { pending = true; break; }    // roles matter here
                 // quiet: container types are all that is needed
-                if (act == A_NUM_END) {
-                    const uint16_t e2 = fused[S_AFTER * 256 + c];
-                    act = (uint8_t)(e2 >> 8);
-                    ns = (uint8_t)e2;
-                }
+                const unsigned act = (e >> 24) & 0x7fu;
+                e &= 0xFFFFFFu;
                 if (act == A_OPEN) {
                     if (depth >= kMaxBitDepth) { flag = kFlagTooDeep; break; }
                     bits = (bits << 1) | (c == '[' ? 1u : 0u);
@@ -694,37 +746,23 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
                     depth--;
                     if (depth == quiet_base) quiet_base = kNotQuiet;   // the subtree is over; its value needed no handling
                 } else if (act == A_COMMA) {
-                    ns = (bits & 1) ? S_VAL : S_KEY;
-                } else if (act == A_KEY_BEGIN) {
-                    is_key = true;
-                } else if (act == A_STR_BEGIN) {
-                    is_key = false;
-                } else if (act == A_STR_END) {
-                    ns = is_key ? S_COLON : S_AFTER;
+                    e = lex.row((bits & 1) ? S_VAL : S_KEY);
                 } else if (act == A_ERR) {
                     flag = kFlagSyntax;
                     break;
                 }
-                act = A_NONE;
             } else {
                 hash = (hash ^ c) * 16777619u;
-                if (ns == S_ESC) escaped = true;
             }
-            st = ns;
+            row = e;
             pos++;
-#if defined(__CUDA_ARCH__)
-            buf >>= 8;
-            if ((pos & 7u) == 0) refill();
-#endif
+            if ((pos & 15u) == 0) feed.entered_window(pos);
         }
-        if (act == A_NONE || flag) continue;                           // ran out of bytes, or flagged while quiet
+        if (!pending) continue;                                        // out of bytes, or flagged while quiet
         // SLOW: the lanes of a warp arrive here together
-        slow(act, ns, c, pos);
+        slow(e >> 24, e & 0xFFFFFFu, c, pos);
         pos++;
-#if defined(__CUDA_ARCH__)
-        buf >>= 8;
-        if ((pos & 7u) == 0) refill();
-#endif
+        if ((pos & 15u) == 0) feed.entered_window(pos);
     }
     if (!flag && !done) flag = kFlagSyntax;                            // ran out of bytes inside the item
     if (!flag)
