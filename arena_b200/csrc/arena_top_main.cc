@@ -5,7 +5,10 @@
 //   arena-top node [-d|--details] --pods PODLIST.json --nodes NODELIST.json
 //   arena-top job  --pods PODLIST.json --nodes NODELIST.json --jobs JOBLIST.json
 //                  [--tfjobs TFJOBLIST.json] --releases HELM_LIST.txt [--now UNIX_SECONDS]
-// Common: [--device N] [--time]
+// Common: [--device N] [--time] [--loader host|device]
+//   --loader device (the default for `node` without -d): the PodList is parsed on the GPU
+//   (arena_load_json_device); host: the C++ loader + upload (always used for -d and for `job`,
+//   which need pod names and labels on the host).
 // Errors are printed to stdout and the exit status is 1, as in the reference
 // (`fmt.Println(err); os.Exit(1)`, top_node.go:34-48).
 #include "../../include/arena_top.h"
@@ -50,6 +53,7 @@ int main(int argc, char **argv)
     }
     const bool is_node = strcmp(argv[1], "node") == 0;
     bool details = false, timing = false;
+    const char *loader = nullptr;
     int device = 0;
     long long now = (long long)time(nullptr);
     const char *pods_path = nullptr, *nodes_path = nullptr, *jobs_path = nullptr, *tfjobs_path = nullptr,
@@ -66,6 +70,7 @@ int main(int argc, char **argv)
         else if (a == "--tfjobs") { if (!need(&tfjobs_path)) return die("flag needs an argument: --tfjobs"); }
         else if (a == "--releases") { if (!need(&releases_path)) return die("flag needs an argument: --releases"); }
         else if (a == "--device") { if (!need(&tmp)) return die("flag needs an argument: --device"); device = atoi(tmp); }
+        else if (a == "--loader") { if (!need(&loader)) return die("flag needs an argument: --loader"); }
         else if (a == "--now") { if (!need(&tmp)) return die("flag needs an argument: --now"); now = atoll(tmp); }
         else return die("unknown flag: " + a);
     }
@@ -77,6 +82,40 @@ int main(int argc, char **argv)
     if (jobs_path && !slurp(jobs_path, jobs)) return die(std::string("open ") + jobs_path + ": no such file or directory");
     if (tfjobs_path && !slurp(tfjobs_path, tfjobs)) return die(std::string("open ") + tfjobs_path + ": no such file or directory");
     if (releases_path && !slurp(releases_path, releases)) return die(std::string("open ") + releases_path + ": no such file or directory");
+
+    if (loader && strcmp(loader, "host") != 0 && strcmp(loader, "device") != 0) return die("--loader must be host or device");
+    const bool device_loader = is_node && !details && !(loader && strcmp(loader, "host") == 0);
+    if (loader && strcmp(loader, "device") == 0 && !device_loader) return die("--loader device serves `top node` without -d only");
+    if (device_loader) {
+        if (arena_acct_init(device)) return die_arena();
+        auto t0 = std::chrono::steady_clock::now();
+        arena_host_snapshot *node_names = nullptr;
+        arena_snapshot *dev = nullptr;
+        arena_load_device_stats st;
+        if (arena_load_json_device(pods.data(), pods.size(), nodes.data(), nodes.size(), &node_names, &dev, &st)) return die_arena();
+        auto t1 = std::chrono::steady_clock::now();
+        uint64_t counts[4];
+        arena_snapshot_counts(dev, counts);
+        std::vector<int64_t> total(counts[2] + 1), alloc(counts[2] + 1);
+        int64_t cluster[2];
+        char *text = nullptr;
+        size_t len = 0;
+        if (arena_top_node(dev, total.data(), alloc.data(), cluster, nullptr)) return die_arena();
+        if (arena_format_top_node(node_names, total.data(), alloc.data(), nullptr, 0, &text, &len)) return die_arena();
+        auto t2 = std::chrono::steady_clock::now();
+        fwrite(text, 1, len, stdout);
+        arena_free_text(text);
+        if (timing) {
+            auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+            fprintf(stderr, "[arena-top] pods=%llu nodes=%llu  device load %.2f ms (%s; copy %.2f ms), query+format %.2f ms\n",
+                    (unsigned long long)counts[0], (unsigned long long)counts[2], ms(t0, t1),
+                    st.fell_back ? "host loader took over" : "parsed on the GPU", st.ms_h2d, ms(t1, t2));
+        }
+        arena_snapshot_free(dev);
+        arena_host_snapshot_free(node_names);
+        arena_acct_shutdown();
+        return 0;
+    }
 
     auto t0 = std::chrono::steady_clock::now();
     arena_host_snapshot *host = nullptr;

@@ -175,6 +175,45 @@ def run_reference_arm(args):
     return 0
 
 
+def wire_format_leg(ab, n_pods=10_000, n_nodes=1000, reps=5):
+    """JSON PodList/NodeList -> columns -> `top node` table, wall clock around the C-ABI calls."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import loader_timing
+    log(f"[rank 0] wire_format leg ({n_pods} pods)...")
+    pods, nodes = loader_timing.make_docs(n_pods, n_nodes, seed=1)
+    pinned = ab.PinnedBuffer(len(pods)).fill(pods)
+
+    def best(fn):
+        t_best, out = float("inf"), None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            out = fn()
+            t_best = min(t_best, time.perf_counter() - t0)
+        return t_best * 1e3, out
+
+    def host_path():
+        h = ab.HostSnapshot.from_json(pods, nodes)
+        return ab.top_node(ab.DeviceSnapshot.upload(h)).cluster.tolist()
+
+    def device_path(src):
+        dev, st = ab.DeviceSnapshot.from_json_device(src, nodes)
+        return ab.top_node(dev).cluster.tolist(), st
+
+    host_ms, host_cluster = best(host_path)
+    dev_ms, (dev_cluster, st) = best(lambda: device_path(pods))
+    pin_ms, (pin_cluster, st_pin) = best(lambda: device_path(pinned))
+    assert host_cluster == dev_cluster == pin_cluster, "loaders disagree"
+    return {
+        "workload": f"API-server-shaped PodList, {n_pods} pods / {n_nodes} nodes (BASELINE configs[1] scale), "
+                    f"{len(pods)} bytes of JSON, then one `top node`",
+        "host_loader_ms": host_ms, "host_threads": os.cpu_count(),
+        "gpu_loader_ms": dev_ms, "gpu_loader_pinned_input_ms": pin_ms,
+        "gpu_loader_h2d_ms": st_pin["ms_h2d"], "fell_back": int(st["fell_back"] or st_pin["fell_back"]),
+        "pods_per_s_host": n_pods / host_ms * 1e3, "pods_per_s_gpu_pinned": n_pods / pin_ms * 1e3,
+        "json_gb_per_s_gpu_pinned": len(pods) / pin_ms / 1e6,
+    }
+
+
 def workload_config(n_gpus: int, scaling: str):
     if scaling == "strong" and n_gpus > 1:
         wl = (f"BASELINE configs[3]: synthetic snapshot of 1e8 pods / 1e6 nodes (seed 1) cut into {n_gpus} node ranges, "
@@ -200,6 +239,7 @@ def main():
     ap.add_argument("--nodes", type=int, default=NODES_FULL)
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
@@ -402,6 +442,13 @@ def main():
             "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
             "faithful_nested_loop_sample": r["b1_sample"],
         }
+    if not args.no_wire and world == 1:
+        # the step in FRONT of the hot path, reported beside it: an API-server-shaped PodList of
+        # BASELINE configs[1]'s size parsed by the host loader and by the GPU loader
+        try:
+            line["wire_format"] = wire_format_leg(ab)
+        except Exception as e:                      # never lose the headline over the side measurement
+            line["wire_format"] = {"error": repr(e)}
     sys.stdout.flush()
     os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:

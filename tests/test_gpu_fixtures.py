@@ -74,7 +74,10 @@ def run_cli(*args):
 
 def test_cli_matches_expected_output(gpu):
     pods, nodes = os.path.join(D, "pods.json"), os.path.join(D, "nodes.json")
-    rc, out, _ = run_cli("node", "--pods", pods, "--nodes", nodes)
+    rc, out, err = run_cli("node", "--pods", pods, "--nodes", nodes, "--time")     # default: the GPU loader ...
+    assert rc == 0 and out == rd("expected_top_node.txt", "r")
+    assert "host loader took over" in err           # ... which hands this edge-case fixture to the host loader
+    rc, out, _ = run_cli("node", "--pods", pods, "--nodes", nodes, "--loader", "host")
     assert rc == 0 and out == rd("expected_top_node.txt", "r")
     rc, out, _ = run_cli("node", "-d", "--pods", pods, "--nodes", nodes)
     assert rc == 0 and out == rd("expected_top_node_details.txt", "r")
@@ -82,6 +85,23 @@ def test_cli_matches_expected_output(gpu):
                            os.path.join(D, "tfjobs.json"), "--releases", os.path.join(D, "helm_list.txt"), "--now",
                            str(MF.NOW), "--time")
     assert rc == 0 and out == rd("expected_top_job.txt", "r") and "[arena-top]" in err
+
+
+def test_cli_parses_an_api_server_shaped_list_on_the_gpu(gpu, tmp_path):
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import loader_timing as LT
+    pods, nodes = LT.make_docs(2000, 40, seed=9)
+    (tmp_path / "pods.json").write_bytes(pods)
+    (tmp_path / "nodes.json").write_bytes(nodes)
+    want, _ = top_ref.top_node(pods, nodes)
+    for loader in ("device", "host"):
+        rc, out, err = run_cli("node", "--pods", str(tmp_path / "pods.json"), "--nodes", str(tmp_path / "nodes.json"),
+                               "--loader", loader, "--time")
+        assert rc == 0 and out == want, loader
+        assert ("parsed on the GPU" in err) == (loader == "device")
+    rc, out, _ = run_cli("node", "-d", "--pods", str(tmp_path / "pods.json"), "--nodes", str(tmp_path / "nodes.json"),
+                         "--loader", "device")
+    assert rc == 1 and "without -d" in out
 
 
 def test_cli_error_behaviour(gpu, tmp_path):
