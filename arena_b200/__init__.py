@@ -5,7 +5,7 @@ sm_100a kernels behind a C ABI, include/*.h); this package is the thin host
 mirror used by the tests, the bench and the multi-GPU driver."""
 
 from ._lib import ARENA_NONE, ArenaError, init, lib  # noqa: F401
-from .snapshot import DeviceSnapshot, HostSnapshot, PinnedBuffer  # noqa: F401
+from .snapshot import DeviceSnapshot, HostSnapshot, PackedSnapshot, PinnedBuffer  # noqa: F401
 from .top import (TopJobResult, TopNodeResult, format_top_job, format_top_node,  # noqa: F401
                   quantity_values, top_job, top_job_device, top_job_device_noalloc, top_node,
-                  top_node_device)
+                  top_node_device, top_node_packed)

@@ -33,6 +33,15 @@ class SnapshotView(C.Structure):
     ]
 
 
+class PackedView(C.Structure):
+    """struct arena_packed_view"""
+    _fields_ = [
+        ("n_pods", C.c_uint64), ("n_containers", C.c_uint64), ("n_nodes", C.c_uint64),
+        ("node_pod_begin", C.c_void_p), ("pod_meta", C.c_void_p), ("ctr_gpu", C.c_void_p),
+        ("node_cap_val", C.c_void_p), ("node_cap_scale", C.c_void_p), ("ctr_bits", C.c_uint32),
+    ]
+
+
 class LoadDeviceStats(C.Structure):
     """struct arena_load_device_stats"""
     _fields_ = [
@@ -67,6 +76,7 @@ _SIGS = [
     ("arena_top_node", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_host", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP]),
+    ("arena_top_node_host_packed", C.c_int, [C.POINTER(PackedView), _VP, _VP, _VP, _VP]),
     ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device_noalloc", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP, _VP, _VP]),
@@ -87,6 +97,9 @@ _SIGS = [
                                          C.POINTER(LoadDeviceStats)]),
     ("arena_scan_podlist_host", C.c_int, [C.c_char_p, C.c_size_t, _VP, C.c_uint64, C.POINTER(C.c_uint64), _VP, _VP, _VP,
                                           _VP, _VP]),
+    ("arena_host_snapshot_pack", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.POINTER(_VP)]),
+    ("arena_packed_snapshot_view", C.c_int, [_VP, C.POINTER(PackedView)]),
+    ("arena_packed_snapshot_free", None, [_VP]),
     ("arena_host_pod_order", _VP, [_VP]),
     ("arena_host_job_name", C.c_char_p, [_VP, C.c_uint32]),
     ("arena_host_job_trainer", C.c_char_p, [_VP, C.c_uint32]),

@@ -78,6 +78,8 @@ struct arena_snapshot {
 };
 
 static arena_snapshot *g_host_snap = nullptr;    // staging snapshot of arena_top_node_host
+static void *g_packed_block = nullptr;           // staging of arena_top_node_host_packed: packed columns + tile sums
+static size_t g_packed_bytes = 0;
 
 extern "C" {
 
@@ -117,6 +119,7 @@ void arena_acct_shutdown(void)
     cudaSetDevice(g_ctx.device);
     cudaStreamSynchronize(g_ctx.stream);
     if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
+    if (g_packed_block) { cudaFree(g_packed_block); g_packed_block = nullptr; g_packed_bytes = 0; }
     arena_internal::free_loader_workspace();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx = Context{};
@@ -350,12 +353,18 @@ extern "C" {
 // column padded to 16 bytes plus a spare vector so aligned 128-bit reads stay
 // inside it) and point s->v at the device copies.  Asynchronous on the
 // library stream.
-static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool jobs)
+// Device block of `s` sized for (P, C, N) wide columns; with `h` the host columns are copied in
+// (async, library stream), without it they are left for the caller to fill.
+static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool jobs, const u64 *pcn = nullptr)
 {
-    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
+    const u64 P = h ? h->n_pods : pcn[0], C = h ? h->n_containers : pcn[1], N = h ? h->n_nodes : pcn[2];
     size_t sizes[10] = {P * 4, P, (P + 1) * 4, C * 8, C, N * 8, N, jobs ? P * 4 : 0, jobs ? P : 0, jobs ? P * 8 : 0};
-    const void *src[10] = {h->pod_node, h->pod_phase, h->pod_ctr_begin, h->ctr_val, h->ctr_scale,
-                           h->node_cap_val, h->node_cap_scale, h->pod_job, h->pod_role, h->pod_created};
+    const void *src[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (h) {
+        const void *from[10] = {h->pod_node, h->pod_phase, h->pod_ctr_begin, h->ctr_val, h->ctr_scale,
+                                h->node_cap_val, h->node_cap_scale, h->pod_job, h->pod_role, h->pod_created};
+        for (int i = 0; i < 10; i++) src[i] = from[i];
+    }
     size_t total = 0;
     for (size_t z : sizes) total += pad16(z) + 16;
     if (total < 16) total = 16;
@@ -374,13 +383,14 @@ static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool j
     const void *dst[10];
     for (int i = 0; i < 10; i++) {
         dst[i] = p;
-        if (sizes[i]) {
+        if (sizes[i] && src[i]) {
             cudaError_t e = cudaMemcpyAsync(p, src[i], sizes[i], cudaMemcpyHostToDevice, g_ctx.stream);
             if (e != cudaSuccess) return fail(ARENA_E_CUDA, "H2D copy of column %d: %s", i, cudaGetErrorString(e));
         }
         p += pad16(sizes[i]) + 16;
     }
-    s->v = *h;
+    if (h) s->v = *h;
+    else { s->v = arena_snapshot_view{}; s->v.n_pods = P; s->v.n_containers = C; s->v.n_nodes = N; }
     s->v.pod_node = (const uint32_t *)dst[0];
     s->v.pod_phase = (const uint8_t *)dst[1];
     s->v.pod_ctr_begin = (const uint32_t *)dst[2];
@@ -587,6 +597,79 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
         g_host_snap->direct = diff * 4u > n;
     }
     return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
+}
+
+int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2],
+                               int64_t *pod_gpu)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!h) return fail(ARENA_E_INVALID, "packed view is NULL");
+    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
+    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
+    if (!h->node_pod_begin || (P && !h->pod_meta) || (C && !h->ctr_gpu) || (N && (!h->node_cap_val || !h->node_cap_scale)))
+        return fail(ARENA_E_INVALID, "packed columns are NULL");
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    if (!g_host_snap) {
+        g_host_snap = new (std::nothrow) arena_snapshot();
+        if (!g_host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
+        rc = alloc_common(g_host_snap);
+        if (rc) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; return rc; }
+    }
+    const u64 pcn[3] = {P, C, N};
+    rc = fill_snapshot(g_host_snap, nullptr, false, pcn);       // wide columns: reserved, filled below on the device
+    if (rc) return rc;
+    const arena_snapshot_view &w = g_host_snap->v;
+    cudaStream_t st = g_ctx.stream;
+
+    // packed staging: [node_pod_begin | pod_meta (word padded) | ctr_gpu (word padded) | tile sums]
+    if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);
+    const u64 gpu_bytes = h->ctr_bits == 4 ? (C + 1) / 2 : C;
+    const u64 meta_words = (P + 3) / 4, gpu_words = (gpu_bytes + 3) / 4, tiles = (meta_words + 255) / 256;
+    const size_t o_begin = 0, o_meta = o_begin + pad16((N + 1) * 4), o_gpu = o_meta + pad16(meta_words * 4 + 4),
+                 o_tiles = o_gpu + pad16(gpu_words * 4 + 4), need = o_tiles + pad16((tiles + 1) * 4);
+    if (g_packed_bytes < need) {
+        if (g_packed_block) cudaFree(g_packed_block);
+        g_packed_block = nullptr;
+        g_packed_bytes = 0;
+        CUDA_TRY(cudaMalloc(&g_packed_block, need));
+        g_packed_bytes = need;
+    }
+    char *pb = (char *)g_packed_block;
+    unsigned *d_begin = (unsigned *)(pb + o_begin), *d_meta = (unsigned *)(pb + o_meta), *d_gpu = (unsigned *)(pb + o_gpu),
+             *d_tiles = (unsigned *)(pb + o_tiles);
+    if (P & 3) CUDA_TRY(cudaMemsetAsync(d_meta + (meta_words - 1), 0, 4, st));       // the pods past P count nothing
+    if (gpu_bytes & 3) CUDA_TRY(cudaMemsetAsync(d_gpu + (gpu_words - 1), 0, 4, st));
+    CUDA_TRY(cudaMemcpyAsync(d_begin, h->node_pod_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (P) CUDA_TRY(cudaMemcpyAsync(d_meta, h->pod_meta, P, cudaMemcpyHostToDevice, st));
+    if (C) CUDA_TRY(cudaMemcpyAsync(d_gpu, h->ctr_gpu, gpu_bytes, cudaMemcpyHostToDevice, st));
+    if (N) {
+        CUDA_TRY(cudaMemcpyAsync(const_cast<int64_t *>(w.node_cap_val), h->node_cap_val, N * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(const_cast<int8_t *>(w.node_cap_scale), h->node_cap_scale, N, cudaMemcpyHostToDevice, st));
+    }
+    // expansion into the wide layout
+    if (C) CUDA_TRY(cudaMemsetAsync(const_cast<int8_t *>(w.ctr_scale), 0, C, st));   // ctr_gpu is a resolved Value(): scale 0
+    if (P) {
+        packed_tile_counts_kernel<<<(unsigned)tiles, 256, 0, st>>>(d_meta, meta_words, d_tiles);
+        packed_tile_scan_kernel<<<1, 1024, 0, st>>>(d_tiles, tiles);
+        packed_expand_pods_kernel<<<(unsigned)tiles, 256, 0, st>>>(d_meta, meta_words, P, C, d_tiles,
+                                                                  const_cast<unsigned *>(w.pod_ctr_begin),
+                                                                  (unsigned *)const_cast<uint8_t *>(w.pod_phase));
+        packed_expand_nodes_kernel<<<(unsigned)((N + 1 + 7) / 8), 256, 0, st>>>(d_begin, N, P, const_cast<unsigned *>(w.pod_node));
+        g_launches.fetch_add(4, std::memory_order_relaxed);
+    } else {
+        CUDA_TRY(cudaMemsetAsync(const_cast<unsigned *>(w.pod_ctr_begin), 0, 4, st));
+    }
+    if (C) {
+        longlong2 *dst = (longlong2 *)const_cast<int64_t *>(w.ctr_val);
+        const unsigned grid = (unsigned)((gpu_words + 255) / 256);
+        if (h->ctr_bits == 4) packed_expand_ctrs_kernel<4><<<grid, 256, 0, st>>>(d_gpu, gpu_words, (C + 1) / 2, dst);
+        else packed_expand_ctrs_kernel<8><<<grid, 256, 0, st>>>(d_gpu, gpu_words, (C + 1) / 2, dst);
+        count_launch();
+    }
+    CUDA_TRY(cudaGetLastError());
+    g_host_snap->direct = false;                                // grouped by construction
+    return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);
 }
 
 int arena_top_job_device(const arena_snapshot *cs, int64_t *d_job_req, int64_t *d_job_alloc,

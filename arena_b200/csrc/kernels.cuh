@@ -1012,3 +1012,120 @@ __global__ void quantity_values_kernel(const i64 *val, const signed char *scale,
 }
 
 }  // namespace arena
+
+// ---- packed host snapshots: expansion into the wide layout (arena_top_node_host_packed) ---------
+// pod_meta: low nibble phase, high nibble container count.  Tile = 1024 pods = one CTA of 256
+// threads, four pods (one 32-bit word) per thread.
+namespace arena {
+
+constexpr int kPackTile = 1024;
+
+__device__ __forceinline__ unsigned packed_counts(unsigned meta4) { return (meta4 >> 4) & 0x0f0f0f0fu; }
+
+__device__ __forceinline__ unsigned cta256_exclusive_sum(unsigned mine, unsigned &total)
+{
+    __shared__ unsigned warp_tot[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned inc = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += up;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    unsigned before = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        if (w < warp) before += warp_tot[w];
+        all += warp_tot[w];
+    }
+    total = all;
+    __syncthreads();
+    return before + inc - mine;
+}
+
+// containers per tile
+__global__ void __launch_bounds__(256) packed_tile_counts_kernel(const unsigned *__restrict__ meta4, u64 n_words,
+                                                                 unsigned *__restrict__ tile_sum)
+{
+    const u64 w = (u64)blockIdx.x * 256 + threadIdx.x;
+    const unsigned c = w < n_words ? packed_counts(__ldg(meta4 + w)) : 0u;
+    unsigned total;
+    cta256_exclusive_sum((c * 0x01010101u) >> 24, total);
+    if (threadIdx.x == 0) tile_sum[blockIdx.x] = total;
+}
+
+// exclusive scan of the tile sums, in place: one CTA of 1024 threads
+__global__ void __launch_bounds__(1024) packed_tile_scan_kernel(unsigned *__restrict__ tile_sum, u64 n_tiles)
+{
+    __shared__ unsigned part[1024];
+    const u64 per = (n_tiles + 1023) / 1024;
+    const u64 lo = (u64)threadIdx.x * per, hi = lo + per < n_tiles ? lo + per : n_tiles;
+    unsigned s = 0;
+    for (u64 t = lo; t < hi; t++) s += tile_sum[t];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {                 // Hillis-Steele: 10 rounds
+        const unsigned v = threadIdx.x >= (unsigned)off ? part[threadIdx.x - off] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned run = part[threadIdx.x] - s;
+    for (u64 t = lo; t < hi; t++) { const unsigned v = tile_sum[t]; tile_sum[t] = run; run += v; }
+}
+
+// pod_ctr_begin and pod_phase of four pods per thread
+__global__ void __launch_bounds__(256) packed_expand_pods_kernel(const unsigned *__restrict__ meta4, u64 n_words, u64 P, u64 C,
+                                                                 const unsigned *__restrict__ tile_base,
+                                                                 unsigned *__restrict__ pod_ctr_begin,
+                                                                 unsigned *__restrict__ pod_phase4)
+{
+    const u64 w = (u64)blockIdx.x * 256 + threadIdx.x;
+    const unsigned m = w < n_words ? __ldg(meta4 + w) : 0u;
+    const unsigned c = packed_counts(m);
+    unsigned total;
+    const unsigned b0 = tile_base[blockIdx.x] + cta256_exclusive_sum((c * 0x01010101u) >> 24, total);
+    if (w < n_words) {
+        const unsigned b1 = b0 + (c & 0xffu), b2 = b1 + ((c >> 8) & 0xffu), b3 = b2 + ((c >> 16) & 0xffu);
+        reinterpret_cast<uint4 *>(pod_ctr_begin)[w] = make_uint4(b0, b1, b2, b3);
+        unsigned ph = m & 0x0f0f0f0fu;                           // nibble 15 = "some other phase" = 255
+        ph |= __vcmpeq4(ph, 0x0f0f0f0fu) & 0xf0f0f0f0u;
+        pod_phase4[w] = ph;
+    }
+    if (w == 0) pod_ctr_begin[P] = (unsigned)C;                 // (written after the vector store of a tiny snapshot too)
+}
+
+// ctr_val (int64, scale 0): four containers per thread from bytes, eight from nibbles
+// (n_pairs = ceil(C / 2): the column has room for whole pairs, not for whole words of them)
+template <int kBits>
+__global__ void __launch_bounds__(256) packed_expand_ctrs_kernel(const unsigned *__restrict__ gpu4, u64 n_words, u64 n_pairs,
+                                                                 longlong2 *__restrict__ ctr_val2)
+{
+    const u64 w = (u64)blockIdx.x * 256 + threadIdx.x;
+    if (w >= n_words) return;
+    const unsigned g = __ldg(gpu4 + w);
+    if (kBits == 8) {
+        if (2 * w < n_pairs) ctr_val2[2 * w] = make_longlong2((long long)(g & 0xffu), (long long)((g >> 8) & 0xffu));
+        if (2 * w + 1 < n_pairs) ctr_val2[2 * w + 1] = make_longlong2((long long)((g >> 16) & 0xffu), (long long)(g >> 24));
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (4 * w + k < n_pairs)
+                ctr_val2[4 * w + k] = make_longlong2((long long)((g >> (8 * k)) & 0xfu), (long long)((g >> (8 * k + 4)) & 0xfu));
+    }
+}
+
+// pod_node: one warp per node fills its rows; warp N fills the rows that name no node
+__global__ void __launch_bounds__(256) packed_expand_nodes_kernel(const unsigned *__restrict__ node_pod_begin, u64 N, u64 P,
+                                                                  unsigned *__restrict__ pod_node)
+{
+    const u64 n = (u64)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (n > N) return;
+    const u64 lo = node_pod_begin[n], hi = n < N ? (u64)node_pod_begin[n + 1] : P;
+    const unsigned id = n < N ? (unsigned)n : kNone;
+    for (u64 r = lo + (threadIdx.x & 31); r < hi; r += 32) pod_node[r] = id;
+}
+
+}  // namespace arena

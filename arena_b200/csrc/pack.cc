@@ -1,0 +1,100 @@
+// Wide host snapshot -> packed host snapshot (include/arena_gpuacct.h: arena_packed_view):
+// one byte per pod, one per container, one row range per node.  The container byte is the
+// RESOLVED Quantity.Value() (amount and scale folded on the host, quantity.cc), so what the
+// device expands and sums is what the wide path decodes and sums.
+#include "host_snapshot.h"
+#include "quantity.h"
+
+#include <new>
+
+using namespace arena_host;
+
+struct arena_packed_snapshot {
+    arena_packed_view v{};
+    Column c_node_pod_begin, c_pod_meta, c_ctr_gpu, c_node_cap_val, c_node_cap_scale;
+};
+
+extern "C" {
+
+int arena_host_snapshot_pack(const arena_snapshot_view *h, int pinned, arena_packed_snapshot **out)
+{
+    if (!h || !out) return fail(ARENA_E_INVALID, "snapshot or out is NULL");
+    *out = nullptr;
+    const uint64_t P = h->n_pods, C = h->n_containers, N = h->n_nodes;
+    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
+    if (!h->pod_ctr_begin || (P && (!h->pod_node || !h->pod_phase)) || (C && (!h->ctr_val || !h->ctr_scale)) ||
+        (N && (!h->node_cap_val || !h->node_cap_scale)))
+        return fail(ARENA_E_INVALID, "snapshot columns are NULL");
+    arena_packed_snapshot *p = new (std::nothrow) arena_packed_snapshot();
+    if (!p) return fail(ARENA_E_NOMEM, "out of host memory");
+    int rc;
+    // sizes are rounded up so that the device can read whole 32-bit words past the end
+    if ((rc = p->c_node_pod_begin.alloc((N + 1) * 4, pinned != 0)) || (rc = p->c_pod_meta.alloc(P + 4, pinned != 0)) ||
+        (rc = p->c_ctr_gpu.alloc(C + 4, pinned != 0)) || (rc = p->c_node_cap_val.alloc(N * 8, pinned != 0)) ||
+        (rc = p->c_node_cap_scale.alloc(N, pinned != 0))) {
+        delete p;
+        return rc;
+    }
+    uint32_t *begin = p->c_node_pod_begin.as<uint32_t>();
+    uint8_t *meta = p->c_pod_meta.as<uint8_t>();
+    uint8_t *gpu = p->c_ctr_gpu.as<uint8_t>();
+    for (uint64_t k = 0; k < 4; k++) { meta[P + k] = 0; gpu[C + k] = 0; }
+
+    // rows must be grouped by node, in node order, the pods of no node last
+    uint64_t node = 0, prev_key = 0;         // node: next node whose first row has not been seen
+    for (uint64_t r = 0; r < P; r++) {
+        const uint32_t n = h->pod_node[r];
+        const uint64_t key = n == ARENA_NONE ? N : (uint64_t)n;
+        if (n != ARENA_NONE && n >= N) { delete p; return fail(ARENA_E_INVALID, "pod row %llu names node %u of %llu", (unsigned long long)r, n, (unsigned long long)N); }
+        if (key < prev_key) { delete p; return fail(ARENA_E_INVALID, "no packed form: rows are not grouped by node (row %llu)", (unsigned long long)r); }
+        prev_key = key;
+        while (node <= key) begin[node++] = (uint32_t)r;
+        const uint32_t cb = h->pod_ctr_begin[r], ce = h->pod_ctr_begin[r + 1];
+        if (ce < cb || ce > C) { delete p; return fail(ARENA_E_INVALID, "pod_ctr_begin is not a monotonic CSR at row %llu", (unsigned long long)r); }
+        if (ce - cb > 15) { delete p; return fail(ARENA_E_INVALID, "no packed form: pod row %llu has %u containers (15 at most)", (unsigned long long)r, ce - cb); }
+        const uint8_t ph = h->pod_phase[r];
+        uint8_t code;
+        if (ph <= ARENA_PHASE_UNKNOWN) code = ph;
+        else if (ph == ARENA_PHASE_OTHER) code = 15;
+        else { delete p; return fail(ARENA_E_INVALID, "no packed form: unknown phase code %u at row %llu", ph, (unsigned long long)r); }
+        meta[r] = (uint8_t)(code | ((ce - cb) << 4));
+    }
+    while (node <= N) begin[node++] = (uint32_t)P;
+    if (P && h->pod_ctr_begin[0] != 0) { delete p; return fail(ARENA_E_INVALID, "pod_ctr_begin[0] != 0"); }
+    if (h->pod_ctr_begin[P] != C) { delete p; return fail(ARENA_E_INVALID, "pod_ctr_begin[P] != n_containers"); }
+    uint8_t top = 0;
+    for (uint64_t c = 0; c < C; c++) {
+        const int64_t v = amount_value(h->ctr_val[c], h->ctr_scale[c]);        // Quantity.Value()
+        if (v < 0 || v > 255) { delete p; return fail(ARENA_E_INVALID, "no packed form: container %llu holds %lld GPUs (0..255)", (unsigned long long)c, (long long)v); }
+        gpu[c] = (uint8_t)v;
+        top |= (uint8_t)v;
+    }
+    p->v.ctr_bits = 8;
+    if (top < 16) {                          // every container fits a nibble: halve the column in place
+        for (uint64_t c = 0; c + 1 < C; c += 2) gpu[c / 2] = (uint8_t)(gpu[c] | (gpu[c + 1] << 4));
+        if (C & 1) gpu[C / 2] = gpu[C - 1];
+        for (uint64_t k = (C + 1) / 2; k < (C + 1) / 2 + 4 && k < C + 4; k++) gpu[k] = 0;
+        p->v.ctr_bits = 4;
+    }
+    for (uint64_t n = 0; n < N; n++) {
+        p->c_node_cap_val.as<int64_t>()[n] = h->node_cap_val[n];
+        p->c_node_cap_scale.as<int8_t>()[n] = h->node_cap_scale[n];
+    }
+    p->v.n_pods = P; p->v.n_containers = C; p->v.n_nodes = N;
+    p->v.node_pod_begin = begin; p->v.pod_meta = meta; p->v.ctr_gpu = gpu;
+    p->v.node_cap_val = p->c_node_cap_val.as<int64_t>();
+    p->v.node_cap_scale = p->c_node_cap_scale.as<int8_t>();
+    *out = p;
+    return ARENA_OK;
+}
+
+int arena_packed_snapshot_view(const arena_packed_snapshot *p, arena_packed_view *out)
+{
+    if (!p || !out) return fail(ARENA_E_INVALID, "packed snapshot or out is NULL");
+    *out = p->v;
+    return ARENA_OK;
+}
+
+void arena_packed_snapshot_free(arena_packed_snapshot *p) { delete p; }
+
+}  // extern "C"

@@ -61,12 +61,17 @@ def gather_tables(local_total: np.ndarray, local_alloc: np.ndarray, dst: int = 0
     return np.concatenate([o[0] for o in out]), np.concatenate([o[1] for o in out])
 
 
-def top_node_sharded(host_shard, details: bool = False):
-    """End-to-end sharded `top node` for this rank's shard (a HostSnapshot):
-    upload + kernels + download through the C ABI, then the totals all-reduce.
-    Returns (TopNodeResult of the shard, global cluster totals int64[2])."""
-    from .top import top_node
-    res = top_node(host_shard, details=details)
+def top_node_sharded(host_shard, details: bool = False, out=None):
+    """End-to-end sharded `top node` for this rank's shard (a HostSnapshot, or a
+    PackedSnapshot of it): upload + kernels + download through the C ABI, then the totals
+    all-reduce.  `out`: a TopNodeResult to write into (page-locked arrays make the download a
+    straight DMA).  Returns (TopNodeResult of the shard, global cluster totals int64[2])."""
+    from .snapshot import PackedSnapshot
+    from .top import top_node, top_node_packed
+    if isinstance(host_shard, PackedSnapshot):
+        res = top_node_packed(host_shard, details=details, out=out)
+    else:
+        res = top_node(host_shard, details=details, out=out)
     t = torch.from_numpy(res.cluster.copy())
     if dist.is_initialized() and dist.get_world_size() > 1 and dist.get_backend() == "nccl":
         t = t.cuda()

@@ -13,7 +13,7 @@ from typing import Dict, Optional
 import numpy as np
 
 from . import _lib
-from ._lib import ArenaError, LoadDeviceStats, SnapshotView, SynthParams, check, lib
+from ._lib import ArenaError, LoadDeviceStats, PackedView, SnapshotView, SynthParams, check, lib
 
 _COLS = [
     # name, dtype, length as a function of the view
@@ -147,6 +147,10 @@ class HostSnapshot:
     def pod_name(self, row: int) -> str:
         return lib().arena_host_pod_name(self._h, row).decode()
 
+    def pack(self, pinned: bool = False) -> "PackedSnapshot":
+        """arena_host_snapshot_pack (raises ArenaError -1 when there is no packed form)."""
+        return PackedSnapshot(self, pinned)
+
     # -- sharding ---------------------------------------------------------------
     def shard_plan(self, n_shards: int, by_job: bool = False):
         key_cut = np.zeros(n_shards + 1, np.uint64)
@@ -184,6 +188,37 @@ class HostSnapshot:
             lib().arena_host_snapshot_free(self._h)
             self._h = None
         self.cols = {}
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PackedSnapshot:
+    """`arena_packed_snapshot*`: one byte per pod, one per container, one row range per node
+    (the host side of arena_top_node_host_packed)."""
+
+    def __init__(self, host: "HostSnapshot", pinned: bool = False):
+        h = C.c_void_p()
+        check(lib().arena_host_snapshot_pack(C.byref(host.view), int(pinned), C.byref(h)))
+        self._h = h.value
+        self.view = PackedView()
+        check(lib().arena_packed_snapshot_view(self._h, C.byref(self.view)))
+        self.n_pods, self.n_containers, self.n_nodes = (int(self.view.n_pods), int(self.view.n_containers),
+                                                        int(self.view.n_nodes))
+
+    @property
+    def nbytes(self) -> int:
+        """bytes the one-shot call copies to the device"""
+        ctr = (self.n_containers + 1) // 2 if self.view.ctr_bits == 4 else self.n_containers
+        return self.n_pods + ctr + 4 * (self.n_nodes + 1) + 9 * self.n_nodes
+
+    def close(self) -> None:
+        if self._h:
+            lib().arena_packed_snapshot_free(self._h)
+            self._h = None
 
     def __del__(self):
         try:

@@ -55,20 +55,34 @@ def _ptr(a: Optional[np.ndarray]):
     return a.ctypes.data if a is not None and a.size else None
 
 
-def top_node(snap: Union[DeviceSnapshot, HostSnapshot], details: bool = False) -> TopNodeResult:
+def _outputs(N: int, P: int, details: bool, out):
+    """Result arrays: fresh ones, or the caller's (e.g. page-locked, reused every call)."""
+    if out is not None:
+        assert len(out.node_total) == N and len(out.node_alloc) == N and (not details or len(out.pod_gpu) == P)
+        return out.node_total, out.node_alloc, out.cluster, out.pod_gpu if details else None
+    return (np.zeros(N, np.int64), np.zeros(N, np.int64), np.zeros(2, np.int64), np.zeros(P, np.int64) if details else None)
+
+
+def top_node(snap: Union[DeviceSnapshot, HostSnapshot], details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
     """Per-node table + cluster totals.  A HostSnapshot goes through the
     one-shot arena_top_node_host (upload + kernels + download)."""
     N, P = snap.n_nodes, snap.n_pods
-    total = np.zeros(N, np.int64)
-    alloc = np.zeros(N, np.int64)
-    cluster = np.zeros(2, np.int64)
-    pod_gpu = np.zeros(P, np.int64) if details else None
+    total, alloc, cluster, pod_gpu = _outputs(N, P, details, out)
     if isinstance(snap, HostSnapshot):
         check(lib().arena_top_node_host(C.byref(snap.view), _ptr(total), _ptr(alloc), cluster.ctypes.data,
                                         pod_gpu.ctypes.data if details and P else None))
     else:
         check(lib().arena_top_node(snap.handle, _ptr(total), _ptr(alloc), cluster.ctypes.data,
                                    pod_gpu.ctypes.data if details and P else None))
+    return TopNodeResult(total, alloc, cluster, pod_gpu)
+
+
+def top_node_packed(packed, details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
+    """arena_top_node_host_packed: one-shot upload of a PackedSnapshot + kernels + download."""
+    N, P = packed.n_nodes, packed.n_pods
+    total, alloc, cluster, pod_gpu = _outputs(N, P, details, out)
+    check(lib().arena_top_node_host_packed(C.byref(packed.view), _ptr(total), _ptr(alloc), cluster.ctypes.data,
+                                           pod_gpu.ctypes.data if details and P else None))
     return TopNodeResult(total, alloc, cluster, pod_gpu)
 
 

@@ -139,6 +139,39 @@ int  arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total,
                          int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
 
 /*
+ * The same one-shot call for a PACKED host snapshot: the narrowest exact encoding of what
+ * `top node` reads, for callers on the far side of PCIe (the copy is the whole cost of
+ * arena_top_node_host: 9 bytes per pod + 9 per container; packed it is 1 + 1).
+ *
+ *   node_pod_begin[N+1]  rows of node n are [b[n], b[n+1]): pods are grouped by node, in
+ *                        node order; rows from b[N] on name no node of the NodeList
+ *   pod_meta[P]          low nibble: phase (ARENA_PHASE_EMPTY..UNKNOWN = 0..5, 15 = any other
+ *                        phase string); high nibble: number of containers (0..15)
+ *   ctr_gpu              Quantity.Value() of the container's selected GPU limit (gpu.go:61-79,
+ *                        quantity.go:699-718) in pod order: ctr_bits == 8: one byte each, 0..255;
+ *                        ctr_bits == 4: two per byte, 0..15, container 2k in the low nibble
+ *   node_cap_val/scale   as in arena_snapshot_view
+ *
+ * A snapshot with a pod of more than 15 containers, a container above 255 GPUs or pods that
+ * are not grouped has no packed form: use the wide one (arena_host_snapshot_pack says so).
+ * On the device the packed columns are expanded into the wide layout by four small kernels
+ * and the ordinary kernels run on that: results are bit-identical by construction.
+ * pod_gpu (may be NULL) is per row, as in arena_top_node.  No reference counterpart.
+ */
+typedef struct arena_packed_view {
+    uint64_t n_pods, n_containers, n_nodes;
+    const uint32_t *node_pod_begin;
+    const uint8_t  *pod_meta;
+    const uint8_t  *ctr_gpu;
+    const int64_t  *node_cap_val;
+    const int8_t   *node_cap_scale;
+    uint32_t ctr_bits;                /* 8 or 4 */
+} arena_packed_view;
+
+int  arena_top_node_host_packed(const arena_packed_view *host, int64_t *node_total,
+                                int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
+
+/*
  * `arena top job`: TrainingJob.RequestedGPU / AllocatedGPU (job_info.go:51-70,
  * trainer_tensorflow.go:135-155) for every job, the "latest pod wins" rule of
  * trainer_mpi.go:263-278 / trainer_standalone.go:198-221, the ordering of

@@ -116,6 +116,17 @@ int  arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const
                              uint64_t capacity, uint64_t *n_items_out, uint32_t *pod_node, uint8_t *pod_phase,
                              uint32_t *pod_n_ctrs, int64_t *ctr_val, uint8_t *pod_flag);
 
+/*
+ * Packs a host snapshot (arena_snapshot_view with HOST pointers, rows grouped by node as the
+ * loader and the generators produce them) into the form arena_top_node_host_packed takes.
+ * ARENA_E_INVALID, with the reason in arena_last_error(), when the snapshot has no packed
+ * form.  pinned != 0 puts the columns in page-locked memory.
+ */
+typedef struct arena_packed_snapshot arena_packed_snapshot;
+int  arena_host_snapshot_pack(const arena_snapshot_view *host, int pinned, arena_packed_snapshot **out);
+int  arena_packed_snapshot_view(const arena_packed_snapshot *p, arena_packed_view *out);
+void arena_packed_snapshot_free(arena_packed_snapshot *p);
+
 /* Row -> original PodList index ([P]); job id -> name / trainer type; node id and
  * row -> metadata.name ("" for synthetic snapshots, which carry no names). */
 const uint32_t *arena_host_pod_order(const arena_host_snapshot *h);

@@ -1,0 +1,109 @@
+"""Packed host snapshots (arena_host_snapshot_pack / arena_top_node_host_packed): one byte per
+pod, one per container, one row range per node.  CPU part: the packing itself against numpy;
+GPU part: results bit-identical to the wide path and to the C oracle."""
+
+import numpy as np
+import pytest
+
+from oracle import cref
+
+
+def unpack(p):
+    """PackedSnapshot -> the wide columns it stands for (numpy), for comparison."""
+    import ctypes as C
+    P, Cn, N = p.n_pods, p.n_containers, p.n_nodes
+
+    def arr(ptr, n, dt):
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n * np.dtype(dt).itemsize,)).view(dt).copy()
+
+    begin = arr(p.view.node_pod_begin, N + 1, np.uint32)
+    meta = arr(p.view.pod_meta, P, np.uint8) if P else np.zeros(0, np.uint8)
+    if p.view.ctr_bits == 4:
+        half = arr(p.view.ctr_gpu, (Cn + 1) // 2, np.uint8) if Cn else np.zeros(0, np.uint8)
+        gpu = np.stack([half & 15, half >> 4], axis=1).reshape(-1)[:Cn]
+    else:
+        gpu = arr(p.view.ctr_gpu, Cn, np.uint8) if Cn else np.zeros(0, np.uint8)
+    return begin, meta, gpu
+
+
+@pytest.mark.parametrize("skewed", [False, True])
+def test_pack_is_the_wide_snapshot_in_fewer_bytes(built, skewed):
+    from arena_b200 import HostSnapshot
+    h = HostSnapshot.synth(30_000, 700, seed=11, skewed=skewed)
+    p = h.pack()
+    begin, meta, gpu = unpack(p)
+    pn = h.cols["pod_node"].astype(np.int64)
+    pn[pn == 0xFFFFFFFF] = h.n_nodes
+    assert np.array_equal(begin, np.searchsorted(pn, np.arange(h.n_nodes + 1), side="left").astype(np.uint32))
+    ph = h.cols["pod_phase"].copy()
+    ph[ph == 255] = 15
+    assert np.array_equal(meta & 15, ph)
+    assert np.array_equal(meta >> 4, np.diff(h.cols["pod_ctr_begin"]).astype(np.uint8))
+    want = np.array([cref.quantity_value(int(v), int(s)) for v, s in zip(h.cols["ctr_val"][:2000], h.cols["ctr_scale"][:2000])])
+    assert np.array_equal(gpu[:2000].astype(np.int64), want)
+    assert p.nbytes < h.algorithmic_bytes_top_node() / 5
+
+
+def test_snapshots_without_a_packed_form_say_why(built):
+    from arena_b200 import ArenaError, HostSnapshot
+
+    def snap(pod_node, phases, counts, vals, scales, n_nodes=3):
+        cb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+        return HostSnapshot.from_arrays(dict(
+            pod_node=np.array(pod_node, np.uint32), pod_phase=np.array(phases, np.uint8), pod_ctr_begin=cb,
+            ctr_val=np.array(vals, np.int64), ctr_scale=np.array(scales, np.int8),
+            node_cap_val=np.full(n_nodes, 8, np.int64), node_cap_scale=np.zeros(n_nodes, np.int8)))
+
+    ok = snap([0, 0, 2, 0xFFFFFFFF], [2, 3, 255, 0], [1, 0, 2, 1], [4, 1500, 255, 1], [0, -3, 0, 0]).pack()
+    begin, meta, gpu = unpack(ok)
+    assert begin.tolist() == [0, 2, 2, 3] and gpu.tolist() == [4, 2, 255, 1]       # 1500m rounds up to 2
+    assert ok.view.ctr_bits == 8
+    small = snap([0, 1, 1], [2, 2, 2], [2, 0, 3], [15, 0, 7, 8, 1], [0, 0, 0, 0, 0]).pack()
+    assert small.view.ctr_bits == 4 and unpack(small)[2].tolist() == [15, 0, 7, 8, 1] and small.nbytes == 3 + 3 + 16 + 27
+    assert (meta & 15).tolist() == [2, 3, 15, 0] and (meta >> 4).tolist() == [1, 0, 2, 1]
+    for bad, why in ((snap([1, 0], [2, 2], [0, 0], [], []), "not grouped"),
+                     (snap([0xFFFFFFFF, 0], [2, 2], [0, 0], [], []), "not grouped"),
+                     (snap([0], [2], [16], [1] * 16, [0] * 16), "16 containers"),
+                     (snap([0], [2], [1], [256], [0]), "256 GPUs"),
+                     (snap([0], [2], [1], [-1], [0]), "-1 GPUs"),
+                     (snap([0], [2], [1], [3], [2]), "300 GPUs"),
+                     (snap([0], [9], [0], [], []), "phase code 9"),
+                     (snap([3], [2], [0], [], []), "names node 3")):
+        with pytest.raises(ArenaError) as e:
+            bad.pack()
+        assert e.value.code == -1 and why in str(e.value), str(e.value)
+    empty = snap([], [], [], [], [], n_nodes=2).pack()
+    assert unpack(empty)[0].tolist() == [0, 0, 0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,N,skewed", [(0, 4, False), (1, 1, False), (3, 1, False), (1000, 7, False), (4097, 33, True),
+                                        (200_000, 3000, False), (1_000_003, 50_000, True)])
+def test_packed_path_is_bit_identical_to_the_wide_path(gpu, P, N, skewed):
+    h = gpu.HostSnapshot.synth(P, N, seed=P + 7, skewed=skewed)
+    packed = h.pack(pinned=True)
+    got = gpu.top_node_packed(packed, details=True)
+    tot, alloc, cl, pg = cref.top_node_columnar(h.cols, True)
+    assert np.array_equal(got.node_total, tot) and np.array_equal(got.node_alloc, alloc)
+    assert np.array_equal(got.cluster, cl) and np.array_equal(got.pod_gpu, pg)
+    wide = gpu.top_node(h, details=True)                      # arena_top_node_host on the wide columns
+    assert np.array_equal(wide.node_alloc, got.node_alloc) and np.array_equal(wide.pod_gpu, got.pod_gpu)
+    again = gpu.top_node_packed(packed)                       # staging buffers are reused
+    assert np.array_equal(again.node_alloc, alloc) and np.array_equal(again.cluster, cl)
+
+
+@pytest.mark.gpu
+def test_packed_path_on_the_json_fixture(gpu):
+    """configs[0]: quantities like "1500m" or "2k" decide whether a packed form exists."""
+    import os
+    D = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config1")
+    rd = lambda n: open(os.path.join(D, n), "rb").read()
+    h = gpu.HostSnapshot.from_json(rd("pods.json"), rd("nodes.json"))
+    tot, alloc, cl, _ = cref.top_node_columnar(h.cols)
+    try:
+        packed = h.pack()
+    except gpu.ArenaError as e:
+        assert "no packed form" in str(e)
+        return
+    got = gpu.top_node_packed(packed)
+    assert np.array_equal(got.node_total, tot) and np.array_equal(got.node_alloc, alloc) and np.array_equal(got.cluster, cl)
