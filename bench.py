@@ -214,8 +214,11 @@ def wire_format_leg(ab, n_pods=10_000, n_nodes=1000, reps=5):
     }
 
 
-def workload_config(n_gpus: int, scaling: str):
-    if scaling == "strong" and n_gpus > 1:
+def workload_config(n_gpus: int, scaling: str, skewed: bool = False):
+    if skewed:
+        wl = ("BASELINE configs[4]: skewed snapshot of 1e8 pods / 1e6 nodes (power-law pods per node, GPU-sharing nodes, "
+              f"seed 5) cut into {n_gpus} node range(s) of equal pod count, NCCL totals all-reduce")
+    elif scaling == "strong" and n_gpus > 1:
         wl = (f"BASELINE configs[3]: synthetic snapshot of 1e8 pods / 1e6 nodes (seed 1) cut into {n_gpus} node ranges, "
               "NCCL totals all-reduce")
     elif n_gpus > 1:
@@ -239,6 +242,9 @@ def main():
     ap.add_argument("--nodes", type=int, default=NODES_FULL)
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--skewed", action="store_true",
+                    help="BASELINE configs[4]: power-law pods per node + GPU-sharing nodes (seed 5); with --gpus > 1 one "
+                         "snapshot is cut into node ranges (implies --scaling strong) and the pod-count imbalance is reported")
     ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
     args = ap.parse_args()
@@ -278,20 +284,26 @@ def main():
 
     # ---- workload ------------------------------------------------------------
     t_gen = time.time()
+    if args.skewed:
+        args.scaling = "strong"
+    seed0 = 5 if args.skewed else 1
     if args.scaling == "strong" and world > 1:
-        full = ab.HostSnapshot.synth(args.pods, args.nodes, seed=1, pinned=False)
+        full = ab.HostSnapshot.synth(args.pods, args.nodes, seed=seed0, pinned=False, skewed=args.skewed)
         host = full.shard(rank, world)
         # pinned staging of the shard for the e2e leg
         host = ab.HostSnapshot.from_arrays({k: v.copy() for k, v in host.cols.items() if v.size or k == "pod_ctr_begin"})
         del full
     else:
-        host = ab.HostSnapshot.synth(args.pods, args.nodes, seed=1 + rank, pinned=True)
+        host = ab.HostSnapshot.synth(args.pods, args.nodes, seed=seed0 + rank, pinned=True, skewed=args.skewed)
     P, C, N = host.n_pods, host.n_containers, host.n_nodes
     log(f"[rank {rank}] snapshot: P={P} C={C} N={N} generated in {time.time() - t_gen:.1f}s")
     total_pods = torch.tensor([P], dtype=torch.int64, device="cuda")
+    max_pods = torch.tensor([P], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(total_pods)
+        dist.all_reduce(max_pods, op=dist.ReduceOp.MAX)
     total_pods = int(total_pods.item())
+    imbalance = int(max_pods.item()) * world / max(1, total_pods)      # 1.0 = every rank holds the same number of pods
 
     dev = ab.DeviceSnapshot.upload(host)
     d_total = torch.empty(N, dtype=torch.int64, device="cuda")
@@ -441,8 +453,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
         "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": dict(workload_config(n_gpus, args.scaling), pods_per_gpu=P, nodes_per_gpu=N, containers_per_gpu=C,
-                       total_pods=total_pods),
+        "config": dict(workload_config(n_gpus, args.scaling, args.skewed), pods_per_gpu=P, nodes_per_gpu=N,
+                       containers_per_gpu=C, total_pods=total_pods, shard_imbalance_max_over_mean=imbalance),
         "clocks": clocks,
         "e2e": {"value": total_pods * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
