@@ -76,6 +76,11 @@ _SIGS = [
     ("arena_top_node", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_host", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP]),
+    ("arena_peer_exchange_create", C.c_int, [C.c_int, C.c_int, _VP]),
+    ("arena_peer_exchange_connect", C.c_int, [_VP]),
+    ("arena_peer_exchange_destroy", None, []),
+    ("arena_peer_exchange_timed_out", C.c_int, []),
+    ("arena_top_node_device_fused", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_top_node_host_packed", C.c_int, [C.POINTER(PackedView), _VP, _VP, _VP, _VP]),
     ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -78,6 +78,12 @@ struct arena_snapshot {
 };
 
 static arena_snapshot *g_host_snap = nullptr;    // staging snapshot of arena_top_node_host
+// multi-GPU totals exchange (arena_peer_exchange_*): this rank's mailbox, the peers' mappings
+static PeerMailbox *g_my_box = nullptr;
+static PeerExchange *g_px = nullptr;             // device copy of the descriptor
+static PeerExchange g_px_host{};
+static void *g_peer_mapped[kMaxPeers] = {};
+static std::atomic<uint64_t> g_epoch{0};
 static void *g_packed_block = nullptr;           // staging of arena_top_node_host_packed: packed columns + tile sums
 static size_t g_packed_bytes = 0;
 
@@ -120,6 +126,7 @@ void arena_acct_shutdown(void)
     cudaStreamSynchronize(g_ctx.stream);
     if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
     if (g_packed_block) { cudaFree(g_packed_block); g_packed_block = nullptr; g_packed_bytes = 0; }
+    arena_peer_exchange_destroy();
     arena_internal::free_loader_workspace();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx = Context{};
@@ -229,7 +236,7 @@ int ensure_job_arrays(arena_snapshot *s)
 }
 
 int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_cluster, i64 *d_pod_gpu,
-                    cudaStream_t st)
+                    cudaStream_t st, bool exchange = false)
 {
     const arena_snapshot_view &v = s->v;
     const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
@@ -255,6 +262,10 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     pa.cap_scale = (const signed char *)v.node_cap_scale;
     pa.node_total = d_total;
     pa.total_capacity = d_cluster;
+    if (exchange) {
+        pa.px = g_px;
+        pa.epoch = g_epoch.fetch_add(1) + 1;
+    }
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
     const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
     if (gn > gp) gp = gn;
@@ -670,6 +681,75 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
     CUDA_TRY(cudaGetLastError());
     g_host_snap->direct = false;                                // grouped by construction
     return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);
+}
+
+// ---- multi-GPU totals exchange inside the kernel (see PeerExchange in kernels.cuh) ----------
+int arena_peer_exchange_create(int rank, int world, unsigned char handle_out[64])
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !handle_out)
+        return fail(ARENA_E_INVALID, "rank %d / world %d (at most %d ranks)", rank, world, kMaxPeers);
+    if (g_my_box) return fail(ARENA_E_INVALID, "peer exchange already created");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CUDA_TRY(cudaMalloc((void **)&g_my_box, sizeof(PeerMailbox)));
+    CUDA_TRY(cudaMemset(g_my_box, 0, sizeof(PeerMailbox)));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, g_my_box));
+    std::memcpy(handle_out, &h, 64);
+    g_px_host = PeerExchange{};
+    g_px_host.rank = rank;
+    g_px_host.world = world;
+    return ARENA_OK;
+}
+
+int arena_peer_exchange_connect(const unsigned char *handles)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!g_my_box || !handles) return fail(ARENA_E_INVALID, "arena_peer_exchange_create() first");
+    for (int i = 0; i < g_px_host.world; i++) {
+        if (i == g_px_host.rank) { g_px_host.box[i] = g_my_box; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + 64 * i, 64);
+        void *p = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        g_peer_mapped[i] = p;
+        g_px_host.box[i] = (PeerMailbox *)p;
+    }
+    CUDA_TRY(cudaMalloc((void **)&g_px, sizeof(PeerExchange)));
+    CUDA_TRY(cudaMemcpy(g_px, &g_px_host, sizeof(PeerExchange), cudaMemcpyHostToDevice));
+    return ARENA_OK;
+}
+
+void arena_peer_exchange_destroy(void)
+{
+    if (g_ctx.ready) cudaSetDevice(g_ctx.device);
+    for (int i = 0; i < kMaxPeers; i++)
+        if (g_peer_mapped[i]) { cudaIpcCloseMemHandle(g_peer_mapped[i]); g_peer_mapped[i] = nullptr; }
+    if (g_px) { cudaFree(g_px); g_px = nullptr; }
+    if (g_my_box) { cudaFree(g_my_box); g_my_box = nullptr; }
+    g_px_host = PeerExchange{};
+}
+
+int arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                                int64_t *d_cluster, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!s || !d_cluster) return fail(ARENA_E_INVALID, "snapshot or d_cluster is NULL");
+    if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, nullptr, st, true);
+}
+
+int arena_peer_exchange_timed_out(void)
+{
+    if (!g_px) return 0;
+    PeerExchange h{};
+    if (cudaMemcpy(&h, g_px, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int)h.timed_out;
 }
 
 int arena_top_job_device(const arena_snapshot *cs, int64_t *d_job_req, int64_t *d_job_alloc,

@@ -189,10 +189,29 @@ struct Scratch {
     unsigned ticket[4];
 };
 
+// ---- totals across GPUs without a collective launch -------------------------------------------
+// Every rank owns a mailbox in its own HBM that all ranks (itself included) can write through
+// NVLink peer mappings (CUDA IPC).  The last CTA of a rank's kernel stores the rank's two totals
+// and then the step's epoch into slot [rank] of EVERY mailbox, waits until its own mailbox
+// shows the epoch in all slots, and adds them up: the exchange rides in the tail of the kernel
+// that produced the numbers.  Two parities: a rank can be at most one step ahead of a peer
+// that is still reading (it cannot finish step e+1 before that peer has posted e+1).
+constexpr int kMaxPeers = 16;
+struct PeerMailbox {
+    unsigned long long flag[2][kMaxPeers];       // [parity][writer] = epoch of totals[parity][writer]
+    long long totals[2][kMaxPeers][2];           // {first total, second total}
+};
+struct PeerExchange {
+    int rank, world;
+    unsigned timed_out;                          // set when a peer did not show up within the spin budget
+    PeerMailbox *box[kMaxPeers];                 // rank i's mailbox as mapped into this process
+};
+
 // Last-CTA-done reduction of per-CTA partial sums into *out (and *out_b).
 // Every CTA calls this once with its partial(s) in thread 0.
 __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two,
-                                              Scratch *sc, int ticket_id, i64 *out_a, i64 *out_b)
+                                              Scratch *sc, int ticket_id, i64 *out_a, i64 *out_b,
+                                              PeerExchange *px = nullptr, u64 epoch = 0)
 {
     __shared__ bool s_last;
     if (threadIdx.x == 0) {
@@ -215,12 +234,50 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
     b = warp_reduce_sum(b);
     if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
     __syncthreads();
+    __shared__ u64 s_tot[2];
     if (threadIdx.x == 0) {
         u64 ta = 0, tb = 0;
         for (int w = 0; w < (int)(blockDim.x >> 5); w++) { ta += s_a[w]; tb += s_b[w]; }
-        *out_a = (i64)ta;
-        if (two) *out_b = (i64)tb;
+        s_tot[0] = ta; s_tot[1] = tb;
+        if (!px) {
+            *out_a = (i64)ta;
+            if (two) *out_b = (i64)tb;
+        }
         sc->ticket[ticket_id] = 0;      // ready for the next launch
+    }
+    if (!px) return;
+    __syncthreads();
+    // post to every rank, then collect from every rank: thread i talks to rank i
+    const int par = (int)(epoch & 1ull);
+    u64 ga = 0, gb = 0;
+    if ((int)threadIdx.x < px->world) {
+        PeerMailbox *theirs = px->box[threadIdx.x];
+        theirs->totals[par][px->rank][0] = (long long)s_tot[0];
+        theirs->totals[par][px->rank][1] = (long long)s_tot[1];
+        __threadfence_system();
+        *((volatile unsigned long long *)&theirs->flag[par][px->rank]) = epoch;
+        PeerMailbox *mine = px->box[px->rank];
+        const long long t0 = clock64();
+        bool ok = true;
+        while (*((volatile unsigned long long *)&mine->flag[par][threadIdx.x]) != epoch) {
+            __nanosleep(100);
+            if (clock64() - t0 > 4000000000ll) { ok = false; break; }      // ~2 s: a peer is gone
+        }
+        __threadfence_system();
+        if (ok) {
+            ga = (u64)*((volatile long long *)&mine->totals[par][threadIdx.x][0]);
+            gb = (u64)*((volatile long long *)&mine->totals[par][threadIdx.x][1]);
+        } else {
+            px->timed_out = 1u;
+        }
+    }
+    if (threadIdx.x < 32) {            // world <= 16: all in the first warp
+        ga = warp_reduce_sum(ga);
+        gb = warp_reduce_sum(gb);
+        if (threadIdx.x == 0) {
+            *out_a = (i64)ga;
+            if (two) *out_b = (i64)gb;
+        }
     }
 }
 
@@ -270,6 +327,9 @@ struct PodsArgs {
     const signed char *cap_scale;
     i64 *node_total;                // [N] Value(capacity)
     i64 *total_capacity;            // sum of node_total
+    // multi-GPU: exchange the two totals with the peer GPUs inside this launch (or nullptr)
+    PeerExchange *px;
+    u64 epoch;
 };
 
 // Rare path (a row that runs past the end of the container columns) kept out
@@ -777,7 +837,7 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
         for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
-    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity);
+    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.epoch);
 }
 
 // ---------------------------------------------------------------------------

@@ -61,6 +61,38 @@ def gather_tables(local_total: np.ndarray, local_alloc: np.ndarray, dst: int = 0
     return np.concatenate([o[0] for o in out]), np.concatenate([o[1] for o in out])
 
 
+def setup_peer_exchange() -> bool:
+    """Map every rank's totals mailbox into every process (CUDA IPC over NVLink) so that
+    top_node_device_fused can trade the cluster totals inside the kernel.  Collective: every
+    rank calls it.  Returns False (and leaves NCCL as the only way) when IPC is unavailable."""
+    import ctypes as C
+    from ._lib import lib
+    rank, world, _ = env_rank()
+    if world > 16:
+        return False
+    mine = (C.c_ubyte * 64)()
+    ok = lib().arena_peer_exchange_create(rank, world, mine) == 0
+    handles = [None] * world
+    if dist.is_initialized() and world > 1:
+        dist.all_gather_object(handles, (ok, bytes(mine)))
+    else:
+        handles = [(ok, bytes(mine))]
+    if all(h[0] for h in handles):
+        blob = b"".join(h[1] for h in handles)
+        ok = lib().arena_peer_exchange_connect(blob) == 0
+    else:
+        ok = False
+    flags = [None] * world
+    if dist.is_initialized() and world > 1:
+        dist.all_gather_object(flags, ok)
+    else:
+        flags = [ok]
+    if not all(flags):
+        lib().arena_peer_exchange_destroy()
+        return False
+    return True
+
+
 def top_node_sharded(host_shard, details: bool = False, out=None):
     """End-to-end sharded `top node` for this rank's shard (a HostSnapshot, or a
     PackedSnapshot of it): upload + kernels + download through the C ABI, then the totals

@@ -77,6 +77,16 @@ def top_node(snap: Union[DeviceSnapshot, HostSnapshot], details: bool = False, o
     return TopNodeResult(total, alloc, cluster, pod_gpu)
 
 
+def top_node_device_fused(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cluster, stream: Optional[int] = None) -> None:
+    """arena_top_node_device_fused: the kernels plus the in-kernel totals exchange with the
+    peer GPUs (multigpu.setup_peer_exchange first); d_cluster receives the GLOBAL totals."""
+    check(lib().arena_top_node_device_fused(
+        snap.handle,
+        d_node_total.data_ptr() if d_node_total is not None and d_node_total.numel() else None,
+        d_node_alloc.data_ptr() if d_node_alloc is not None and d_node_alloc.numel() else None,
+        d_cluster.data_ptr(), _stream_arg(stream)))
+
+
 def top_node_packed(packed, details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
     """arena_top_node_host_packed: one-shot upload of a PackedSnapshot + kernels + download."""
     N, P = packed.n_nodes, packed.n_pods

@@ -245,6 +245,9 @@ def main():
     ap.add_argument("--skewed", action="store_true",
                     help="BASELINE configs[4]: power-law pods per node + GPU-sharing nodes (seed 5); with --gpus > 1 one "
                          "snapshot is cut into node ranges (implies --scaling strong) and the pod-count imbalance is reported")
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
+                    help="multi-GPU totals: traded inside the kernel over NVLink peer memory (fused), or a NCCL all-reduce "
+                         "after it (nccl)")
     ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
     args = ap.parse_args()
@@ -311,9 +314,17 @@ def main():
     d_cluster = torch.empty(2, dtype=torch.int64, device="cuda")
     stream = torch.cuda.current_stream()
 
+    fused = False
+    if world > 1 and args.collective == "fused":
+        fused = multigpu.setup_peer_exchange()
+        log(f"[rank {rank}] in-kernel totals exchange over peer memory: {'on' if fused else 'unavailable, using NCCL'}")
+
     def step():
-        ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, stream.cuda_stream)
-        multigpu.all_reduce_totals(d_cluster)
+        if fused:
+            ab.top_node_device_fused(dev, d_total, d_alloc, d_cluster, stream.cuda_stream)
+        else:
+            ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, stream.cuda_stream)
+            multigpu.all_reduce_totals(d_cluster)
 
     def barrier():
         if world > 1:
@@ -353,6 +364,8 @@ def main():
     ms_per_step = ms_total / args.steps
     value = total_pods * args.steps / (ms_total / 1e3)
 
+    if fused and ab.lib().arena_peer_exchange_timed_out():
+        raise SystemExit("bench.py: a peer did not post its totals in time (in-kernel exchange)")
     # sanity: table sums equal the totals this rank contributed (cheap; parity proper is tests/)
     cl = d_cluster.cpu().numpy()
     local_alloc_sum = int(d_alloc.sum().item())
@@ -463,6 +476,8 @@ def main():
                          "ms_per_step": wide_s / wide_steps * 1e3,
                          "call": "arena_top_node_host (wide columns: 9 B per pod + 9 B per container)"}},
         "gpu_launches": launches,
+        "collective": ("in-kernel exchange over NVLink peer memory (CUDA IPC mailboxes), no collective launch" if fused
+                       else "NCCL all-reduce of int64[2]" if world > 1 else None),
         "roofline": roofline,
         "hbm_gbs_step": step_bytes / (ms_per_step / 1e3) / 1e9,
     }

@@ -139,6 +139,27 @@ int  arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total,
                          int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
 
 /*
+ * Multi-GPU `top node` without a collective launch (one process per GPU, one node range per
+ * process).  Each rank creates a mailbox in its own HBM and publishes its 64-byte CUDA IPC
+ * handle (arena_peer_exchange_create); the ranks trade handles by any means they have (the
+ * torchrun driver gathers them as Python objects) and map each other's mailboxes
+ * (arena_peer_exchange_connect: `handles` = world x 64 bytes in rank order).  After that
+ * arena_top_node_device_fused is arena_top_node_device whose kernel also trades the two
+ * cluster totals with every peer over NVLink in its last CTA -- peer stores, an epoch flag,
+ * a bounded spin (~2 s, then arena_peer_exchange_timed_out() != 0 and the totals are not
+ * meaningful) -- so d_cluster receives the GLOBAL {total, allocated} and no all-reduce is launched.
+ * Every rank must make the same sequence of fused calls.  At most 16 ranks.  Replaces the
+ * single-process loop over all nodes of top_node.go:109-118; no reference counterpart for
+ * the exchange itself.
+ */
+int  arena_peer_exchange_create(int rank, int world, unsigned char ipc_handle_out[64]);
+int  arena_peer_exchange_connect(const unsigned char *handles);
+void arena_peer_exchange_destroy(void);
+int  arena_peer_exchange_timed_out(void);
+int  arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                                 int64_t *d_cluster, void *stream);
+
+/*
  * The same one-shot call for a PACKED host snapshot: the narrowest exact encoding of what
  * `top node` reads, for callers on the far side of PCIe (the copy is the whole cost of
  * arena_top_node_host: 9 bytes per pod + 9 per container; packed it is 1 + 1).

@@ -187,3 +187,27 @@ def test_corrupt_csr_offsets_do_not_fault(gpu):
     r2 = gpu.top_node(good)
     tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
     assert np.array_equal(r2.node_alloc, alloc)
+
+
+def test_fused_totals_exchange_with_itself(gpu):
+    """World of one: the kernel posts its totals to its own mailbox and reads them back
+    (the multi-rank form needs more GPUs than the test box has; bench.py runs it)."""
+    import torch
+    from arena_b200 import multigpu
+    assert multigpu.setup_peer_exchange()
+    try:
+        host = gpu.HostSnapshot.synth(300_000, 4_000, seed=21)
+        dev = gpu.DeviceSnapshot.upload(host)
+        tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+        d_total = torch.empty(host.n_nodes, dtype=torch.int64, device="cuda")
+        d_alloc = torch.empty(host.n_nodes, dtype=torch.int64, device="cuda")
+        d_cluster = torch.zeros(2, dtype=torch.int64, device="cuda")
+        for _ in range(5):                                  # epochs alternate the mailbox parity
+            d_cluster.zero_()
+            gpu.top_node_device_fused(dev, d_total, d_alloc, d_cluster, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            assert d_cluster.cpu().numpy().tolist() == cl.tolist()
+            assert np.array_equal(d_alloc.cpu().numpy(), alloc) and np.array_equal(d_total.cpu().numpy(), tot)
+        assert gpu.lib().arena_peer_exchange_timed_out() == 0
+    finally:
+        gpu.lib().arena_peer_exchange_destroy()
