@@ -39,6 +39,7 @@ class PackedView(C.Structure):
         ("n_pods", C.c_uint64), ("n_containers", C.c_uint64), ("n_nodes", C.c_uint64),
         ("node_pod_begin", C.c_void_p), ("pod_meta", C.c_void_p), ("ctr_gpu", C.c_void_p),
         ("node_cap_val", C.c_void_p), ("node_cap_scale", C.c_void_p), ("ctr_bits", C.c_uint32),
+        ("node_ctr_begin", C.c_void_p), ("pieces", C.c_void_p), ("n_pieces", C.c_uint64),
     ]
 
 

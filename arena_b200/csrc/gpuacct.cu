@@ -610,6 +610,63 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
     return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
 }
 
+// summary straight from the packed columns: copy, one memset, one kernel, copy back
+static int top_node_packed_native(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2])
+{
+    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes, K = h->n_pieces;
+    if (!h->node_ctr_begin || (K && !h->pieces)) return fail(ARENA_E_INVALID, "node_ctr_begin / pieces are NULL");
+    const u64 gpu_bytes = h->ctr_bits == 4 ? (C + 1) / 2 : C;
+    cudaStream_t st = g_ctx.stream;
+    const size_t o_begin = 0, o_cbegin = o_begin + pad16((N + 1) * 4), o_meta = o_cbegin + pad16((N + 1) * 4),
+                 o_gpu = o_meta + pad16(P + 4), o_pieces = o_gpu + pad16(gpu_bytes + 4), o_capv = o_pieces + pad16(K * 16),
+                 o_caps = o_capv + pad16(N * 8), o_total = o_caps + pad16(N), o_alloc = o_total + pad16(N * 8),
+                 o_cluster = o_alloc + pad16(N * 8), need = o_cluster + 16;
+    if (g_packed_bytes < need) {
+        if (g_packed_block) cudaFree(g_packed_block);
+        g_packed_block = nullptr;
+        g_packed_bytes = 0;
+        CUDA_TRY(cudaMalloc(&g_packed_block, need));
+        g_packed_bytes = need;
+    }
+    char *pb = (char *)g_packed_block;
+    CUDA_TRY(cudaMemcpyAsync(pb + o_begin, h->node_pod_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(pb + o_cbegin, h->node_ctr_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (P) CUDA_TRY(cudaMemcpyAsync(pb + o_meta, h->pod_meta, P, cudaMemcpyHostToDevice, st));
+    if (C) CUDA_TRY(cudaMemcpyAsync(pb + o_gpu, h->ctr_gpu, gpu_bytes, cudaMemcpyHostToDevice, st));
+    if (K) CUDA_TRY(cudaMemcpyAsync(pb + o_pieces, h->pieces, K * 16, cudaMemcpyHostToDevice, st));
+    if (N) {
+        CUDA_TRY(cudaMemcpyAsync(pb + o_capv, h->node_cap_val, N * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(pb + o_caps, h->node_cap_scale, N, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemsetAsync(pb + o_alloc, 0, N * 8, st));
+    }
+    PackedArgs a{};
+    a.N = N; a.n_pieces = K;
+    a.node_pod_begin = (const unsigned *)(pb + o_begin);
+    a.node_ctr_begin = (const unsigned *)(pb + o_cbegin);
+    a.meta = (const unsigned char *)(pb + o_meta);
+    a.gpu = (const unsigned char *)(pb + o_gpu);
+    a.pieces = (const uint4 *)(pb + o_pieces);
+    a.cap_val = (const i64 *)(pb + o_capv);
+    a.cap_scale = (const signed char *)(pb + o_caps);
+    a.node_total = (i64 *)(pb + o_total);
+    a.node_alloc = (u64 *)(pb + o_alloc);
+    a.total_capacity = (i64 *)(pb + o_cluster);
+    a.total_alloc = (i64 *)(pb + o_cluster) + 1;
+    a.scratch = g_host_snap->scratch;
+    const int grid = grid_for(N + K, kWarps, g_ctx.pods_ctas_per_sm);
+    if (h->ctr_bits == 4) top_node_packed_kernel<4><<<grid, kThreads, 0, st>>>(a);
+    else top_node_packed_kernel<8><<<grid, kThreads, 0, st>>>(a);
+    count_launch();
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(cluster, pb + o_cluster, 16, cudaMemcpyDeviceToHost, st));
+    if (N) {
+        CUDA_TRY(cudaMemcpyAsync(node_total, pb + o_total, N * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(node_alloc, pb + o_alloc, N * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return ARENA_OK;
+}
+
 int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2],
                                int64_t *pod_gpu)
 {
@@ -627,6 +684,10 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
         rc = alloc_common(g_host_snap);
         if (rc) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; return rc; }
     }
+    if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);
+    if (N && (!node_total || !node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    if (!cluster) return fail(ARENA_E_INVALID, "cluster is NULL");
+    if (!pod_gpu) return top_node_packed_native(h, node_total, node_alloc, cluster);
     const u64 pcn[3] = {P, C, N};
     rc = fill_snapshot(g_host_snap, nullptr, false, pcn);       // wide columns: reserved, filled below on the device
     if (rc) return rc;

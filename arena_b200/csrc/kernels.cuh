@@ -1189,3 +1189,91 @@ __global__ void __launch_bounds__(256) packed_expand_nodes_kernel(const unsigned
 }
 
 }  // namespace arena
+
+// ---- `top node` summary straight from the packed columns (no expansion) ---------------------------
+// One warp per node: its pods are the rows [b[n], b[n+1]) and their containers the values from
+// node_ctr_begin[n] on, so the join is a pair of offsets and nothing is shared between warps: no
+// atomics, no pod_node column.  32 pods per trip: one meta byte per lane, a warp scan of the container
+// counts places every lane in the value column, each lane adds up its own pod's few values.  Nodes
+// above kBigNodePods rows (power-law snapshots) are cut by the host into pieces of at most that many
+// rows, each with its own container offset; pieces are spread over the grid and meet in node_alloc
+// with one atomic each.
+namespace arena {
+
+constexpr unsigned kBigNodePods = 2048;
+
+struct PackedArgs {
+    u64 N, n_pieces;
+    const unsigned *node_pod_begin, *node_ctr_begin;    // [N+1]
+    const unsigned char *meta, *gpu;
+    const uint4 *pieces;                                // {node, first row, end row, first container}
+    const i64 *cap_val;
+    const signed char *cap_scale;
+    u64 *node_alloc;                                    // [N] zeroed before the launch
+    i64 *node_total;
+    i64 *total_alloc, *total_capacity;
+    Scratch *scratch;
+    PeerExchange *px;
+    u64 epoch;
+};
+
+template <int kBits>
+__device__ __forceinline__ unsigned packed_value(const unsigned char *gpu, unsigned i)
+{
+    if (kBits == 8) return __ldg(gpu + i);
+    return (__ldg(gpu + (i >> 1)) >> ((i & 1u) * 4u)) & 15u;
+}
+
+// masked GPU sum of the rows [lo, hi) whose containers start at c0; the same value in every lane
+template <int kBits>
+__device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const unsigned char *gpu, unsigned lo, unsigned hi,
+                                               unsigned c0, int lane)
+{
+    unsigned acc = 0;
+    for (unsigned p0 = lo; p0 < hi; p0 += 32) {
+        const unsigned p = p0 + lane;
+        const unsigned m = p < hi ? (unsigned)__ldg(meta + p) : 0u;
+        const unsigned cnt = m >> 4, ph = m & 15u;
+        const unsigned inc = warp_inclusive_scan_u32(cnt);
+        unsigned i = c0 + inc - cnt, s = 0;
+        for (unsigned k = 0; k < cnt; k++) s += packed_value<kBits>(gpu, i + k);
+        if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += s;          // rows past hi have cnt 0
+        c0 += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    return warp_reduce_sum((u64)acc);
+}
+
+template <int kBits>
+__global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_constant__ PackedArgs a)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u64 n_warps = (u64)gridDim.x * kWarps, w0 = (u64)blockIdx.x * kWarps + warp;
+    u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every warp
+    for (u64 n = w0; n < a.N; n += n_warps) {
+        const unsigned lo = __ldg(a.node_pod_begin + n), hi = __ldg(a.node_pod_begin + n + 1);
+        if (hi - lo <= kBigNodePods) {
+            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, __ldg(a.node_ctr_begin + n), lane);
+            if (lane == 0) { a.node_alloc[n] = s; alloc_sum += s; }
+        }
+        if (lane == 0) {
+            const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
+            a.node_total[n] = t;
+            cap_sum += (u64)t;
+        }
+    }
+    for (u64 k = w0; k < a.n_pieces; k += n_warps) {
+        const uint4 pc = __ldg(a.pieces + k);
+        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, lane);
+        if (lane == 0 && s) { red_add_u64(a.node_alloc + pc.x, s); }
+        if (lane == 0) alloc_sum += s;
+    }
+    __shared__ u64 s_a[kWarps], s_c[kWarps];
+    if (lane == 0) { s_a[warp] = alloc_sum; s_c[warp] = cap_sum; }
+    __syncthreads();
+    u64 block_a = 0, block_c = 0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kWarps; w++) { block_a += s_a[w]; block_c += s_c[w]; }
+    finish_totals(block_a, block_c, true, a.scratch, 2, a.total_alloc, a.total_capacity, a.px, a.epoch);
+}
+
+}  // namespace arena

@@ -11,7 +11,7 @@ using namespace arena_host;
 
 struct arena_packed_snapshot {
     arena_packed_view v{};
-    Column c_node_pod_begin, c_pod_meta, c_ctr_gpu, c_node_cap_val, c_node_cap_scale;
+    Column c_node_pod_begin, c_pod_meta, c_ctr_gpu, c_node_cap_val, c_node_cap_scale, c_node_ctr_begin, c_pieces;
 };
 
 extern "C" {
@@ -80,6 +80,31 @@ int arena_host_snapshot_pack(const arena_snapshot_view *h, int pinned, arena_pac
         p->c_node_cap_val.as<int64_t>()[n] = h->node_cap_val[n];
         p->c_node_cap_scale.as<int8_t>()[n] = h->node_cap_scale[n];
     }
+    // container offsets per node, and the big nodes cut into pieces
+    const uint32_t kPiece = 2048;
+    uint64_t n_pieces = 0;
+    for (uint64_t n = 0; n < N; n++) {
+        const uint64_t rows = begin[n + 1] - begin[n];
+        if (rows > kPiece) n_pieces += (rows + kPiece - 1) / kPiece;
+    }
+    if ((rc = p->c_node_ctr_begin.alloc((N + 1) * 4, pinned != 0)) || (rc = p->c_pieces.alloc(n_pieces * 16, pinned != 0))) {
+        delete p;
+        return rc;
+    }
+    uint32_t *ncb = p->c_node_ctr_begin.as<uint32_t>(), *pc = p->c_pieces.as<uint32_t>();
+    for (uint64_t n = 0; n <= N; n++) ncb[n] = h->pod_ctr_begin[begin[n]];
+    for (uint64_t n = 0, k = 0; n < N; n++) {
+        if (begin[n + 1] - begin[n] <= kPiece) continue;
+        for (uint32_t r = begin[n]; r < begin[n + 1]; r += kPiece, k++) {
+            pc[4 * k] = (uint32_t)n;
+            pc[4 * k + 1] = r;
+            pc[4 * k + 2] = begin[n + 1] - r > kPiece ? r + kPiece : begin[n + 1];
+            pc[4 * k + 3] = h->pod_ctr_begin[r];
+        }
+    }
+    p->v.node_ctr_begin = ncb;
+    p->v.pieces = pc;
+    p->v.n_pieces = n_pieces;
     p->v.n_pods = P; p->v.n_containers = C; p->v.n_nodes = N;
     p->v.node_pod_begin = begin; p->v.pod_meta = meta; p->v.ctr_gpu = gpu;
     p->v.node_cap_val = p->c_node_cap_val.as<int64_t>();

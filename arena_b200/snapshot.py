@@ -213,7 +213,7 @@ class PackedSnapshot:
     def nbytes(self) -> int:
         """bytes the one-shot call copies to the device"""
         ctr = (self.n_containers + 1) // 2 if self.view.ctr_bits == 4 else self.n_containers
-        return self.n_pods + ctr + 4 * (self.n_nodes + 1) + 9 * self.n_nodes
+        return self.n_pods + ctr + 8 * (self.n_nodes + 1) + 9 * self.n_nodes + 16 * int(self.view.n_pieces)
 
     def close(self) -> None:
         if self._h:

@@ -414,7 +414,7 @@ def main():
         dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if int(flags.item()):
         e2e_s = e2e_leg(packed, e2e_steps)
-        h2d, e2e_call = packed.nbytes, "arena_top_node_host_packed (packed upload, expansion + kernels on the device, download)"
+        h2d, e2e_call = packed.nbytes, "arena_top_node_host_packed (packed upload, one kernel straight on the packed columns, download)"
     else:
         e2e_s, e2e_steps, h2d = wide_s, wide_steps, h2d_wide
         e2e_call = "arena_top_node_host (upload + kernels + download)"

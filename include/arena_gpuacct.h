@@ -175,9 +175,9 @@ int  arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total,
  *
  * A snapshot with a pod of more than 15 containers, a container above 255 GPUs or pods that
  * are not grouped has no packed form: use the wide one (arena_host_snapshot_pack says so).
- * On the device the packed columns are expanded into the wide layout by four small kernels
- * and the ordinary kernels run on that: results are bit-identical by construction.
- * pod_gpu (may be NULL) is per row, as in arena_top_node.  No reference counterpart.
+ * The summary (pod_gpu == NULL) is computed straight from the packed columns, one warp per
+ * node; with pod_gpu (per row, as in arena_top_node) the columns are first expanded into the
+ * wide layout on the device and the ordinary kernels run on that.  No reference counterpart.
  */
 typedef struct arena_packed_view {
     uint64_t n_pods, n_containers, n_nodes;
@@ -187,6 +187,12 @@ typedef struct arena_packed_view {
     const int64_t  *node_cap_val;
     const int8_t   *node_cap_scale;
     uint32_t ctr_bits;                /* 8 or 4 */
+    /* where each node's containers start in ctr_gpu ([N+1]; [N] = those of the rows that name no
+     * node), and the rows of every node above 2048 pods cut into pieces of at most 2048:
+     * pieces[4k..4k+3] = { node, first row, end row, first container } */
+    const uint32_t *node_ctr_begin;
+    const uint32_t *pieces;
+    uint64_t n_pieces;
 } arena_packed_view;
 
 int  arena_top_node_host_packed(const arena_packed_view *host, int64_t *node_total,

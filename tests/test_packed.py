@@ -59,7 +59,7 @@ def test_snapshots_without_a_packed_form_say_why(built):
     assert begin.tolist() == [0, 2, 2, 3] and gpu.tolist() == [4, 2, 255, 1]       # 1500m rounds up to 2
     assert ok.view.ctr_bits == 8
     small = snap([0, 1, 1], [2, 2, 2], [2, 0, 3], [15, 0, 7, 8, 1], [0, 0, 0, 0, 0]).pack()
-    assert small.view.ctr_bits == 4 and unpack(small)[2].tolist() == [15, 0, 7, 8, 1] and small.nbytes == 3 + 3 + 16 + 27
+    assert small.view.ctr_bits == 4 and unpack(small)[2].tolist() == [15, 0, 7, 8, 1] and small.nbytes == 3 + 3 + 32 + 27
     assert (meta & 15).tolist() == [2, 3, 15, 0] and (meta >> 4).tolist() == [1, 0, 2, 1]
     for bad, why in ((snap([1, 0], [2, 2], [0, 0], [], []), "not grouped"),
                      (snap([0xFFFFFFFF, 0], [2, 2], [0, 0], [], []), "not grouped"),
@@ -88,8 +88,32 @@ def test_packed_path_is_bit_identical_to_the_wide_path(gpu, P, N, skewed):
     assert np.array_equal(got.cluster, cl) and np.array_equal(got.pod_gpu, pg)
     wide = gpu.top_node(h, details=True)                      # arena_top_node_host on the wide columns
     assert np.array_equal(wide.node_alloc, got.node_alloc) and np.array_equal(wide.pod_gpu, got.pod_gpu)
-    again = gpu.top_node_packed(packed)                       # staging buffers are reused
-    assert np.array_equal(again.node_alloc, alloc) and np.array_equal(again.cluster, cl)
+    for _ in range(2):                                        # summary: straight from the packed columns
+        again = gpu.top_node_packed(packed)
+        assert np.array_equal(again.node_alloc, alloc) and np.array_equal(again.cluster, cl)
+        assert np.array_equal(again.node_total, tot)
+
+
+@pytest.mark.gpu
+def test_packed_summary_with_giant_nodes_and_byte_values(gpu):
+    """Nodes above 2048 pods are cut into pieces; values above 15 keep a byte each."""
+    rng = np.random.default_rng(3)
+    sizes = [5000, 0, 1, 2049, 2048, 70000, 3, 0, 40]
+    pod_node = np.concatenate([np.full(k, n, np.uint32) for n, k in enumerate(sizes)] + [np.full(77, 0xFFFFFFFF, np.uint32)])
+    P = len(pod_node)
+    counts = rng.integers(0, 5, P)
+    cb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+    for top in (15, 255):
+        vals = rng.integers(0, top + 1, int(cb[-1])).astype(np.int64)
+        h = gpu.HostSnapshot.from_arrays(dict(
+            pod_node=pod_node, pod_phase=rng.choice([0, 1, 2, 3, 4, 5, 255], P).astype(np.uint8), pod_ctr_begin=cb,
+            ctr_val=vals, ctr_scale=np.zeros(len(vals), np.int8),
+            node_cap_val=rng.integers(0, 9, len(sizes)).astype(np.int64), node_cap_scale=np.zeros(len(sizes), np.int8)))
+        packed = h.pack()
+        assert packed.view.ctr_bits == (4 if top == 15 else 8) and packed.view.n_pieces == 3 + 2 + 35
+        tot, alloc, cl, _ = cref.top_node_columnar(h.cols)
+        got = gpu.top_node_packed(packed)
+        assert np.array_equal(got.node_alloc, alloc) and np.array_equal(got.node_total, tot) and np.array_equal(got.cluster, cl)
 
 
 @pytest.mark.gpu
