@@ -34,6 +34,7 @@ struct Context {
     int sm_count = 0;
     int pods_ctas_per_sm = 0;
     int jobs_ctas_per_sm = 0;
+    int packed_ctas_per_sm = 0;
     cudaStream_t stream = nullptr;
 };
 
@@ -111,7 +112,8 @@ int arena_acct_init(int device)
     g_ctx.sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
-    if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1)
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
+    if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1 || g_ctx.packed_ctas_per_sm < 1)
         return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
     CUDA_TRY(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
     g_ctx.ready = true;
@@ -618,7 +620,7 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     const u64 gpu_bytes = h->ctr_bits == 4 ? (C + 1) / 2 : C;
     cudaStream_t st = g_ctx.stream;
     const size_t o_begin = 0, o_cbegin = o_begin + pad16((N + 1) * 4), o_meta = o_cbegin + pad16((N + 1) * 4),
-                 o_gpu = o_meta + pad16(P + 4), o_pieces = o_gpu + pad16(gpu_bytes + 4), o_capv = o_pieces + pad16(K * 16),
+                 o_gpu = o_meta + pad16(P + 4), o_pieces = o_gpu + pad16(gpu_bytes + 16), o_capv = o_pieces + pad16(K * 16),
                  o_caps = o_capv + pad16(N * 8), o_total = o_caps + pad16(N), o_alloc = o_total + pad16(N * 8),
                  o_cluster = o_alloc + pad16(N * 8), need = o_cluster + 16;
     if (g_packed_bytes < need) {
@@ -653,7 +655,7 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     a.total_capacity = (i64 *)(pb + o_cluster);
     a.total_alloc = (i64 *)(pb + o_cluster) + 1;
     a.scratch = g_host_snap->scratch;
-    const int grid = grid_for(N + K, kWarps, g_ctx.pods_ctas_per_sm);
+    const int grid = grid_for(N + K, kWarps, g_ctx.packed_ctas_per_sm);
     if (h->ctr_bits == 4) top_node_packed_kernel<4><<<grid, kThreads, 0, st>>>(a);
     else top_node_packed_kernel<8><<<grid, kThreads, 0, st>>>(a);
     count_launch();

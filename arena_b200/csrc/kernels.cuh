@@ -1217,11 +1217,30 @@ struct PackedArgs {
     u64 epoch;
 };
 
+// sum of the `cnt` values that start at value index i: eight nibbles (four bytes) per round, taken
+// from two aligned words with a funnel shift and added up inside the register
 template <int kBits>
-__device__ __forceinline__ unsigned packed_value(const unsigned char *gpu, unsigned i)
+__device__ __forceinline__ unsigned packed_values_sum(const unsigned char *gpu, unsigned i, unsigned cnt)
 {
-    if (kBits == 8) return __ldg(gpu + i);
-    return (__ldg(gpu + (i >> 1)) >> ((i & 1u) * 4u)) & 15u;
+    constexpr unsigned kPer = kBits == 4 ? 8u : 4u;
+    const unsigned *words = reinterpret_cast<const unsigned *>(gpu);
+    unsigned s = 0;
+    while (cnt) {
+        const unsigned *w = words + i / kPer;
+        unsigned x = __funnelshift_r(__ldg(w), __ldg(w + 1), (i % kPer) * kBits);
+        const unsigned take = cnt < kPer ? cnt : kPer;
+        if (take < kPer) x &= (1u << (take * kBits)) - 1u;
+        if (kBits == 4) {
+            x = (x & 0x0f0f0f0fu) + ((x >> 4) & 0x0f0f0f0fu);
+            s += (x * 0x01010101u) >> 24;
+        } else {
+            x = (x & 0x00ff00ffu) + ((x >> 8) & 0x00ff00ffu);
+            s += (x * 0x00010001u) >> 16;
+        }
+        i += take;
+        cnt -= take;
+    }
+    return s;
 }
 
 // masked GPU sum of the rows [lo, hi) whose containers start at c0; the same value in every lane
@@ -1230,13 +1249,13 @@ __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const 
                                                unsigned c0, int lane)
 {
     unsigned acc = 0;
+    unsigned m_next = lo + lane < hi ? (unsigned)__ldg(meta + lo + lane) : 0u;
     for (unsigned p0 = lo; p0 < hi; p0 += 32) {
-        const unsigned p = p0 + lane;
-        const unsigned m = p < hi ? (unsigned)__ldg(meta + p) : 0u;
+        const unsigned m = m_next;                      // the next trip's bytes are already on their way
+        m_next = p0 + 32 + lane < hi ? (unsigned)__ldg(meta + p0 + 32 + lane) : 0u;
         const unsigned cnt = m >> 4, ph = m & 15u;
         const unsigned inc = warp_inclusive_scan_u32(cnt);
-        unsigned i = c0 + inc - cnt, s = 0;
-        for (unsigned k = 0; k < cnt; k++) s += packed_value<kBits>(gpu, i + k);
+        const unsigned s = packed_values_sum<kBits>(gpu, c0 + inc - cnt, cnt);
         if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += s;          // rows past hi have cnt 0
         c0 += __shfl_sync(0xffffffffu, inc, 31);
     }
@@ -1249,10 +1268,17 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u64 n_warps = (u64)gridDim.x * kWarps, w0 = (u64)blockIdx.x * kWarps + warp;
     u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every warp
+    unsigned lo_n = 0, hi_n = 0, c_n = 0;               // the next node's offsets, fetched one node ahead
+    if (w0 < a.N) { lo_n = __ldg(a.node_pod_begin + w0); hi_n = __ldg(a.node_pod_begin + w0 + 1); c_n = __ldg(a.node_ctr_begin + w0); }
     for (u64 n = w0; n < a.N; n += n_warps) {
-        const unsigned lo = __ldg(a.node_pod_begin + n), hi = __ldg(a.node_pod_begin + n + 1);
+        const unsigned lo = lo_n, hi = hi_n, c0 = c_n;
+        if (n + n_warps < a.N) {
+            lo_n = __ldg(a.node_pod_begin + n + n_warps);
+            hi_n = __ldg(a.node_pod_begin + n + n_warps + 1);
+            c_n = __ldg(a.node_ctr_begin + n + n_warps);
+        }
         if (hi - lo <= kBigNodePods) {
-            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, __ldg(a.node_ctr_begin + n), lane);
+            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, lane);
             if (lane == 0) { a.node_alloc[n] = s; alloc_sum += s; }
         }
         if (lane == 0) {
