@@ -763,6 +763,7 @@ int arena_peer_exchange_create(int rank, int world, unsigned char handle_out[64]
     g_px_host = PeerExchange{};
     g_px_host.rank = rank;
     g_px_host.world = world;
+    g_epoch.store(0);                     // every rank starts counting steps from the same place
     return ARENA_OK;
 }
 
