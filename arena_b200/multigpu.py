@@ -61,6 +61,36 @@ def gather_tables(local_total: np.ndarray, local_alloc: np.ndarray, dst: int = 0
     return np.concatenate([o[0] for o in out]), np.concatenate([o[1] for o in out])
 
 
+def bind_to_gpu_numa_node(local_rank: int):
+    """Run this process on the CPUs of the NUMA node its GPU hangs off, so that the page-locked
+    staging buffers it allocates afterwards (first touch) sit next to the GPU's PCIe root: with
+    one process per GPU all uploading at once, remote-socket memory is what limits them.
+    Returns the node number, or None when the topology cannot be read (nothing is changed)."""
+    import os
+    import subprocess
+    try:
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]                                   # sysfs uses a 4-digit PCI domain
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def setup_peer_exchange() -> bool:
     """Map every rank's totals mailbox into every process (CUDA IPC over NVLink) so that
     top_node_device_fused can trade the cluster totals inside the kernel.  Collective: every

@@ -281,6 +281,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    numa = multigpu.bind_to_gpu_numa_node(local) if world > 1 else None
     multigpu.init_process_group("nccl")
     ab.init(local)
     n_gpus = world
@@ -299,7 +300,7 @@ def main():
     else:
         host = ab.HostSnapshot.synth(args.pods, args.nodes, seed=seed0 + rank, pinned=True, skewed=args.skewed)
     P, C, N = host.n_pods, host.n_containers, host.n_nodes
-    log(f"[rank {rank}] snapshot: P={P} C={C} N={N} generated in {time.time() - t_gen:.1f}s")
+    log(f"[rank {rank}] snapshot: P={P} C={C} N={N} generated in {time.time() - t_gen:.1f}s (NUMA node {numa})")
     total_pods = torch.tensor([P], dtype=torch.int64, device="cuda")
     max_pods = torch.tensor([P], dtype=torch.int64, device="cuda")
     if world > 1:
