@@ -34,6 +34,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using arena_host::fail;
@@ -477,6 +478,64 @@ struct DeviceBuffers {
     }
 };
 
+// ---- pageable documents: staged upload ---------------------------------------------------------
+// A caller's buffer is usually ordinary (pageable) memory -- a Go []byte, a Python bytes -- which the
+// driver copies through its own small staging area at a fraction of the PCIe rate.  A large pageable
+// document is therefore cut into 4 MiB chunks that kStageThreads host threads copy into page-locked
+// slots (two per thread, kept between calls) and send from there, each on its own stream: the
+// memcpys of several cores overlap one another and the DMA.
+constexpr int kStageThreads = 4;
+constexpr size_t kStageChunk = 4u << 20;
+struct StageLane {
+    void *slot[2] = {nullptr, nullptr};
+    cudaEvent_t sent[2] = {nullptr, nullptr};
+    cudaStream_t stream = nullptr;
+};
+StageLane g_stage[kStageThreads];            // guarded by g_load_mu
+
+bool is_pageable(const void *p)
+{
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return at.type == cudaMemoryTypeUnregistered;
+}
+
+int staged_upload(unsigned char *d_dst, const char *src, size_t len, cudaStream_t st, int device)
+{
+    for (StageLane &l : g_stage) {
+        if (l.stream) continue;
+        CUDA_TRY(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            CUDA_TRY(cudaHostAlloc(&l.slot[k], kStageChunk, cudaHostAllocDefault));
+            CUDA_TRY(cudaEventCreateWithFlags(&l.sent[k], cudaEventDisableTiming));
+        }
+    }
+    const size_t n_chunks = (len + kStageChunk - 1) / kStageChunk;
+    cudaError_t err[kStageThreads];
+    std::vector<std::thread> pool;
+    auto work = [&](int t) {
+        err[t] = cudaSetDevice(device);
+        StageLane &l = g_stage[t];
+        int k = 0;
+        for (size_t c = t; c < n_chunks && err[t] == cudaSuccess; c += kStageThreads, k ^= 1) {
+            const size_t off = c * kStageChunk, n = std::min(kStageChunk, len - off);
+            err[t] = cudaEventSynchronize(l.sent[k]);            // the slot's previous chunk has left
+            if (err[t] != cudaSuccess) break;
+            std::memcpy(l.slot[k], src + off, n);
+            err[t] = cudaMemcpyAsync(d_dst + off, l.slot[k], n, cudaMemcpyHostToDevice, l.stream);
+            if (err[t] == cudaSuccess) err[t] = cudaEventRecord(l.sent[k], l.stream);
+        }
+    };
+    for (int t = 1; t < kStageThreads; t++) pool.emplace_back(work, t);
+    work(0);
+    for (std::thread &th : pool) th.join();
+    for (int t = 0; t < kStageThreads; t++) {
+        if (err[t] != cudaSuccess) return fail(ARENA_E_CUDA, "staged upload: %s", cudaGetErrorString(err[t]));
+        for (int k = 0; k < 2; k++) CUDA_TRY(cudaStreamWaitEvent(st, g_stage[t].sent[k], 0));   // kernels wait for every chunk
+    }
+    return ARENA_OK;
+}
+
 int exclusive_scan(const u64 *d_in, u64 n, u64 *d_out, u64 *d_tile_sums, u64 *d_total, cudaStream_t st)
 {
     const u64 tiles = (n + kScanTile - 1) / kScanTile;
@@ -498,6 +557,14 @@ void free_loader_workspace()
     std::lock_guard<std::mutex> lock(g_load_mu);
     for (Chunk &c : g_chunks) cudaFree(c.base);
     g_chunks.clear();
+    for (StageLane &l : g_stage) {
+        for (int k = 0; k < 2; k++) {
+            if (l.slot[k]) cudaFreeHost(l.slot[k]);
+            if (l.sent[k]) cudaEventDestroy(l.sent[k]);
+        }
+        if (l.stream) cudaStreamDestroy(l.stream);
+        l = StageLane{};
+    }
 }
 
 }  // namespace arena_internal
@@ -581,7 +648,15 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
 
     CUDA_TRY(cudaMemsetAsync(d_res, 0, offsetof(ScanResult, root_open), st));
     CUDA_TRY(cudaMemsetAsync(d_text + (n_words - 1) * kWordBytes, ' ', kWordBytes + 64, st));
-    CUDA_TRY(cudaMemcpyAsync(d_text, podlist, len, cudaMemcpyHostToDevice, st));
+    if (len >= 4 * kStageChunk && is_pageable(podlist)) {
+        int device = 0;
+        CUDA_TRY(cudaGetDevice(&device));
+        CUDA_TRY(cudaStreamSynchronize(st));                     // the padding memset lands before the chunks
+        rc = staged_upload(d_text, podlist, len, st, device);
+        if (rc) return rc;
+    } else {
+        CUDA_TRY(cudaMemcpyAsync(d_text, podlist, len, cudaMemcpyHostToDevice, st));
+    }
     if (stats) { CUDA_TRY(cudaStreamSynchronize(st)); stats->ms_h2d = ms_since(t_start); }
 
     classify_words_kernel<<<(unsigned)n_ctas, kCta, 0, st>>>((const uint4 *)d_text, n_words, d_quote, d_open, d_close, d_effect,
