@@ -397,8 +397,8 @@ static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool j
     for (int i = 0; i < 10; i++) {
         dst[i] = p;
         if (sizes[i] && src[i]) {
-            cudaError_t e = cudaMemcpyAsync(p, src[i], sizes[i], cudaMemcpyHostToDevice, g_ctx.stream);
-            if (e != cudaSuccess) return fail(ARENA_E_CUDA, "H2D copy of column %d: %s", i, cudaGetErrorString(e));
+            const int crc = arena_internal::copy_to_device(p, src[i], sizes[i], g_ctx.stream);
+            if (crc) return crc;
         }
         p += pad16(sizes[i]) + 16;
     }
@@ -633,8 +633,9 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     char *pb = (char *)g_packed_block;
     CUDA_TRY(cudaMemcpyAsync(pb + o_begin, h->node_pod_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(pb + o_cbegin, h->node_ctr_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
-    if (P) CUDA_TRY(cudaMemcpyAsync(pb + o_meta, h->pod_meta, P, cudaMemcpyHostToDevice, st));
-    if (C) CUDA_TRY(cudaMemcpyAsync(pb + o_gpu, h->ctr_gpu, gpu_bytes, cudaMemcpyHostToDevice, st));
+    int crc;
+    if ((crc = arena_internal::copy_to_device(pb + o_meta, h->pod_meta, P, st))) return crc;
+    if ((crc = arena_internal::copy_to_device(pb + o_gpu, h->ctr_gpu, gpu_bytes, st))) return crc;
     if (K) CUDA_TRY(cudaMemcpyAsync(pb + o_pieces, h->pieces, K * 16, cudaMemcpyHostToDevice, st));
     if (N) {
         CUDA_TRY(cudaMemcpyAsync(pb + o_capv, h->node_cap_val, N * 8, cudaMemcpyHostToDevice, st));

@@ -491,7 +491,8 @@ struct StageLane {
     cudaEvent_t sent[2] = {nullptr, nullptr};
     cudaStream_t stream = nullptr;
 };
-StageLane g_stage[kStageThreads];            // guarded by g_load_mu
+StageLane g_stage[kStageThreads];
+std::mutex g_stage_mu;
 
 bool is_pageable(const void *p)
 {
@@ -502,6 +503,7 @@ bool is_pageable(const void *p)
 
 int staged_upload(unsigned char *d_dst, const char *src, size_t len, cudaStream_t st, int device)
 {
+    std::lock_guard<std::mutex> lock(g_stage_mu);
     for (StageLane &l : g_stage) {
         if (l.stream) continue;
         CUDA_TRY(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
@@ -552,11 +554,25 @@ int exclusive_scan(const u64 *d_in, u64 n, u64 *d_out, u64 *d_tile_sums, u64 *d_
 
 namespace arena_internal {
 
+int copy_to_device(void *d_dst, const void *src, size_t bytes, cudaStream_t st)
+{
+    if (!bytes) return ARENA_OK;
+    if (bytes >= 4 * kStageChunk && is_pageable(src)) {
+        int device = 0;
+        CUDA_TRY(cudaGetDevice(&device));
+        CUDA_TRY(cudaStreamSynchronize(st));                     // earlier work on `st` that touches the target is done
+        return staged_upload((unsigned char *)d_dst, (const char *)src, bytes, st, device);
+    }
+    CUDA_TRY(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, st));
+    return ARENA_OK;
+}
+
 void free_loader_workspace()
 {
     std::lock_guard<std::mutex> lock(g_load_mu);
     for (Chunk &c : g_chunks) cudaFree(c.base);
     g_chunks.clear();
+    std::lock_guard<std::mutex> stage_lock(g_stage_mu);
     for (StageLane &l : g_stage) {
         for (int k = 0; k < 2; k++) {
             if (l.slot[k]) cudaFreeHost(l.slot[k]);
@@ -648,15 +664,8 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
 
     CUDA_TRY(cudaMemsetAsync(d_res, 0, offsetof(ScanResult, root_open), st));
     CUDA_TRY(cudaMemsetAsync(d_text + (n_words - 1) * kWordBytes, ' ', kWordBytes + 64, st));
-    if (len >= 4 * kStageChunk && is_pageable(podlist)) {
-        int device = 0;
-        CUDA_TRY(cudaGetDevice(&device));
-        CUDA_TRY(cudaStreamSynchronize(st));                     // the padding memset lands before the chunks
-        rc = staged_upload(d_text, podlist, len, st, device);
-        if (rc) return rc;
-    } else {
-        CUDA_TRY(cudaMemcpyAsync(d_text, podlist, len, cudaMemcpyHostToDevice, st));
-    }
+    rc = arena_internal::copy_to_device(d_text, podlist, len, st);   // (after the padding memset)
+    if (rc) return rc;
     if (stats) { CUDA_TRY(cudaStreamSynchronize(st)); stats->ms_h2d = ms_since(t_start); }
 
     classify_words_kernel<<<(unsigned)n_ctas, kCta, 0, st>>>((const uint4 *)d_text, n_words, d_quote, d_open, d_close, d_effect,

@@ -211,3 +211,18 @@ def test_fused_totals_exchange_with_itself(gpu):
         assert gpu.lib().arena_peer_exchange_timed_out() == 0
     finally:
         gpu.lib().arena_peer_exchange_destroy()
+
+
+def test_pageable_columns_take_the_staged_upload(gpu):
+    """Columns in ordinary (pageable) memory above 16 MiB go to the device through page-locked
+    slots filled by several host threads; the results must not notice."""
+    host = gpu.HostSnapshot.synth(6_000_000, 50_000, seed=13, pinned=False)      # pod_node alone is 24 MB
+    tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+    for _ in range(2):
+        res = gpu.top_node(host)                                                 # arena_top_node_host
+        assert np.array_equal(res.node_alloc, alloc) and np.array_equal(res.node_total, tot) and np.array_equal(res.cluster, cl)
+    dev = gpu.DeviceSnapshot.upload(host)
+    res = gpu.top_node(dev)
+    assert np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
+    res = gpu.top_node_packed(host.pack(pinned=False))
+    assert np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
