@@ -784,7 +784,10 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                     unsigned key_next = __shfl_down_sync(FULL, k4.x, 1);
                     if (lane == 31) key_next = kNone;
                     const bool e0 = k4.x != k4.y, e1 = k4.y != k4.z, e2 = k4.z != k4.w;
-                    const bool e3 = (k4.w != key_next) | (lane == 31);
+                    // the tile's last run is closed by lane 31 on its own, so that the block below runs
+                    // only in tiles where the node really changes (7 of 10 at 100 pods per node)
+                    const bool e3 = (k4.w != key_next) & (lane != 31);
+                    if (!kDirect && lane == 31 && k4.w < K32) red_add_u64(a.key_alloc + k4.w, (u64)(off + S3));
                     if (kDirect) {
                         if (a0) red_add_u64(a.key_alloc + k4.x, a0);
                         if (a1) red_add_u64(a.key_alloc + k4.y, a1);
@@ -809,7 +812,7 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                         if (e3) {
                             const u64 v = off + S3;
                             if (k4.w < K32) red_add_u64(a.key_alloc + k4.w, v);
-                            if (lane != 31 && key_next < K32) red_add_u64(a.key_alloc + key_next, 0ull - v);
+                            if (key_next < K32) red_add_u64(a.key_alloc + key_next, 0ull - v);
                         }
                     }
                 }
