@@ -125,3 +125,45 @@ func topJobGPU(podList, nodeList, jobList, tfjobList, helmList []byte, nowUnix i
 	defer C.arena_free_text(text)
 	return C.GoStringN(text, C.int(tlen)), nil
 }
+
+// topNodeSummaryGPU is topNodeGPU for the summary view with the PodList parsed on the GPU
+// (arena_load_json_device): the library stages the pageable Go bytes through page-locked
+// slots itself, parses the document on the device and falls back to its host loader for
+// anything unusual, with identical output and error texts either way.
+func topNodeSummaryGPU(podList, nodeList []byte) (string, error) {
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	if err := gpuacctErr(C.arena_acct_init(0)); err != nil {
+		return "", err
+	}
+	var nodes *C.arena_host_snapshot
+	var dev *C.arena_snapshot
+	if err := gpuacctErr(C.arena_load_json_device(
+		(*C.char)(unsafe.Pointer(&podList[0])), C.size_t(len(podList)),
+		(*C.char)(unsafe.Pointer(&nodeList[0])), C.size_t(len(nodeList)),
+		&nodes, &dev, nil)); err != nil {
+		return "", err
+	}
+	defer C.arena_host_snapshot_free(nodes)
+	defer C.arena_snapshot_free(dev)
+	var counts [4]C.uint64_t
+	C.arena_snapshot_counts(dev, &counts[0])
+	n := int(counts[2])
+	total := make([]int64, n+1)
+	alloc := make([]int64, n+1)
+	var cluster [2]C.int64_t
+	if err := gpuacctErr(C.arena_top_node(dev,
+		(*C.int64_t)(unsafe.Pointer(&total[0])), (*C.int64_t)(unsafe.Pointer(&alloc[0])),
+		&cluster[0], nil)); err != nil {
+		return "", err
+	}
+	var text *C.char
+	var tlen C.size_t
+	if err := gpuacctErr(C.arena_format_top_node(nodes,
+		(*C.int64_t)(unsafe.Pointer(&total[0])), (*C.int64_t)(unsafe.Pointer(&alloc[0])),
+		nil, 0, &text, &tlen)); err != nil {
+		return "", err
+	}
+	defer C.arena_free_text(text)
+	return C.GoStringN(text, C.int(tlen)), nil
+}
