@@ -288,9 +288,28 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
                    i64 *d_totals, cudaStream_t st)
 {
     const arena_snapshot_view &v = s->v;
+    const u64 J = v.n_jobs;
+    if (v.n_pods <= kSmallJobPods && J <= kSmallJobs) {         // a small cluster: one launch does it all
+        static bool smem_ok = false;
+        if (!smem_ok) {
+            CUDA_TRY(cudaFuncSetAttribute(job_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallJobSmem));
+            smem_ok = true;
+        }
+        JobSmallArgs sa{};
+        sa.P = v.n_pods; sa.J = J;
+        sa.pod_job = v.pod_job; sa.pod_phase = v.pod_phase; sa.pod_role = v.pod_role;
+        sa.pod_ctr_begin = v.pod_ctr_begin;
+        sa.ctr_val = (const i64 *)v.ctr_val; sa.ctr_scale = (const signed char *)v.ctr_scale;
+        sa.pod_created = (const i64 *)v.pod_created;
+        sa.out_req = d_req; sa.out_alloc = d_alloc; sa.out_order = d_order; sa.out_latest = d_latest;
+        sa.out_totals = d_totals;
+        job_small_kernel<<<1, 1024, kSmallJobSmem, st>>>(sa);
+        count_launch();
+        CUDA_TRY(cudaGetLastError());
+        return ARENA_OK;
+    }
     int rc = ensure_job_arrays(s);
     if (rc) return rc;
-    const u64 J = v.n_jobs;
 
     JobInitArgs ia{J, s->job_req, s->job_alloc, s->job_maxcreated, s->job_latest};
     job_init_kernel<<<grid_for(J, kThreads * 4, 8), kThreads, 0, st>>>(ia);

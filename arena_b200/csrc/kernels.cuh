@@ -1306,3 +1306,111 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
 }
 
 }  // namespace arena
+
+// ---- `top job` for small clusters in ONE launch ------------------------------------------------
+// BASELINE configs[1] (1e4 pods, 1e3 jobs) is latency, not bandwidth: the general path is seven
+// launches of a few microseconds each.  Up to kSmallJobPods pods and kSmallJobs jobs everything --
+// per-job sums, the latest-pod rule, totals, the ordering -- fits one CTA and its shared memory.
+// Same arithmetic and the same tie rules as the general kernels above.
+namespace arena {
+
+constexpr unsigned kSmallJobs = 2048, kSmallJobPods = 65536;
+constexpr size_t kSmallJobSmem = (size_t)kSmallJobs * (4 * 8 + 2 * 4);
+
+struct JobSmallArgs {
+    u64 P, J;
+    const unsigned *pod_job;
+    const unsigned char *pod_phase, *pod_role;
+    const unsigned *pod_ctr_begin;
+    const i64 *ctr_val;
+    const signed char *ctr_scale;
+    const i64 *pod_created;
+    i64 *out_req, *out_alloc;
+    unsigned *out_order, *out_latest;      // out_latest may be nullptr
+    i64 *out_totals;
+};
+
+__device__ __forceinline__ u64 small_gpu_in_pod(const JobSmallArgs &a, u64 p)
+{
+    u64 g = 0;
+    for (unsigned c = a.pod_ctr_begin[p]; c < a.pod_ctr_begin[p + 1]; c++)
+        g += (u64)quantity_value(a.ctr_val[c], a.ctr_scale[c]);
+    return g;
+}
+
+__global__ void __launch_bounds__(1024) job_small_kernel(const __grid_constant__ JobSmallArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64 *req = reinterpret_cast<u64 *>(smem), *alc = req + kSmallJobs, *key = alc + kSmallJobs;
+    i64 *maxc = reinterpret_cast<i64 *>(key + kSmallJobs);
+    unsigned *latest = reinterpret_cast<unsigned *>(maxc + kSmallJobs), *idx = latest + kSmallJobs;
+    const unsigned tid = threadIdx.x;
+    for (unsigned j = tid; j < kSmallJobs; j += 1024) {
+        req[j] = 0; alc[j] = 0; maxc[j] = (i64)0x8000000000000000ull; latest[j] = kNone;
+    }
+    __syncthreads();
+    u64 tot_req = 0, tot_alloc = 0;
+    for (u64 p = tid; p < a.P; p += 1024) {
+        const unsigned j = a.pod_job[p];
+        if (j >= a.J) continue;
+        if (a.pod_role[p] == 1) { atomicMax(reinterpret_cast<long long *>(maxc + j), (long long)a.pod_created[p]); continue; }
+        const u64 g = small_gpu_in_pod(a, p);
+        if (g) atomicAdd(reinterpret_cast<unsigned long long *>(req + j), g);
+        tot_req += g;
+        if (phase_active(a.pod_phase[p])) {
+            if (g) atomicAdd(reinterpret_cast<unsigned long long *>(alc + j), g);
+            tot_alloc += g;
+        }
+    }
+    __syncthreads();
+    for (u64 p = tid; p < a.P; p += 1024) {            // first pod in list order among the newest
+        const unsigned j = a.pod_job[p];
+        if (j < a.J && a.pod_role[p] == 1 && a.pod_created[p] == maxc[j]) atomicMin(latest + j, (unsigned)p);
+    }
+    __syncthreads();
+    for (unsigned j = tid; j < kSmallJobs; j += 1024) {
+        if (j >= a.J) { key[j] = ~0ull; idx[j] = kNone; continue; }
+        u64 r = req[j], al = alc[j];
+        const unsigned p = latest[j];
+        if (p != kNone) {
+            const u64 g = small_gpu_in_pod(a, p);
+            r += g; tot_req += g;
+            if (phase_active(a.pod_phase[p])) { al += g; tot_alloc += g; }
+        }
+        a.out_req[j] = (i64)r;
+        a.out_alloc[j] = (i64)al;
+        if (a.out_latest) a.out_latest[j] = p;
+        key[j] = ~(r ^ 0x8000000000000000ull);          // requested DESC as an ascending key
+        idx[j] = j;
+    }
+    // totals
+    __shared__ u64 s_r[32], s_a[32];
+    tot_req = warp_reduce_sum(tot_req);
+    tot_alloc = warp_reduce_sum(tot_alloc);
+    if ((tid & 31) == 0) { s_r[tid >> 5] = tot_req; s_a[tid >> 5] = tot_alloc; }
+    __syncthreads();
+    if (tid == 0) {
+        u64 r = 0, al = 0;
+        for (int w = 0; w < 32; w++) { r += s_r[w]; al += s_a[w]; }
+        a.out_totals[0] = (i64)r;
+        a.out_totals[1] = (i64)al;
+    }
+    // bitonic sort of the 2048 (key, id) pairs: ascending key, then id
+    for (unsigned k = 2; k <= kSmallJobs; k <<= 1)
+        for (unsigned d = k >> 1; d > 0; d >>= 1) {
+            for (unsigned t = tid; t < kSmallJobs; t += 1024) {
+                const unsigned u = t ^ d;
+                if (u > t) {
+                    const bool up = (t & k) == 0;
+                    const u64 ka = key[t], kb = key[u];
+                    const unsigned ia = idx[t], ib = idx[u];
+                    const bool a_less = ka < kb || (ka == kb && ia < ib);
+                    if (a_less != up) { key[t] = kb; key[u] = ka; idx[t] = ib; idx[u] = ia; }
+                }
+            }
+            __syncthreads();
+        }
+    for (unsigned j = tid; j < a.J; j += 1024) a.out_order[j] = idx[j];
+}
+
+}  // namespace arena
