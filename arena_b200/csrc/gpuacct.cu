@@ -85,6 +85,11 @@ static PeerExchange *g_px = nullptr;             // device copy of the descripto
 static PeerExchange g_px_host{};
 static void *g_peer_mapped[kMaxPeers] = {};
 static std::atomic<uint64_t> g_epoch{0};
+// A few freed device blocks are kept for the next snapshot of about the same size: a polling caller
+// (load, query, free, again) otherwise pays cudaMalloc + cudaFree, which cost more than its kernels.
+struct FreeBlock { void *p; size_t bytes; };
+static FreeBlock g_free_blocks[8] = {};
+static std::mutex g_pool_mu;
 static void *g_packed_block = nullptr;           // staging of arena_top_node_host_packed: packed columns + tile sums
 static size_t g_packed_bytes = 0;
 
@@ -129,6 +134,7 @@ void arena_acct_shutdown(void)
     if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
     if (g_packed_block) { cudaFree(g_packed_block); g_packed_block = nullptr; g_packed_bytes = 0; }
     arena_peer_exchange_destroy();
+    arena_internal::device_pool_clear();
     arena_internal::free_loader_workspace();
     cudaStreamDestroy(g_ctx.stream);
     g_ctx = Context{};
@@ -171,7 +177,7 @@ int check_view(const arena_snapshot_view *v, bool device_ptrs)
 
 int alloc_common(arena_snapshot *s)
 {
-    CUDA_TRY(cudaMalloc((void **)&s->scratch, sizeof(Scratch)));
+    CUDA_TRY(arena_internal::device_alloc((void **)&s->scratch, sizeof(Scratch)));
     CUDA_TRY(cudaMemsetAsync(s->scratch, 0, sizeof(Scratch), g_ctx.stream));
     return ARENA_OK;
 }
@@ -401,10 +407,10 @@ static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool j
     for (size_t z : sizes) total += pad16(z) + 16;
     if (total < 16) total = 16;
     if (s->block_bytes < total) {
-        if (s->block) cudaFree(s->block);
+        if (s->block) arena_internal::device_release(s->block, s->block_bytes);
         s->block = nullptr;
         s->block_bytes = 0;
-        cudaError_t e = cudaMalloc(&s->block, total);
+        cudaError_t e = arena_internal::device_alloc(&s->block, total);
         if (e != cudaSuccess)
             return fail(e == cudaErrorMemoryAllocation ? ARENA_E_NOMEM : ARENA_E_CUDA, "cudaMalloc(%zu): %s", total,
                         cudaGetErrorString(e));
@@ -482,6 +488,61 @@ int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **ou
 
 namespace arena_internal {
 
+cudaError_t device_alloc(void **out, size_t bytes)
+{
+    if (bytes < 256) bytes = 256;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        int best = -1;
+        for (int i = 0; i < 8; i++)
+            if (g_free_blocks[i].p && g_free_blocks[i].bytes >= bytes && g_free_blocks[i].bytes <= 2 * bytes + (1u << 20) &&
+                (best < 0 || g_free_blocks[i].bytes < g_free_blocks[best].bytes))
+                best = i;
+        if (best >= 0) {
+            *out = g_free_blocks[best].p;
+            g_free_blocks[best] = FreeBlock{nullptr, 0};
+            return cudaSuccess;
+        }
+    }
+    cudaError_t e = cudaMalloc(out, bytes);
+    if (e == cudaErrorMemoryAllocation) {          // give the cache back and try once more
+        device_pool_clear();
+        cudaGetLastError();
+        e = cudaMalloc(out, bytes);
+    }
+    return e;
+}
+
+// `bytes` = what the block was allocated with (device_alloc's argument).  Waits for the device, as
+// cudaFree would, so that a block is never handed out while something still runs on it.
+void device_release(void *p, size_t bytes)
+{
+    if (!p) return;
+    if (bytes < 256) bytes = 256;
+    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    int slot = -1;
+    for (int i = 0; i < 8; i++)
+        if (!g_free_blocks[i].p) { slot = i; break; }
+    if (slot < 0) {                                 // full: drop the smallest
+        slot = 0;
+        for (int i = 1; i < 8; i++)
+            if (g_free_blocks[i].bytes < g_free_blocks[slot].bytes) slot = i;
+        if (g_free_blocks[slot].bytes >= bytes) { cudaFree(p); return; }
+        cudaFree(g_free_blocks[slot].p);
+    }
+    g_free_blocks[slot] = FreeBlock{p, bytes};
+}
+
+void device_pool_clear()
+{
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (FreeBlock &b : g_free_blocks) {
+        if (b.p) cudaFree(b.p);
+        b = FreeBlock{nullptr, 0};
+    }
+}
+
 int ready(cudaStream_t *stream, int *sm_count)
 {
     int rc = check_ready();
@@ -500,7 +561,7 @@ int adopt_device_block(void *block, size_t block_bytes, const arena_snapshot_vie
     if (!rc) rc = check_view(&device_view, true);
     arena_snapshot *s = rc ? nullptr : new (std::nothrow) arena_snapshot();
     if (!rc && !s) rc = fail(ARENA_E_NOMEM, "out of host memory");
-    if (rc) { cudaFree(block); return rc; }
+    if (rc) { device_release(block, block_bytes); return rc; }
     s->v = device_view;
     s->v.n_jobs = 0;
     s->owns = true;
@@ -549,8 +610,8 @@ void arena_snapshot_free(arena_snapshot *s)
 {
     if (!s) return;
     if (g_ctx.ready) cudaSetDevice(g_ctx.device);
-    if (s->owns && s->block) cudaFree(s->block);
-    if (s->scratch) cudaFree(s->scratch);
+    if (s->owns && s->block) arena_internal::device_release(s->block, s->block_bytes);
+    if (s->scratch) arena_internal::device_release(s->scratch, sizeof(Scratch));
     if (s->job_req) cudaFree(s->job_req);
     if (s->d_out) cudaFree(s->d_out);
     delete s;

@@ -820,7 +820,8 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
                  o_scale = o_val + pad16(C * 8), o_capv = o_scale + pad16(C), o_caps = o_capv + pad16(N * 8),
                  total = o_caps + pad16(N);
     char *block = nullptr;
-    CUDA_TRY(cudaMalloc((void **)&block, pad256(total ? total : 16)));
+    const size_t block_bytes = pad256(total ? total : 16);
+    CUDA_TRY(arena_internal::device_alloc((void **)&block, block_bytes));
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
     step(cudaMemsetAsync(block + o_cb, 0, pad16((P + 1) * 4), st));
@@ -838,7 +839,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         step(cudaMemcpyAsync(block + o_caps, nodes->v.node_cap_scale, N, cudaMemcpyHostToDevice, st));
     }
     step(cudaStreamSynchronize(st));
-    if (e != cudaSuccess) { cudaFree(block); return fail(ARENA_E_CUDA, "device loader: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) { arena_internal::device_release(block, block_bytes); return fail(ARENA_E_CUDA, "device loader: %s", cudaGetErrorString(e)); }
 
     arena_snapshot_view v{};
     v.n_pods = P; v.n_containers = C; v.n_nodes = N; v.n_jobs = 0;
@@ -849,7 +850,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     v.ctr_scale = (const int8_t *)(block + o_scale);
     v.node_cap_val = (const int64_t *)(block + o_capv);
     v.node_cap_scale = (const int8_t *)(block + o_caps);
-    rc = arena_internal::adopt_device_block(block, total, v, snap_out);
+    rc = arena_internal::adopt_device_block(block, block_bytes, v, snap_out);
     if (rc) return rc;
     if (stats) stats->ms_device = ms_since(t_start);
     *handled = true;
