@@ -336,7 +336,8 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     pa.total_req = d_totals;
     pa.total_alloc = d_totals + 1;
     pa.scratch = s->scratch;
-    job_pods_kernel<<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
+    // the top-node kernel's 32-bit fast tiles, keyed by job (generic tiles where a tile does not qualify)
+    top_node_pods_kernel<true, false, true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm), kThreads, 0, st>>>(pa);
     count_launch();
 
     if (v.n_pods) {

@@ -541,6 +541,11 @@ __device__ __noinline__ TileSums process_tile_fallback(const PodsArgs *a, unsign
     return process_tile_generic<false>(*a, tile, full_tile, lane, prefix);
 }
 
+__device__ __noinline__ TileSums process_tile_fallback_job(const PodsArgs *a, unsigned tile, bool full_tile, int lane, u64 *prefix)
+{
+    return process_tile_generic<true>(*a, tile, full_tile, lane, prefix);
+}
+
 // Job kernel: generic tiles only.
 __global__ void __launch_bounds__(kThreads) job_pods_kernel(PodsArgs a)
 {
@@ -686,7 +691,10 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
 // per pod that contributes anything.  Both instantiations are exact for any order; the host picks
 // one from a sample of the pod_node column (probe_grouping / arena_snapshot_upload).
 // kDetails: also write gpuInPod of every pod (the details view); kept out of the summary kernel.
-template <bool kDirect, bool kDetails>
+// kJob: the same tiles keyed by pod_job for `top job` (job_info.go:51-70): requested = every pod,
+// allocated = active pods, ARENA_ROLE_LATEST pods only bid with their creation time; per-pod adds
+// (pods of one job are scattered over the node-grouped rows), two totals.
+template <bool kDirect, bool kDetails, bool kJob = false>
 __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
@@ -698,6 +706,7 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
 
     u64 acc_alloc = 0;
+    u64 job_req = 0, job_alloc = 0;             // kJob: every lane's own partial totals
     const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
     const unsigned n_full = (unsigned)(a.P / kWarpPods);
     const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
@@ -771,6 +780,25 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                         dst[0] = o0;
                         dst[1] = o1;
                     }
+                    if (kJob) {
+                        const unsigned r4 = __ldg(reinterpret_cast<const unsigned *>(a.pod_role + q));
+                        const unsigned ks[4] = {k4.x, k4.y, k4.z, k4.w}, gs[4] = {g0, g1, g2, g3};
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            if (ks[j] >= K32) continue;
+                            if (((r4 >> (8 * j)) & 0xffu) == 1u) {            // bids for "latest pod of the job"
+                                atomicMax(a.key_maxcreated + ks[j], __ldg(a.pod_created + q + j));
+                                continue;
+                            }
+                            const u64 g = gs[j];
+                            if (g) red_add_u64(a.key_req + ks[j], g);
+                            job_req += g;
+                            if (phase_active((ph4 >> (8 * j)) & 0xffu)) {
+                                if (g) red_add_u64(a.key_alloc + ks[j], g);
+                                job_alloc += g;
+                            }
+                        }
+                    } else {
                     // ---- masks: node exists, phase active ------------------------------
                     const unsigned a0 = (k4.x < K32 && phase_active(ph4 & 0xffu)) ? g0 : 0u;
                     const unsigned a1 = (k4.y < K32 && phase_active((ph4 >> 8) & 0xffu)) ? g1 : 0u;
@@ -815,11 +843,31 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                             if (key_next < K32) red_add_u64(a.key_alloc + key_next, 0ull - v);
                         }
                     }
+                    }
                 }
             }
         }
+        if (kJob) {
+            if (!fast) {
+                const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
+                if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
+            }
+            continue;
+        }
         if (!fast) tile_alloc = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
         if (lane == 31) acc_alloc += tile_alloc;
+    }
+    if (kJob) {
+        __shared__ u64 s_wr[kWarps];
+        job_req = warp_reduce_sum(job_req);
+        job_alloc = warp_reduce_sum(job_alloc);
+        if (lane == 0) { s_wr[warp] = job_req; s_wa[warp] = job_alloc; }
+        __syncthreads();
+        u64 block_r = 0, block_al = 0;
+        if (threadIdx.x == 0)
+            for (int w = 0; w < kWarps; w++) { block_r += s_wr[w]; block_al += s_wa[w]; }
+        finish_totals(block_al, block_r, true, a.scratch, 2, a.total_alloc, a.total_req);
+        return;
     }
 
     // ---- node capacities (gpuInNode, gpu.go:18-37): 9N bytes in, 8N out.  Done by the same
