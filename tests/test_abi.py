@@ -54,3 +54,28 @@ def test_calls_fail_loudly_without_init_or_gpu(built):
     assert L.arena_top_node(None, None, None, cluster, None) == -3      # ARENA_E_NOT_INIT
     v = _lib.SnapshotView()
     assert L.arena_top_node_host(C.byref(v), None, None, cluster, None) == -3
+
+
+def test_newer_entry_points_also_fail_loudly_without_a_gpu(built):
+    """The GPU loader, the packed one-shot call, pinned buffers and the peer exchange have no
+    host stand-in either: without an initialised device they return ARENA_E_NOT_INIT."""
+    import torch
+    from arena_b200 import _lib
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the -m gpu tests")
+    L = _lib.lib()
+    cluster = (C.c_int64 * 2)()
+    nodes, dev, buf = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    doc = b'{"items": []}'
+    assert L.arena_load_json_device(doc, len(doc), doc, len(doc), C.byref(nodes), C.byref(dev), None) == -3
+    assert nodes.value is None and dev.value is None
+    assert L.arena_pinned_alloc(64, C.byref(buf)) == -3 and buf.value is None
+    pv = _lib.PackedView()
+    assert L.arena_top_node_host_packed(C.byref(pv), None, None, cluster, None) == -3
+    handle = (C.c_ubyte * 64)()
+    assert L.arena_peer_exchange_create(0, 1, handle) == -3
+    assert L.arena_peer_exchange_connect(handle) == -3
+    assert L.arena_top_node_device_fused(None, None, None, cluster, None) == -3
+    assert L.arena_peer_exchange_timed_out() == 0
+    L.arena_peer_exchange_destroy()                      # harmless without a mailbox
+    assert b"arena_acct_init" in L.arena_last_error()
