@@ -363,16 +363,22 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
 
     // sort (requested desc, id asc)
     const u64 n = s->jpad;
-    const int tiles = (int)(n / kSortTile);
-    bitonic_tile_kernel<<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, 0, 1);
-    count_launch();
-    for (u64 k = 2 * (u64)kSortTile; k <= n; k <<= 1) {
-        for (u64 j = k >> 1; j >= (u64)kSortTile; j >>= 1) {
+    // large sorts: 4096-pair tiles (fewer passes through global memory); small ones: 2048 (more CTAs)
+    const bool big = n >= (1ull << 18);
+    const u64 tile = big ? kBigSortTile : kSortTile;
+    const int tiles = (int)(n / tile);
+    auto tile_pass = [&](u64 k, int full) {
+        if (big) bitonic_tile_kernel<kBigSortTile><<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, k, full);
+        else bitonic_tile_kernel<kSortTile><<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, k, full);
+        count_launch();
+    };
+    tile_pass(0, 1);
+    for (u64 k = 2 * tile; k <= n; k <<= 1) {
+        for (u64 j = k >> 1; j >= tile; j >>= 1) {
             bitonic_global_kernel<<<grid_for(n / 2, kThreads, 8), kThreads, 0, st>>>(s->sort_key, s->sort_idx, n, k, j);
             count_launch();
         }
-        bitonic_tile_kernel<<<tiles, 1024, 0, st>>>(s->sort_key, s->sort_idx, n, k, 0);
-        count_launch();
+        tile_pass(k, 0);
     }
     CUDA_TRY(cudaGetLastError());
     if (J) {
@@ -1177,7 +1183,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
     job_finish_kernel<<<grid_for(kNoAllocMaxJobs, kThreads, 8), kThreads, 0, st>>>(fa);
     count_launch();
 
-    bitonic_tile_kernel<<<1, 1024, 0, st>>>(w->sort_key, w->sort_idx, kNoAllocMaxJobs, 0, 1);
+    bitonic_tile_kernel<kSortTile><<<1, 1024, 0, st>>>(w->sort_key, w->sort_idx, kNoAllocMaxJobs, 0, 1);
     count_launch();
     CUDA_TRY(cudaGetLastError());
     if (J) CUDA_TRY(cudaMemcpyAsync(d_job_order, w->sort_idx, J * 4, cudaMemcpyDeviceToDevice, st));

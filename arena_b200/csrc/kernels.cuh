@@ -991,10 +991,12 @@ __device__ __forceinline__ bool pair_less(u64 ka, unsigned ia, u64 kb, unsigned 
     return ka < kb || (ka == kb && ia < ib);
 }
 
-constexpr int kSortTile = 2048;    // pairs per CTA in shared memory (24 KB)
+constexpr int kSortTile = 2048;    // pairs per CTA in shared memory (24 KB): the no-alloc entry point's one tile
+constexpr int kBigSortTile = 4096; // the general path: 48 KB, fewer passes through global memory
 
 // Runs every compare-exchange step with distance < kSortTile of stage `k`
 // (or, when full_sort, all stages k = 2..kSortTile) inside shared memory.
+template <int kSortTile>
 __global__ void __launch_bounds__(1024) bitonic_tile_kernel(u64 *key, unsigned *idx, u64 n, u64 k_stage, int full_sort)
 {
     __shared__ u64 s_key[kSortTile];
