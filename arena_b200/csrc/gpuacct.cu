@@ -87,7 +87,7 @@ static void *g_peer_mapped[kMaxPeers] = {};
 static std::atomic<uint64_t> g_epoch{0};
 // A few freed device blocks are kept for the next snapshot of about the same size: a polling caller
 // (load, query, free, again) otherwise pays cudaMalloc + cudaFree, which cost more than its kernels.
-struct FreeBlock { void *p; size_t bytes; };
+struct FreeBlock { void *p; size_t bytes; cudaEvent_t idle; };   // idle: recorded on the library stream at release
 static FreeBlock g_free_blocks[8] = {};
 static std::mutex g_pool_mu;
 static void *g_packed_block = nullptr;           // staging of arena_top_node_host_packed: packed columns + tile sums
@@ -110,9 +110,10 @@ int arena_acct_init(int device)
     CUDA_TRY(cudaSetDevice(device));
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
-    if (prop.major < 10)
-        return fail(ARENA_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device,
-                    prop.major, prop.minor);
+    // the library carries one sm_100a cubin and no PTX: arch-specific code loads on exactly that chip
+    if (prop.major != 10 || prop.minor != 0)
+        return fail(ARENA_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only and carries no "
+                    "code for other architectures", device, prop.major, prop.minor);
     g_ctx.device = device;
     g_ctx.sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
@@ -155,16 +156,18 @@ int check_ready()
     return ARENA_OK;
 }
 
-int check_view(const arena_snapshot_view *v, bool device_ptrs)
+// need_nodes: the `top node` columns (pod_node, node capacities) must be there; `top job` alone
+// (arena_top_job_device_noalloc) reads neither.
+int check_view(const arena_snapshot_view *v, bool device_ptrs, bool need_nodes = true)
 {
     if (!v) return fail(ARENA_E_INVALID, "snapshot view is NULL");
     if (v->n_pods >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_pods %llu >= 2^32-1", (unsigned long long)v->n_pods);
     if (v->n_containers > 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_containers exceeds u32 offsets");
     if (v->n_nodes >= 0xFFFFFFFFull || v->n_jobs >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "n_nodes / n_jobs >= 2^32-1");
     if (!v->pod_ctr_begin) return fail(ARENA_E_INVALID, "pod_ctr_begin is NULL (needs P+1 entries even when P == 0)");
-    if (v->n_pods && (!v->pod_node || !v->pod_phase)) return fail(ARENA_E_INVALID, "pod columns are NULL");
+    if (v->n_pods && ((need_nodes && !v->pod_node) || !v->pod_phase)) return fail(ARENA_E_INVALID, "pod columns are NULL");
     if (v->n_containers && (!v->ctr_val || !v->ctr_scale)) return fail(ARENA_E_INVALID, "container columns are NULL");
-    if (v->n_nodes && (!v->node_cap_val || !v->node_cap_scale)) return fail(ARENA_E_INVALID, "node columns are NULL");
+    if (need_nodes && v->n_nodes && (!v->node_cap_val || !v->node_cap_scale)) return fail(ARENA_E_INVALID, "node columns are NULL");
     if (v->n_jobs && v->n_pods && (!v->pod_job || !v->pod_role || !v->pod_created))
         return fail(ARENA_E_INVALID, "n_jobs > 0 but the job columns are NULL");
     const void *cols[] = {v->pod_node, v->pod_phase, v->pod_ctr_begin, v->ctr_val, v->ctr_scale,
@@ -207,7 +210,7 @@ int grid_for(u64 work_items, u64 items_per_cta, int ctas_per_sm)
 {
     u64 want = (work_items + items_per_cta - 1) / items_per_cta;
     u64 cap = (u64)g_ctx.sm_count * (u64)ctas_per_sm;      // one resident wave: persistent CTAs
-    if (cap > (u64)kMaxPartials) cap = kMaxPartials;
+    if (cap > (u64)kMaxPartials / 2) cap = kMaxPartials / 2;   // finish_totals: half of the partials per ticket id
     if (want < 1) want = 1;
     return (int)(want < cap ? want : cap);
 }
@@ -249,10 +252,10 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     const arena_snapshot_view &v = s->v;
     const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
     cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
-    if (prof) { g_prof.used += 3; cudaEventRecord(pe[0], st); }
+    if (prof) { g_prof.used += 3; CUDA_TRY(cudaEventRecord(pe[0], st)); }
     // node_alloc is accumulated with atomics: it starts from zero
     if (v.n_nodes) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
-    if (prof) cudaEventRecord(pe[1], st);
+    if (prof) CUDA_TRY(cudaEventRecord(pe[1], st));
 
     PodsArgs pa{};
     pa.P = v.n_pods; pa.C = v.n_containers; pa.K = v.n_nodes;
@@ -285,7 +288,7 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
         else top_node_pods_kernel<false, false><<<gp, kThreads, 0, st>>>(pa);
     }
     count_launch();
-    if (prof) cudaEventRecord(pe[2], st);
+    if (prof) CUDA_TRY(cudaEventRecord(pe[2], st));
     CUDA_TRY(cudaGetLastError());
     return ARENA_OK;
 }
@@ -296,10 +299,10 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     const arena_snapshot_view &v = s->v;
     const u64 J = v.n_jobs;
     if (v.n_pods <= kSmallJobPods && J <= kSmallJobs) {         // a small cluster: one launch does it all
-        static bool smem_ok = false;
-        if (!smem_ok) {
+        static std::atomic<bool> smem_ok{false};            // (setting the attribute twice is harmless)
+        if (!smem_ok.load(std::memory_order_acquire)) {
             CUDA_TRY(cudaFuncSetAttribute(job_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallJobSmem));
-            smem_ok = true;
+            smem_ok.store(true, std::memory_order_release);
         }
         JobSmallArgs sa{};
         sa.P = v.n_pods; sa.J = J;
@@ -507,7 +510,12 @@ cudaError_t device_alloc(void **out, size_t bytes)
                 best = i;
         if (best >= 0) {
             *out = g_free_blocks[best].p;
-            g_free_blocks[best] = FreeBlock{nullptr, 0};
+            // whatever the library stream still had to do with the block comes first
+            if (g_free_blocks[best].idle) {
+                cudaStreamWaitEvent(g_ctx.stream, g_free_blocks[best].idle, 0);
+                cudaEventDestroy(g_free_blocks[best].idle);
+            }
+            g_free_blocks[best] = FreeBlock{nullptr, 0, nullptr};
             return cudaSuccess;
         }
     }
@@ -520,13 +528,20 @@ cudaError_t device_alloc(void **out, size_t bytes)
     return e;
 }
 
-// `bytes` = what the block was allocated with (device_alloc's argument).  Waits for the device, as
-// cudaFree would, so that a block is never handed out while something still runs on it.
+// `bytes` = what the block was allocated with (device_alloc's argument).  Stream-ordered: an event
+// on the library stream marks the point after which the block is idle, and whoever takes the block
+// out of the cache makes the library stream wait for it -- no other stream of the process is stalled.
+// (Work a caller enqueued on a stream of its own must be complete before it frees the handle:
+// arena_snapshot_free says so.)  A block that is really freed goes through cudaFree, which waits.
 void device_release(void *p, size_t bytes)
 {
     if (!p) return;
     if (bytes < 256) bytes = 256;
-    cudaDeviceSynchronize();
+    cudaEvent_t idle = nullptr;
+    if (g_ctx.ready && cudaEventCreateWithFlags(&idle, cudaEventDisableTiming) == cudaSuccess) {
+        if (cudaEventRecord(idle, g_ctx.stream) != cudaSuccess) { cudaEventDestroy(idle); idle = nullptr; }
+    }
+    if (!idle) cudaDeviceSynchronize();            // no event to order by: fall back to waiting here
     std::lock_guard<std::mutex> lk(g_pool_mu);
     int slot = -1;
     for (int i = 0; i < 8; i++)
@@ -535,18 +550,20 @@ void device_release(void *p, size_t bytes)
         slot = 0;
         for (int i = 1; i < 8; i++)
             if (g_free_blocks[i].bytes < g_free_blocks[slot].bytes) slot = i;
-        if (g_free_blocks[slot].bytes >= bytes) { cudaFree(p); return; }
+        if (g_free_blocks[slot].bytes >= bytes) { if (idle) cudaEventDestroy(idle); cudaFree(p); return; }
+        if (g_free_blocks[slot].idle) cudaEventDestroy(g_free_blocks[slot].idle);
         cudaFree(g_free_blocks[slot].p);
     }
-    g_free_blocks[slot] = FreeBlock{p, bytes};
+    g_free_blocks[slot] = FreeBlock{p, bytes, idle};
 }
 
 void device_pool_clear()
 {
     std::lock_guard<std::mutex> lk(g_pool_mu);
     for (FreeBlock &b : g_free_blocks) {
+        if (b.idle) cudaEventDestroy(b.idle);
         if (b.p) cudaFree(b.p);
-        b = FreeBlock{nullptr, 0};
+        b = FreeBlock{nullptr, 0, nullptr};
     }
 }
 
@@ -1091,7 +1108,7 @@ struct NoAllocWork {
 static __device__ __align__(256) unsigned char g_noalloc_work[sizeof(NoAllocWork)];
 
 constexpr int kMaxDevices = 64;
-NoAllocWork *g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_work, per device
+std::atomic<NoAllocWork *> g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_work, per device
 
 // One-time, per device: resolve the symbol to a device address.  Passing
 // g_noalloc_work itself to a kernel from host code would hand it the host
@@ -1100,14 +1117,16 @@ int noalloc_work(NoAllocWork **out)
 {
     const int dev = g_ctx.device;
     if (dev < 0 || dev >= kMaxDevices) return fail(ARENA_E_INVALID, "device ordinal %d not supported by the no-alloc path", dev);
-    if (!g_noalloc_ptr[dev]) {
+    NoAllocWork *w = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (!w) {                                    // two threads racing here resolve the same address
         void *p = nullptr;
         cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_work);     // current device == dev (check_ready)
         if (e != cudaSuccess || !p)
             return fail(ARENA_E_CUDA, "cudaGetSymbolAddress(g_noalloc_work): %s", cudaGetErrorString(e));
-        g_noalloc_ptr[dev] = static_cast<NoAllocWork *>(p);
+        w = static_cast<NoAllocWork *>(p);
+        g_noalloc_ptr[dev].store(w, std::memory_order_release);
     }
-    *out = g_noalloc_ptr[dev];
+    *out = w;
     return ARENA_OK;
 }
 
@@ -1120,7 +1139,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
 {
     int rc = check_ready();
     if (rc) return rc;
-    rc = check_view(dev, true);
+    rc = check_view(dev, true, false);           // `top job` reads neither pod_node nor the node capacities
     if (rc) return rc;
     const u64 J = dev->n_jobs, P = dev->n_pods;
     if (J > kNoAllocMaxJobs)

@@ -183,6 +183,8 @@ __device__ __forceinline__ ulonglong2 ldg_stream(const ulonglong2 *p)
 
 // Scratch shared by the kernels of one device context.  Tickets are left at 0
 // by the CTA that finishes last, so no launch needs a memset first.
+// Each ticket id owns its own half of the partial arrays (kMaxPartials / 2 CTAs per launch), so a
+// `top node` query (ticket 1) and a `top job` query (ticket 2) on the same handle do not share them.
 struct Scratch {
     u64 partial_a[kMaxPartials];   // per-CTA partial of the first total
     u64 partial_b[kMaxPartials];   // per-CTA partial of the second total
@@ -214,9 +216,11 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
                                               PeerExchange *px = nullptr, u64 epoch = 0)
 {
     __shared__ bool s_last;
+    u64 *const part_a = sc->partial_a + (ticket_id == 1 ? 0 : kMaxPartials / 2);
+    u64 *const part_b = sc->partial_b + (ticket_id == 1 ? 0 : kMaxPartials / 2);
     if (threadIdx.x == 0) {
-        sc->partial_a[blockIdx.x] = block_a;
-        if (two) sc->partial_b[blockIdx.x] = block_b;
+        part_a[blockIdx.x] = block_a;
+        if (two) part_b[blockIdx.x] = block_b;
         __threadfence();
         unsigned t = atomicAdd(&sc->ticket[ticket_id], 1u);
         s_last = (t == gridDim.x - 1);
@@ -226,8 +230,8 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
     __threadfence();
     u64 a = 0, b = 0;
     for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
-        a += *((volatile u64 *)&sc->partial_a[i]);
-        if (two) b += *((volatile u64 *)&sc->partial_b[i]);
+        a += *((volatile u64 *)&part_a[i]);
+        if (two) b += *((volatile u64 *)&part_b[i]);
     }
     __shared__ u64 s_a[kWarps], s_b[kWarps];
     a = warp_reduce_sum(a);
@@ -274,9 +278,11 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
     if (threadIdx.x < 32) {            // world <= 16: all in the first warp
         ga = warp_reduce_sum(ga);
         gb = warp_reduce_sum(gb);
+        const bool timed_out = __any_sync(0xffffffffu, *((volatile unsigned *)&px->timed_out) != 0u);
         if (threadIdx.x == 0) {
-            *out_a = (i64)ga;
-            if (two) *out_b = (i64)gb;
+            // a peer that never posted: leave no half-sum behind that could be taken for a total
+            *out_a = timed_out ? (i64)0x8000000000000000ull : (i64)ga;
+            if (two) *out_b = timed_out ? (i64)0x8000000000000000ull : (i64)gb;
         }
     }
 }
@@ -402,17 +408,18 @@ __device__ __forceinline__ TileSums process_tile_generic(const PodsArgs &a, cons
     for (int j = 0; j <= kPodsPerLane; j++) B[j] = 0;
 
     u64 carry = 0;
-    for (unsigned chunk_lo = wc0 & ~(unsigned)(kRowCtrs - 1); chunk_lo < wc1; chunk_lo += kChunkCtrs) {
+    // (64-bit loop variable: with C close to 2^32 a 32-bit one would wrap past wc1 and never leave)
+    for (u64 chunk_lo = wc0 & ~(unsigned)(kRowCtrs - 1); chunk_lo < wc1; chunk_lo += kChunkCtrs) {
         ulonglong2 v[kRows];
         unsigned sc[kRows];
         // issue every load of the chunk before using any of them
 #pragma unroll
         for (int r = 0; r < kRows; r++) {
-            const unsigned rs = chunk_lo + r * kRowCtrs;
-            const u64 idx = (u64)rs + 2u * lane;
+            const u64 rs = chunk_lo + r * kRowCtrs;
+            const u64 idx = rs + 2u * lane;
             v[r].x = 0; v[r].y = 0; sc[r] = 0;
             if (rs < wc1) {
-                if ((u64)rs + kRowCtrs <= a.C) {
+                if (rs + kRowCtrs <= a.C) {
                     v[r] = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + idx));
                     sc[r] = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + idx));
                 } else {
@@ -424,7 +431,7 @@ __device__ __forceinline__ TileSums process_tile_generic(const PodsArgs &a, cons
         unsigned n_valid = 0;
 #pragma unroll
         for (int r = 0; r < kRows; r++) {
-            const unsigned rs = chunk_lo + r * kRowCtrs;
+            const u64 rs = chunk_lo + r * kRowCtrs;
             if (rs < wc1) {                                // warp-uniform
                 u64 x0 = v[r].x, x1 = v[r].y;
                 if (__any_sync(FULL, sc[r] != 0u)) {       // some quantity in the row has a scale
@@ -448,7 +455,7 @@ __device__ __forceinline__ TileSums process_tile_generic(const PodsArgs &a, cons
         __syncwarp();
 #pragma unroll
         for (int j = 0; j <= kPodsPerLane; j++) {
-            const unsigned off = cb[j] - chunk_lo;         // wraps when cb[j] < chunk_lo
+            const unsigned off = cb[j] - (unsigned)chunk_lo;   // wraps when cb[j] < chunk_lo
             if (off <= n_valid) B[j] = prefix[off];
         }
         __syncwarp();

@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <map>
 #include <numeric>
 #include <thread>
@@ -663,6 +664,21 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
                 r.role = ARENA_ROLE_COUNTS;
             }
             r.job = it->second;
+        }
+        // "latest pod of the job": `latest.Before(current)` is strict (trainer_mpi.go:263-278,
+        // trainer_standalone.go:198-221), so among ARENA_ROLE_LATEST pods with the same newest
+        // second the FIRST IN LIST ORDER wins.  The kernels break that tie by ROW index, and
+        // rows are about to be regrouped by node: settle it here, while list order is still
+        // known, by moving the later ones of such a tie one second back (they lose either
+        // way; pod_created serves nothing but this rule).
+        std::vector<int64_t> newest(h->jobs.size(), std::numeric_limits<int64_t>::min());
+        for (const PodRec &r : pods)
+            if (r.job != ARENA_NONE && r.role == ARENA_ROLE_LATEST && r.created > newest[r.job]) newest[r.job] = r.created;
+        std::vector<uint8_t> seen(h->jobs.size(), 0);
+        for (PodRec &r : pods) {
+            if (r.job == ARENA_NONE || r.role != ARENA_ROLE_LATEST || r.created != newest[r.job]) continue;
+            if (seen[r.job] && r.created > std::numeric_limits<int64_t>::min()) r.created -= 1;
+            seen[r.job] = 1;
         }
     }
     const size_t J = h->jobs.size();

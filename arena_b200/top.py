@@ -166,7 +166,7 @@ def format_top_job(host: HostSnapshot, res: TopJobResult, now_unix: int) -> str:
 
 
 def top_job_device_noalloc(tensors: dict, n_jobs: int, d_req, d_alloc, d_order, d_latest, d_totals,
-                           stream: Optional[int] = None) -> None:
+                           stream: Optional[int] = None, n_pods: Optional[int] = None) -> None:
     """arena_top_job_device_noalloc: `top job` over CUDA tensors holding the
     columns, for callers that must not allocate device memory on the query
     path (the library keeps the work arrays in a fixed device array instead of
@@ -176,9 +176,9 @@ def top_job_device_noalloc(tensors: dict, n_jobs: int, d_req, d_alloc, d_order, 
     from ._lib import SnapshotView
     from .snapshot import _COLS
     v = SnapshotView()
-    v.n_pods = tensors["pod_node"].numel()
+    v.n_pods = tensors["pod_job"].numel() if n_pods is None else n_pods      # pod_node is optional here
     v.n_containers = tensors["ctr_val"].numel()
-    v.n_nodes = tensors["node_cap_val"].numel()
+    v.n_nodes = tensors["node_cap_val"].numel() if "node_cap_val" in tensors else 0
     v.n_jobs = n_jobs
     for name, _, _ in _COLS:
         t = tensors.get(name)

@@ -105,6 +105,10 @@ int  arena_snapshot_upload(const arena_snapshot_view *host, arena_snapshot **out
 /* Same, but `dev` already holds DEVICE pointers (e.g. torch tensors); nothing
  * is copied and the caller keeps ownership of the columns. */
 int  arena_snapshot_wrap_device(const arena_snapshot_view *dev, arena_snapshot **out);
+/* Stream-ordered on the library's own stream (freed blocks are cached for the next snapshot and no
+ * other stream of the process is stalled).  Queries the caller enqueued on a stream of ITS OWN
+ * (the `stream` argument of the *_device entry points) must have completed before the handle is
+ * freed. */
 void arena_snapshot_free(arena_snapshot *s);
 /* counts_out = { n_pods, n_containers, n_nodes, n_jobs } of a device snapshot. */
 int  arena_snapshot_counts(const arena_snapshot *s, uint64_t counts_out[4]);
@@ -146,8 +150,9 @@ int  arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total,
  * (arena_peer_exchange_connect: `handles` = world x 64 bytes in rank order).  After that
  * arena_top_node_device_fused is arena_top_node_device whose kernel also trades the two
  * cluster totals with every peer over NVLink in its last CTA -- peer stores, an epoch flag,
- * a bounded spin (~2 s, then arena_peer_exchange_timed_out() != 0 and the totals are not
- * meaningful) -- so d_cluster receives the GLOBAL {total, allocated} and no all-reduce is launched.
+ * a bounded spin (~2 s; after that arena_peer_exchange_timed_out() != 0, the call itself has long
+ * returned ARENA_OK, and both entries of d_cluster hold INT64_MIN instead of a partial sum) -- so
+ * d_cluster receives the GLOBAL {total, allocated} and no all-reduce is launched.
  * Every rank must make the same sequence of fused calls.  At most 16 ranks.  Replaces the
  * single-process loop over all nodes of top_node.go:109-118; no reference counterpart for
  * the exchange itself.
@@ -209,6 +214,12 @@ int  arena_top_node_host_packed(const arena_packed_view *host, int64_t *node_tot
  *   job_order[J]               job ids, requested desc then id asc
  *   job_latest[J] or NULL      index of the winning ARENA_ROLE_LATEST pod, or ARENA_NONE
  *   totals[2]                  {sum job_req, sum job_alloc}
+ * Row order and the latest-pod rule: among ARENA_ROLE_LATEST pods of a job with the same newest
+ * pod_created the one with the LOWEST ROW INDEX wins.  The reference takes the first in LIST order
+ * (`latest.Before(current)` is strict), so a caller that builds the columns itself either keeps
+ * such pods in list order or settles the tie beforehand, as arena_load_json does when it regroups
+ * rows by node (it moves the later pods of a tie one second back).  One query in flight per handle
+ * (a `top node` and a `top job` query on the same handle may overlap; two of the same kind may not).
  */
 int  arena_top_job(const arena_snapshot *s, int64_t *job_req, int64_t *job_alloc,
                    uint32_t *job_order, uint32_t *job_latest, int64_t totals[2]);
@@ -223,7 +234,9 @@ int  arena_top_job_device(const arena_snapshot *s, int64_t *d_job_req, int64_t *
  * fixed device-memory budget, a host whose CUDA context forbids or hooks
  * allocation after start-up, a caller for whom an allocation's implicit device
  * synchronisation is unacceptable.  Same results as arena_top_job_device, but:
- *   - `dev` holds DEVICE column pointers (no snapshot handle: making one allocates);
+ *   - `dev` holds DEVICE column pointers (no snapshot handle: making one allocates); only the
+ *     columns `top job` reads are required (pod_node and the node capacities may be NULL), rows
+ *     in the order described at arena_top_job;
  *   - the work arrays live in a fixed ~105 KiB device array inside the library,
  *     so at most ARENA_NOALLOC_MAX_JOBS jobs; more -> ARENA_E_TOO_LARGE;
  *   - d_job_latest is required (it doubles as a work array);

@@ -154,6 +154,26 @@ def test_loader_and_printer_for_top_job(built):
     assert totals.tolist() == [14, 13]
 
 
+def test_timestamp_tie_survives_node_grouping(built):
+    """Two Job-owned launcher pods of `hvd-tie` carry the same creationTimestamp and sit on
+    different nodes, the later one in the list on the LOWER node id.  `latest.Before(current)` is
+    strict (trainer_mpi.go:263-278), so the first in LIST order counts; grouping the rows by node
+    must not change the winner."""
+    from arena_b200 import HostSnapshot, TopJobResult, format_top_job
+    h = HostSnapshot.from_json(rd("pods.json"), rd("nodes.json"), rd("jobs.json"), rd("tfjobs.json"), rd("helm_list.txt"),
+                               group_by_job=False)
+    pn = h.cols["pod_node"]
+    assert np.all(pn[:-1] <= pn[1:]), "rows must be grouped by node"
+    J = h.n_jobs
+    req, alloc, latest, totals = cref.top_job_columnar(h.cols, J)
+    got = {h.job_name(j): (h.job_trainer(j), int(req[j]), int(alloc[j])) for j in range(J)}
+    assert got == MF.HAND_JOB_TABLE
+    tie = [h.job_name(j) for j in range(J)].index("hvd-tie")
+    assert h.pod_name(int(latest[tie])) == "tie-a"
+    order = np.array(sorted(range(J), key=lambda j: (-int(req[j]), j)), np.uint32)
+    assert format_top_job(h, TopJobResult(req, alloc, order, latest, totals), MF.NOW) == rd("expected_top_job.txt", "r")
+
+
 def test_loader_rejects_what_the_reference_decode_rejects(built):
     from arena_b200 import ArenaError, HostSnapshot
     nodes = rd("nodes.json")

@@ -57,11 +57,13 @@ def test_config2_top_job_full_size(gpu):
     h = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=True)
     res = gpu.top_job(gpu.DeviceSnapshot.upload(h))
     assert gpu.format_top_job(h, res, MF.NOW) == text
-    # node-grouped rows: same sums except where two launcher pods tie on the timestamp
-    # (then "first in LIST order" needs the job-grouped, list-stable rows: arena_top.h)
+    # node-grouped rows: the same table, also where two launcher pods tie on the timestamp (the
+    # loader settles "first in LIST order" before it regroups the rows)
     h2 = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=False)
     res2 = gpu.top_job(gpu.DeviceSnapshot.upload(h2))
-    assert int((res2.job_req != res.job_req).sum()) <= 10
+    assert np.array_equal(res2.job_req, res.job_req) and np.array_equal(res2.job_alloc, res.job_alloc)
+    assert np.array_equal(res2.job_order, res.job_order) and np.array_equal(res2.totals, res.totals)
+    assert gpu.format_top_job(h2, res2, MF.NOW) == text
     ntext, _ = top_ref.top_node(P, N)
     r = gpu.top_node(gpu.DeviceSnapshot.upload(h2))
     assert gpu.format_top_node(h2, r) == ntext

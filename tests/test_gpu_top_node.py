@@ -155,6 +155,42 @@ def test_full_size_properties(gpu):
     dev.close()
 
 
+def test_full_size_skewed(gpu):
+    """BASELINE configs[4] at full size: 1e8 pods / 1e6 nodes, power-law pods per node (a few nodes
+    at the 1e6-pod cap, a median of 8) and GPU-sharing nodes, seed 5.  The wide kernel, the packed
+    kernel (giant nodes go through its pieces path) and four node-range shards, one after the
+    other, each against the C oracle's all-threads columnar pass."""
+    host = gpu.HostSnapshot.synth(100_000_000, 1_000_000, seed=5, skewed=True)
+    tot, alloc, cl = cref.top_node_columnar_threads(host.cols, 16)
+    pods_per_node = np.bincount(host.cols["pod_node"][host.cols["pod_node"] != NONE], minlength=host.n_nodes)
+    assert pods_per_node.max() >= 1_000_000 and np.median(pods_per_node) < 20, "not the skewed workload"
+    assert (alloc > tot).any(), "no over-subscribed GPU-sharing node"
+    del pods_per_node
+    dev = gpu.DeviceSnapshot.upload(host)
+    res = gpu.top_node(dev)
+    assert np.array_equal(res.node_total, tot) and np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
+    dev.close()
+    packed = host.pack(pinned=False)
+    assert int(packed.view.n_pieces) > 0, "no node above the packed kernel's piece size"
+    res = gpu.top_node_packed(packed)
+    assert np.array_equal(res.node_total, tot) and np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
+    packed.close()
+    key_cut, pod_cut = host.shard_plan(4)
+    got_total, got_alloc, got_cl = [], [], np.zeros(2, np.int64)
+    for i in range(4):
+        sh = host.shard(i, 4)
+        d = gpu.DeviceSnapshot.upload(sh)
+        r = gpu.top_node(d)
+        d.close()
+        # this shard's slice of the table against the oracle's rows of the same node range
+        lo, hi = int(key_cut[i]), int(key_cut[i + 1])
+        assert np.array_equal(r.node_alloc, alloc[lo:hi]) and np.array_equal(r.node_total, tot[lo:hi]), f"shard {i}"
+        got_total.append(r.node_total); got_alloc.append(r.node_alloc); got_cl += r.cluster
+    assert np.array_equal(np.concatenate(got_alloc), alloc) and np.array_equal(np.concatenate(got_total), tot)
+    assert got_cl.tolist() == cl.tolist()
+    assert int(np.diff(pod_cut.astype(np.int64)).sum()) == host.n_pods
+
+
 def test_quantity_values_kernel(gpu):
     rng = np.random.default_rng(3)
     val = np.concatenate([rng.integers(-2**63, 2**63 - 1, 20000, dtype=np.int64),
