@@ -8,4 +8,5 @@ from ._lib import ARENA_NONE, ArenaError, init, lib  # noqa: F401
 from .snapshot import DeviceSnapshot, HostSnapshot, PackedSnapshot, PinnedBuffer  # noqa: F401
 from .top import (TopJobResult, TopNodeResult, format_top_job, format_top_node,  # noqa: F401
                   quantity_values, top_job, top_job_device, top_job_device_noalloc, top_node,
-                  top_node_device, top_node_device_fused, top_node_packed)
+                  top_node_device, top_node_device_fused, top_node_device_posted, peer_exchange_collect,
+                  top_node_packed)

@@ -82,6 +82,8 @@ _SIGS = [
     ("arena_peer_exchange_destroy", None, []),
     ("arena_peer_exchange_timed_out", C.c_int, []),
     ("arena_top_node_device_fused", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_node_device_posted", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    ("arena_peer_exchange_collect", C.c_int, [_VP, _VP]),
     ("arena_top_node_host_packed", C.c_int, [C.POINTER(PackedView), _VP, _VP, _VP, _VP]),
     ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -6,9 +6,11 @@
 #include "host_snapshot.h"
 #include "gpuacct_internal.h"
 
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -33,8 +35,10 @@ struct Context {
     int device = -1;
     int sm_count = 0;
     int pods_ctas_per_sm = 0;
+    int pods_ctas_per_sm_min = 0;    // the smallest over the top-node instantiations
     int jobs_ctas_per_sm = 0;
     int packed_ctas_per_sm = 0;
+    bool cooperative = false;        // cudaLaunchCooperativeKernel available: the top-node launch zeroes node_alloc itself
     cudaStream_t stream = nullptr;
 };
 
@@ -116,7 +120,23 @@ int arena_acct_init(int device)
                     "code for other architectures", device, prop.major, prop.minor);
     g_ctx.device = device;
     g_ctx.sm_count = prop.multiProcessorCount;
+    {
+        int coop = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+        // Measured (profiles/r02_iterations.md): the barrier costs what the memset it replaces costs
+        // (1e8 pods: 456.3 + 2.6 us against 451.7 + 6.7; 1.25e7 pods: 68.4 + 2.6 against 64.7 + 6.6),
+        // so the memset stays the default and the self-zeroing launch is opt-in.
+        const char *on = getenv("ARENA_COOPERATIVE");
+        g_ctx.cooperative = coop != 0 && on && on[0] == '1';
+    }
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
+    {
+        int o1 = 0, o2 = 0, o3 = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, top_node_pods_kernel<true, false>, kThreads, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, top_node_pods_kernel<false, true>, kThreads, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, top_node_pods_kernel<true, true>, kThreads, 0));
+        g_ctx.pods_ctas_per_sm_min = std::min(std::min(o1, o2), std::min(o3, g_ctx.pods_ctas_per_sm));
+    }
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
     if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1 || g_ctx.packed_ctas_per_sm < 1)
@@ -246,15 +266,34 @@ int ensure_job_arrays(arena_snapshot *s)
     return ARENA_OK;
 }
 
+template <typename K>
+cudaError_t launch_pods(K kernel, int grid, const PodsArgs &pa, bool cooperative, cudaStream_t st)
+{
+    if (!cooperative) {
+        kernel<<<grid, kThreads, 0, st>>>(pa);
+        return cudaGetLastError();
+    }
+    void *args[] = {const_cast<PodsArgs *>(&pa)};
+    return cudaLaunchCooperativeKernel((const void *)kernel, dim3((unsigned)grid), dim3(kThreads), args, 0, st);
+}
+
+// exchange: 0 none, 1 in-kernel totals exchange collected by the same launch, 2 collected one step late
 int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_cluster, i64 *d_pod_gpu,
-                    cudaStream_t st, bool exchange = false)
+                    cudaStream_t st, int exchange = 0)
 {
     const arena_snapshot_view &v = s->v;
     const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
     cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
     if (prof) { g_prof.used += 3; CUDA_TRY(cudaEventRecord(pe[0], st)); }
-    // node_alloc is accumulated with atomics: it starts from zero
-    if (v.n_nodes) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
+    // node_alloc is accumulated with atomics: it starts from zero.  A memset in front of the launch,
+    // or (ARENA_COOPERATIVE=1) the launch clears it itself: cooperative launch + one grid barrier.
+    bool self_zero = g_ctx.cooperative && v.n_nodes > 0 && (((uintptr_t)d_alloc) & 15) == 0;
+    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
+    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
+    if (gn > gp) gp = gn;
+    // all CTAs must be resident for the barrier: the details / ungrouped instantiations may fit fewer per SM
+    if (self_zero && (d_pod_gpu || s->direct) && gp > g_ctx.sm_count * g_ctx.pods_ctas_per_sm_min) self_zero = false;
+    if (v.n_nodes && !self_zero) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
     if (prof) CUDA_TRY(cudaEventRecord(pe[1], st));
 
     PodsArgs pa{};
@@ -276,20 +315,20 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     if (exchange) {
         pa.px = g_px;
         pa.epoch = g_epoch.fetch_add(1) + 1;
+        pa.px_lag = exchange == 2 ? 1u : 0u;
     }
-    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
-    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
-    if (gn > gp) gp = gn;
+    pa.zero_alloc = self_zero ? 1u : 0u;
+    cudaError_t e;
     if (d_pod_gpu) {
-        if (s->direct) top_node_pods_kernel<true, true><<<gp, kThreads, 0, st>>>(pa);
-        else top_node_pods_kernel<false, true><<<gp, kThreads, 0, st>>>(pa);
+        if (s->direct) e = launch_pods(top_node_pods_kernel<true, true>, gp, pa, self_zero, st);
+        else e = launch_pods(top_node_pods_kernel<false, true>, gp, pa, self_zero, st);
     } else {
-        if (s->direct) top_node_pods_kernel<true, false><<<gp, kThreads, 0, st>>>(pa);
-        else top_node_pods_kernel<false, false><<<gp, kThreads, 0, st>>>(pa);
+        if (s->direct) e = launch_pods(top_node_pods_kernel<true, false>, gp, pa, self_zero, st);
+        else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, self_zero, st);
     }
+    if (e != cudaSuccess) return fail(ARENA_E_CUDA, "top-node kernel launch: %s", cudaGetErrorString(e));
     count_launch();
     if (prof) CUDA_TRY(cudaEventRecord(pe[2], st));
-    CUDA_TRY(cudaGetLastError());
     return ARENA_OK;
 }
 
@@ -910,7 +949,34 @@ int arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total, 
     if (!s || !d_cluster) return fail(ARENA_E_INVALID, "snapshot or d_cluster is NULL");
     if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
     cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
-    return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, nullptr, st, true);
+    return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, nullptr, st, 1);
+}
+
+int arena_top_node_device_posted(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                                 int64_t *d_cluster_prev, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!s || !d_cluster_prev) return fail(ARENA_E_INVALID, "snapshot or d_cluster_prev is NULL");
+    if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster_prev, nullptr, st, 2);
+}
+
+int arena_peer_exchange_collect(int64_t *d_cluster, void *stream)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!d_cluster) return fail(ARENA_E_INVALID, "d_cluster is NULL");
+    const uint64_t epoch = g_epoch.load();
+    if (epoch == 0) return fail(ARENA_E_INVALID, "nothing has been posted yet");
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    peer_collect_kernel<<<1, 32, 0, st>>>(g_px, epoch, (i64 *)d_cluster);
+    count_launch();
+    CUDA_TRY(cudaGetLastError());
+    return ARENA_OK;
 }
 
 int arena_peer_exchange_timed_out(void)

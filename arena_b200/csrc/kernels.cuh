@@ -196,12 +196,23 @@ struct Scratch {
 // NVLink peer mappings (CUDA IPC).  The last CTA of a rank's kernel stores the rank's two totals
 // and then the step's epoch into slot [rank] of EVERY mailbox, waits until its own mailbox
 // shows the epoch in all slots, and adds them up: the exchange rides in the tail of the kernel
-// that produced the numbers.  Two parities: a rank can be at most one step ahead of a peer
-// that is still reading (it cannot finish step e+1 before that peer has posted e+1).
+// that produced the numbers.
+//
+// Two ways to collect.  Synchronous (lag 0): the launch that posted epoch e waits for every
+// peer's epoch e, so each step ends at the pace of the slowest rank of THAT step.  Deferred
+// (lag 1): the launch posts epoch e and collects epoch e-1, which every peer posted a whole
+// step ago, so a rank that is late by less than a step stalls nobody; the totals of step e are
+// delivered by step e+1's launch, or by peer_collect_kernel at the end of a sequence.
+//
+// Slots are a ring of kPeerRing epochs.  A rank cannot finish the tail of step e before every
+// peer has posted e-1 (deferred) or e (synchronous), so a writer is never more than three epochs
+// ahead of the oldest epoch a peer may still be reading (e+1 written while e-2 is read): four
+// slots keep them apart.
 constexpr int kMaxPeers = 16;
+constexpr int kPeerRing = 4;
 struct PeerMailbox {
-    unsigned long long flag[2][kMaxPeers];       // [parity][writer] = epoch of totals[parity][writer]
-    long long totals[2][kMaxPeers][2];           // {first total, second total}
+    unsigned long long flag[kPeerRing][kMaxPeers];   // [slot][writer] = epoch of totals[slot][writer]
+    long long totals[kPeerRing][kMaxPeers][2];       // {first total, second total}
 };
 struct PeerExchange {
     int rank, world;
@@ -211,9 +222,30 @@ struct PeerExchange {
 
 // Last-CTA-done reduction of per-CTA partial sums into *out (and *out_b).
 // Every CTA calls this once with its partial(s) in thread 0.
+// Thread i < world: wait until rank i's totals of `epoch` have arrived in this rank's mailbox and
+// return them (bounded spin; a rank that never shows up sets px->timed_out).
+__device__ __forceinline__ void peer_collect(PeerExchange *px, u64 epoch, u64 &ga, u64 &gb)
+{
+    PeerMailbox *mine = px->box[px->rank];
+    const int slot = (int)(epoch % (u64)kPeerRing);
+    const long long t0 = clock64();
+    bool ok = true;
+    while (*((volatile unsigned long long *)&mine->flag[slot][threadIdx.x]) != epoch) {
+        __nanosleep(100);
+        if (clock64() - t0 > 4000000000ll) { ok = false; break; }      // ~2 s: a peer is gone
+    }
+    __threadfence_system();
+    if (ok) {
+        ga = (u64)*((volatile long long *)&mine->totals[slot][threadIdx.x][0]);
+        gb = (u64)*((volatile long long *)&mine->totals[slot][threadIdx.x][1]);
+    } else {
+        px->timed_out = 1u;
+    }
+}
+
 __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two,
                                               Scratch *sc, int ticket_id, i64 *out_a, i64 *out_b,
-                                              PeerExchange *px = nullptr, u64 epoch = 0)
+                                              PeerExchange *px = nullptr, u64 epoch = 0, unsigned lag = 0)
 {
     __shared__ bool s_last;
     u64 *const part_a = sc->partial_a + (ticket_id == 1 ? 0 : kMaxPartials / 2);
@@ -248,33 +280,22 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
             if (two) *out_b = (i64)tb;
         }
         sc->ticket[ticket_id] = 0;      // ready for the next launch
+        sc->ticket[0] = 0;              // the start-of-launch barrier (everybody is long past it)
     }
     if (!px) return;
     __syncthreads();
     // post to every rank, then collect from every rank: thread i talks to rank i
-    const int par = (int)(epoch & 1ull);
+    const int slot = (int)(epoch % (u64)kPeerRing);
     u64 ga = 0, gb = 0;
     if ((int)threadIdx.x < px->world) {
         PeerMailbox *theirs = px->box[threadIdx.x];
-        theirs->totals[par][px->rank][0] = (long long)s_tot[0];
-        theirs->totals[par][px->rank][1] = (long long)s_tot[1];
+        theirs->totals[slot][px->rank][0] = (long long)s_tot[0];
+        theirs->totals[slot][px->rank][1] = (long long)s_tot[1];
         __threadfence_system();
-        *((volatile unsigned long long *)&theirs->flag[par][px->rank]) = epoch;
-        PeerMailbox *mine = px->box[px->rank];
-        const long long t0 = clock64();
-        bool ok = true;
-        while (*((volatile unsigned long long *)&mine->flag[par][threadIdx.x]) != epoch) {
-            __nanosleep(100);
-            if (clock64() - t0 > 4000000000ll) { ok = false; break; }      // ~2 s: a peer is gone
-        }
-        __threadfence_system();
-        if (ok) {
-            ga = (u64)*((volatile long long *)&mine->totals[par][threadIdx.x][0]);
-            gb = (u64)*((volatile long long *)&mine->totals[par][threadIdx.x][1]);
-        } else {
-            px->timed_out = 1u;
-        }
+        *((volatile unsigned long long *)&theirs->flag[slot][px->rank]) = epoch;
+        if (epoch > (u64)lag) peer_collect(px, epoch - lag, ga, gb);
     }
+    if (epoch <= (u64)lag) return;     // deferred collection, first step: nothing older to deliver
     if (threadIdx.x < 32) {            // world <= 16: all in the first warp
         ga = warp_reduce_sum(ga);
         gb = warp_reduce_sum(gb);
@@ -336,6 +357,10 @@ struct PodsArgs {
     // multi-GPU: exchange the two totals with the peer GPUs inside this launch (or nullptr)
     PeerExchange *px;
     u64 epoch;
+    unsigned px_lag;                // 0: collect this step's totals; 1: the previous step's (deferred)
+    // key_alloc is zeroed by this launch itself (cooperative launch: every CTA clears a slice, one
+    // grid-wide barrier, then the tiles) instead of by a memset in front of it
+    unsigned zero_alloc;
 };
 
 // Rare path (a row that runs past the end of the container columns) kept out
@@ -712,6 +737,24 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     const unsigned FULL = 0xffffffffu;
     unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
 
+    if (!kJob && a.zero_alloc) {
+        // node_alloc starts from zero: 128-bit stores, then everybody waits for everybody (the
+        // launch is cooperative, so all CTAs are resident and the spin cannot starve one of them)
+        ulonglong2 *z = reinterpret_cast<ulonglong2 *>(a.key_alloc);
+        const u64 n2 = a.K / 2;
+        for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (u64)gridDim.x * blockDim.x)
+            z[i] = make_ulonglong2(0ull, 0ull);
+        if ((a.K & 1) && blockIdx.x == 0 && threadIdx.x == 0) a.key_alloc[a.K - 1] = 0;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(&a.scratch->ticket[0], 1u);
+            while (*((volatile unsigned *)&a.scratch->ticket[0]) < gridDim.x) __nanosleep(40);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+
     u64 acc_alloc = 0;
     u64 job_req = 0, job_alloc = 0;             // kJob: every lane's own partial totals
     const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
@@ -895,7 +938,23 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
         for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
-    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.epoch);
+    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.epoch, a.px_lag);
+}
+
+// The totals of `epoch` (posted by the launches of every rank) summed into out = {total capacity,
+// allocated} (the mailbox carries them in the kernel's order: allocated first): the end of a
+// sequence of deferred-collection steps.  One CTA of 32 threads.
+__global__ void peer_collect_kernel(PeerExchange *px, u64 epoch, i64 *out)
+{
+    u64 ga = 0, gb = 0;
+    if ((int)threadIdx.x < px->world) peer_collect(px, epoch, ga, gb);
+    ga = warp_reduce_sum(ga);
+    gb = warp_reduce_sum(gb);
+    const bool timed_out = *((volatile unsigned *)&px->timed_out) != 0u;
+    if (threadIdx.x == 0) {
+        out[1] = timed_out ? (i64)0x8000000000000000ull : (i64)ga;
+        out[0] = timed_out ? (i64)0x8000000000000000ull : (i64)gb;
+    }
 }
 
 // ---------------------------------------------------------------------------

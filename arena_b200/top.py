@@ -87,6 +87,22 @@ def top_node_device_fused(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cl
         d_cluster.data_ptr(), _stream_arg(stream)))
 
 
+def top_node_device_posted(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cluster_prev, stream: Optional[int] = None) -> None:
+    """arena_top_node_device_posted: as top_node_device_fused, but the launch collects the PREVIOUS
+    step's global totals (into d_cluster_prev) and only posts its own; peer_exchange_collect()
+    delivers the last step's."""
+    check(lib().arena_top_node_device_posted(
+        snap.handle,
+        d_node_total.data_ptr() if d_node_total is not None and d_node_total.numel() else None,
+        d_node_alloc.data_ptr() if d_node_alloc is not None and d_node_alloc.numel() else None,
+        d_cluster_prev.data_ptr(), _stream_arg(stream)))
+
+
+def peer_exchange_collect(d_cluster, stream: Optional[int] = None) -> None:
+    """arena_peer_exchange_collect: the global totals of the most recent posted step."""
+    check(lib().arena_peer_exchange_collect(d_cluster.data_ptr(), _stream_arg(stream)))
+
+
 def top_node_packed(packed, details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
     """arena_top_node_host_packed: one-shot upload of a PackedSnapshot + kernels + download."""
     N, P = packed.n_nodes, packed.n_pods

@@ -4,14 +4,14 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 A "step" is one pass of the hot path (memset of node_alloc + the top-node
-kernel, plus the int64[2] totals all-reduce when N > 1) over one synthetic columnar snapshot
-that is already resident in HBM.  Workload at N = 1: BASELINE.json configs[3]'s
-snapshot (1e8 pods / 1e6 nodes, seed 1; 2.3 GB, larger than the 126 MB L2, so
-no flush is needed between steps) on ONE GPU -- the configuration the >= 70 %
-of HBM bandwidth target is quoted on.  At N > 1 every rank holds a node-range
-shard of the same per-GPU size (weak scaling: N x 1e8 pods over N x 1e6 nodes,
-seed 1 + rank); `--scaling strong` instead cuts ONE 1e8-pod snapshot into N
-node ranges (BASELINE configs[3] as written).
+launch, plus the exchange of the int64[2] cluster totals when N > 1) over one
+synthetic columnar snapshot that is already resident in HBM.  Workload at N = 1:
+BASELINE.json configs[3]'s snapshot (1e8 pods / 1e6 nodes, seed 1; 2.3 GB, larger
+than the 126 MB L2, so no flush is needed between steps) on ONE GPU -- the
+configuration the >= 70 % of HBM bandwidth target is quoted on.  At N > 1 the SAME
+snapshot is cut into N node ranges of about equal pod count, one per rank (strong
+scaling: BASELINE configs[3] as written); `--scaling weak` instead gives every rank
+a snapshot of the full size (N x 1e8 pods, seed 1 + rank).
 
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement".
 """
@@ -110,6 +110,16 @@ class ClockSampler:
 # --------------------------------------------------------------------------
 # CPU legs (the ONLY place bench.py touches oracle/): bounded samples.
 # --------------------------------------------------------------------------
+def oracle_parity(host, d_total, d_alloc):
+    """This rank's slice of the table against the C oracle's columnar pass over the same shard
+    (oracle/ used as the checker, after the timed region).  Returns (ok, oracle cluster totals)."""
+    from oracle import cref
+    tot, alloc, cl = cref.top_node_columnar_threads(host.cols, min(16, os.cpu_count() or 1))
+    import numpy as np
+    ok = bool(np.array_equal(d_total.cpu().numpy(), tot) and np.array_equal(d_alloc.cpu().numpy(), alloc))
+    return ok, cl
+
+
 def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int, min_seconds: float = 0.0):
     """The reference's CPU algorithm (C restatement, oracle/acct_ref.c) on a
     bounded sample of the workload: array-of-structs pods with string node
@@ -133,6 +143,14 @@ def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int, m
     t1 = time.perf_counter()
     cref.top_node_columnar(host.cols)
     b3 = host.n_pods / (time.perf_counter() - t1)
+    # the same columnar pass on all host threads: the comparator for a caller that already holds columns
+    cref.top_node_columnar_threads(host.cols, threads)
+    t1 = time.perf_counter()
+    reps = 0
+    while reps < 3 or time.perf_counter() - t1 < 1.0:
+        cref.top_node_columnar_threads(host.cols, threads)
+        reps += 1
+    b3_all = host.n_pods * reps / (time.perf_counter() - t1)
     small = HostSnapshot.synth(20_000, 200, seed=1)
     a2 = cref.AoS(small.cols)
     t2 = time.perf_counter()
@@ -143,7 +161,8 @@ def cpu_reference_run(steps: int, warmup: int, sample_pods: int, threads: int, m
     return {
         "value": host.n_pods * steps / dt, "ms_per_step": dt / steps * 1e3, "sample_pods": host.n_pods, "passes": steps,
         "seconds": dt,
-        "sample_nodes": sample_nodes, "b3_columnar_1thread": b3, "b1_nested_loop_1thread": b1,
+        "sample_nodes": sample_nodes, "b3_columnar_1thread": b3, "b3_columnar_all_threads": b3_all,
+        "b1_nested_loop_1thread": b1,
         "b1_sample": "20000 pods x 200 nodes",
     }
 
@@ -157,8 +176,10 @@ def run_reference_arm(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": dict(workload_config(args.gpus, args.scaling), pods_per_gpu=PODS_FULL, nodes_per_gpu=NODES_FULL,
+        "scaling": args.scaling if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": dict(workload_config(args.gpus, args.scaling, collective=args.collective),
+                       pods_per_gpu=PODS_FULL // (args.gpus if args.scaling == "strong" else 1),
+                       nodes_per_gpu=NODES_FULL // (args.gpus if args.scaling == "strong" else 1),
                        total_pods=PODS_FULL * (args.gpus if args.scaling == "weak" else 1)),
         "cpu_baseline": {
             "value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
@@ -166,6 +187,7 @@ def run_reference_arm(args):
                       "generator (seed 1) as array-of-structs with string node names and keyed limits, string-hash "
                       "join (C restatement of gpu.go + top_node.go; the Go reference cannot be built: no toolchain)",
             "columnar_single_pass_1thread": r["b3_columnar_1thread"],
+            "columnar_all_threads": r["b3_columnar_all_threads"],
             "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
             "faithful_nested_loop_sample": r["b1_sample"],
         },
@@ -214,16 +236,25 @@ def wire_format_leg(ab, n_pods=10_000, n_nodes=1000, reps=5):
     }
 
 
-def workload_config(n_gpus: int, scaling: str, skewed: bool = False):
+EXCHANGES = {
+    "posted": "cluster totals traded inside the top-node kernel over NVLink peer memory (CUDA IPC mailboxes), "
+              "collected one step late (no collective launch)",
+    "fused": "cluster totals traded inside the top-node kernel over NVLink peer memory (CUDA IPC mailboxes), "
+             "collected by the same launch (no collective launch)",
+    "nccl": "NCCL all-reduce of the int64[2] cluster totals after the kernel",
+}
+
+
+def workload_config(n_gpus: int, scaling: str, skewed: bool = False, collective: str = "posted"):
+    ex = EXCHANGES[collective]
     if skewed:
         wl = ("BASELINE configs[4]: skewed snapshot of 1e8 pods / 1e6 nodes (power-law pods per node, GPU-sharing nodes, "
-              f"seed 5) cut into {n_gpus} node range(s) of equal pod count, NCCL totals all-reduce")
+              f"seed 5) cut into {n_gpus} node range(s) of equal pod count" + (f"; {ex}" if n_gpus > 1 else ""))
     elif scaling == "strong" and n_gpus > 1:
-        wl = (f"BASELINE configs[3]: synthetic snapshot of 1e8 pods / 1e6 nodes (seed 1) cut into {n_gpus} node ranges, "
-              "NCCL totals all-reduce")
+        wl = (f"BASELINE configs[3]: synthetic snapshot of 1e8 pods / 1e6 nodes (seed 1) cut into {n_gpus} node ranges; {ex}")
     elif n_gpus > 1:
         wl = (f"BASELINE configs[3] per GPU: {n_gpus} node-range shards of 1e8 pods / 1e6 nodes each "
-              f"(cluster of {n_gpus}e8 pods / {n_gpus}e6 nodes, seeds 1..{n_gpus}), NCCL totals all-reduce")
+              f"(cluster of {n_gpus}e8 pods / {n_gpus}e6 nodes, seeds 1..{n_gpus}); {ex}")
     else:
         wl = "BASELINE configs[3] on one GPU: synthetic snapshot of 1e8 pods / 1e6 nodes, mixed phases, multi-container pods, seed 1"
     return {"workload": wl, "command": "arena top node (summary)", "pods_per_gpu": None, "nodes_per_gpu": None,
@@ -237,7 +268,9 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"],
+                    help="N > 1: strong (default) = ONE snapshot of --pods cut into N node ranges (BASELINE configs[3]); "
+                         "weak = --pods per GPU")
     ap.add_argument("--pods", type=int, default=PODS_FULL, help="pods per GPU (weak) or in total (strong)")
     ap.add_argument("--nodes", type=int, default=NODES_FULL)
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
@@ -245,14 +278,16 @@ def main():
     ap.add_argument("--skewed", action="store_true",
                     help="BASELINE configs[4]: power-law pods per node + GPU-sharing nodes (seed 5); with --gpus > 1 one "
                          "snapshot is cut into node ranges (implies --scaling strong) and the pod-count imbalance is reported")
-    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
-                    help="multi-GPU totals: traded inside the kernel over NVLink peer memory (fused), or a NCCL all-reduce "
-                         "after it (nccl)")
+    ap.add_argument("--collective", default="posted", choices=["posted", "fused", "nccl"],
+                    help="multi-GPU totals: traded inside the kernel over NVLink peer memory and collected one step late "
+                         "(posted) or by the same launch (fused), or a NCCL all-reduce after the kernel (nccl)")
     ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3                         # timing rule: W >= 3
+    if args.scaling is None:
+        args.scaling = "strong" if args.gpus > 1 else "weak"
 
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -316,16 +351,26 @@ def main():
     stream = torch.cuda.current_stream()
 
     fused = False
-    if world > 1 and args.collective == "fused":
+    if world > 1 and args.collective in ("fused", "posted"):
         fused = multigpu.setup_peer_exchange()
         log(f"[rank {rank}] in-kernel totals exchange over peer memory: {'on' if fused else 'unavailable, using NCCL'}")
+        if not fused:
+            args.collective = "nccl"
+    posted = fused and args.collective == "posted"
 
     def step():
-        if fused:
+        if posted:
+            ab.top_node_device_posted(dev, d_total, d_alloc, d_cluster, stream.cuda_stream)
+        elif fused:
             ab.top_node_device_fused(dev, d_total, d_alloc, d_cluster, stream.cuda_stream)
         else:
             ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, stream.cuda_stream)
             multigpu.all_reduce_totals(d_cluster)
+
+    def finish_steps():
+        # deferred collection: the last step's totals are fetched by one more (one-warp) launch
+        if posted:
+            ab.peer_exchange_collect(d_cluster, stream.cuda_stream)
 
     def barrier():
         if world > 1:
@@ -334,6 +379,7 @@ def main():
 
     for _ in range(args.warmup):
         step()
+    finish_steps()
     barrier()
 
     sampler = ClockSampler(local)
@@ -350,6 +396,7 @@ def main():
     ev0.record(stream)
     for _ in range(args.steps):
         step()
+    finish_steps()
     ev1.record(stream)
     barrier()
     t_wall1 = time.time()
@@ -376,6 +423,16 @@ def main():
         dist.all_reduce(sums)
     if sums.cpu().numpy().tolist() != cl.tolist():
         raise SystemExit(f"bench.py: cluster totals {cl.tolist()} != table sums {sums.tolist()}")
+    # parity proper, outside the timed region: THIS rank's slice of the table against the C oracle on the
+    # same shard, and the exchanged global totals against the sum of the per-rank oracle totals
+    ok_local, oracle_cl = oracle_parity(host, d_total, d_alloc)
+    oc = torch.tensor(oracle_cl.tolist() + [0 if ok_local else 1], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(oc)
+    oc = oc.cpu().numpy().tolist()
+    parity_ok = oc[2] == 0 and oc[:2] == cl.tolist()
+    if not parity_ok:
+        raise SystemExit(f"bench.py: parity failure: {oc[2]} rank(s) differ from the oracle; totals {cl.tolist()} vs oracle {oc[:2]}")
 
     # ---- e2e: the public one-shot call with HOST buffers, copies in the timed region.  The snapshot goes over
     # PCIe in its packed form (1 byte per pod + 1 per container) when it has one; the wide form (9 + 9) is timed
@@ -405,8 +462,11 @@ def main():
     wide_steps = max(2, e2e_steps // 2)
     h2d_wide = 9 * P + 4 + 9 * C + 9 * N     # columns uploaded per step (top node needs no job columns)
     d2h = 16 * N + 16
+    pack_s = None
     try:
+        t_pack = time.perf_counter()
         packed = host.pack(pinned=True)
+        pack_s = time.perf_counter() - t_pack              # host time of arena_host_snapshot_pack, once per snapshot
     except ab.ArenaError as e:
         log(f"[rank {rank}] no packed form: {e}")
         packed = None
@@ -467,18 +527,24 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
         "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": dict(workload_config(n_gpus, args.scaling, args.skewed), pods_per_gpu=P, nodes_per_gpu=N,
+        "parity_ok": parity_ok,
+        "config": dict(workload_config(n_gpus, args.scaling, args.skewed, args.collective), pods_per_gpu=P, nodes_per_gpu=N,
                        containers_per_gpu=C, total_pods=total_pods, shard_imbalance_max_over_mean=imbalance),
         "clocks": clocks,
         "e2e": {"value": total_pods * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
                 "call": e2e_call,
+                "pack_ms": pack_s * 1e3 if pack_s is not None and packed is not None else None,
+                "pack_note": "host time of arena_host_snapshot_pack (wide columns -> packed form), once per snapshot, "
+                             "outside the timed e2e steps; e2e_incl_pack adds it to EVERY step (a caller that repacks "
+                             "per query)",
+                "e2e_incl_pack": (total_pods / (e2e_s / e2e_steps + pack_s) if pack_s is not None and packed is not None
+                                  and int(flags.item()) else None),
                 "wide": {"value": total_pods * wide_steps / wide_s, "h2d_bytes_per_step": h2d_wide,
                          "ms_per_step": wide_s / wide_steps * 1e3,
                          "call": "arena_top_node_host (wide columns: 9 B per pod + 9 B per container)"}},
         "gpu_launches": launches,
-        "collective": ("in-kernel exchange over NVLink peer memory (CUDA IPC mailboxes), no collective launch" if fused
-                       else "NCCL all-reduce of int64[2]" if world > 1 else None),
+        "collective": EXCHANGES[args.collective] if world > 1 else None,
         "roofline": roofline,
         "hbm_gbs_step": step_bytes / (ms_per_step / 1e3) / 1e9,
     }
@@ -493,6 +559,7 @@ def main():
                       f"{r['sample_nodes']} nodes of the generator (seed 1), array-of-structs + string-hash join, all "
                       "host threads (C restatement of the Go path; the Go reference cannot be built here)",
             "columnar_single_pass_1thread": r["b3_columnar_1thread"],
+            "columnar_all_threads": r["b3_columnar_all_threads"],
             "faithful_nested_loop_1thread": r["b1_nested_loop_1thread"],
             "faithful_nested_loop_sample": r["b1_sample"],
         }

@@ -163,6 +163,19 @@ void arena_peer_exchange_destroy(void);
 int  arena_peer_exchange_timed_out(void);
 int  arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
                                  int64_t *d_cluster, void *stream);
+/*
+ * The same launch with the collection deferred by one step, for a caller that issues a SEQUENCE of
+ * queries (a poller, a benchmark): the kernel posts this step's totals to every peer and collects
+ * the PREVIOUS step's, which every peer posted a whole step ago -- a rank that runs late by less
+ * than a step stalls nobody.  d_cluster_prev receives the global totals of the previous posted step
+ * (untouched by the first call after arena_peer_exchange_create); arena_peer_exchange_collect
+ * enqueues a one-warp kernel that delivers the totals of the most recent step, at the end of the
+ * sequence or whenever the caller wants them now.  Same rules as above: every rank makes the same
+ * sequence of calls; the per-node slices are complete when the launch is.
+ */
+int  arena_top_node_device_posted(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
+                                  int64_t *d_cluster_prev, void *stream);
+int  arena_peer_exchange_collect(int64_t *d_cluster, void *stream);
 
 /*
  * The same one-shot call for a PACKED host snapshot: the narrowest exact encoding of what

@@ -245,8 +245,52 @@ def test_fused_totals_exchange_with_itself(gpu):
             assert d_cluster.cpu().numpy().tolist() == cl.tolist()
             assert np.array_equal(d_alloc.cpu().numpy(), alloc) and np.array_equal(d_total.cpu().numpy(), tot)
         assert gpu.lib().arena_peer_exchange_timed_out() == 0
+        # deferred collection: every launch delivers the totals of the step before it, the collect
+        # call those of the last one.  Two snapshots alternate so that a stale total would show.
+        host2 = gpu.HostSnapshot.synth(200_000, 3_000, seed=22)
+        dev2 = gpu.DeviceSnapshot.upload(host2)
+        tot2, alloc2, cl2, _ = cref.top_node_columnar(host2.cols)
+        d_total2 = torch.empty(host2.n_nodes, dtype=torch.int64, device="cuda")
+        d_alloc2 = torch.empty(host2.n_nodes, dtype=torch.int64, device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        prev = cl                                           # the fused steps above posted `cl` last
+        for k in range(6):
+            d_cluster.fill_(-1)
+            if k % 2 == 0:
+                gpu.top_node_device_posted(dev2, d_total2, d_alloc2, d_cluster, st)
+                mine, table, want_alloc = cl2, d_alloc2, alloc2
+            else:
+                gpu.top_node_device_posted(dev, d_total, d_alloc, d_cluster, st)
+                mine, table, want_alloc = cl, d_alloc, alloc
+            torch.cuda.synchronize()
+            assert d_cluster.cpu().numpy().tolist() == prev.tolist(), f"step {k}: not the previous step's totals"
+            assert np.array_equal(table.cpu().numpy(), want_alloc)
+            prev = mine
+        gpu.peer_exchange_collect(d_cluster, st)
+        torch.cuda.synchronize()
+        assert d_cluster.cpu().numpy().tolist() == prev.tolist()
+        assert gpu.lib().arena_peer_exchange_timed_out() == 0
     finally:
         gpu.lib().arena_peer_exchange_destroy()
+
+
+def test_unaligned_and_dirty_output_buffers(gpu):
+    """node_alloc is accumulated with atomics, so the call must clear it first whatever it held; the
+    self-zeroing launch (ARENA_COOPERATIVE=1) needs 16-byte alignment and falls back to the memset
+    for a buffer that is 8 bytes off."""
+    import torch
+    host = gpu.HostSnapshot.synth(700_000, 9_001, seed=23)
+    dev = gpu.DeviceSnapshot.upload(host)
+    tot, alloc, cl, _ = cref.top_node_columnar(host.cols)
+    N = host.n_nodes
+    d_total = torch.empty(N, dtype=torch.int64, device="cuda")
+    buf = torch.full((N + 1,), -3, dtype=torch.int64, device="cuda")       # garbage in both
+    d_cluster = torch.empty(2, dtype=torch.int64, device="cuda")
+    for view in (buf[:N], buf[1:]):                                          # aligned, then 8 bytes off
+        view.fill_(-3)
+        gpu.top_node_device(dev, d_total, view, d_cluster, None, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert np.array_equal(view.cpu().numpy(), alloc) and d_cluster.cpu().numpy().tolist() == cl.tolist()
 
 
 def test_pageable_columns_take_the_staged_upload(gpu):
