@@ -120,6 +120,7 @@ _SIGS = [
     ("arena_free_text", None, [_VP]),
     ("arena_synth_snapshot", C.c_int, [C.POINTER(SynthParams), C.POINTER(_VP)]),
     ("arena_shard_plan", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.c_int, _VP, _VP]),
+    ("arena_host_snapshot_regroup", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.POINTER(_VP)]),
     ("arena_shard_extract", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64,
                                       C.c_uint64, C.POINTER(_VP)]),
 ]

@@ -210,10 +210,24 @@ struct Scratch {
 // slots keep them apart.
 constexpr int kMaxPeers = 16;
 constexpr int kPeerRing = 4;
+// A cell is {value, epoch} written with ONE aligned 16-byte store and polled with one 16-byte
+// load: the value is valid as soon as the epoch beside it is the expected one, so no fence (a round
+// trip over NVLink) has to separate data from flag.
+struct __align__(16) PeerCell { unsigned long long value, epoch; };
 struct PeerMailbox {
-    unsigned long long flag[kPeerRing][kMaxPeers];   // [slot][writer] = epoch of totals[slot][writer]
-    long long totals[kPeerRing][kMaxPeers][2];       // {first total, second total}
+    PeerCell cell[kPeerRing][kMaxPeers][2];          // [slot][writer][first total, second total]
 };
+
+__device__ __forceinline__ void peer_cell_store(PeerCell *p, u64 value, u64 epoch)
+{
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" :: "l"(p), "l"(value), "l"(epoch) : "memory");
+}
+__device__ __forceinline__ PeerCell peer_cell_load(const PeerCell *p)
+{
+    PeerCell c;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(c.value), "=l"(c.epoch) : "l"(p) : "memory");
+    return c;
+}
 struct PeerExchange {
     int rank, world;
     unsigned timed_out;                          // set when a peer did not show up within the spin budget
@@ -229,17 +243,12 @@ __device__ __forceinline__ void peer_collect(PeerExchange *px, u64 epoch, u64 &g
     PeerMailbox *mine = px->box[px->rank];
     const int slot = (int)(epoch % (u64)kPeerRing);
     const long long t0 = clock64();
-    bool ok = true;
-    while (*((volatile unsigned long long *)&mine->flag[slot][threadIdx.x]) != epoch) {
-        __nanosleep(100);
-        if (clock64() - t0 > 4000000000ll) { ok = false; break; }      // ~2 s: a peer is gone
-    }
-    __threadfence_system();
-    if (ok) {
-        ga = (u64)*((volatile long long *)&mine->totals[slot][threadIdx.x][0]);
-        gb = (u64)*((volatile long long *)&mine->totals[slot][threadIdx.x][1]);
-    } else {
-        px->timed_out = 1u;
+    for (;;) {
+        const PeerCell a = peer_cell_load(&mine->cell[slot][threadIdx.x][0]);
+        const PeerCell b = peer_cell_load(&mine->cell[slot][threadIdx.x][1]);
+        if (a.epoch == epoch && b.epoch == epoch) { ga = a.value; gb = b.value; return; }
+        __nanosleep(64);
+        if (clock64() - t0 > 4000000000ll) { px->timed_out = 1u; return; }      // ~2 s: a peer is gone
     }
 }
 
@@ -289,10 +298,8 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
     u64 ga = 0, gb = 0;
     if ((int)threadIdx.x < px->world) {
         PeerMailbox *theirs = px->box[threadIdx.x];
-        theirs->totals[slot][px->rank][0] = (long long)s_tot[0];
-        theirs->totals[slot][px->rank][1] = (long long)s_tot[1];
-        __threadfence_system();
-        *((volatile unsigned long long *)&theirs->flag[slot][px->rank]) = epoch;
+        peer_cell_store(&theirs->cell[slot][px->rank][0], s_tot[0], epoch);
+        peer_cell_store(&theirs->cell[slot][px->rank][1], s_tot[1], epoch);
         if (epoch > (u64)lag) peer_collect(px, epoch - lag, ga, gb);
     }
     if (epoch <= (u64)lag) return;     // deferred collection, first step: nothing older to deliver

@@ -391,4 +391,71 @@ int arena_shard_extract(const arena_snapshot_view *v, int by_job, uint64_t key_l
     return ARENA_OK;
 }
 
+// Rows regrouped by key (stable counting sort: rows of one key keep their order, which is what the
+// latest-pod tie rule needs); rows whose key names no node / job go last.  Owns all its pod and
+// container columns; the node columns are copied so that the result outlives its source.
+int arena_host_snapshot_regroup(const arena_snapshot_view *v, int by_job, arena_host_snapshot **out)
+{
+    if (!v || !out) return fail(ARENA_E_INVALID, "NULL argument");
+    *out = nullptr;
+    const uint32_t *key = by_job ? v->pod_job : v->pod_node;
+    const uint64_t K = by_job ? v->n_jobs : v->n_nodes, P = v->n_pods, C = v->n_containers, N = v->n_nodes;
+    if (P && (!key || !v->pod_node || !v->pod_phase || !v->pod_ctr_begin)) return fail(ARENA_E_INVALID, "pod columns are NULL");
+    const bool jobs = v->pod_job && v->pod_role && v->pod_created;
+    if (by_job && !jobs) return fail(ARENA_E_INVALID, "snapshot has no job columns to group by");
+    arena_host_snapshot *h = new arena_host_snapshot();
+    int rc;
+    auto bail = [&](int code) { delete h; return code; };
+    if ((rc = h->c_pod_node.alloc(P * 4, false)) || (rc = h->c_pod_phase.alloc(P, false)) ||
+        (rc = h->c_pod_ctr_begin.alloc((P + 1) * 4, false)) || (rc = h->c_ctr_val.alloc(C * 8, false)) ||
+        (rc = h->c_ctr_scale.alloc(C, false)) || (rc = h->c_node_cap_val.alloc(N * 8, false)) ||
+        (rc = h->c_node_cap_scale.alloc(N, false)))
+        return bail(rc);
+    if (jobs && ((rc = h->c_pod_job.alloc(P * 4, false)) || (rc = h->c_pod_role.alloc(P, false)) ||
+                 (rc = h->c_pod_created.alloc(P * 8, false))))
+        return bail(rc);
+    std::vector<uint64_t> start(K + 2, 0);                       // bucket K: rows with no key
+    for (uint64_t p = 0; p < P; p++) start[std::min<uint64_t>(key[p], K) + 1]++;
+    for (uint64_t k = 0; k <= K; k++) start[k + 1] += start[k];
+    std::vector<uint32_t> row_of(P);                             // old row -> new row
+    for (uint64_t p = 0; p < P; p++) row_of[p] = (uint32_t)start[std::min<uint64_t>(key[p], K)]++;
+    uint32_t *cb = h->c_pod_ctr_begin.as<uint32_t>();
+    for (uint64_t p = 0; p < P; p++) cb[row_of[p] + 1] = v->pod_ctr_begin[p + 1] - v->pod_ctr_begin[p];
+    if (P + 1) cb[0] = 0;
+    for (uint64_t r = 0; r < P; r++) cb[r + 1] += cb[r];
+    uint32_t *pn = h->c_pod_node.as<uint32_t>();
+    uint8_t *ph = h->c_pod_phase.as<uint8_t>();
+    int64_t *cv = h->c_ctr_val.as<int64_t>();
+    int8_t *cs = h->c_ctr_scale.as<int8_t>();
+    uint32_t *pj = h->c_pod_job.as<uint32_t>();
+    uint8_t *pr = h->c_pod_role.as<uint8_t>();
+    int64_t *pc = h->c_pod_created.as<int64_t>();
+    for (uint64_t p = 0; p < P; p++) {
+        const uint32_t r = row_of[p];
+        pn[r] = v->pod_node[p];
+        ph[r] = v->pod_phase[p];
+        if (jobs) { pj[r] = v->pod_job[p]; pr[r] = v->pod_role[p]; pc[r] = v->pod_created[p]; }
+        const uint32_t n = v->pod_ctr_begin[p + 1] - v->pod_ctr_begin[p];
+        if (n) {
+            std::memcpy(cv + cb[r], v->ctr_val + v->pod_ctr_begin[p], (size_t)n * 8);
+            std::memcpy(cs + cb[r], v->ctr_scale + v->pod_ctr_begin[p], n);
+        }
+    }
+    if (N) {
+        std::memcpy(h->c_node_cap_val.ptr, v->node_cap_val, N * 8);
+        std::memcpy(h->c_node_cap_scale.ptr, v->node_cap_scale, N);
+    }
+    h->v = *v;
+    h->v.pod_node = pn; h->v.pod_phase = ph; h->v.pod_ctr_begin = cb; h->v.ctr_val = cv; h->v.ctr_scale = cs;
+    h->v.node_cap_val = h->c_node_cap_val.as<int64_t>(); h->v.node_cap_scale = h->c_node_cap_scale.as<int8_t>();
+    if (jobs) { h->v.pod_job = pj; h->v.pod_role = pr; h->v.pod_created = pc; }
+    else { h->v.pod_job = nullptr; h->v.pod_role = nullptr; h->v.pod_created = nullptr; h->v.n_jobs = 0; }
+    h->pod_order = std::move(row_of);                            // (row -> source row needs the inverse)
+    std::vector<uint32_t> inv(P);
+    for (uint64_t p = 0; p < P; p++) inv[h->pod_order[p]] = (uint32_t)p;
+    h->pod_order = std::move(inv);
+    *out = h;
+    return ARENA_OK;
+}
+
 }  // extern "C"

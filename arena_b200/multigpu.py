@@ -139,3 +139,57 @@ def top_node_sharded(host_shard, details: bool = False, out=None):
         t = t.cuda()
     all_reduce_totals(t)
     return res, t.cpu().numpy()
+
+
+def merge_job_orders(reqs, orders, key_cut):
+    """The global `top job` ordering from per-shard results.  Shard i holds the jobs
+    [key_cut[i], key_cut[i+1]) and has them ordered by (requested desc, id asc) already
+    (trainer.go:25-37 + the documented tie-break), so the global order is a MERGE of runs:
+    a stable sort by requested of the runs laid end to end in shard order, because equal
+    requested values then stay in ascending-id order.  reqs[i]: int64 per-job requested of shard i
+    (shard-local ids), orders[i]: uint32 shard-local order.  Returns global job ids, uint32."""
+    runs_id, runs_req = [], []
+    for i, (req, order) in enumerate(zip(reqs, orders)):
+        order = np.asarray(order, np.int64)
+        runs_id.append(order + int(key_cut[i]))
+        runs_req.append(np.asarray(req, np.int64)[order])
+    ids = np.concatenate(runs_id) if runs_id else np.zeros(0, np.int64)
+    req = np.concatenate(runs_req) if runs_req else np.zeros(0, np.int64)
+    # descending by requested, stable: flip the sign bit trick is not needed with int64 keys
+    # unless requested can be INT64_MIN; negate through uint64 to stay exact
+    key = (~req.view(np.uint64)) ^ np.uint64(0x8000000000000000)      # ascending key == requested descending
+    return ids[np.argsort(key, kind="stable")].astype(np.uint32)
+
+
+def top_job_sharded(host_by_job, out_device=None):
+    """Multi-GPU `top job`: jobs span nodes, so the snapshot -- rows grouped by job,
+    HostSnapshot.regroup(by_job=True) -- is cut into job-id ranges of about equal pod count, one per
+    rank; each rank runs the ordinary `top job` kernels on its range; the per-job tables are disjoint
+    slices, the two totals (list.go:102-103) are all-reduced, and the per-rank orderings are merged.
+    Every rank passes the same full snapshot.  Returns (TopJobResult of this rank's shard with
+    job_latest as GLOBAL row indices, key range (lo, hi), global totals int64[2], and on rank 0 the
+    global job order (else None))."""
+    from .snapshot import DeviceSnapshot
+    from .top import top_job
+    rank, world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+    key_cut, pod_cut = host_by_job.shard_plan(world, by_job=True)
+    shard = host_by_job.shard(rank, world, by_job=True)
+    dev = DeviceSnapshot.upload(shard)
+    res = top_job(dev)
+    dev.close()
+    latest = res.job_latest.astype(np.int64)
+    latest[res.job_latest != 0xFFFFFFFF] += int(pod_cut[rank])
+    res.job_latest = latest.astype(np.uint32)
+    t = torch.from_numpy(res.totals.copy())
+    if dist.is_initialized() and world > 1 and dist.get_backend() == "nccl":
+        t = t.cuda()
+    all_reduce_totals(t)
+    order = None
+    if world > 1:
+        gathered = [None] * world if rank == 0 else None
+        dist.gather_object((res.job_req, res.job_order), gathered, dst=0)
+        if rank == 0:
+            order = merge_job_orders([g[0] for g in gathered], [g[1] for g in gathered], key_cut)
+    else:
+        order = res.job_order
+    return res, (int(key_cut[rank]), int(key_cut[rank + 1])), t.cpu().numpy(), order

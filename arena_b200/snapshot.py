@@ -151,6 +151,12 @@ class HostSnapshot:
         """arena_host_snapshot_pack (raises ArenaError -1 when there is no packed form)."""
         return PackedSnapshot(self, pinned)
 
+    def regroup(self, by_job: bool = False) -> "HostSnapshot":
+        """arena_host_snapshot_regroup: rows grouped (stably) by node id or by job id."""
+        h = C.c_void_p()
+        check(lib().arena_host_snapshot_regroup(C.byref(self.view), int(by_job), C.byref(h)))
+        return HostSnapshot.from_handle(h.value)
+
     # -- sharding ---------------------------------------------------------------
     def shard_plan(self, n_shards: int, by_job: bool = False):
         key_cut = np.zeros(n_shards + 1, np.uint64)

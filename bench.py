@@ -262,6 +262,103 @@ def workload_config(n_gpus: int, scaling: str, skewed: bool = False, collective:
             "parallelism": f"node-range shards x{n_gpus}" if n_gpus > 1 else "single GPU"}
 
 
+def run_job_arm(args):
+    """`--command job`: multi-GPU `top job`.  ONE snapshot (default 2e7 pods / 1e6 jobs,
+    seed 3), rows regrouped by job and cut into N job-id ranges of about equal pod count; a step is
+    the `top job` query of every rank on its resident shard (per-job sums, latest-pod rule, ordering)
+    plus the all-reduce of the two totals.  Device-timed, max over ranks; per-rank tables and the
+    global totals are checked against the C oracle after the timed region."""
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import arena_b200 as ab
+    from arena_b200 import multigpu
+    from oracle import cref
+    rank, world, local = multigpu.env_rank()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    multigpu.init_process_group("nccl")
+    ab.init(local)
+    P, J = args.job_pods, args.jobs
+    full = ab.HostSnapshot.synth(P, max(1, P // 100), seed=3, n_jobs=J).regroup(by_job=True)
+    key_cut, pod_cut = full.shard_plan(world, by_job=True)
+    shard = full.shard(rank, world, by_job=True)
+    Js = shard.n_jobs
+    dev = ab.DeviceSnapshot.upload(shard)
+    d_req = torch.empty(Js, dtype=torch.int64, device="cuda")
+    d_alloc = torch.empty_like(d_req)
+    d_order = torch.empty(Js, dtype=torch.int32, device="cuda")
+    d_latest = torch.empty_like(d_order)
+    d_tot = torch.empty(2, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step():
+        ab.top_job_device(dev, d_req, d_alloc, d_order, d_latest, d_tot, stream.cuda_stream)
+        multigpu.all_reduce_totals(d_tot)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    L0 = ab.lib().arena_kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    t1 = time.time()
+    launches = int(ab.lib().arena_kernel_launches() - L0)
+    tmax = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_per_step = float(tmax.item()) / args.steps
+    # parity: this rank's job range against the oracle on the shard, totals against the oracle on the whole
+    req, alloc, latest, totals = cref.top_job_columnar(shard.cols, Js)
+    ok = (np.array_equal(d_req.cpu().numpy(), req) and np.array_equal(d_alloc.cpu().numpy(), alloc)
+          and np.array_equal(d_latest.cpu().numpy().view(np.uint32), latest))
+    want_order = np.lexsort((np.arange(Js), -req)).astype(np.uint32) if Js else np.zeros(0, np.uint32)
+    ok = ok and np.array_equal(d_order.cpu().numpy().view(np.uint32), want_order)
+    _, _, _, full_totals = cref.top_job_columnar(full.cols, J)
+    ok = ok and d_tot.cpu().numpy().tolist() == full_totals.tolist()
+    bad = torch.tensor([0 if ok else 1], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(bad)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    if rank == 0:
+        line = {
+            "metric": "pod-records/sec for top-job GPU accounting", "value": P / (ms_per_step / 1e3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "parity_ok": int(bad.item()) == 0,
+            "config": {"workload": f"synthetic snapshot of {P} pods / {J} jobs (seed 3) regrouped by job and cut into "
+                                   f"{world} job-id range(s); per-rank `top job` query + NCCL all-reduce of the int64[2] totals",
+                       "command": "arena top job", "pods_per_gpu": shard.n_pods, "jobs_per_gpu": Js,
+                       "parallelism": f"job-range shards x{world}" if world > 1 else "single GPU"},
+            "clocks": clocks, "gpu_launches": launches,
+        }
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if int(bad.item()):
+        raise SystemExit("bench.py --command job: parity failure")
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -283,6 +380,10 @@ def main():
                          "(posted) or by the same launch (fused), or a NCCL all-reduce after the kernel (nccl)")
     ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
+    ap.add_argument("--command", default="node", choices=["node", "job"],
+                    help="node: the headline `top node` path; job: the multi-GPU `top job` arm (job-id range shards)")
+    ap.add_argument("--job-pods", type=int, default=20_000_000)
+    ap.add_argument("--jobs", type=int, default=1_000_000)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3                         # timing rule: W >= 3
@@ -299,6 +400,9 @@ def main():
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"),
                os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
+
+    if args.command == "job":
+        return run_job_arm(args)
 
     # stdout carries exactly ONE JSON line: libraries that print there (NCCL's
     # version banner) are sent to stderr for the duration of the run

@@ -180,6 +180,12 @@ int  arena_synth_snapshot(const arena_synth_params *p, arena_host_snapshot **out
  */
 int  arena_shard_plan(const arena_snapshot_view *host, int n_shards, int by_job,
                       uint64_t *key_cut, uint64_t *pod_cut);
+/* A copy of `host` with its rows regrouped by node id (by_job == 0) or by job id (by_job != 0):
+ * stable, so rows of one key keep their order; rows that name no node / job go last.  What
+ * arena_shard_plan needs before it can cut by that key (e.g. job ranges for a multi-GPU `top job`
+ * from a node-grouped snapshot).  arena_host_pod_order() of the result maps a row to its source
+ * row.  The result owns its columns.  No reference counterpart. */
+int  arena_host_snapshot_regroup(const arena_snapshot_view *host, int by_job, arena_host_snapshot **out);
 /* Shard [key_lo,key_hi) x [pod_lo,pod_hi) as a host snapshot of its own: keys
  * and container offsets are rebased to the shard (keys outside the range
  * become ARENA_NONE); the other columns alias the parent's memory, which must

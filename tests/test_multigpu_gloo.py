@@ -114,3 +114,40 @@ def test_job_range_shards_reproduce_top_job(built):
     assert np.array_equal(np.concatenate([p[0] for p in parts]), req)
     assert np.array_equal(np.concatenate([p[1] for p in parts]), alloc)
     assert (sum(int(p[2][0]) for p in parts), sum(int(p[2][1]) for p in parts)) == (int(totals[0]), int(totals[1]))
+
+
+def test_regroup_by_job_then_merge_orders(built):
+    """The host logic of the multi-GPU `top job`: regroup a node-grouped snapshot by job, cut it into
+    job-id ranges, and merge the per-shard orderings -- per-shard tables from the C oracle."""
+    from arena_b200 import HostSnapshot, multigpu
+    from oracle import cref
+    J = 900
+    host = HostSnapshot.synth(150_000, 700, seed=6, n_jobs=J)
+    byjob = host.regroup(by_job=True)
+    pj = byjob.cols["pod_job"].astype(np.int64)
+    pj[pj == 0xFFFFFFFF] = J
+    assert np.all(pj[:-1] <= pj[1:]), "rows must be grouped by job"
+    # regrouping changes no sum and keeps list order inside a job (the latest-pod tie rule)
+    req, alloc, latest, totals = cref.top_job_columnar(host.cols, J)
+    req2, alloc2, latest2, totals2 = cref.top_job_columnar(byjob.cols, J)
+    assert np.array_equal(req, req2) and np.array_equal(alloc, alloc2) and np.array_equal(totals, totals2)
+    src = byjob.pod_order()
+    has = latest != 0xFFFFFFFF
+    assert np.array_equal(src[latest2[has]], latest[has])
+    want_order = np.array(sorted(range(J), key=lambda j: (-int(req[j]), j)), np.uint32)
+    for G in (1, 2, 5):
+        key_cut, pod_cut = byjob.shard_plan(G, by_job=True)
+        reqs, orders, tot = [], [], np.zeros(2, np.int64)
+        for i in range(G):
+            sh = byjob.shard(i, G, by_job=True)
+            r, a, l, t = cref.top_job_columnar(sh.cols, sh.n_jobs)
+            reqs.append(r)
+            orders.append(np.array(sorted(range(sh.n_jobs), key=lambda j: (-int(r[j]), j)), np.uint32))
+            tot += t
+        assert np.array_equal(np.concatenate(reqs), req) and tot.tolist() == totals.tolist()
+        assert np.array_equal(multigpu.merge_job_orders(reqs, orders, key_cut), want_order)
+    # and back: grouped by node again, the node table is the original one
+    again = byjob.regroup(by_job=False)
+    assert np.array_equal(again.cols["pod_node"], host.cols["pod_node"])
+    for x, y in zip(cref.top_node_columnar(again.cols, False)[:3], cref.top_node_columnar(host.cols, False)[:3]):
+        assert np.array_equal(x, y)
