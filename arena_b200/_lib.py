@@ -93,6 +93,7 @@ _SIGS = [
     ("arena_calibrate_stream_read", C.c_int, [_VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     ("arena_calibrate_stream_pattern", C.c_int, [_VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     ("arena_profile_begin", C.c_int, [C.c_int]),
+    ("arena_profile_begin_sampled", C.c_int, [C.c_int, C.c_int]),
     ("arena_profile_end", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     # arena_top.h
     ("arena_host_snapshot_free", None, [_VP]),

@@ -53,6 +53,7 @@ inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed);
 // arena_top_node*() call between arena_profile_begin() and arena_profile_end().
 struct Profile {
     bool on = false;
+    unsigned every = 1, seen = 0;    // record every `every`-th call only (the three event records cost ~10 us per call)
     std::vector<cudaEvent_t> ev;     // 3 per call: before nodes, between, after pods
     size_t used = 0;
 };
@@ -88,7 +89,6 @@ static PeerMailbox *g_my_box = nullptr;
 static PeerExchange *g_px = nullptr;             // device copy of the descriptor
 static PeerExchange g_px_host{};
 static void *g_peer_mapped[kMaxPeers] = {};
-static std::atomic<uint64_t> g_epoch{0};
 // A few freed device blocks are kept for the next snapshot of about the same size: a polling caller
 // (load, query, free, again) otherwise pays cudaMalloc + cudaFree, which cost more than its kernels.
 struct FreeBlock { void *p; size_t bytes; cudaEvent_t idle; };   // idle: recorded on the library stream at release
@@ -282,7 +282,7 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
                     cudaStream_t st, int exchange = 0)
 {
     const arena_snapshot_view &v = s->v;
-    const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size();
+    const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size() && (g_prof.seen++ % g_prof.every) == 0;
     cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
     if (prof) { g_prof.used += 3; CUDA_TRY(cudaEventRecord(pe[0], st)); }
     // node_alloc is accumulated with atomics: it starts from zero.  A memset in front of the launch,
@@ -314,7 +314,6 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     pa.total_capacity = d_cluster;
     if (exchange) {
         pa.px = g_px;
-        pa.epoch = g_epoch.fetch_add(1) + 1;
         pa.px_lag = exchange == 2 ? 1u : 0u;
     }
     pa.zero_alloc = self_zero ? 1u : 0u;
@@ -907,7 +906,7 @@ int arena_peer_exchange_create(int rank, int world, unsigned char handle_out[64]
     g_px_host = PeerExchange{};
     g_px_host.rank = rank;
     g_px_host.world = world;
-    g_epoch.store(0);                     // every rank starts counting steps from the same place
+    // (the step counter lives in the device copy of the descriptor and starts from 0 on every rank)
     return ARENA_OK;
 }
 
@@ -970,10 +969,8 @@ int arena_peer_exchange_collect(int64_t *d_cluster, void *stream)
     if (rc) return rc;
     if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
     if (!d_cluster) return fail(ARENA_E_INVALID, "d_cluster is NULL");
-    const uint64_t epoch = g_epoch.load();
-    if (epoch == 0) return fail(ARENA_E_INVALID, "nothing has been posted yet");
     cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
-    peer_collect_kernel<<<1, 32, 0, st>>>(g_px, epoch, (i64 *)d_cluster);
+    peer_collect_kernel<<<1, 32, 0, st>>>(g_px, (i64 *)d_cluster);
     count_launch();
     CUDA_TRY(cudaGetLastError());
     return ARENA_OK;
@@ -1104,7 +1101,18 @@ int arena_profile_begin(int max_calls)
     g_prof.ev.assign((size_t)max_calls * 3, nullptr);
     for (auto &e : g_prof.ev) CUDA_TRY(cudaEventCreate(&e));
     g_prof.used = 0;
+    g_prof.seen = 0;
+    g_prof.every = 1;
     g_prof.on = true;
+    return ARENA_OK;
+}
+
+int arena_profile_begin_sampled(int max_calls, int every)
+{
+    if (every < 1) return fail(ARENA_E_INVALID, "every must be >= 1");
+    int rc = arena_profile_begin(max_calls);
+    if (rc) return rc;
+    g_prof.every = (unsigned)every;
     return ARENA_OK;
 }
 

@@ -231,6 +231,8 @@ __device__ __forceinline__ PeerCell peer_cell_load(const PeerCell *p)
 struct PeerExchange {
     int rank, world;
     unsigned timed_out;                          // set when a peer did not show up within the spin budget
+    unsigned long long epoch;                    // steps posted so far: kept on the DEVICE and advanced by the launch
+                                                 // itself, so a captured launch (CUDA graph) can be replayed
     PeerMailbox *box[kMaxPeers];                 // rank i's mailbox as mapped into this process
 };
 
@@ -254,7 +256,7 @@ __device__ __forceinline__ void peer_collect(PeerExchange *px, u64 epoch, u64 &g
 
 __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two,
                                               Scratch *sc, int ticket_id, i64 *out_a, i64 *out_b,
-                                              PeerExchange *px = nullptr, u64 epoch = 0, unsigned lag = 0)
+                                              PeerExchange *px = nullptr, unsigned lag = 0)
 {
     __shared__ bool s_last;
     u64 *const part_a = sc->partial_a + (ticket_id == 1 ? 0 : kMaxPartials / 2);
@@ -290,9 +292,11 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
         }
         sc->ticket[ticket_id] = 0;      // ready for the next launch
         sc->ticket[0] = 0;              // the start-of-launch barrier (everybody is long past it)
+        if (px) px->epoch += 1;         // this CTA is the only writer; the next launch is ordered behind it
     }
     if (!px) return;
     __syncthreads();
+    const u64 epoch = *((volatile unsigned long long *)&px->epoch);
     // post to every rank, then collect from every rank: thread i talks to rank i
     const int slot = (int)(epoch % (u64)kPeerRing);
     u64 ga = 0, gb = 0;
@@ -363,7 +367,6 @@ struct PodsArgs {
     i64 *total_capacity;            // sum of node_total
     // multi-GPU: exchange the two totals with the peer GPUs inside this launch (or nullptr)
     PeerExchange *px;
-    u64 epoch;
     unsigned px_lag;                // 0: collect this step's totals; 1: the previous step's (deferred)
     // key_alloc is zeroed by this launch itself (cooperative launch: every CTA clears a slice, one
     // grid-wide barrier, then the tiles) instead of by a memset in front of it
@@ -945,15 +948,20 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
         for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
-    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.epoch, a.px_lag);
+    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.px_lag);
 }
 
-// The totals of `epoch` (posted by the launches of every rank) summed into out = {total capacity,
+// The totals of the most recent step (posted by the launches of every rank) summed into out = {total capacity,
 // allocated} (the mailbox carries them in the kernel's order: allocated first): the end of a
 // sequence of deferred-collection steps.  One CTA of 32 threads.
-__global__ void peer_collect_kernel(PeerExchange *px, u64 epoch, i64 *out)
+__global__ void peer_collect_kernel(PeerExchange *px, i64 *out)
 {
     u64 ga = 0, gb = 0;
+    const u64 epoch = *((volatile unsigned long long *)&px->epoch);
+    if (epoch == 0) {                             // nothing posted yet
+        if (threadIdx.x == 0) { out[0] = 0; out[1] = 0; }
+        return;
+    }
     if ((int)threadIdx.x < px->world) peer_collect(px, epoch, ga, gb);
     ga = warp_reduce_sum(ga);
     gb = warp_reduce_sum(gb);
@@ -1340,7 +1348,6 @@ struct PackedArgs {
     i64 *total_alloc, *total_capacity;
     Scratch *scratch;
     PeerExchange *px;
-    u64 epoch;
 };
 
 // sum of the `cnt` values that start at value index i: eight nibbles (four bytes) per round, taken
@@ -1425,7 +1432,7 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
         for (int w = 0; w < kWarps; w++) { block_a += s_a[w]; block_c += s_c[w]; }
-    finish_totals(block_a, block_c, true, a.scratch, 2, a.total_alloc, a.total_capacity, a.px, a.epoch);
+    finish_totals(block_a, block_c, true, a.scratch, 2, a.total_alloc, a.total_capacity, a.px);
 }
 
 }  // namespace arena

@@ -380,6 +380,7 @@ def main():
                          "(posted) or by the same launch (fused), or a NCCL all-reduce after the kernel (nccl)")
     ap.add_argument("--no-wire", action="store_true", help="skip the wire_format leg (JSON PodList -> columns)")
     ap.add_argument("--sample-pods", type=int, default=10_000_000, help="pods per step of the CPU legs (bounded sample)")
+    ap.add_argument("--graph", action="store_true", help="also time the step replayed from a CUDA graph (reported as graph_ms_per_step)")
     ap.add_argument("--command", default="node", choices=["node", "job"],
                     help="node: the headline `top node` path; job: the multi-GPU `top job` arm (job-id range shards)")
     ap.add_argument("--job-pods", type=int, default=20_000_000)
@@ -493,7 +494,9 @@ def main():
 
     # ---- timed region: exactly K steps, device-timed, max over ranks -----------
     L0 = ab.lib().arena_kernel_launches()
-    ab._lib.check(ab.lib().arena_profile_begin(args.steps))
+    # the kernel's own duration is sampled on every 8th step of the timed region (recording the events on
+    # every step costs ~10 us of stream time per step, tools/kbench_step.py)
+    ab._lib.check(ab.lib().arena_profile_begin_sampled(args.steps, 8))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_wall0 = time.time()
@@ -515,6 +518,44 @@ def main():
     ms_total = float(tmax.item())
     ms_per_step = ms_total / args.steps
     value = total_pods * args.steps / (ms_total / 1e3)
+
+    # the same step replayed from a CUDA graph (captured through the C ABI on this stream), reported beside the
+    # headline, which is timed on plain launches
+    graph_ms = None
+    if args.graph and (world == 1 or fused):
+        try:
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(stream)
+            with torch.cuda.stream(side):
+                def gstep():
+                    if posted:
+                        ab.top_node_device_posted(dev, d_total, d_alloc, d_cluster, side.cuda_stream)
+                    elif fused:
+                        ab.top_node_device_fused(dev, d_total, d_alloc, d_cluster, side.cuda_stream)
+                    else:
+                        ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, side.cuda_stream)
+                with torch.cuda.graph(g, stream=side):
+                    gstep()
+                for _ in range(args.warmup):
+                    g.replay()
+                barrier()
+                g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                g0.record(side)
+                for _ in range(args.steps):
+                    g.replay()
+                if posted:
+                    ab.peer_exchange_collect(d_cluster, side.cuda_stream)
+                g1.record(side)
+                barrier()
+                gms = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device="cuda")
+            stream.wait_stream(side)
+            if world > 1:
+                dist.all_reduce(gms, op=dist.ReduceOp.MAX)
+            graph_ms = float(gms.item()) / args.steps
+        except Exception as e:                      # a side measurement: never lose the headline over it
+            log(f"[rank {rank}] graph replay leg failed: {e!r}")
+            graph_ms = None
 
     if fused and ab.lib().arena_peer_exchange_timed_out():
         raise SystemExit("bench.py: a peer did not post its totals in time (in-kernel exchange)")
@@ -648,6 +689,7 @@ def main():
                          "ms_per_step": wide_s / wide_steps * 1e3,
                          "call": "arena_top_node_host (wide columns: 9 B per pod + 9 B per container)"}},
         "gpu_launches": launches,
+        "graph_ms_per_step": graph_ms,
         "collective": EXCHANGES[args.collective] if world > 1 else None,
         "roofline": roofline,
         "hbm_gbs_step": step_bytes / (ms_per_step / 1e3) / 1e9,
