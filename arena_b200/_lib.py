@@ -85,6 +85,13 @@ _SIGS = [
     ("arena_top_node_device_posted", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_peer_exchange_collect", C.c_int, [_VP, _VP]),
     ("arena_top_node_host_packed", C.c_int, [C.POINTER(PackedView), _VP, _VP, _VP, _VP]),
+    ("arena_acct_init_devices", C.c_int, [C.c_int, C.POINTER(C.c_int)]),
+    ("arena_acct_device_count", C.c_int, []),
+    ("arena_multi_snapshot_upload", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.POINTER(_VP)]),
+    ("arena_multi_snapshot_free", None, [_VP]),
+    ("arena_multi_snapshot_shards", C.c_int, [_VP, C.POINTER(C.c_int), _VP, _VP]),
+    ("arena_top_node_multi", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    ("arena_top_job_multi", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device", C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     ("arena_top_job_device_noalloc", C.c_int, [C.POINTER(SnapshotView), _VP, _VP, _VP, _VP, _VP, _VP]),
@@ -151,6 +158,15 @@ def check(rc: int) -> None:
 
 
 _initialised_device = None
+
+
+def init_devices(devices) -> None:
+    """arena_acct_init_devices: one process, several GPUs (devices[0] is also the device of the
+    single-device calls)."""
+    global _initialised_device
+    ids = (C.c_int * len(devices))(*[int(d) for d in devices])
+    check(lib().arena_acct_init_devices(len(devices), ids))
+    _initialised_device = int(devices[0])
 
 
 def init(device: int = 0) -> None:

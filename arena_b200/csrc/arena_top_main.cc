@@ -5,7 +5,9 @@
 //   arena-top node [-d|--details] --pods PODLIST.json --nodes NODELIST.json
 //   arena-top job  --pods PODLIST.json --nodes NODELIST.json --jobs JOBLIST.json
 //                  [--tfjobs TFJOBLIST.json] --releases HELM_LIST.txt [--now UNIX_SECONDS]
-// Common: [--device N] [--time] [--loader host|device]
+// Common: [--device N] [--gpus N] [--time] [--loader host|device]
+//   --gpus N (N > 1): this one process drives devices 0..N-1 (arena_acct_init_devices): node ranges for
+//   `node`, job-id ranges for `job`; the host loader is used.  Same output for any N.
 //   --loader device (the default for `node` without -d): the PodList is parsed on the GPU
 //   (arena_load_json_device); host: the C++ loader + upload (always used for -d and for `job`,
 //   which need pod names and labels on the host).
@@ -54,7 +56,7 @@ int main(int argc, char **argv)
     const bool is_node = strcmp(argv[1], "node") == 0;
     bool details = false, timing = false;
     const char *loader = nullptr;
-    int device = 0;
+    int device = 0, gpus = 1;
     long long now = (long long)time(nullptr);
     const char *pods_path = nullptr, *nodes_path = nullptr, *jobs_path = nullptr, *tfjobs_path = nullptr,
                *releases_path = nullptr;
@@ -70,6 +72,7 @@ int main(int argc, char **argv)
         else if (a == "--tfjobs") { if (!need(&tfjobs_path)) return die("flag needs an argument: --tfjobs"); }
         else if (a == "--releases") { if (!need(&releases_path)) return die("flag needs an argument: --releases"); }
         else if (a == "--device") { if (!need(&tmp)) return die("flag needs an argument: --device"); device = atoi(tmp); }
+        else if (a == "--gpus") { if (!need(&tmp)) return die("flag needs an argument: --gpus"); gpus = atoi(tmp); if (gpus < 1 || gpus > 16) return die("--gpus must be 1..16"); }
         else if (a == "--loader") { if (!need(&loader)) return die("flag needs an argument: --loader"); }
         else if (a == "--now") { if (!need(&tmp)) return die("flag needs an argument: --now"); now = atoll(tmp); }
         else return die("unknown flag: " + a);
@@ -84,7 +87,7 @@ int main(int argc, char **argv)
     if (releases_path && !slurp(releases_path, releases)) return die(std::string("open ") + releases_path + ": no such file or directory");
 
     if (loader && strcmp(loader, "host") != 0 && strcmp(loader, "device") != 0) return die("--loader must be host or device");
-    const bool device_loader = is_node && !details && !(loader && strcmp(loader, "host") == 0);
+    const bool device_loader = is_node && !details && gpus == 1 && !(loader && strcmp(loader, "host") == 0);
     if (loader && strcmp(loader, "device") == 0 && !device_loader) return die("--loader device serves `top node` without -d only");
     if (device_loader) {
         if (arena_acct_init(device)) return die_arena();
@@ -124,9 +127,47 @@ int main(int argc, char **argv)
                         (!is_node && releases_path) ? releases.data() : nullptr, releases.size(), is_node ? 0 : 1, &host))
         return die_arena();
     auto t1 = std::chrono::steady_clock::now();
-    if (arena_acct_init(device)) return die_arena();
     arena_snapshot_view view;
     arena_host_snapshot_view(host, &view);
+    if (gpus > 1) {
+        // one process, several GPUs: the loops of top_node.go:109-118 / top_job.go:53-66 split by key range
+        std::vector<int> ids(gpus);
+        for (int i = 0; i < gpus; i++) ids[i] = i;
+        if (arena_acct_init_devices(gpus, ids.data())) return die_arena();
+        arena_multi_snapshot *ms = nullptr;
+        if (arena_multi_snapshot_upload(&view, is_node ? 0 : 1, &ms)) return die_arena();
+        auto t2 = std::chrono::steady_clock::now();
+        char *text = nullptr;
+        size_t len = 0;
+        if (is_node) {
+            std::vector<int64_t> total(view.n_nodes + 1), alloc(view.n_nodes + 1), pod_gpu(details ? view.n_pods + 1 : 1);
+            int64_t cluster[2];
+            if (arena_top_node_multi(ms, total.data(), alloc.data(), cluster, details ? pod_gpu.data() : nullptr)) return die_arena();
+            if (arena_format_top_node(host, total.data(), alloc.data(), details ? pod_gpu.data() : nullptr, details ? 1 : 0, &text, &len))
+                return die_arena();
+        } else {
+            const size_t J = view.n_jobs;
+            std::vector<int64_t> req(J + 1), alloc(J + 1);
+            std::vector<uint32_t> order(J + 1), latest(J + 1);
+            int64_t totals[2];
+            if (arena_top_job_multi(ms, req.data(), alloc.data(), order.data(), latest.data(), totals)) return die_arena();
+            if (arena_format_top_job(host, req.data(), alloc.data(), order.data(), latest.data(), now, &text, &len)) return die_arena();
+        }
+        auto t3 = std::chrono::steady_clock::now();
+        fwrite(text, 1, len, stdout);
+        arena_free_text(text);
+        if (timing) {
+            auto ms_ = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+            fprintf(stderr, "[arena-top] gpus=%d pods=%llu nodes=%llu jobs=%llu  load %.2f ms, init+upload %.2f ms, query+format %.2f ms\n",
+                    gpus, (unsigned long long)view.n_pods, (unsigned long long)view.n_nodes, (unsigned long long)view.n_jobs,
+                    ms_(t0, t1), ms_(t1, t2), ms_(t2, t3));
+        }
+        arena_multi_snapshot_free(ms);
+        arena_host_snapshot_free(host);
+        arena_acct_shutdown();
+        return 0;
+    }
+    if (arena_acct_init(device)) return die_arena();
     arena_snapshot *dev = nullptr;
     if (arena_snapshot_upload(&view, &dev)) return die_arena();
     auto t2 = std::chrono::steady_clock::now();

@@ -40,9 +40,24 @@ struct Context {
     int packed_ctas_per_sm = 0;
     bool cooperative = false;        // cudaLaunchCooperativeKernel available: the top-node launch zeroes node_alloc itself
     cudaStream_t stream = nullptr;
+    // one-shot host calls: staging snapshot and packed staging block, kept between calls
+    arena_snapshot *host_snap = nullptr;
+    void *packed_block = nullptr;
+    size_t packed_bytes = 0;
+    // multi-GPU totals exchange: this device's mailbox, the peers' mappings, the descriptor
+    PeerMailbox *my_box = nullptr;
+    PeerExchange *px = nullptr;                  // device copy of the descriptor
+    PeerExchange px_host{};
+    void *peer_mapped[kMaxPeers] = {};           // CUDA IPC mappings to close (none for in-process peers)
 };
 
-Context g_ctx;
+// One context per GPU this process drives.  Slot 0 is the device of arena_acct_init(); the others
+// exist after arena_acct_init_devices().  Every entry point works on the CALLING THREAD's current
+// slot (0 unless the multi-device driver selected another), so the single-device API is unchanged.
+constexpr int kMaxSlots = 16;
+Context g_ctxs[kMaxSlots];
+thread_local int t_slot = 0;
+inline Context &ctx() { return g_ctxs[t_slot]; }
 std::mutex g_mu, g_host_mu;
 std::atomic<uint64_t> g_launches{0};
 
@@ -67,6 +82,7 @@ size_t pad16(size_t n) { return (n + 15) & ~(size_t)15; }
 struct arena_snapshot {
     arena_snapshot_view v{};     // device pointers
     bool owns = false;
+    int slot = t_slot;           // the device context the handle lives on (the creating thread's current slot)
     void *block = nullptr;       // single allocation holding all owned columns
     size_t block_bytes = 0;
     Scratch *scratch = nullptr;  // per-handle: distinct handles may run concurrently
@@ -83,30 +99,23 @@ struct arena_snapshot {
     size_t d_out_bytes = 0;
 };
 
-static arena_snapshot *g_host_snap = nullptr;    // staging snapshot of arena_top_node_host
 // multi-GPU totals exchange (arena_peer_exchange_*): this rank's mailbox, the peers' mappings
-static PeerMailbox *g_my_box = nullptr;
-static PeerExchange *g_px = nullptr;             // device copy of the descriptor
-static PeerExchange g_px_host{};
-static void *g_peer_mapped[kMaxPeers] = {};
 // A few freed device blocks are kept for the next snapshot of about the same size: a polling caller
 // (load, query, free, again) otherwise pays cudaMalloc + cudaFree, which cost more than its kernels.
-struct FreeBlock { void *p; size_t bytes; cudaEvent_t idle; };   // idle: recorded on the library stream at release
+struct FreeBlock { void *p; size_t bytes; cudaEvent_t idle; int device; };   // idle: recorded on the library stream at release
 static FreeBlock g_free_blocks[8] = {};
 static std::mutex g_pool_mu;
-static void *g_packed_block = nullptr;           // staging of arena_top_node_host_packed: packed columns + tile sums
-static size_t g_packed_bytes = 0;
 
 extern "C" {
 
 uint64_t arena_kernel_launches(void) { return g_launches.load(); }
 
-int arena_acct_init(int device)
+// Binds the calling thread's current slot to `device` (g_mu held).
+static int init_current_slot(int device)
 {
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (g_ctx.ready) {
-        if (g_ctx.device == device) return ARENA_OK;
-        return fail(ARENA_E_INVALID, "already initialised on device %d", g_ctx.device);
+    if (ctx().ready) {
+        if (ctx().device == device) return ARENA_OK;
+        return fail(ARENA_E_INVALID, "already initialised on device %d", ctx().device);
     }
     int n = 0;
     CUDA_TRY(cudaGetDeviceCount(&n));
@@ -118,8 +127,8 @@ int arena_acct_init(int device)
     if (prop.major != 10 || prop.minor != 0)
         return fail(ARENA_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only and carries no "
                     "code for other architectures", device, prop.major, prop.minor);
-    g_ctx.device = device;
-    g_ctx.sm_count = prop.multiProcessorCount;
+    ctx().device = device;
+    ctx().sm_count = prop.multiProcessorCount;
     {
         int coop = 0;
         CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
@@ -127,42 +136,54 @@ int arena_acct_init(int device)
         // (1e8 pods: 456.3 + 2.6 us against 451.7 + 6.7; 1.25e7 pods: 68.4 + 2.6 against 64.7 + 6.6),
         // so the memset stays the default and the self-zeroing launch is opt-in.
         const char *on = getenv("ARENA_COOPERATIVE");
-        g_ctx.cooperative = coop != 0 && on && on[0] == '1';
+        ctx().cooperative = coop != 0 && on && on[0] == '1';
     }
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
     {
         int o1 = 0, o2 = 0, o3 = 0;
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, top_node_pods_kernel<true, false>, kThreads, 0));
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, top_node_pods_kernel<false, true>, kThreads, 0));
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, top_node_pods_kernel<true, true>, kThreads, 0));
-        g_ctx.pods_ctas_per_sm_min = std::min(std::min(o1, o2), std::min(o3, g_ctx.pods_ctas_per_sm));
+        ctx().pods_ctas_per_sm_min = std::min(std::min(o1, o2), std::min(o3, ctx().pods_ctas_per_sm));
     }
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_ctx.packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
-    if (g_ctx.pods_ctas_per_sm < 1 || g_ctx.jobs_ctas_per_sm < 1 || g_ctx.packed_ctas_per_sm < 1)
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
+    if (ctx().pods_ctas_per_sm < 1 || ctx().jobs_ctas_per_sm < 1 || ctx().packed_ctas_per_sm < 1)
         return fail(ARENA_E_CUDA, "kernel does not fit on an SM");
-    CUDA_TRY(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
-    g_ctx.ready = true;
+    CUDA_TRY(cudaStreamCreateWithFlags(&ctx().stream, cudaStreamNonBlocking));
+    ctx().ready = true;
     return ARENA_OK;
+}
+
+int arena_acct_init(int device)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    arena_internal::UseSlot first(0);
+    return init_current_slot(device);
 }
 
 void arena_acct_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_ctx.ready) return;
-    cudaSetDevice(g_ctx.device);
-    cudaStreamSynchronize(g_ctx.stream);
-    if (g_host_snap) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; }
-    if (g_packed_block) { cudaFree(g_packed_block); g_packed_block = nullptr; g_packed_bytes = 0; }
-    arena_peer_exchange_destroy();
-    arena_internal::device_pool_clear();
-    arena_internal::free_loader_workspace();
-    cudaStreamDestroy(g_ctx.stream);
-    g_ctx = Context{};
+    for (int slot = kMaxSlots - 1; slot >= 0; slot--) {
+        arena_internal::UseSlot use(slot);
+        if (!ctx().ready) continue;
+        cudaSetDevice(ctx().device);
+        cudaStreamSynchronize(ctx().stream);
+        if (ctx().host_snap) { arena_snapshot_free(ctx().host_snap); ctx().host_snap = nullptr; }
+        if (ctx().packed_block) { cudaFree(ctx().packed_block); ctx().packed_block = nullptr; ctx().packed_bytes = 0; }
+        arena_peer_exchange_destroy();
+        if (slot == 0) {
+            arena_internal::device_pool_clear();
+            arena_internal::free_loader_workspace();
+        }
+        cudaStreamDestroy(ctx().stream);
+        ctx() = Context{};
+    }
 }
 
-int arena_acct_device(void) { return g_ctx.ready ? g_ctx.device : (int)ARENA_E_NOT_INIT; }
-int arena_acct_sm_count(void) { return g_ctx.ready ? g_ctx.sm_count : (int)ARENA_E_NOT_INIT; }
+int arena_acct_device(void) { return g_ctxs[0].ready ? g_ctxs[0].device : (int)ARENA_E_NOT_INIT; }
+int arena_acct_sm_count(void) { return g_ctxs[0].ready ? g_ctxs[0].sm_count : (int)ARENA_E_NOT_INIT; }
 
 }  // extern "C"
 
@@ -170,8 +191,8 @@ namespace {
 
 int check_ready()
 {
-    if (!g_ctx.ready) return fail(ARENA_E_NOT_INIT, "arena_acct_init() has not been called");
-    cudaError_t e = cudaSetDevice(g_ctx.device);
+    if (!ctx().ready) return fail(ARENA_E_NOT_INIT, "arena_acct_init() has not been called");
+    cudaError_t e = cudaSetDevice(ctx().device);
     if (e != cudaSuccess) return fail(ARENA_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
     return ARENA_OK;
 }
@@ -201,7 +222,7 @@ int check_view(const arena_snapshot_view *v, bool device_ptrs, bool need_nodes =
 int alloc_common(arena_snapshot *s)
 {
     CUDA_TRY(arena_internal::device_alloc((void **)&s->scratch, sizeof(Scratch)));
-    CUDA_TRY(cudaMemsetAsync(s->scratch, 0, sizeof(Scratch), g_ctx.stream));
+    CUDA_TRY(cudaMemsetAsync(s->scratch, 0, sizeof(Scratch), ctx().stream));
     return ARENA_OK;
 }
 
@@ -215,13 +236,13 @@ int probe_grouping(arena_snapshot *s)
     if (P < 2 || !s->scratch) return ARENA_OK;
     const unsigned n = P - 1 < 4096 ? (unsigned)(P - 1) : 4096u;
     unsigned *flag = &s->scratch->ticket[3];
-    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), g_ctx.stream));
-    probe_grouping_kernel<<<16, 256, 0, g_ctx.stream>>>(s->v.pod_node, P, n, flag);
+    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), ctx().stream));
+    probe_grouping_kernel<<<16, 256, 0, ctx().stream>>>(s->v.pod_node, P, n, flag);
     count_launch();
     unsigned diff = 0;
-    CUDA_TRY(cudaMemcpyAsync(&diff, flag, sizeof(unsigned), cudaMemcpyDeviceToHost, g_ctx.stream));
-    CUDA_TRY(cudaStreamSynchronize(g_ctx.stream));
-    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), g_ctx.stream));
+    CUDA_TRY(cudaMemcpyAsync(&diff, flag, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx().stream));
+    CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(unsigned), ctx().stream));
     s->direct = diff * 4u > n;
     return ARENA_OK;
 }
@@ -229,7 +250,7 @@ int probe_grouping(arena_snapshot *s)
 int grid_for(u64 work_items, u64 items_per_cta, int ctas_per_sm)
 {
     u64 want = (work_items + items_per_cta - 1) / items_per_cta;
-    u64 cap = (u64)g_ctx.sm_count * (u64)ctas_per_sm;      // one resident wave: persistent CTAs
+    u64 cap = (u64)ctx().sm_count * (u64)ctas_per_sm;      // one resident wave: persistent CTAs
     if (cap > (u64)kMaxPartials / 2) cap = kMaxPartials / 2;   // finish_totals: half of the partials per ticket id
     if (want < 1) want = 1;
     return (int)(want < cap ? want : cap);
@@ -287,12 +308,12 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     if (prof) { g_prof.used += 3; CUDA_TRY(cudaEventRecord(pe[0], st)); }
     // node_alloc is accumulated with atomics: it starts from zero.  A memset in front of the launch,
     // or (ARENA_COOPERATIVE=1) the launch clears it itself: cooperative launch + one grid barrier.
-    bool self_zero = g_ctx.cooperative && v.n_nodes > 0 && (((uintptr_t)d_alloc) & 15) == 0;
-    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
-    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, g_ctx.pods_ctas_per_sm);
+    bool self_zero = ctx().cooperative && v.n_nodes > 0 && (((uintptr_t)d_alloc) & 15) == 0;
+    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm);
+    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, ctx().pods_ctas_per_sm);
     if (gn > gp) gp = gn;
     // all CTAs must be resident for the barrier: the details / ungrouped instantiations may fit fewer per SM
-    if (self_zero && (d_pod_gpu || s->direct) && gp > g_ctx.sm_count * g_ctx.pods_ctas_per_sm_min) self_zero = false;
+    if (self_zero && (d_pod_gpu || s->direct) && gp > ctx().sm_count * ctx().pods_ctas_per_sm_min) self_zero = false;
     if (v.n_nodes && !self_zero) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
     if (prof) CUDA_TRY(cudaEventRecord(pe[1], st));
 
@@ -313,7 +334,7 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     pa.node_total = d_total;
     pa.total_capacity = d_cluster;
     if (exchange) {
-        pa.px = g_px;
+        pa.px = ctx().px;
         pa.px_lag = exchange == 2 ? 1u : 0u;
     }
     pa.zero_alloc = self_zero ? 1u : 0u;
@@ -336,6 +357,10 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
 {
     const arena_snapshot_view &v = s->v;
     const u64 J = v.n_jobs;
+    if (J == 0) {                                               // no job at all (an empty job range of a multi-GPU cut)
+        CUDA_TRY(cudaMemsetAsync(d_totals, 0, 16, st));
+        return ARENA_OK;
+    }
     if (v.n_pods <= kSmallJobPods && J <= kSmallJobs) {         // a small cluster: one launch does it all
         static std::atomic<bool> smem_ok{false};            // (setting the attribute twice is harmless)
         if (!smem_ok.load(std::memory_order_acquire)) {
@@ -378,7 +403,7 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     pa.total_alloc = d_totals + 1;
     pa.scratch = s->scratch;
     // the top-node kernel's 32-bit fast tiles, keyed by job (generic tiles where a tile does not qualify)
-    top_node_pods_kernel<true, false, true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm), kThreads, 0, st>>>(pa);
+    top_node_pods_kernel<true, false, true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm), kThreads, 0, st>>>(pa);
     count_launch();
 
     if (v.n_pods) {
@@ -470,7 +495,7 @@ static int fill_snapshot(arena_snapshot *s, const arena_snapshot_view *h, bool j
     for (int i = 0; i < 10; i++) {
         dst[i] = p;
         if (sizes[i] && src[i]) {
-            const int crc = arena_internal::copy_to_device(p, src[i], sizes[i], g_ctx.stream);
+            const int crc = arena_internal::copy_to_device(p, src[i], sizes[i], ctx().stream);
             if (crc) return crc;
         }
         p += pad16(sizes[i]) + 16;
@@ -505,7 +530,7 @@ int arena_snapshot_upload(const arena_snapshot_view *h, arena_snapshot **out)
     if (!rc) rc = alloc_common(s);
     if (!rc) rc = probe_grouping(s);
     if (rc) { arena_snapshot_free(s); return rc; }
-    cudaError_t e = cudaStreamSynchronize(g_ctx.stream);     // host buffers may be reused on return
+    cudaError_t e = cudaStreamSynchronize(ctx().stream);     // host buffers may be reused on return
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "upload: %s", cudaGetErrorString(e)); }
     *out = s;
     return ARENA_OK;
@@ -526,7 +551,7 @@ int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **ou
     rc = alloc_common(s);
     if (!rc) rc = probe_grouping(s);
     if (rc) { arena_snapshot_free(s); return rc; }
-    cudaError_t e = cudaStreamSynchronize(g_ctx.stream);
+    cudaError_t e = cudaStreamSynchronize(ctx().stream);
     if (e != cudaSuccess) { arena_snapshot_free(s); return fail(ARENA_E_CUDA, "wrap: %s", cudaGetErrorString(e)); }
     *out = s;
     return ARENA_OK;
@@ -536,6 +561,57 @@ int arena_snapshot_wrap_device(const arena_snapshot_view *d, arena_snapshot **ou
 
 namespace arena_internal {
 
+int current_slot() { return t_slot; }
+void set_slot(int slot) { t_slot = slot; }
+
+int init_slot(int device)
+{
+    if (t_slot < 0 || t_slot >= kMaxSlots) return fail(ARENA_E_INVALID, "at most %d devices per process", kMaxSlots);
+    std::lock_guard<std::mutex> lk(g_mu);
+    return init_current_slot(device);
+}
+
+// Mailboxes of slots 0..n-1 wired to one another through peer access: a device pointer of slot j is
+// valid on slot i once cudaDeviceEnablePeerAccess(j) has been called with i current (one address
+// space per process).  Returns ARENA_E_INVALID (and leaves nothing behind) when some pair of devices
+// cannot reach each other; the caller then adds the per-device totals on the host.
+int peer_exchange_in_process(int n)
+{
+    if (n < 1 || n > kMaxPeers || n > kMaxSlots) return fail(ARENA_E_INVALID, "%d devices (at most %d)", n, kMaxPeers);
+    for (int i = 0; i < n; i++) {
+        if (!g_ctxs[i].ready) return fail(ARENA_E_NOT_INIT, "slot %d is not initialised", i);
+        if (g_ctxs[i].my_box) return fail(ARENA_E_INVALID, "peer exchange already created");
+    }
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) {
+            if (i == j || g_ctxs[i].device == g_ctxs[j].device) continue;
+            int can = 0;
+            CUDA_TRY(cudaDeviceCanAccessPeer(&can, g_ctxs[i].device, g_ctxs[j].device));
+            if (!can) return fail(ARENA_E_INVALID, "device %d cannot access device %d", g_ctxs[i].device, g_ctxs[j].device);
+        }
+    for (int i = 0; i < n; i++) {
+        CUDA_TRY(cudaSetDevice(g_ctxs[i].device));
+        for (int j = 0; j < n; j++) {
+            if (i == j || g_ctxs[i].device == g_ctxs[j].device) continue;
+            cudaError_t e = cudaDeviceEnablePeerAccess(g_ctxs[j].device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return fail(ARENA_E_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+        }
+        CUDA_TRY(cudaMalloc((void **)&g_ctxs[i].my_box, sizeof(PeerMailbox)));
+        CUDA_TRY(cudaMemset(g_ctxs[i].my_box, 0, sizeof(PeerMailbox)));
+    }
+    for (int i = 0; i < n; i++) {
+        CUDA_TRY(cudaSetDevice(g_ctxs[i].device));
+        g_ctxs[i].px_host = PeerExchange{};
+        g_ctxs[i].px_host.rank = i;
+        g_ctxs[i].px_host.world = n;
+        for (int j = 0; j < n; j++) g_ctxs[i].px_host.box[j] = g_ctxs[j].my_box;
+        CUDA_TRY(cudaMalloc((void **)&g_ctxs[i].px, sizeof(PeerExchange)));
+        CUDA_TRY(cudaMemcpy(g_ctxs[i].px, &g_ctxs[i].px_host, sizeof(PeerExchange), cudaMemcpyHostToDevice));
+    }
+    return ARENA_OK;
+}
+
 cudaError_t device_alloc(void **out, size_t bytes)
 {
     if (bytes < 256) bytes = 256;
@@ -543,17 +619,18 @@ cudaError_t device_alloc(void **out, size_t bytes)
         std::lock_guard<std::mutex> lk(g_pool_mu);
         int best = -1;
         for (int i = 0; i < 8; i++)
-            if (g_free_blocks[i].p && g_free_blocks[i].bytes >= bytes && g_free_blocks[i].bytes <= 2 * bytes + (1u << 20) &&
+            if (g_free_blocks[i].p && g_free_blocks[i].device == ctx().device && g_free_blocks[i].bytes >= bytes &&
+                g_free_blocks[i].bytes <= 2 * bytes + (1u << 20) &&
                 (best < 0 || g_free_blocks[i].bytes < g_free_blocks[best].bytes))
                 best = i;
         if (best >= 0) {
             *out = g_free_blocks[best].p;
             // whatever the library stream still had to do with the block comes first
             if (g_free_blocks[best].idle) {
-                cudaStreamWaitEvent(g_ctx.stream, g_free_blocks[best].idle, 0);
+                cudaStreamWaitEvent(ctx().stream, g_free_blocks[best].idle, 0);
                 cudaEventDestroy(g_free_blocks[best].idle);
             }
-            g_free_blocks[best] = FreeBlock{nullptr, 0, nullptr};
+            g_free_blocks[best] = FreeBlock{nullptr, 0, nullptr, -1};
             return cudaSuccess;
         }
     }
@@ -576,8 +653,8 @@ void device_release(void *p, size_t bytes)
     if (!p) return;
     if (bytes < 256) bytes = 256;
     cudaEvent_t idle = nullptr;
-    if (g_ctx.ready && cudaEventCreateWithFlags(&idle, cudaEventDisableTiming) == cudaSuccess) {
-        if (cudaEventRecord(idle, g_ctx.stream) != cudaSuccess) { cudaEventDestroy(idle); idle = nullptr; }
+    if (ctx().ready && cudaEventCreateWithFlags(&idle, cudaEventDisableTiming) == cudaSuccess) {
+        if (cudaEventRecord(idle, ctx().stream) != cudaSuccess) { cudaEventDestroy(idle); idle = nullptr; }
     }
     if (!idle) cudaDeviceSynchronize();            // no event to order by: fall back to waiting here
     std::lock_guard<std::mutex> lk(g_pool_mu);
@@ -592,7 +669,7 @@ void device_release(void *p, size_t bytes)
         if (g_free_blocks[slot].idle) cudaEventDestroy(g_free_blocks[slot].idle);
         cudaFree(g_free_blocks[slot].p);
     }
-    g_free_blocks[slot] = FreeBlock{p, bytes, idle};
+    g_free_blocks[slot] = FreeBlock{p, bytes, idle, ctx().device};
 }
 
 void device_pool_clear()
@@ -601,7 +678,7 @@ void device_pool_clear()
     for (FreeBlock &b : g_free_blocks) {
         if (b.idle) cudaEventDestroy(b.idle);
         if (b.p) cudaFree(b.p);
-        b = FreeBlock{nullptr, 0, nullptr};
+        b = FreeBlock{nullptr, 0, nullptr, -1};
     }
 }
 
@@ -609,8 +686,8 @@ int ready(cudaStream_t *stream, int *sm_count)
 {
     int rc = check_ready();
     if (rc) return rc;
-    if (stream) *stream = g_ctx.stream;
-    if (sm_count) *sm_count = g_ctx.sm_count;
+    if (stream) *stream = ctx().stream;
+    if (sm_count) *sm_count = ctx().sm_count;
     return ARENA_OK;
 }
 
@@ -650,6 +727,7 @@ int arena_snapshot_counts(const arena_snapshot *s, uint64_t counts_out[4])
 
 int arena_snapshot_download(const arena_snapshot *s, const arena_snapshot_view *o)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!s || !o) return fail(ARENA_E_INVALID, "snapshot or host_out is NULL");
@@ -663,15 +741,16 @@ int arena_snapshot_download(const arena_snapshot *s, const arena_snapshot_view *
         {v.pod_created, o->pod_created, P * 8}};
     for (const Col &c : cols)
         if (c.src && c.dst && c.bytes)
-            CUDA_TRY(cudaMemcpyAsync(const_cast<void *>(c.dst), c.src, c.bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
-    CUDA_TRY(cudaStreamSynchronize(g_ctx.stream));
+            CUDA_TRY(cudaMemcpyAsync(const_cast<void *>(c.dst), c.src, c.bytes, cudaMemcpyDeviceToHost, ctx().stream));
+    CUDA_TRY(cudaStreamSynchronize(ctx().stream));
     return ARENA_OK;
 }
 
 void arena_snapshot_free(arena_snapshot *s)
 {
     if (!s) return;
-    if (g_ctx.ready) cudaSetDevice(g_ctx.device);
+    arena_internal::UseSlot use(s->slot);
+    if (ctx().ready) cudaSetDevice(ctx().device);
     if (s->owns && s->block) arena_internal::device_release(s->block, s->block_bytes);
     if (s->scratch) arena_internal::device_release(s->scratch, sizeof(Scratch));
     if (s->job_req) cudaFree(s->job_req);
@@ -682,18 +761,20 @@ void arena_snapshot_free(arena_snapshot *s)
 int arena_top_node_device(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
                           int64_t *d_cluster, int64_t *d_pod_gpu, void *stream)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!s || !d_cluster) return fail(ARENA_E_INVALID, "snapshot or d_cluster is NULL");
     if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
     if (((uintptr_t)d_pod_gpu & 15) != 0) return fail(ARENA_E_INVALID, "d_pod_gpu is not 16-byte aligned");
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
     return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, (i64 *)d_pod_gpu, st);
 }
 
 int arena_top_node(const arena_snapshot *cs, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2],
                    int64_t *pod_gpu)
 {
+    arena_internal::UseSlot use(cs ? cs->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!cs || !cluster) return fail(ARENA_E_INVALID, "snapshot or cluster is NULL");
@@ -708,7 +789,7 @@ int arena_top_node(const arena_snapshot *cs, int64_t *node_total, int64_t *node_
     i64 *d_total = (i64 *)(base + 16);
     i64 *d_alloc = (i64 *)(base + 16 + pad16(N * 8));
     i64 *d_pg = pod_gpu ? (i64 *)(base + 16 + 2 * pad16(N * 8)) : nullptr;
-    cudaStream_t st = g_ctx.stream;
+    cudaStream_t st = ctx().stream;
     rc = launch_top_node(s, d_total, d_alloc, d_cluster, d_pg, st);
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(cluster, d_cluster, 16, cudaMemcpyDeviceToHost, st));
@@ -731,13 +812,13 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
     // One staging snapshot per process, kept between calls: a polling caller
     // pays for cudaMalloc only when its snapshot grows.  Calls are serialised.
     std::lock_guard<std::mutex> lk(g_host_mu);
-    if (!g_host_snap) {
-        g_host_snap = new (std::nothrow) arena_snapshot();
-        if (!g_host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
-        rc = alloc_common(g_host_snap);
-        if (rc) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; return rc; }
+    if (!ctx().host_snap) {
+        ctx().host_snap = new (std::nothrow) arena_snapshot();
+        if (!ctx().host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
+        rc = alloc_common(ctx().host_snap);
+        if (rc) { arena_snapshot_free(ctx().host_snap); ctx().host_snap = nullptr; return rc; }
     }
-    rc = fill_snapshot(g_host_snap, host, false);            // async H2D on the library stream ...
+    rc = fill_snapshot(ctx().host_snap, host, false);            // async H2D on the library stream ...
     if (rc) return rc;
     {   // grouping probe on the HOST column (no extra device round trip on this path)
         const u64 P = host->n_pods;
@@ -749,9 +830,9 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
                 diff += host->pod_node[p] != host->pod_node[p + 1];
             }
         }
-        g_host_snap->direct = diff * 4u > n;
+        ctx().host_snap->direct = diff * 4u > n;
     }
-    return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
+    return arena_top_node(ctx().host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
 }
 
 // summary straight from the packed columns: copy, one memset, one kernel, copy back
@@ -760,19 +841,19 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes, K = h->n_pieces;
     if (!h->node_ctr_begin || (K && !h->pieces)) return fail(ARENA_E_INVALID, "node_ctr_begin / pieces are NULL");
     const u64 gpu_bytes = h->ctr_bits == 4 ? (C + 1) / 2 : C;
-    cudaStream_t st = g_ctx.stream;
+    cudaStream_t st = ctx().stream;
     const size_t o_begin = 0, o_cbegin = o_begin + pad16((N + 1) * 4), o_meta = o_cbegin + pad16((N + 1) * 4),
                  o_gpu = o_meta + pad16(P + 4), o_pieces = o_gpu + pad16(gpu_bytes + 16), o_capv = o_pieces + pad16(K * 16),
                  o_caps = o_capv + pad16(N * 8), o_total = o_caps + pad16(N), o_alloc = o_total + pad16(N * 8),
                  o_cluster = o_alloc + pad16(N * 8), need = o_cluster + 16;
-    if (g_packed_bytes < need) {
-        if (g_packed_block) cudaFree(g_packed_block);
-        g_packed_block = nullptr;
-        g_packed_bytes = 0;
-        CUDA_TRY(cudaMalloc(&g_packed_block, need));
-        g_packed_bytes = need;
+    if (ctx().packed_bytes < need) {
+        if (ctx().packed_block) cudaFree(ctx().packed_block);
+        ctx().packed_block = nullptr;
+        ctx().packed_bytes = 0;
+        CUDA_TRY(cudaMalloc(&ctx().packed_block, need));
+        ctx().packed_bytes = need;
     }
-    char *pb = (char *)g_packed_block;
+    char *pb = (char *)ctx().packed_block;
     CUDA_TRY(cudaMemcpyAsync(pb + o_begin, h->node_pod_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(pb + o_cbegin, h->node_ctr_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
     int crc;
@@ -797,8 +878,8 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     a.node_alloc = (u64 *)(pb + o_alloc);
     a.total_capacity = (i64 *)(pb + o_cluster);
     a.total_alloc = (i64 *)(pb + o_cluster) + 1;
-    a.scratch = g_host_snap->scratch;
-    const int grid = grid_for(N + K, kWarps, g_ctx.packed_ctas_per_sm);
+    a.scratch = ctx().host_snap->scratch;
+    const int grid = grid_for(N + K, kWarps, ctx().packed_ctas_per_sm);
     if (h->ctr_bits == 4) top_node_packed_kernel<4><<<grid, kThreads, 0, st>>>(a);
     else top_node_packed_kernel<8><<<grid, kThreads, 0, st>>>(a);
     count_launch();
@@ -823,21 +904,21 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
     if (!h->node_pod_begin || (P && !h->pod_meta) || (C && !h->ctr_gpu) || (N && (!h->node_cap_val || !h->node_cap_scale)))
         return fail(ARENA_E_INVALID, "packed columns are NULL");
     std::lock_guard<std::mutex> lk(g_host_mu);
-    if (!g_host_snap) {
-        g_host_snap = new (std::nothrow) arena_snapshot();
-        if (!g_host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
-        rc = alloc_common(g_host_snap);
-        if (rc) { arena_snapshot_free(g_host_snap); g_host_snap = nullptr; return rc; }
+    if (!ctx().host_snap) {
+        ctx().host_snap = new (std::nothrow) arena_snapshot();
+        if (!ctx().host_snap) return fail(ARENA_E_NOMEM, "out of host memory");
+        rc = alloc_common(ctx().host_snap);
+        if (rc) { arena_snapshot_free(ctx().host_snap); ctx().host_snap = nullptr; return rc; }
     }
     if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);
     if (N && (!node_total || !node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
     if (!cluster) return fail(ARENA_E_INVALID, "cluster is NULL");
     if (!pod_gpu) return top_node_packed_native(h, node_total, node_alloc, cluster);
     const u64 pcn[3] = {P, C, N};
-    rc = fill_snapshot(g_host_snap, nullptr, false, pcn);       // wide columns: reserved, filled below on the device
+    rc = fill_snapshot(ctx().host_snap, nullptr, false, pcn);       // wide columns: reserved, filled below on the device
     if (rc) return rc;
-    const arena_snapshot_view &w = g_host_snap->v;
-    cudaStream_t st = g_ctx.stream;
+    const arena_snapshot_view &w = ctx().host_snap->v;
+    cudaStream_t st = ctx().stream;
 
     // packed staging: [node_pod_begin | pod_meta (word padded) | ctr_gpu (word padded) | tile sums]
     if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);
@@ -845,14 +926,14 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
     const u64 meta_words = (P + 3) / 4, gpu_words = (gpu_bytes + 3) / 4, tiles = (meta_words + 255) / 256;
     const size_t o_begin = 0, o_meta = o_begin + pad16((N + 1) * 4), o_gpu = o_meta + pad16(meta_words * 4 + 4),
                  o_tiles = o_gpu + pad16(gpu_words * 4 + 4), need = o_tiles + pad16((tiles + 1) * 4);
-    if (g_packed_bytes < need) {
-        if (g_packed_block) cudaFree(g_packed_block);
-        g_packed_block = nullptr;
-        g_packed_bytes = 0;
-        CUDA_TRY(cudaMalloc(&g_packed_block, need));
-        g_packed_bytes = need;
+    if (ctx().packed_bytes < need) {
+        if (ctx().packed_block) cudaFree(ctx().packed_block);
+        ctx().packed_block = nullptr;
+        ctx().packed_bytes = 0;
+        CUDA_TRY(cudaMalloc(&ctx().packed_block, need));
+        ctx().packed_bytes = need;
     }
-    char *pb = (char *)g_packed_block;
+    char *pb = (char *)ctx().packed_block;
     unsigned *d_begin = (unsigned *)(pb + o_begin), *d_meta = (unsigned *)(pb + o_meta), *d_gpu = (unsigned *)(pb + o_gpu),
              *d_tiles = (unsigned *)(pb + o_tiles);
     if (P & 3) CUDA_TRY(cudaMemsetAsync(d_meta + (meta_words - 1), 0, 4, st));       // the pods past P count nothing
@@ -885,8 +966,8 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
         count_launch();
     }
     CUDA_TRY(cudaGetLastError());
-    g_host_snap->direct = false;                                // grouped by construction
-    return arena_top_node(g_host_snap, node_total, node_alloc, cluster, pod_gpu);
+    ctx().host_snap->direct = false;                                // grouped by construction
+    return arena_top_node(ctx().host_snap, node_total, node_alloc, cluster, pod_gpu);
 }
 
 // ---- multi-GPU totals exchange inside the kernel (see PeerExchange in kernels.cuh) ----------
@@ -896,16 +977,16 @@ int arena_peer_exchange_create(int rank, int world, unsigned char handle_out[64]
     if (rc) return rc;
     if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !handle_out)
         return fail(ARENA_E_INVALID, "rank %d / world %d (at most %d ranks)", rank, world, kMaxPeers);
-    if (g_my_box) return fail(ARENA_E_INVALID, "peer exchange already created");
+    if (ctx().my_box) return fail(ARENA_E_INVALID, "peer exchange already created");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-    CUDA_TRY(cudaMalloc((void **)&g_my_box, sizeof(PeerMailbox)));
-    CUDA_TRY(cudaMemset(g_my_box, 0, sizeof(PeerMailbox)));
+    CUDA_TRY(cudaMalloc((void **)&ctx().my_box, sizeof(PeerMailbox)));
+    CUDA_TRY(cudaMemset(ctx().my_box, 0, sizeof(PeerMailbox)));
     cudaIpcMemHandle_t h;
-    CUDA_TRY(cudaIpcGetMemHandle(&h, g_my_box));
+    CUDA_TRY(cudaIpcGetMemHandle(&h, ctx().my_box));
     std::memcpy(handle_out, &h, 64);
-    g_px_host = PeerExchange{};
-    g_px_host.rank = rank;
-    g_px_host.world = world;
+    ctx().px_host = PeerExchange{};
+    ctx().px_host.rank = rank;
+    ctx().px_host.world = world;
     // (the step counter lives in the device copy of the descriptor and starts from 0 on every rank)
     return ARENA_OK;
 }
@@ -914,52 +995,54 @@ int arena_peer_exchange_connect(const unsigned char *handles)
 {
     int rc = check_ready();
     if (rc) return rc;
-    if (!g_my_box || !handles) return fail(ARENA_E_INVALID, "arena_peer_exchange_create() first");
-    for (int i = 0; i < g_px_host.world; i++) {
-        if (i == g_px_host.rank) { g_px_host.box[i] = g_my_box; continue; }
+    if (!ctx().my_box || !handles) return fail(ARENA_E_INVALID, "arena_peer_exchange_create() first");
+    for (int i = 0; i < ctx().px_host.world; i++) {
+        if (i == ctx().px_host.rank) { ctx().px_host.box[i] = ctx().my_box; continue; }
         cudaIpcMemHandle_t h;
         std::memcpy(&h, handles + 64 * i, 64);
         void *p = nullptr;
         CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
-        g_peer_mapped[i] = p;
-        g_px_host.box[i] = (PeerMailbox *)p;
+        ctx().peer_mapped[i] = p;
+        ctx().px_host.box[i] = (PeerMailbox *)p;
     }
-    CUDA_TRY(cudaMalloc((void **)&g_px, sizeof(PeerExchange)));
-    CUDA_TRY(cudaMemcpy(g_px, &g_px_host, sizeof(PeerExchange), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc((void **)&ctx().px, sizeof(PeerExchange)));
+    CUDA_TRY(cudaMemcpy(ctx().px, &ctx().px_host, sizeof(PeerExchange), cudaMemcpyHostToDevice));
     return ARENA_OK;
 }
 
 void arena_peer_exchange_destroy(void)
 {
-    if (g_ctx.ready) cudaSetDevice(g_ctx.device);
+    if (ctx().ready) cudaSetDevice(ctx().device);
     for (int i = 0; i < kMaxPeers; i++)
-        if (g_peer_mapped[i]) { cudaIpcCloseMemHandle(g_peer_mapped[i]); g_peer_mapped[i] = nullptr; }
-    if (g_px) { cudaFree(g_px); g_px = nullptr; }
-    if (g_my_box) { cudaFree(g_my_box); g_my_box = nullptr; }
-    g_px_host = PeerExchange{};
+        if (ctx().peer_mapped[i]) { cudaIpcCloseMemHandle(ctx().peer_mapped[i]); ctx().peer_mapped[i] = nullptr; }
+    if (ctx().px) { cudaFree(ctx().px); ctx().px = nullptr; }
+    if (ctx().my_box) { cudaFree(ctx().my_box); ctx().my_box = nullptr; }
+    ctx().px_host = PeerExchange{};
 }
 
 int arena_top_node_device_fused(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
                                 int64_t *d_cluster, void *stream)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
-    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!ctx().px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
     if (!s || !d_cluster) return fail(ARENA_E_INVALID, "snapshot or d_cluster is NULL");
     if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
     return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster, nullptr, st, 1);
 }
 
 int arena_top_node_device_posted(const arena_snapshot *s, int64_t *d_node_total, int64_t *d_node_alloc,
                                  int64_t *d_cluster_prev, void *stream)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
-    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!ctx().px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
     if (!s || !d_cluster_prev) return fail(ARENA_E_INVALID, "snapshot or d_cluster_prev is NULL");
     if (s->v.n_nodes && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
     return launch_top_node(s, (i64 *)d_node_total, (i64 *)d_node_alloc, (i64 *)d_cluster_prev, nullptr, st, 2);
 }
 
@@ -967,10 +1050,10 @@ int arena_peer_exchange_collect(int64_t *d_cluster, void *stream)
 {
     int rc = check_ready();
     if (rc) return rc;
-    if (!g_px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
+    if (!ctx().px) return fail(ARENA_E_INVALID, "arena_peer_exchange_connect() has not been called");
     if (!d_cluster) return fail(ARENA_E_INVALID, "d_cluster is NULL");
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
-    peer_collect_kernel<<<1, 32, 0, st>>>(g_px, (i64 *)d_cluster);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
+    peer_collect_kernel<<<1, 32, 0, st>>>(ctx().px, (i64 *)d_cluster);
     count_launch();
     CUDA_TRY(cudaGetLastError());
     return ARENA_OK;
@@ -978,28 +1061,30 @@ int arena_peer_exchange_collect(int64_t *d_cluster, void *stream)
 
 int arena_peer_exchange_timed_out(void)
 {
-    if (!g_px) return 0;
+    if (!ctx().px) return 0;
     PeerExchange h{};
-    if (cudaMemcpy(&h, g_px, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    if (cudaMemcpy(&h, ctx().px, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
     return (int)h.timed_out;
 }
 
 int arena_top_job_device(const arena_snapshot *cs, int64_t *d_job_req, int64_t *d_job_alloc,
                          uint32_t *d_job_order, uint32_t *d_job_latest, int64_t *d_totals, void *stream)
 {
+    arena_internal::UseSlot use(cs ? cs->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!cs || !d_totals) return fail(ARENA_E_INVALID, "snapshot or d_totals is NULL");
     arena_snapshot *s = const_cast<arena_snapshot *>(cs);
-    if (s->v.n_pods && !s->v.pod_job) return fail(ARENA_E_INVALID, "snapshot has no job columns");
+    if (s->v.n_pods && s->v.n_jobs && !s->v.pod_job) return fail(ARENA_E_INVALID, "snapshot has no job columns");
     if (s->v.n_jobs && (!d_job_req || !d_job_alloc || !d_job_order)) return fail(ARENA_E_INVALID, "job output buffers are NULL");
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
     return launch_top_job(s, (i64 *)d_job_req, (i64 *)d_job_alloc, d_job_order, d_job_latest, (i64 *)d_totals, st);
 }
 
 int arena_top_job(const arena_snapshot *cs, int64_t *job_req, int64_t *job_alloc, uint32_t *job_order,
                   uint32_t *job_latest, int64_t totals[2])
 {
+    arena_internal::UseSlot use(cs ? cs->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!cs || !totals) return fail(ARENA_E_INVALID, "snapshot or totals is NULL");
@@ -1016,7 +1101,7 @@ int arena_top_job(const arena_snapshot *cs, int64_t *job_req, int64_t *job_alloc
     i64 *d_alloc = (i64 *)(base + 16 + pad16(J * 8));
     unsigned *d_order = (unsigned *)(base + 16 + 2 * pad16(J * 8));
     unsigned *d_latest = (unsigned *)(base + 16 + 2 * pad16(J * 8) + pad16(J * 4));
-    cudaStream_t st = g_ctx.stream;
+    cudaStream_t st = ctx().stream;
     rc = launch_top_job(s, d_req, d_alloc, d_order, d_latest, d_totals, st);
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(totals, d_totals, 16, cudaMemcpyDeviceToHost, st));
@@ -1032,6 +1117,7 @@ int arena_top_job(const arena_snapshot *cs, int64_t *job_req, int64_t *job_alloc
 
 int arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!s || iters < 1 || !gbs_out) return fail(ARENA_E_INVALID, "bad argument");
@@ -1045,8 +1131,8 @@ int arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_
     cudaEvent_t e0, e1;
     CUDA_TRY(cudaEventCreate(&e0));
     CUDA_TRY(cudaEventCreate(&e1));
-    const int grid = g_ctx.sm_count * 8;
-    cudaStream_t st = g_ctx.stream;
+    const int grid = ctx().sm_count * 8;
+    cudaStream_t st = ctx().stream;
     stream_read_kernel<<<grid, kThreads, 0, st>>>(a);           // warm-up
     CUDA_TRY(cudaEventRecord(e0, st));
     for (int i = 0; i < iters; i++) { stream_read_kernel<<<grid, kThreads, 0, st>>>(a); count_launch(); }
@@ -1063,6 +1149,7 @@ int arena_calibrate_stream_read(const arena_snapshot *s, int iters, double *gbs_
 
 int arena_calibrate_stream_pattern(const arena_snapshot *s, int iters, double *gbs_out, double *ms_out)
 {
+    arena_internal::UseSlot use(s ? s->slot : arena_internal::current_slot());
     int rc = check_ready();
     if (rc) return rc;
     if (!s || iters < 1 || !gbs_out) return fail(ARENA_E_INVALID, "bad argument");
@@ -1076,8 +1163,8 @@ int arena_calibrate_stream_pattern(const arena_snapshot *s, int iters, double *g
     cudaEvent_t e0, e1;
     CUDA_TRY(cudaEventCreate(&e0));
     CUDA_TRY(cudaEventCreate(&e1));
-    const int grid = grid_for(v.n_pods, (u64)kWarps * kWarpPods, g_ctx.pods_ctas_per_sm);
-    cudaStream_t st = g_ctx.stream;
+    const int grid = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm);
+    cudaStream_t st = ctx().stream;
     stream_pattern_kernel<<<grid, kThreads, 0, st>>>(pa, (u64 *)s->scratch);
     CUDA_TRY(cudaEventRecord(e0, st));
     for (int i = 0; i < iters; i++) { stream_pattern_kernel<<<grid, kThreads, 0, st>>>(pa, (u64 *)s->scratch); count_launch(); }
@@ -1189,7 +1276,7 @@ std::atomic<NoAllocWork *> g_noalloc_ptr[kMaxDevices] = {};   // device address 
 // shadow of the symbol.
 int noalloc_work(NoAllocWork **out)
 {
-    const int dev = g_ctx.device;
+    const int dev = ctx().device;
     if (dev < 0 || dev >= kMaxDevices) return fail(ARENA_E_INVALID, "device ordinal %d not supported by the no-alloc path", dev);
     NoAllocWork *w = g_noalloc_ptr[dev].load(std::memory_order_acquire);
     if (!w) {                                    // two threads racing here resolve the same address
@@ -1228,7 +1315,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
     NoAllocWork *w = nullptr;
     rc = noalloc_work(&w);
     if (rc) return rc;
-    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
 
     // leftovers of an earlier (possibly interrupted) call must not leak into this one
     CUDA_TRY(cudaMemsetAsync(w->scratch.ticket, 0, sizeof(w->scratch.ticket), st));
@@ -1253,7 +1340,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
     pa.total_req = (i64 *)d_totals;
     pa.total_alloc = (i64 *)d_totals + 1;
     pa.scratch = &w->scratch;
-    job_pods_kernel<<<grid_for(P, (u64)kWarps * kWarpPods, g_ctx.jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
+    job_pods_kernel<<<grid_for(P, (u64)kWarps * kWarpPods, ctx().jobs_ctas_per_sm), kThreads, 0, st>>>(pa);
     count_launch();
 
     if (P) {
@@ -1294,7 +1381,7 @@ int arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, i
     i64 *dv = (i64 *)d;
     i64 *dout = (i64 *)(d + pad16(n * 8));
     signed char *ds = (signed char *)(d + 2 * pad16(n * 8));
-    cudaStream_t st = g_ctx.stream;
+    cudaStream_t st = ctx().stream;
     cudaError_t e = cudaMemcpyAsync(dv, val, n * 8, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(ds, scale, n, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) {

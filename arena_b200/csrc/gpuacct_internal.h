@@ -6,6 +6,24 @@
 
 namespace arena_internal {
 
+// The library keeps one device context per GPU ("slot"; slot 0 = arena_acct_init's device) and every
+// entry point works on the calling thread's current slot.  The multi-device driver (multi.cu) selects
+// a slot around the calls it makes for that device; entry points that take a snapshot handle select
+// the handle's own slot themselves.
+int current_slot();
+void set_slot(int slot);
+struct UseSlot {
+    int prev;
+    explicit UseSlot(int slot) : prev(current_slot()) { set_slot(slot); }
+    ~UseSlot() { set_slot(prev); }
+    UseSlot(const UseSlot &) = delete;
+    UseSlot &operator=(const UseSlot &) = delete;
+};
+// arena_acct_init for the current slot (used by arena_acct_init_devices).
+int init_slot(int device);
+// In-process totals exchange between the first n slots (peer access instead of CUDA IPC).
+int peer_exchange_in_process(int n);
+
 // arena_acct_init() done?  Selects the device and returns the library stream.
 int ready(cudaStream_t *stream, int *sm_count);
 void add_launches(unsigned long long n);

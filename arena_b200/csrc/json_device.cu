@@ -491,8 +491,9 @@ struct StageLane {
     cudaEvent_t sent[2] = {nullptr, nullptr};
     cudaStream_t stream = nullptr;
 };
-StageLane g_stage[kStageThreads];
-std::mutex g_stage_mu;
+constexpr int kStageDevices = 16;                 // lanes (streams, page-locked slots) are per device
+StageLane g_stage_all[kStageDevices][kStageThreads];
+std::mutex g_stage_mu_all[kStageDevices];
 
 bool is_pageable(const void *p)
 {
@@ -503,8 +504,11 @@ bool is_pageable(const void *p)
 
 int staged_upload(unsigned char *d_dst, const char *src, size_t len, cudaStream_t st, int device)
 {
-    std::lock_guard<std::mutex> lock(g_stage_mu);
-    for (StageLane &l : g_stage) {
+    if (device < 0 || device >= kStageDevices) return fail(ARENA_E_INVALID, "device ordinal %d beyond the staging lanes", device);
+    std::lock_guard<std::mutex> lock(g_stage_mu_all[device]);
+    StageLane *g_stage = g_stage_all[device];
+    for (int t = 0; t < kStageThreads; t++) {
+        StageLane &l = g_stage[t];
         if (l.stream) continue;
         CUDA_TRY(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
         for (int k = 0; k < 2; k++) {
@@ -572,14 +576,16 @@ void free_loader_workspace()
     std::lock_guard<std::mutex> lock(g_load_mu);
     for (Chunk &c : g_chunks) cudaFree(c.base);
     g_chunks.clear();
-    std::lock_guard<std::mutex> stage_lock(g_stage_mu);
-    for (StageLane &l : g_stage) {
-        for (int k = 0; k < 2; k++) {
-            if (l.slot[k]) cudaFreeHost(l.slot[k]);
-            if (l.sent[k]) cudaEventDestroy(l.sent[k]);
+    for (int d = 0; d < kStageDevices; d++) {
+        std::lock_guard<std::mutex> stage_lock(g_stage_mu_all[d]);
+        for (StageLane &l : g_stage_all[d]) {
+            for (int k = 0; k < 2; k++) {
+                if (l.slot[k]) cudaFreeHost(l.slot[k]);
+                if (l.sent[k]) cudaEventDestroy(l.sent[k]);
+            }
+            if (l.stream) cudaStreamDestroy(l.stream);
+            l = StageLane{};
         }
-        if (l.stream) cudaStreamDestroy(l.stream);
-        l = StageLane{};
     }
 }
 

@@ -260,6 +260,40 @@ class PinnedBuffer:
             pass
 
 
+class MultiSnapshot:
+    """`arena_multi_snapshot*`: ONE host snapshot cut into key ranges, one per device of this process
+    (init_devices first).  by_job=False: node ranges for top_node_multi; by_job=True: job-id ranges
+    for top_job_multi (rows grouped by job: HostSnapshot.regroup(by_job=True))."""
+
+    def __init__(self, host: HostSnapshot, by_job: bool = False):
+        h = C.c_void_p()
+        check(lib().arena_multi_snapshot_upload(C.byref(host.view), int(by_job), C.byref(h)))
+        self._h = h.value
+        self.host, self.by_job = host, by_job
+        self.n_pods, self.n_nodes, self.n_jobs = host.n_pods, host.n_nodes, host.n_jobs
+        n = C.c_int()
+        check(lib().arena_multi_snapshot_shards(self._h, C.byref(n), None, None))
+        self.n_shards = n.value
+        self.key_cut = np.zeros(self.n_shards + 1, np.uint64)
+        self.pod_cut = np.zeros(self.n_shards + 1, np.uint64)
+        check(lib().arena_multi_snapshot_shards(self._h, None, self.key_cut.ctypes.data, self.pod_cut.ctypes.data))
+
+    @property
+    def handle(self) -> int:
+        return self._h
+
+    def close(self) -> None:
+        if self._h:
+            lib().arena_multi_snapshot_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DeviceSnapshot:
     """`arena_snapshot*`: columns resident in HBM."""
 

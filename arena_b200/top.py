@@ -131,6 +131,25 @@ def top_node_device(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cluster,
         _stream_arg(stream)))
 
 
+def top_node_multi(snap, details: bool = False) -> TopNodeResult:
+    """arena_top_node_multi: every device of the process computes its node range; one table comes back."""
+    N, P = snap.n_nodes, snap.n_pods
+    total, alloc, cluster, pod_gpu = _outputs(N, P, details, None)
+    check(lib().arena_top_node_multi(snap.handle, _ptr(total), _ptr(alloc), cluster.ctypes.data,
+                                     pod_gpu.ctypes.data if details and P else None))
+    return TopNodeResult(total, alloc, cluster, pod_gpu)
+
+
+def top_job_multi(snap) -> TopJobResult:
+    """arena_top_job_multi: job-id ranges, one per device; merged ordering."""
+    J = snap.n_jobs
+    req, alloc = np.zeros(J, np.int64), np.zeros(J, np.int64)
+    order, latest = np.zeros(J, np.uint32), np.zeros(J, np.uint32)
+    totals = np.zeros(2, np.int64)
+    check(lib().arena_top_job_multi(snap.handle, _ptr(req), _ptr(alloc), _ptr(order), _ptr(latest), totals.ctypes.data))
+    return TopJobResult(req, alloc, order, latest, totals)
+
+
 def top_job(snap: DeviceSnapshot) -> TopJobResult:
     J = snap.n_jobs
     req = np.zeros(J, np.int64)

@@ -12,9 +12,10 @@
  *     arena_last_error() gives the message for the calling thread.
  *   - the caller owns every host buffer it passes; the library keeps no host
  *     pointer after a call returns (cgo pointer-passing rule).
- *   - one process drives one GPU (one rank per GPU under torchrun / one
- *     goroutine locked to an OS thread); every entry point makes its device
- *     current itself.
+ *   - arena_acct_init binds the process to one GPU (one rank per GPU under
+ *     torchrun / one goroutine locked to an OS thread); a process that wants
+ *     every GPU of the box uses arena_acct_init_devices and the *_multi entry
+ *     points instead.  Every entry point makes its device current itself.
  *   - one query in flight per snapshot handle.
  *   - int64 sums wrap modulo 2^64 exactly like Go's `+=`.
  *   - all columns must be 16-byte aligned (cudaMalloc / malloc'd arrays are).
@@ -215,6 +216,40 @@ typedef struct arena_packed_view {
 
 int  arena_top_node_host_packed(const arena_packed_view *host, int64_t *node_total,
                                 int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
+
+/*
+ * Single process, several GPUs.  The reference CLI is one process (cmd/arena/main.go:12-28); its
+ * `top node` loops over all nodes (top_node.go:109-118) and its `top job` over all releases
+ * (top_job.go:53-66).  These entry points split those loops over the devices of one process:
+ *
+ *   arena_acct_init_devices      binds dev_ids[0..n_dev-1]; dev_ids[0] also becomes the device of the
+ *                                single-device API above (as if arena_acct_init(dev_ids[0]) had been called)
+ *   arena_multi_snapshot_upload  cuts a HOST snapshot into n_dev contiguous key ranges of about equal
+ *                                pod count (arena_shard_plan: node ranges for `top node`, by_job = 0; job-id
+ *                                ranges for `top job`, by_job = 1 -- rows must be grouped by that key,
+ *                                arena_host_snapshot_regroup) and uploads one range per device
+ *   arena_top_node_multi         every device computes its node range at once; the per-node slices are
+ *                                disjoint and land side by side in node_total / node_alloc (HOST, [N]); the
+ *                                two cluster totals are traded inside the kernels over peer memory (peer
+ *                                access, no IPC) when every pair of devices can reach each other, else added
+ *                                on the host.  pod_gpu (HOST, [P], rows as uploaded) or NULL
+ *   arena_top_job_multi          every device answers `top job` for its job range; per-job tables are
+ *                                disjoint slices, totals are added, the per-device orderings are merged
+ *                                (requested desc, id asc); job_latest holds rows of the uploaded snapshot
+ * Results are bit-identical to the single-device entry points for any number of devices (integer sums).
+ * Calls on one multi snapshot must not overlap.  No reference counterpart beyond the loops named above.
+ */
+typedef struct arena_multi_snapshot arena_multi_snapshot;
+int  arena_acct_init_devices(int n_dev, const int *dev_ids);
+int  arena_acct_device_count(void);                       /* devices bound by arena_acct_init_devices, else 0 */
+int  arena_multi_snapshot_upload(const arena_snapshot_view *host, int by_job, arena_multi_snapshot **out);
+void arena_multi_snapshot_free(arena_multi_snapshot *m);
+/* n_shards, and the key / pod boundaries of the shards ([n_shards + 1] each; NULL pointers are skipped) */
+int  arena_multi_snapshot_shards(const arena_multi_snapshot *m, int *n_shards, uint64_t *key_cut, uint64_t *pod_cut);
+int  arena_top_node_multi(const arena_multi_snapshot *m, int64_t *node_total, int64_t *node_alloc,
+                          int64_t cluster[2], int64_t *pod_gpu);
+int  arena_top_job_multi(const arena_multi_snapshot *m, int64_t *job_req, int64_t *job_alloc,
+                         uint32_t *job_order, uint32_t *job_latest, int64_t totals[2]);
 
 /*
  * `arena top job`: TrainingJob.RequestedGPU / AllocatedGPU (job_info.go:51-70,

@@ -20,3 +20,74 @@ def test_every_rank_agrees_with_the_oracle(gpu):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert p.returncode == 0, (p.stdout[-3000:], p.stderr[-3000:])
     assert "FAIL" not in p.stdout and p.stdout.count("OK") >= 12
+
+
+def _n_devices():
+    import torch
+    return min(8, torch.cuda.device_count())
+
+
+def test_single_process_multi_device_top_node(gpu):
+    """arena_acct_init_devices + arena_top_node_multi: one process drives every GPU of the box (one on
+    a one-GPU box), node-range shards, against the C oracle: uniform, skewed, and the details view."""
+    import numpy as np
+    from oracle import cref
+    gpu.init_devices(list(range(_n_devices())))
+    assert gpu.lib().arena_acct_device_count() == _n_devices()
+    for skewed, seed in ((False, 41), (True, 5)):
+        host = gpu.HostSnapshot.synth(3_000_000, 30_000, seed=seed, skewed=skewed)
+        tot, alloc, cl, pg = cref.top_node_columnar(host.cols, True)
+        ms = gpu.MultiSnapshot(host)
+        assert ms.n_shards == _n_devices() and int(ms.key_cut[-1]) == host.n_nodes and int(ms.pod_cut[-1]) == host.n_pods
+        for details in (False, True, False):
+            r = gpu.top_node_multi(ms, details=details)
+            assert np.array_equal(r.node_total, tot) and np.array_equal(r.node_alloc, alloc) and np.array_equal(r.cluster, cl)
+            if details:
+                assert np.array_equal(r.pod_gpu, pg)
+        ms.close()
+    # the single-device API still works beside it (slot 0)
+    r = gpu.top_node(gpu.DeviceSnapshot.upload(host))
+    assert np.array_equal(r.node_alloc, alloc)
+
+
+def test_single_process_multi_device_top_job(gpu):
+    import numpy as np
+    from oracle import cref
+    gpu.init_devices(list(range(_n_devices())))
+    J = 70_000
+    host = gpu.HostSnapshot.synth(2_000_000, 20_000, seed=43, n_jobs=J)
+    req, alloc, latest, totals = cref.top_job_columnar(host.cols, J)
+    byjob = host.regroup(by_job=True)
+    src = byjob.pod_order()
+    ms = gpu.MultiSnapshot(byjob, by_job=True)
+    for _ in range(2):
+        r = gpu.top_job_multi(ms)
+        assert np.array_equal(r.job_req, req) and np.array_equal(r.job_alloc, alloc) and np.array_equal(r.totals, totals)
+        has = latest != 0xFFFFFFFF
+        assert np.array_equal(r.job_latest != 0xFFFFFFFF, has) and np.array_equal(src[r.job_latest[has]], latest[has])
+        assert np.array_equal(r.job_order, np.lexsort((np.arange(J), -req)).astype(np.uint32))
+    ms.close()
+    # a node-range snapshot is refused by the job call, and the other way round
+    ms = gpu.MultiSnapshot(host)
+    with pytest.raises(gpu.ArenaError):
+        gpu.top_job_multi(ms)
+    ms.close()
+
+
+def test_cli_gpus_flag_prints_the_golden_text(gpu):
+    """arena-top node|job --gpus N: the config-1 fixture through the multi-device path, byte for byte."""
+    cli = os.path.join(ROOT, "arena_b200", "arena-top")
+    g = os.path.join(ROOT, "tests", "golden", "config1")
+    n = str(max(1, _n_devices()))
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_fixtures as MF
+    for args, want in (
+        (["node", "--gpus", n, "--loader", "host"], "expected_top_node.txt"),
+        (["node", "-d", "--gpus", n], "expected_top_node_details.txt"),
+        (["job", "--gpus", n, "--jobs", os.path.join(g, "jobs.json"), "--tfjobs", os.path.join(g, "tfjobs.json"),
+          "--releases", os.path.join(g, "helm_list.txt"), "--now", str(MF.NOW)], "expected_top_job.txt"),
+    ):
+        p = subprocess.run([cli, *args, "--pods", os.path.join(g, "pods.json"), "--nodes", os.path.join(g, "nodes.json")],
+                           capture_output=True, text=True, timeout=120)
+        assert p.returncode == 0, p.stdout + p.stderr
+        assert p.stdout == open(os.path.join(g, want)).read(), args

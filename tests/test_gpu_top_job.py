@@ -54,3 +54,12 @@ def test_top_job_large_sort(gpu):
     """More jobs than one shared-memory sort tile: exercises the global merge steps."""
     host = gpu.HostSnapshot.synth(400_000, 1_000, seed=8, n_jobs=70_000)
     _check_job(gpu, host)
+
+
+def test_top_job_without_any_job(gpu):
+    """Pods but no job (what an empty job range of a multi-GPU cut looks like): zero totals, no fault."""
+    host = gpu.HostSnapshot.synth(5_000, 50, seed=9)
+    dev = gpu.DeviceSnapshot.upload(host)
+    res = gpu.top_job(dev)
+    assert res.totals.tolist() == [0, 0] and len(res.job_req) == 0
+    dev.close()
