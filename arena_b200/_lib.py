@@ -125,6 +125,8 @@ _SIGS = [
                                        C.POINTER(C.c_int32), C.POINTER(C.c_int)]),
     ("arena_format_top_node", C.c_int, [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
     ("arena_format_top_job", C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int64, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
+    ("arena_job_order_by_age", C.c_int, [_VP, _VP]),
+    ("arena_format_job_list", C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int64, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
     ("arena_free_text", None, [_VP]),
     ("arena_synth_snapshot", C.c_int, [C.POINTER(SynthParams), C.POINTER(_VP)]),
     ("arena_shard_plan", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.c_int, _VP, _VP]),

@@ -5,6 +5,8 @@
 //   arena-top node [-d|--details] --pods PODLIST.json --nodes NODELIST.json
 //   arena-top job  --pods PODLIST.json --nodes NODELIST.json --jobs JOBLIST.json
 //                  [--tfjobs TFJOBLIST.json] --releases HELM_LIST.txt [--now UNIX_SECONDS]
+//   arena-top list (same flags as job): `arena list` (cmd/arena/commands/list.go:16-80), the other
+//                  user of the job printer: ordered by age, no GPU columns
 // Common: [--device N] [--gpus N] [--time] [--loader host|device]
 //   --gpus N (N > 1): this one process drives devices 0..N-1 (arena_acct_init_devices): node ranges for
 //   `node`, job-id ranges for `job`; the host loader is used.  Same output for any N.
@@ -49,11 +51,11 @@ static int die_arena() { return die(arena_last_error()); }
 
 int main(int argc, char **argv)
 {
-    if (argc < 2 || (strcmp(argv[1], "node") != 0 && strcmp(argv[1], "job") != 0)) {
+    if (argc < 2 || (strcmp(argv[1], "node") != 0 && strcmp(argv[1], "job") != 0 && strcmp(argv[1], "list") != 0)) {
         fputs(kTopLong, stdout);
         return argc < 2 ? 0 : 1;
     }
-    const bool is_node = strcmp(argv[1], "node") == 0;
+    const bool is_node = strcmp(argv[1], "node") == 0, is_list = strcmp(argv[1], "list") == 0;
     bool details = false, timing = false;
     const char *loader = nullptr;
     int device = 0, gpus = 1;
@@ -78,7 +80,7 @@ int main(int argc, char **argv)
         else return die("unknown flag: " + a);
     }
     if (!pods_path || !nodes_path) return die("--pods and --nodes are required");
-    if (!is_node && !releases_path) return die("top job needs --releases (the output of `helm list`)");
+    if (!is_node && !releases_path) return die(is_list ? "list needs --releases (the output of `helm list`)" : "top job needs --releases (the output of `helm list`)");
     std::string pods, nodes, jobs, tfjobs, releases;
     if (!slurp(pods_path, pods)) return die(std::string("open ") + pods_path + ": no such file or directory");
     if (!slurp(nodes_path, nodes)) return die(std::string("open ") + nodes_path + ": no such file or directory");
@@ -151,7 +153,8 @@ int main(int argc, char **argv)
             std::vector<uint32_t> order(J + 1), latest(J + 1);
             int64_t totals[2];
             if (arena_top_job_multi(ms, req.data(), alloc.data(), order.data(), latest.data(), totals)) return die_arena();
-            if (arena_format_top_job(host, req.data(), alloc.data(), order.data(), latest.data(), now, &text, &len)) return die_arena();
+            if (is_list && arena_job_order_by_age(host, order.data())) return die_arena();
+            if (arena_format_job_list(host, req.data(), alloc.data(), order.data(), latest.data(), now, is_list ? 0 : 1, &text, &len)) return die_arena();
         }
         auto t3 = std::chrono::steady_clock::now();
         fwrite(text, 1, len, stdout);
@@ -186,7 +189,8 @@ int main(int argc, char **argv)
         std::vector<uint32_t> order(J + 1), latest(J + 1);
         int64_t totals[2];
         if (arena_top_job(dev, req.data(), alloc.data(), order.data(), latest.data(), totals)) return die_arena();
-        if (arena_format_top_job(host, req.data(), alloc.data(), order.data(), latest.data(), now, &text, &len)) return die_arena();
+        if (is_list && arena_job_order_by_age(host, order.data())) return die_arena();
+        if (arena_format_job_list(host, req.data(), alloc.data(), order.data(), latest.data(), now, is_list ? 0 : 1, &text, &len)) return die_arena();
     }
     auto t3 = std::chrono::steady_clock::now();
     fwrite(text, 1, len, stdout);

@@ -34,6 +34,7 @@ struct JobMeta {
     bool tf_found = false;
     std::string tf_status;     // "SUCCEEDED" | "FAILED" | "PENDING" | "RUNNING"
     uint32_t tf_chief_row = 0xFFFFFFFFu;   // row of the chief pod (worker index 0), or none
+    bool start_present = false;   // status.startTime is not nil (what makeTrainingJobOrderdByAge tests)
     bool has_start = false;    // status.startTime present and not the zero time
     int64_t start_unix = 0;
 };

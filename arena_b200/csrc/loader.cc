@@ -641,6 +641,7 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
             }
             if (const Value *t = child(st, "startTime")) {
                 jm.start_unix = parse_time(t, "status.startTime");
+                jm.start_present = true;
                 jm.has_start = jm.start_unix != kZeroTimeUnix;
             }
             job_of_release.emplace(name, (uint32_t)h->jobs.size());

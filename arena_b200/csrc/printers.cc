@@ -242,16 +242,44 @@ int arena_format_top_node(const arena_host_snapshot *h, const int64_t *node_tota
     return emit(w.flush(), text_out, len_out);
 }
 
+// makeTrainingJobOrderdByAge (trainer.go:39-66): Less(i, j) = StartTime(i) == nil, else false when
+// StartTime(j) == nil, else StartTime(i).After(StartTime(j)) -- jobs without a start time first, then
+// the newest first.  sort.Sort leaves ties open (and two nil times compare "less" both ways): they
+// are broken by ascending job id here, as for `top job`.  Host work: the keys are job metadata.
+int arena_job_order_by_age(const arena_host_snapshot *h, uint32_t *job_order)
+{
+    if (!h) return fail(ARENA_E_INVALID, "host snapshot is NULL");
+    const size_t J = h->jobs.size();
+    if (J && !job_order) return fail(ARENA_E_INVALID, "job_order is NULL");
+    for (size_t j = 0; j < J; j++) job_order[j] = (uint32_t)j;
+    std::stable_sort(job_order, job_order + J, [&](uint32_t a, uint32_t b) {
+        const JobMeta &x = h->jobs[a], &y = h->jobs[b];
+        if (x.start_present != y.start_present) return !x.start_present;
+        if (!x.start_present) return false;
+        return x.start_unix > y.start_unix;
+    });
+    return ARENA_OK;
+}
+
 int arena_format_top_job(const arena_host_snapshot *h, const int64_t *job_req, const int64_t *job_alloc,
                          const uint32_t *job_order, const uint32_t *job_latest, int64_t now_unix, char **text_out,
                          size_t *len_out)
 {
+    return arena_format_job_list(h, job_req, job_alloc, job_order, job_latest, now_unix, 1, text_out, len_out);
+}
+
+int arena_format_job_list(const arena_host_snapshot *h, const int64_t *job_req, const int64_t *job_alloc,
+                          const uint32_t *job_order, const uint32_t *job_latest, int64_t now_unix, int display_gpu,
+                          char **text_out, size_t *len_out)
+{
     if (!h || !text_out) return fail(ARENA_E_INVALID, "NULL argument");
     const size_t J = h->jobs.size();
-    if (J && (!job_req || !job_alloc || !job_order || !job_latest)) return fail(ARENA_E_INVALID, "job table is NULL");
+    if (J && (!job_order || !job_latest)) return fail(ARENA_E_INVALID, "job table is NULL");
+    if (J && display_gpu && (!job_req || !job_alloc)) return fail(ARENA_E_INVALID, "job table is NULL");
     TabWriter w(2);
     uint64_t total_alloc = 0, total_req = 0;
-    w.write("NAME\tSTATUS\tTRAINER\tAGE\tNODE\tGPU(Requests)\tGPU(Allocated)\n");
+    if (display_gpu) w.write("NAME\tSTATUS\tTRAINER\tAGE\tNODE\tGPU(Requests)\tGPU(Allocated)\n");
+    else w.write("NAME\tSTATUS\tTRAINER\tAGE\tNODE\n");                       // list.go:92-96
     for (size_t k = 0; k < J; k++) {
         const uint32_t j = job_order[k];
         if (j >= J) return fail(ARENA_E_INVALID, "job_order[%zu] = %u out of range", k, j);
@@ -275,11 +303,16 @@ int arena_format_top_job(const arena_host_snapshot *h, const int64_t *job_req, c
             if (status == "RUNNING") host_ip = pod_ip;
         }
         const std::string age = jm.has_start ? short_human_duration(now_unix - jm.start_unix) : "0s";
+        if (!display_gpu) {                                       // list.go:112-118
+            w.write(jm.name + "\t" + status + "\t" + upper(jm.trainer) + "\t" + age + "\t" + host_ip + "\n");
+            continue;
+        }
         total_alloc += (uint64_t)job_alloc[j];
         total_req += (uint64_t)job_req[j];
         w.write(jm.name + "\t" + status + "\t" + upper(jm.trainer) + "\t" + age + "\t" + host_ip + "\t" + i64s(job_req[j]) +
                 "\t" + i64s(job_alloc[j]) + "\n");
     }
+    if (!display_gpu) return emit(w.flush(), text_out, len_out);
     w.write("\n");
     w.write("\n");
     w.write("Total Allocated GPUs of Training Job:\n");

@@ -200,6 +200,17 @@ def format_top_job(host: HostSnapshot, res: TopJobResult, now_unix: int) -> str:
     return _take_text(p, n)
 
 
+def format_job_list(host: HostSnapshot, res: TopJobResult, now_unix: int) -> str:
+    """`arena list` (list.go:16-80): the jobs of `res` ordered by age (arena_job_order_by_age) and
+    printed without the GPU columns (arena_format_job_list, display_gpu = 0)."""
+    order = np.zeros(host.n_jobs, np.uint32)
+    check(lib().arena_job_order_by_age(host.handle, _ptr(order)))
+    p, n = C.c_void_p(), C.c_size_t()
+    check(lib().arena_format_job_list(host.handle, None, None, _ptr(order), _ptr(res.job_latest), now_unix, 0,
+                                      C.byref(p), C.byref(n)))
+    return _take_text(p, n)
+
+
 def top_job_device_noalloc(tensors: dict, n_jobs: int, d_req, d_alloc, d_order, d_latest, d_totals,
                            stream: Optional[int] = None, n_pods: Optional[int] = None) -> None:
     """arena_top_job_device_noalloc: `top job` over CUDA tensors holding the

@@ -152,6 +152,19 @@ int  arena_format_top_job(const arena_host_snapshot *h, const int64_t *job_req,
                           const int64_t *job_alloc, const uint32_t *job_order,
                           const uint32_t *job_latest, int64_t now_unix,
                           char **text_out, size_t *len_out);
+/* `arena list` (cmd/arena/commands/list.go:16-80): the other user of the same printer.
+ * arena_job_order_by_age is makeTrainingJobOrderdByAge (trainer.go:39-66): jobs without
+ * status.startTime first, then the newest start first (ties, which sort.Sort leaves open, by
+ * ascending job id) -- host work, the keys are job metadata.  arena_format_job_list is
+ * displayTrainingJobList(jobs, displayGPU) (list.go:82-133): display_gpu != 0 is the `top job`
+ * text above; display_gpu == 0 prints NAME STATUS TRAINER AGE NODE only (job_req / job_alloc may be
+ * NULL), but STATUS and NODE still need job_latest -- the latest-pod rule the `top job` kernels
+ * evaluate -- for mpijob and standalonejob rows. */
+int  arena_job_order_by_age(const arena_host_snapshot *h, uint32_t *job_order);
+int  arena_format_job_list(const arena_host_snapshot *h, const int64_t *job_req,
+                           const int64_t *job_alloc, const uint32_t *job_order,
+                           const uint32_t *job_latest, int64_t now_unix, int display_gpu,
+                           char **text_out, size_t *len_out);
 void arena_free_text(char *text);
 
 /* ---- synthetic snapshots --------------------------------------------------- */

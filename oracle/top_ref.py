@@ -468,7 +468,15 @@ def _latest_scan(cands: List[Pod]) -> Pod:
     return job_pod
 
 
-def top_job(podlist_json, joblist_json, tfjoblist_json, helm_text, now: int):
+def job_list(podlist_json, joblist_json, tfjoblist_json, helm_text, now: int):
+    """`arena list` (cmd/arena/commands/list.go:16-80): the same jobs as `top job`, ordered by
+    makeTrainingJobOrderdByAge (trainer.go:39-66: a job without status.startTime first, then newest
+    start first; ties, which sort.Sort leaves open, by name) and printed without the GPU columns and
+    totals (displayTrainingJobList(jobs, false), list.go:82-133).  Returns (text, [names])."""
+    return top_job(podlist_json, joblist_json, tfjoblist_json, helm_text, now, display_gpu=False)
+
+
+def top_job(podlist_json, joblist_json, tfjoblist_json, helm_text, now: int, display_gpu: bool = True):
     """Returns (text, rows) with rows = [(name, trainer, requested, allocated)] in print order."""
     all_pods = [Pod(p) for p in (loads(podlist_json).get("items") or [])]            # acquireAllPods: every phase
     all_jobs = [JobObj(j) for j in (loads(joblist_json).get("items") or [])] if joblist_json else []
@@ -512,11 +520,20 @@ def top_job(podlist_json, joblist_json, tfjoblist_json, helm_text, now: int):
                     chief = item
                 pods.append(item)
             jobs.append(TrainingJob(name, "tfjob", obj, pods, chief))
-    # orderedTrainingJob: requested desc; ties (unspecified in the reference) by name
-    jobs.sort(key=lambda j: (-j.requested_gpu(), j.name))
+    if display_gpu:
+        # orderedTrainingJob: requested desc; ties (unspecified in the reference) by name
+        jobs.sort(key=lambda j: (-j.requested_gpu(), j.name))
+    else:
+        # orderedTrainingJobByAge.Less (trainer.go:45-53): nil StartTime sorts first, then After()
+        jobs.sort(key=lambda j: (0, 0, j.name) if j.obj.start_time() is None else (1, -j.obj.start_time(), j.name))
 
     w = TabWriter()
     total_alloc = total_req = 0
+    if not display_gpu:
+        w.write("NAME\tSTATUS\tTRAINER\tAGE\tNODE\n")
+        for j in jobs:
+            w.write(f"{j.name}\t{j.get_status()}\t{j.trainer.upper()}\t{j.age(now)}\t{j.host_ip_of_chief()}\n")
+        return w.flush(), [j.name for j in jobs]
     w.write("NAME\tSTATUS\tTRAINER\tAGE\tNODE\tGPU(Requests)\tGPU(Allocated)\n")
     rows = []
     for j in jobs:

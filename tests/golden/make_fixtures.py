@@ -260,6 +260,8 @@ def main():
     jtext, rows = top_ref.top_job(P, json.dumps(joblist), json.dumps(tfjoblist), helm, NOW)
     open(os.path.join(d, "expected_top_job.txt"), "w").write(jtext)
     dump([list(r) for r in rows], os.path.join(d, "expected_job_table.json"))
+    ltext, _ = top_ref.job_list(P, json.dumps(joblist), json.dumps(tfjoblist), helm, NOW)
+    open(os.path.join(d, "expected_list.txt"), "w").write(ltext)
     print(text)
     print(jtext)
     return 0

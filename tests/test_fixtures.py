@@ -174,6 +174,36 @@ def test_timestamp_tie_survives_node_grouping(built):
     assert format_top_job(h, TopJobResult(req, alloc, order, latest, totals), MF.NOW) == rd("expected_top_job.txt", "r")
 
 
+def test_arena_list_text(built):
+    """`arena list` (list.go:16-80): age order, no GPU columns.  The golden text, then variants where
+    a job has no status.startTime (sorts first, AGE 0s) and where two jobs start in the same second
+    (tie by name), product printer against the Python oracle."""
+    from arena_b200 import HostSnapshot, TopJobResult, format_job_list
+    docs = [rd("pods.json"), rd("nodes.json"), rd("jobs.json"), rd("tfjobs.json"), rd("helm_list.txt")]
+
+    def product(jobs_json, tfjobs_json):
+        h = HostSnapshot.from_json(docs[0], docs[1], jobs_json, tfjobs_json, docs[4], group_by_job=True)
+        req, alloc, latest, totals = cref.top_job_columnar(h.cols, h.n_jobs)
+        return format_job_list(h, TopJobResult(req, alloc, np.zeros(h.n_jobs, np.uint32), latest, totals), MF.NOW)
+
+    assert product(docs[2], docs[3]) == rd("expected_list.txt", "r")
+    jobs, tfjobs = json.loads(docs[2]), json.loads(docs[3])
+    for mutate in ("drop", "null", "same"):
+        j2, t2 = json.loads(docs[2]), json.loads(docs[3])
+        if mutate == "drop":
+            del [it for it in j2["items"] if it["metadata"]["name"] == "hvd"][0]["status"]["startTime"]
+        elif mutate == "null":
+            t2["items"][0]["status"]["startTime"] = None
+        else:
+            for it in j2["items"]:
+                it["status"]["startTime"] = "2018-07-23T01:00:00Z"
+        J2, T2 = json.dumps(j2).encode(), json.dumps(t2).encode()
+        want, _ = top_ref.job_list(docs[0], J2, T2, docs[4], MF.NOW)
+        assert product(J2, T2) == want, mutate
+        if mutate != "same":
+            assert "0s" in want.splitlines()[1], "a job without a start time is listed first"
+
+
 def test_loader_rejects_what_the_reference_decode_rejects(built):
     from arena_b200 import ArenaError, HostSnapshot
     nodes = rd("nodes.json")

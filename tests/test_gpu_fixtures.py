@@ -69,6 +69,21 @@ def test_config2_top_job_full_size(gpu):
     assert gpu.format_top_node(h2, r) == ntext
 
 
+def test_arena_list_on_the_gpu(gpu):
+    """`arena list`: STATUS / NODE of mpijob and standalonejob rows come from the latest-pod rule the
+    `top job` kernels evaluate; config 1 golden text and the generated config 2 against the oracle."""
+    h = gpu.HostSnapshot.from_json(rd("pods.json"), rd("nodes.json"), rd("jobs.json"), rd("tfjobs.json"),
+                                   rd("helm_list.txt"), group_by_job=True)
+    res = gpu.top_job(gpu.DeviceSnapshot.upload(h))
+    assert gpu.format_job_list(h, res, MF.NOW) == rd("expected_list.txt", "r")
+    podlist, nodelist, joblist, tfjoblist, helm = MF.config2(n_pods_target=3000, n_nodes=300)
+    P, N, Jl, T = (json.dumps(x).encode() for x in (podlist, nodelist, joblist, tfjoblist))
+    want, _ = top_ref.job_list(P, Jl, T, helm, MF.NOW)
+    h = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=False)
+    res = gpu.top_job(gpu.DeviceSnapshot.upload(h))
+    assert gpu.format_job_list(h, res, MF.NOW) == want
+
+
 def run_cli(*args):
     p = subprocess.run([CLI, *args], capture_output=True, text=True, timeout=120)
     return p.returncode, p.stdout, p.stderr
@@ -87,6 +102,9 @@ def test_cli_matches_expected_output(gpu):
                            os.path.join(D, "tfjobs.json"), "--releases", os.path.join(D, "helm_list.txt"), "--now",
                            str(MF.NOW), "--time")
     assert rc == 0 and out == rd("expected_top_job.txt", "r") and "[arena-top]" in err
+    rc, out, err = run_cli("list", "--pods", pods, "--nodes", nodes, "--jobs", os.path.join(D, "jobs.json"), "--tfjobs",
+                           os.path.join(D, "tfjobs.json"), "--releases", os.path.join(D, "helm_list.txt"), "--now", str(MF.NOW))
+    assert rc == 0 and out == rd("expected_list.txt", "r")
 
 
 def test_cli_parses_an_api_server_shaped_list_on_the_gpu(gpu, tmp_path):
