@@ -711,8 +711,10 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
     uint32_t *pod_job = h->c_pod_job.as<uint32_t>();
     uint8_t *pod_role = h->c_pod_role.as<uint8_t>();
     int64_t *pod_created = h->c_pod_created.as<int64_t>();
-    std::memcpy(h->c_node_cap_val.ptr, cap_val.data(), N * 8);
-    std::memcpy(h->c_node_cap_scale.ptr, cap_scale.data(), N);
+    if (N) {                                 // (an empty vector's data() may be null: not a memcpy argument)
+        std::memcpy(h->c_node_cap_val.ptr, cap_val.data(), N * 8);
+        std::memcpy(h->c_node_cap_scale.ptr, cap_scale.data(), N);
+    }
     h->pod_names.resize(P); h->pod_namespaces.resize(P); h->pod_host_ip.resize(P);
     std::vector<uint32_t> row_of(P);
     size_t c = 0;
