@@ -85,6 +85,10 @@ _SIGS = [
     ("arena_top_node_device_posted", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_peer_exchange_collect", C.c_int, [_VP, _VP]),
     ("arena_top_node_host_packed", C.c_int, [C.POINTER(PackedView), _VP, _VP, _VP, _VP]),
+    ("arena_snapshot_upload_packed", C.c_int, [C.POINTER(PackedView), C.POINTER(_VP)]),
+    ("arena_packed_device_free", None, [_VP]),
+    ("arena_packed_device_bytes", C.c_int, [_VP, C.POINTER(C.c_uint64)]),
+    ("arena_top_node_packed_device", C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     ("arena_acct_init_devices", C.c_int, [C.c_int, C.POINTER(C.c_int)]),
     ("arena_acct_device_count", C.c_int, []),
     ("arena_multi_snapshot_upload", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.POINTER(_VP)]),

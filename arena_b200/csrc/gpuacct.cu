@@ -44,6 +44,9 @@ struct Context {
     arena_snapshot *host_snap = nullptr;
     void *packed_block = nullptr;
     size_t packed_bytes = 0;
+    bool pipe_ready = false;                     // streams / events of the pipelined packed one-shot call
+    cudaStream_t pipe_stream[2] = {nullptr, nullptr};
+    cudaEvent_t pipe_event[17] = {};
     // multi-GPU totals exchange: this device's mailbox, the peers' mappings, the descriptor
     PeerMailbox *my_box = nullptr;
     PeerExchange *px = nullptr;                  // device copy of the descriptor
@@ -835,62 +838,243 @@ int arena_top_node_host(const arena_snapshot_view *host, int64_t *node_total, in
     return arena_top_node(ctx().host_snap, node_total, node_alloc, cluster, pod_gpu);   // ... kernels + D2H behind it
 }
 
-// summary straight from the packed columns: copy, one memset, one kernel, copy back
-static int top_node_packed_native(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2])
+// ---- the packed columns on the device ------------------------------------------------------------
+// One block: [node_pod_begin | node_ctr_begin | pod_meta | ctr_gpu | pieces | cap_val | cap_scale |
+// node_total | node_alloc | cluster pairs], every column padded so that the kernel's whole-word reads
+// past a column's end stay inside the block.
+constexpr int kPackedChunks = 8;                 // pipeline depth of the one-shot call
+struct PackedLayout {
+    u64 P, C, N, K, gpu_bytes;
+    unsigned bits;
+    size_t o_begin, o_cbegin, o_meta, o_gpu, o_pieces, o_capv, o_caps, o_total, o_alloc, o_cluster, need;
+};
+struct arena_packed_device {     // device-resident packed snapshot (arena_snapshot_upload_packed)
+    PackedLayout L{};
+    void *block = nullptr;
+    Scratch *scratch = nullptr;
+    int slot = t_slot;
+};
+static PackedLayout packed_layout(const arena_packed_view *h)
 {
-    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes, K = h->n_pieces;
-    if (!h->node_ctr_begin || (K && !h->pieces)) return fail(ARENA_E_INVALID, "node_ctr_begin / pieces are NULL");
-    const u64 gpu_bytes = h->ctr_bits == 4 ? (C + 1) / 2 : C;
-    cudaStream_t st = ctx().stream;
-    const size_t o_begin = 0, o_cbegin = o_begin + pad16((N + 1) * 4), o_meta = o_cbegin + pad16((N + 1) * 4),
-                 o_gpu = o_meta + pad16(P + 4), o_pieces = o_gpu + pad16(gpu_bytes + 16), o_capv = o_pieces + pad16(K * 16),
-                 o_caps = o_capv + pad16(N * 8), o_total = o_caps + pad16(N), o_alloc = o_total + pad16(N * 8),
-                 o_cluster = o_alloc + pad16(N * 8), need = o_cluster + 16;
-    if (ctx().packed_bytes < need) {
-        if (ctx().packed_block) cudaFree(ctx().packed_block);
-        ctx().packed_block = nullptr;
-        ctx().packed_bytes = 0;
-        CUDA_TRY(cudaMalloc(&ctx().packed_block, need));
-        ctx().packed_bytes = need;
-    }
-    char *pb = (char *)ctx().packed_block;
-    CUDA_TRY(cudaMemcpyAsync(pb + o_begin, h->node_pod_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(pb + o_cbegin, h->node_ctr_begin, (N + 1) * 4, cudaMemcpyHostToDevice, st));
-    int crc;
-    if ((crc = arena_internal::copy_to_device(pb + o_meta, h->pod_meta, P, st))) return crc;
-    if ((crc = arena_internal::copy_to_device(pb + o_gpu, h->ctr_gpu, gpu_bytes, st))) return crc;
-    if (K) CUDA_TRY(cudaMemcpyAsync(pb + o_pieces, h->pieces, K * 16, cudaMemcpyHostToDevice, st));
-    if (N) {
-        CUDA_TRY(cudaMemcpyAsync(pb + o_capv, h->node_cap_val, N * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(pb + o_caps, h->node_cap_scale, N, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemsetAsync(pb + o_alloc, 0, N * 8, st));
-    }
+    PackedLayout L{};
+    L.P = h->n_pods; L.C = h->n_containers; L.N = h->n_nodes; L.K = h->n_pieces; L.bits = h->ctr_bits;
+    L.gpu_bytes = h->ctr_bits == 4 ? (L.C + 1) / 2 : L.C;
+    L.o_begin = 0;
+    L.o_cbegin = L.o_begin + pad16((L.N + 1) * 4);
+    L.o_meta = L.o_cbegin + pad16((L.N + 1) * 4);
+    L.o_gpu = L.o_meta + pad16(L.P + 16);
+    L.o_pieces = L.o_gpu + pad16(L.gpu_bytes + 16);
+    L.o_capv = L.o_pieces + pad16(L.K * 16);
+    L.o_caps = L.o_capv + pad16(L.N * 8);
+    L.o_total = L.o_caps + pad16(L.N);
+    L.o_alloc = L.o_total + pad16(L.N * 8);
+    L.o_cluster = L.o_alloc + pad16(L.N * 8);
+    L.need = L.o_cluster + 16 * kPackedChunks;
+    return L;
+}
+static PackedArgs packed_args(const PackedLayout &L, char *pb, Scratch *scratch)
+{
     PackedArgs a{};
-    a.N = N; a.n_pieces = K;
-    a.node_pod_begin = (const unsigned *)(pb + o_begin);
-    a.node_ctr_begin = (const unsigned *)(pb + o_cbegin);
-    a.meta = (const unsigned char *)(pb + o_meta);
-    a.gpu = (const unsigned char *)(pb + o_gpu);
-    a.pieces = (const uint4 *)(pb + o_pieces);
-    a.cap_val = (const i64 *)(pb + o_capv);
-    a.cap_scale = (const signed char *)(pb + o_caps);
-    a.node_total = (i64 *)(pb + o_total);
-    a.node_alloc = (u64 *)(pb + o_alloc);
-    a.total_capacity = (i64 *)(pb + o_cluster);
-    a.total_alloc = (i64 *)(pb + o_cluster) + 1;
-    a.scratch = ctx().host_snap->scratch;
-    const int grid = grid_for(N + K, kWarps, ctx().packed_ctas_per_sm);
-    if (h->ctr_bits == 4) top_node_packed_kernel<4><<<grid, kThreads, 0, st>>>(a);
+    a.N = L.N; a.n_pieces = L.K;
+    a.node_pod_begin = (const unsigned *)(pb + L.o_begin);
+    a.node_ctr_begin = (const unsigned *)(pb + L.o_cbegin);
+    a.meta = (const unsigned char *)(pb + L.o_meta);
+    a.gpu = (const unsigned char *)(pb + L.o_gpu);
+    a.pieces = (const uint4 *)(pb + L.o_pieces);
+    a.cap_val = (const i64 *)(pb + L.o_capv);
+    a.cap_scale = (const signed char *)(pb + L.o_caps);
+    a.node_total = (i64 *)(pb + L.o_total);
+    a.node_alloc = (u64 *)(pb + L.o_alloc);
+    a.total_capacity = (i64 *)(pb + L.o_cluster);
+    a.total_alloc = (i64 *)(pb + L.o_cluster) + 1;
+    a.scratch = scratch;
+    return a;
+}
+static int packed_launch(const PackedArgs &a, unsigned bits, cudaStream_t st)
+{
+    const int grid = grid_for((a.N - a.n_lo) + (a.n_pieces - a.piece_lo), kWarps * 2, ctx().packed_ctas_per_sm);
+    if (bits == 4) top_node_packed_kernel<4><<<grid, kThreads, 0, st>>>(a);
     else top_node_packed_kernel<8><<<grid, kThreads, 0, st>>>(a);
     count_launch();
     CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaMemcpyAsync(cluster, pb + o_cluster, 16, cudaMemcpyDeviceToHost, st));
-    if (N) {
-        CUDA_TRY(cudaMemcpyAsync(node_total, pb + o_total, N * 8, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaMemcpyAsync(node_alloc, pb + o_alloc, N * 8, cudaMemcpyDeviceToHost, st));
-    }
-    CUDA_TRY(cudaStreamSynchronize(st));
     return ARENA_OK;
+}
+static int check_packed(const arena_packed_view *h)
+{
+    if (!h) return fail(ARENA_E_INVALID, "packed view is NULL");
+    const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
+    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
+    if (!h->node_pod_begin || (P && !h->pod_meta) || (C && !h->ctr_gpu) || (N && (!h->node_cap_val || !h->node_cap_scale)))
+        return fail(ARENA_E_INVALID, "packed columns are NULL");
+    if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);
+    if (!h->node_ctr_begin || (h->n_pieces && !h->pieces)) return fail(ARENA_E_INVALID, "node_ctr_begin / pieces are NULL");
+    return ARENA_OK;
+}
+
+// Summary straight from the packed columns, pipelined: the node range is cut into kPackedChunks
+// pieces of about equal pod count; chunk k's columns go up on the copy stream while chunk k-1 is
+// summed on the compute stream and chunk k-2's slice of the table comes down on the download
+// stream (PCIe is full duplex), so the kernel and the download hide behind the upload.  Every
+// chunk leaves its own pair of totals; the host adds them (wrapping, like Go's +=).
+static int top_node_packed_native(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2])
+{
+    const PackedLayout L = packed_layout(h);
+    const u64 P = L.P, N = L.N, K = L.K;
+    if (ctx().packed_bytes < L.need) {
+        if (ctx().packed_block) cudaFree(ctx().packed_block);
+        ctx().packed_block = nullptr;
+        ctx().packed_bytes = 0;
+        CUDA_TRY(cudaMalloc(&ctx().packed_block, L.need));
+        ctx().packed_bytes = L.need;
+    }
+    char *pb = (char *)ctx().packed_block;
+    if (!ctx().pipe_ready) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx().pipe_stream[0], cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx().pipe_stream[1], cudaStreamNonBlocking));
+        for (int k = 0; k < 2 * kPackedChunks + 1; k++) CUDA_TRY(cudaEventCreateWithFlags(&ctx().pipe_event[k], cudaEventDisableTiming));
+        ctx().pipe_ready = true;
+    }
+    cudaStream_t up = ctx().stream, run = ctx().pipe_stream[0], down = ctx().pipe_stream[1];
+    // chunk boundaries in nodes: equal shares of the rows (a node is never cut)
+    const int chunks = (P >= (4u << 20) && N >= (u64)kPackedChunks) ? kPackedChunks : 1;
+    u64 cut[kPackedChunks + 1];
+    cut[0] = 0;
+    for (int k = 1; k < chunks; k++) {
+        const uint32_t target = (uint32_t)(P * (u64)k / (u64)chunks);
+        u64 n = std::upper_bound(h->node_pod_begin, h->node_pod_begin + N + 1, target) - h->node_pod_begin;
+        n = n ? n - 1 : 0;
+        cut[k] = std::max(cut[k - 1], std::min(n, N));
+    }
+    cut[chunks] = N;
+    const uint4 *pieces = (const uint4 *)h->pieces;
+    int64_t part[kPackedChunks][2];
+    int crc;
+    if (K) CUDA_TRY(cudaMemcpyAsync(pb + L.o_pieces, h->pieces, K * 16, cudaMemcpyHostToDevice, up));
+    CUDA_TRY(cudaEventRecord(ctx().pipe_event[2 * kPackedChunks], up));      // what earlier calls left on the library stream
+    CUDA_TRY(cudaStreamWaitEvent(run, ctx().pipe_event[2 * kPackedChunks], 0));
+    u64 piece_lo = 0;
+    for (int k = 0; k < chunks; k++) {
+        const u64 n0 = cut[k], n1 = cut[k + 1];
+        // rows and containers of the chunk; the rows that name no node (after node N - 1) are never read
+        const u64 r0 = h->node_pod_begin[n0], r1 = h->node_pod_begin[n1];
+        const u64 c0 = h->node_ctr_begin[n0], c1 = h->node_ctr_begin[n1];
+        const u64 g0 = L.bits == 4 ? c0 / 2 : c0, g1 = L.bits == 4 ? (c1 + 1) / 2 : c1;
+        // (one entry past the chunk: the kernel reads begin[n + 1])
+        CUDA_TRY(cudaMemcpyAsync(pb + L.o_begin + n0 * 4, h->node_pod_begin + n0, (n1 - n0 + 1) * 4, cudaMemcpyHostToDevice, up));
+        CUDA_TRY(cudaMemcpyAsync(pb + L.o_cbegin + n0 * 4, h->node_ctr_begin + n0, (n1 - n0 + 1) * 4, cudaMemcpyHostToDevice, up));
+        if (r1 > r0 && (crc = arena_internal::copy_to_device(pb + L.o_meta + r0, h->pod_meta + r0, r1 - r0, up))) return crc;
+        if (g1 > g0 && (crc = arena_internal::copy_to_device(pb + L.o_gpu + g0, h->ctr_gpu + g0, g1 - g0, up))) return crc;
+        if (n1 > n0) {
+            CUDA_TRY(cudaMemcpyAsync(pb + L.o_capv + n0 * 8, h->node_cap_val + n0, (n1 - n0) * 8, cudaMemcpyHostToDevice, up));
+            CUDA_TRY(cudaMemcpyAsync(pb + L.o_caps + n0, h->node_cap_scale + n0, n1 - n0, cudaMemcpyHostToDevice, up));
+        }
+        CUDA_TRY(cudaEventRecord(ctx().pipe_event[2 * k], up));
+        // compute
+        CUDA_TRY(cudaStreamWaitEvent(run, ctx().pipe_event[2 * k], 0));
+        u64 piece_hi = piece_lo;
+        while (piece_hi < K && pieces[piece_hi].x < n1) piece_hi++;
+        if (piece_hi > piece_lo) CUDA_TRY(cudaMemsetAsync(pb + L.o_alloc + n0 * 8, 0, (n1 - n0) * 8, run));   // big nodes are summed with atomics
+        PackedArgs a = packed_args(L, pb, ctx().host_snap->scratch);
+        a.n_lo = n0; a.N = n1; a.piece_lo = piece_lo; a.n_pieces = piece_hi;
+        a.total_capacity = (i64 *)(pb + L.o_cluster) + 2 * k;
+        a.total_alloc = a.total_capacity + 1;
+        if ((crc = packed_launch(a, L.bits, run))) return crc;
+        piece_lo = piece_hi;
+        CUDA_TRY(cudaEventRecord(ctx().pipe_event[2 * k + 1], run));
+    }
+    // downloads, issued after every upload and launch is queued: a copy into pageable memory blocks the host
+    for (int k = 0; k < chunks; k++) {
+        const u64 n0 = cut[k], n1 = cut[k + 1];
+        CUDA_TRY(cudaStreamWaitEvent(down, ctx().pipe_event[2 * k + 1], 0));
+        CUDA_TRY(cudaMemcpyAsync(part[k], pb + L.o_cluster + 16 * k, 16, cudaMemcpyDeviceToHost, down));
+        if (n1 > n0) {
+            CUDA_TRY(cudaMemcpyAsync(node_total + n0, pb + L.o_total + n0 * 8, (n1 - n0) * 8, cudaMemcpyDeviceToHost, down));
+            CUDA_TRY(cudaMemcpyAsync(node_alloc + n0, pb + L.o_alloc + n0 * 8, (n1 - n0) * 8, cudaMemcpyDeviceToHost, down));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(down));
+    CUDA_TRY(cudaStreamSynchronize(up));
+    u64 tc = 0, ta = 0;
+    for (int k = 0; k < chunks; k++) { tc += (u64)part[k][0]; ta += (u64)part[k][1]; }
+    cluster[0] = (int64_t)tc;
+    cluster[1] = (int64_t)ta;
+    return ARENA_OK;
+}
+
+int arena_snapshot_upload_packed(const arena_packed_view *h, arena_packed_device **out)
+{
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    rc = check_packed(h);
+    if (rc) return rc;
+    arena_packed_device *p = new (std::nothrow) arena_packed_device();
+    if (!p) return fail(ARENA_E_NOMEM, "out of host memory");
+    p->L = packed_layout(h);
+    const PackedLayout &L = p->L;
+    cudaError_t e = arena_internal::device_alloc(&p->block, L.need);
+    if (e == cudaSuccess) e = arena_internal::device_alloc((void **)&p->scratch, sizeof(Scratch));
+    if (e != cudaSuccess) {
+        arena_packed_device_free(p);
+        return fail(e == cudaErrorMemoryAllocation ? ARENA_E_NOMEM : ARENA_E_CUDA, "cudaMalloc(%zu): %s", L.need, cudaGetErrorString(e));
+    }
+    cudaStream_t st = ctx().stream;
+    char *pb = (char *)p->block;
+    rc = ARENA_OK;
+    auto up = [&](size_t off, const void *src, size_t bytes) {
+        if (!rc && bytes) rc = arena_internal::copy_to_device(pb + off, src, bytes, st);
+    };
+    if (cudaMemsetAsync(p->scratch, 0, sizeof(Scratch), st) != cudaSuccess) rc = fail(ARENA_E_CUDA, "cudaMemsetAsync failed");
+    up(L.o_begin, h->node_pod_begin, (L.N + 1) * 4);
+    up(L.o_cbegin, h->node_ctr_begin, (L.N + 1) * 4);
+    up(L.o_meta, h->pod_meta, L.P);
+    up(L.o_gpu, h->ctr_gpu, L.gpu_bytes);
+    up(L.o_pieces, h->pieces, L.K * 16);
+    up(L.o_capv, h->node_cap_val, L.N * 8);
+    up(L.o_caps, h->node_cap_scale, L.N);
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(ARENA_E_CUDA, "packed upload failed");
+    if (rc) { arena_packed_device_free(p); return rc; }
+    *out = p;
+    return ARENA_OK;
+}
+
+void arena_packed_device_free(arena_packed_device *p)
+{
+    if (!p) return;
+    arena_internal::UseSlot use(p->slot);
+    if (ctx().ready) cudaSetDevice(ctx().device);
+    if (p->block) arena_internal::device_release(p->block, p->L.need);
+    if (p->scratch) arena_internal::device_release(p->scratch, sizeof(Scratch));
+    delete p;
+}
+
+int arena_packed_device_bytes(const arena_packed_device *p, uint64_t *read_write_bytes)
+{
+    if (!p || !read_write_bytes) return fail(ARENA_E_INVALID, "NULL argument");
+    const PackedLayout &L = p->L;
+    // what one summary launch reads and writes: both offset columns, one byte per pod, the value
+    // column, the pieces, the capacities; the two table columns and the totals out
+    *read_write_bytes = 8 * (L.N + 1) + L.P + L.gpu_bytes + 16 * L.K + 9 * L.N + 16 * L.N + 16;
+    return ARENA_OK;
+}
+
+int arena_top_node_packed_device(const arena_packed_device *p, int64_t *d_node_total, int64_t *d_node_alloc,
+                                 int64_t *d_cluster, void *stream)
+{
+    arena_internal::UseSlot use(p ? p->slot : arena_internal::current_slot());
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!p || !d_cluster) return fail(ARENA_E_INVALID, "packed snapshot or d_cluster is NULL");
+    if (p->L.N && (!d_node_total || !d_node_alloc)) return fail(ARENA_E_INVALID, "node output buffers are NULL");
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
+    if (p->L.K) CUDA_TRY(cudaMemsetAsync(d_node_alloc, 0, p->L.N * 8, st));      // nodes cut into pieces meet in atomics
+    PackedArgs a = packed_args(p->L, (char *)p->block, p->scratch);
+    a.node_total = (i64 *)d_node_total;
+    a.node_alloc = (u64 *)d_node_alloc;
+    a.total_capacity = (i64 *)d_cluster;
+    a.total_alloc = (i64 *)d_cluster + 1;
+    return packed_launch(a, p->L.bits, st);
 }
 
 int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, int64_t *node_alloc, int64_t cluster[2],
@@ -898,11 +1082,9 @@ int arena_top_node_host_packed(const arena_packed_view *h, int64_t *node_total, 
 {
     int rc = check_ready();
     if (rc) return rc;
-    if (!h) return fail(ARENA_E_INVALID, "packed view is NULL");
+    rc = check_packed(h);
+    if (rc) return rc;
     const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
-    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
-    if (!h->node_pod_begin || (P && !h->pod_meta) || (C && !h->ctr_gpu) || (N && (!h->node_cap_val || !h->node_cap_scale)))
-        return fail(ARENA_E_INVALID, "packed columns are NULL");
     std::lock_guard<std::mutex> lk(g_host_mu);
     if (!ctx().host_snap) {
         ctx().host_snap = new (std::nothrow) arena_snapshot();

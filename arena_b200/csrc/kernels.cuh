@@ -1337,7 +1337,8 @@ namespace arena {
 constexpr unsigned kBigNodePods = 2048;
 
 struct PackedArgs {
-    u64 N, n_pieces;
+    u64 N, n_pieces;                                    // this launch covers nodes [n_lo, N) and pieces [piece_lo, n_pieces)
+    u64 n_lo, piece_lo;
     const unsigned *node_pod_begin, *node_ctr_begin;    // [N+1]
     const unsigned char *meta, *gpu;
     const uint4 *pieces;                                // {node, first row, end row, first container}
@@ -1376,56 +1377,102 @@ __device__ __forceinline__ unsigned packed_values_sum(const unsigned char *gpu, 
     return s;
 }
 
-// masked GPU sum of the rows [lo, hi) whose containers start at c0; the same value in every lane
+// Masked GPU sum of the rows [lo, hi) whose containers start at value index c0, by one HALF-WARP
+// (16 lanes, `hmask` = its lanes): the same value in every lane of the half.  A lane owns EIGHT
+// consecutive pods per trip, so a half-warp covers 128 rows at once and an ordinary node (about a
+// hundred pods) is one trip; the two halves of a warp work on two different nodes, which doubles
+// the number of independent load chains in flight (the kernel is a chain of dependent loads per
+// node: offsets -> meta bytes -> container values).
+//   meta bytes   two funnel-shifted 32-bit words (the rows start at any byte), rows past hi zeroed
+//   counts       high nibbles; a multiply by 0x01010101 turns four count bytes into their running sums
+//   placement    a 16-lane scan of the lane totals places every lane in the value column
+//   values       each pod's few nibbles (bytes): packed_values_sum, skipped for pods without containers
 template <int kBits>
 __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const unsigned char *gpu, unsigned lo, unsigned hi,
-                                               unsigned c0, int lane)
+                                               unsigned c0, int l16, unsigned hmask)
 {
+    const unsigned *mw = reinterpret_cast<const unsigned *>(meta);
     unsigned acc = 0;
-    unsigned m_next = lo + lane < hi ? (unsigned)__ldg(meta + lo + lane) : 0u;
-    for (unsigned p0 = lo; p0 < hi; p0 += 32) {
-        const unsigned m = m_next;                      // the next trip's bytes are already on their way
-        m_next = p0 + 32 + lane < hi ? (unsigned)__ldg(meta + p0 + 32 + lane) : 0u;
-        const unsigned cnt = m >> 4, ph = m & 15u;
-        const unsigned inc = warp_inclusive_scan_u32(cnt);
-        const unsigned s = packed_values_sum<kBits>(gpu, c0 + inc - cnt, cnt);
-        if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += s;          // rows past hi have cnt 0
-        c0 += __shfl_sync(0xffffffffu, inc, 31);
+    for (unsigned p0 = lo; p0 < hi; p0 += 128) {
+        const unsigned q = p0 + 8u * (unsigned)l16;
+        unsigned m_lo = 0, m_hi = 0;
+        if (q < hi) {
+            const unsigned *w = mw + (q >> 2);
+            const unsigned w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2), sh = (q & 3u) * 8u;
+            m_lo = __funnelshift_r(w0, w1, sh);
+            m_hi = __funnelshift_r(w1, w2, sh);
+            const unsigned n = hi - q;                               // rows of this lane inside the range
+            if (n < 4) { m_lo &= (1u << (8 * n)) - 1u; m_hi = 0; }
+            else if (n < 8) m_hi &= n == 4 ? 0u : (1u << (8 * (n - 4))) - 1u;
+        }
+        const unsigned cnt_lo = (m_lo >> 4) & 0x0f0f0f0fu, cnt_hi = (m_hi >> 4) & 0x0f0f0f0fu;
+        const unsigned pre_lo = cnt_lo * 0x01010101u;               // byte k = counts 0..k (at most 60: no carry)
+        const unsigned pre_hi = cnt_hi * 0x01010101u + (pre_lo >> 24) * 0x01010101u;     // at most 120
+        const unsigned total = pre_hi >> 24;
+        unsigned inc = total;
+#pragma unroll
+        for (int d = 1; d < 16; d <<= 1) {
+            const unsigned up = __shfl_up_sync(hmask, inc, d, 16);
+            if (l16 >= d) inc += up;
+        }
+        const unsigned start = c0 + inc - total;
+        const unsigned ex_lo = pre_lo - cnt_lo, ex_hi = pre_hi - cnt_hi;   // byte k = counts before pod k
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const unsigned sh = 8u * (unsigned)(j & 3);
+            const unsigned cnt = ((j < 4 ? cnt_lo : cnt_hi) >> sh) & 0xffu;
+            if (cnt == 0) continue;                                  // (also every row past hi)
+            const unsigned ph = ((j < 4 ? m_lo : m_hi) >> sh) & 0xfu;
+            const unsigned off = ((j < 4 ? ex_lo : ex_hi) >> sh) & 0xffu;
+            const unsigned v = packed_values_sum<kBits>(gpu, start + off, cnt);
+            if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += v;
+        }
+        c0 += __shfl_sync(hmask, inc, 15, 16);
     }
-    return warp_reduce_sum((u64)acc);
+    u64 sum = acc;
+#pragma unroll
+    for (int d = 8; d > 0; d >>= 1) sum += __shfl_xor_sync(hmask, sum, d, 16);
+    return sum;
 }
 
 template <int kBits>
 __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_constant__ PackedArgs a)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u64 n_warps = (u64)gridDim.x * kWarps, w0 = (u64)blockIdx.x * kWarps + warp;
-    u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every warp
+    const int l16 = lane & 15;
+    const unsigned hmask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
+    // one unit of work per HALF-warp
+    const u64 n_units = (u64)gridDim.x * kWarps * 2, u0 = ((u64)blockIdx.x * kWarps + warp) * 2 + (lane >> 4);
+    u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every half
     unsigned lo_n = 0, hi_n = 0, c_n = 0;               // the next node's offsets, fetched one node ahead
-    if (w0 < a.N) { lo_n = __ldg(a.node_pod_begin + w0); hi_n = __ldg(a.node_pod_begin + w0 + 1); c_n = __ldg(a.node_ctr_begin + w0); }
-    for (u64 n = w0; n < a.N; n += n_warps) {
+    const u64 first = a.n_lo + u0;
+    if (first < a.N) { lo_n = __ldg(a.node_pod_begin + first); hi_n = __ldg(a.node_pod_begin + first + 1); c_n = __ldg(a.node_ctr_begin + first); }
+    for (u64 n = first; n < a.N; n += n_units) {
         const unsigned lo = lo_n, hi = hi_n, c0 = c_n;
-        if (n + n_warps < a.N) {
-            lo_n = __ldg(a.node_pod_begin + n + n_warps);
-            hi_n = __ldg(a.node_pod_begin + n + n_warps + 1);
-            c_n = __ldg(a.node_ctr_begin + n + n_warps);
+        if (n + n_units < a.N) {
+            lo_n = __ldg(a.node_pod_begin + n + n_units);
+            hi_n = __ldg(a.node_pod_begin + n + n_units + 1);
+            c_n = __ldg(a.node_ctr_begin + n + n_units);
         }
         if (hi - lo <= kBigNodePods) {
-            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, lane);
-            if (lane == 0) { a.node_alloc[n] = s; alloc_sum += s; }
+            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, hmask);
+            if (l16 == 0) { a.node_alloc[n] = s; alloc_sum += s; }
         }
-        if (lane == 0) {
+        if (l16 == 0) {
             const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
             a.node_total[n] = t;
             cap_sum += (u64)t;
         }
     }
-    for (u64 k = w0; k < a.n_pieces; k += n_warps) {
+    for (u64 k = a.piece_lo + u0; k < a.n_pieces; k += n_units) {
         const uint4 pc = __ldg(a.pieces + k);
-        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, lane);
-        if (lane == 0 && s) { red_add_u64(a.node_alloc + pc.x, s); }
-        if (lane == 0) alloc_sum += s;
+        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, hmask);
+        if (l16 == 0 && s) { red_add_u64(a.node_alloc + pc.x, s); }
+        if (l16 == 0) alloc_sum += s;
     }
+    __syncwarp();
+    alloc_sum += __shfl_down_sync(0xffffffffu, alloc_sum, 16);
+    cap_sum += __shfl_down_sync(0xffffffffu, cap_sum, 16);
     __shared__ u64 s_a[kWarps], s_c[kWarps];
     if (lane == 0) { s_a[warp] = alloc_sum; s_c[warp] = cap_sum; }
     __syncthreads();

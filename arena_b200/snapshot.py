@@ -233,6 +233,34 @@ class PackedSnapshot:
             pass
 
 
+class PackedDeviceSnapshot:
+    """`arena_packed_device*`: the packed columns resident in HBM (arena_snapshot_upload_packed)."""
+
+    def __init__(self, packed: "PackedSnapshot"):
+        h = C.c_void_p()
+        check(lib().arena_snapshot_upload_packed(C.byref(packed.view), C.byref(h)))
+        self._h = h.value
+        self.n_pods, self.n_containers, self.n_nodes = packed.n_pods, packed.n_containers, packed.n_nodes
+        b = C.c_uint64()
+        check(lib().arena_packed_device_bytes(self._h, C.byref(b)))
+        self.launch_bytes = int(b.value)
+
+    @property
+    def handle(self) -> int:
+        return self._h
+
+    def close(self) -> None:
+        if self._h:
+            lib().arena_packed_device_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class PinnedBuffer:
     """arena_pinned_alloc: page-locked host bytes (read a PodList into one of these and the
     copy to the device runs at PCIe speed)."""

@@ -103,6 +103,15 @@ def peer_exchange_collect(d_cluster, stream: Optional[int] = None) -> None:
     check(lib().arena_peer_exchange_collect(d_cluster.data_ptr(), _stream_arg(stream)))
 
 
+def top_node_packed_device(snap, d_node_total, d_node_alloc, d_cluster, stream: Optional[int] = None) -> None:
+    """arena_top_node_packed_device: the summary kernel on a device-resident packed snapshot; no sync."""
+    check(lib().arena_top_node_packed_device(
+        snap.handle,
+        d_node_total.data_ptr() if d_node_total is not None and d_node_total.numel() else None,
+        d_node_alloc.data_ptr() if d_node_alloc is not None and d_node_alloc.numel() else None,
+        d_cluster.data_ptr(), _stream_arg(stream)))
+
+
 def top_node_packed(packed, details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
     """arena_top_node_host_packed: one-shot upload of a PackedSnapshot + kernels + download."""
     N, P = packed.n_nodes, packed.n_pods

@@ -194,8 +194,9 @@ int  arena_peer_exchange_collect(int64_t *d_cluster, void *stream);
  *
  * A snapshot with a pod of more than 15 containers, a container above 255 GPUs or pods that
  * are not grouped has no packed form: use the wide one (arena_host_snapshot_pack says so).
- * The summary (pod_gpu == NULL) is computed straight from the packed columns, one warp per
- * node; with pod_gpu (per row, as in arena_top_node) the columns are first expanded into the
+ * The summary (pod_gpu == NULL) is computed straight from the packed columns, one half-warp per
+ * node, and pipelined: the node range is cut into eight chunks whose uploads, kernels and
+ * downloads overlap (page-locked buffers, arena_pinned_alloc, make the copies asynchronous); with pod_gpu (per row, as in arena_top_node) the columns are first expanded into the
  * wide layout on the device and the ordinary kernels run on that.  No reference counterpart.
  */
 typedef struct arena_packed_view {
@@ -216,6 +217,19 @@ typedef struct arena_packed_view {
 
 int  arena_top_node_host_packed(const arena_packed_view *host, int64_t *node_total,
                                 int64_t *node_alloc, int64_t cluster[2], int64_t *pod_gpu);
+
+/* The packed columns RESIDENT on the device, for a caller that queries one snapshot many times and
+ * can afford to hold it in its narrow form only (0.2 GB instead of 2.3 GB per 1e8 pods): upload once,
+ * then arena_top_node_packed_device enqueues the summary kernel on `stream` (NULL = the library's)
+ * with DEVICE outputs, like arena_top_node_device.  arena_packed_device_bytes reports the bytes one
+ * such launch reads and writes (its own roofline denominator: it reads other columns than the wide
+ * kernel does).  No reference counterpart. */
+typedef struct arena_packed_device arena_packed_device;
+int  arena_snapshot_upload_packed(const arena_packed_view *host, arena_packed_device **out);
+void arena_packed_device_free(arena_packed_device *p);
+int  arena_packed_device_bytes(const arena_packed_device *p, uint64_t *read_write_bytes);
+int  arena_top_node_packed_device(const arena_packed_device *p, int64_t *d_node_total, int64_t *d_node_alloc,
+                                  int64_t *d_cluster, void *stream);
 
 /*
  * Single process, several GPUs.  The reference CLI is one process (cmd/arena/main.go:12-28); its

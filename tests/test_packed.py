@@ -26,10 +26,12 @@ def unpack(p):
     return begin, meta, gpu
 
 
-@pytest.mark.parametrize("skewed", [False, True])
-def test_pack_is_the_wide_snapshot_in_fewer_bytes(built, skewed):
+@pytest.mark.parametrize("skewed,P,N", [(False, 30_000, 700), (True, 30_000, 700), (False, 1_500_000, 12_345),
+                                        (True, 1_500_000, 12_345)])
+def test_pack_is_the_wide_snapshot_in_fewer_bytes(built, skewed, P, N):
+    """(From 2^20 rows + containers up the packing runs on every host thread, one row range each.)"""
     from arena_b200 import HostSnapshot
-    h = HostSnapshot.synth(30_000, 700, seed=11, skewed=skewed)
+    h = HostSnapshot.synth(P, N, seed=11, skewed=skewed)
     p = h.pack()
     begin, meta, gpu = unpack(p)
     pn = h.cols["pod_node"].astype(np.int64)
@@ -131,3 +133,56 @@ def test_packed_path_on_the_json_fixture(gpu):
         return
     got = gpu.top_node_packed(packed)
     assert np.array_equal(got.node_total, tot) and np.array_equal(got.node_alloc, alloc) and np.array_equal(got.cluster, cl)
+
+
+@pytest.mark.gpu
+def test_packed_one_shot_call_is_pipelined_above_4m_pods(gpu):
+    """From 4 Mi pods up the one-shot call cuts the node range into eight chunks whose uploads, kernels and
+    downloads overlap; page-locked and ordinary buffers, uniform and skewed (giant nodes straddle nothing: a
+    node is never cut, its pieces go with its chunk)."""
+    for skewed, seed in ((False, 17), (True, 5)):
+        h = gpu.HostSnapshot.synth(6_000_000, 60_000, seed=seed, skewed=skewed)
+        tot, alloc, cl, _ = cref.top_node_columnar(h.cols)
+        for pinned in (True, False):
+            packed = h.pack(pinned=pinned)
+            for _ in range(2):
+                got = gpu.top_node_packed(packed)
+                assert np.array_equal(got.node_total, tot) and np.array_equal(got.node_alloc, alloc) and np.array_equal(got.cluster, cl)
+            packed.close()
+
+
+@pytest.mark.gpu
+def test_packed_snapshot_resident_on_the_device(gpu):
+    """arena_snapshot_upload_packed + arena_top_node_packed_device: the summary kernel on packed columns that
+    stay in HBM, against the C oracle -- generator snapshots, and pods with up to 15 containers each."""
+    import torch
+    rng = np.random.default_rng(8)
+    P, N = 50_000, 300
+    counts = rng.integers(0, 16, P)
+    cb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+    many = gpu.HostSnapshot.from_arrays(dict(
+        pod_node=np.sort(rng.integers(0, N + 1, P)).astype(np.uint32) % np.uint32(N + 1),
+        pod_phase=rng.choice([0, 1, 2, 3, 4, 5, 255], P).astype(np.uint8), pod_ctr_begin=cb,
+        ctr_val=rng.integers(0, 16, int(cb[-1])).astype(np.int64), ctr_scale=np.zeros(int(cb[-1]), np.int8),
+        node_cap_val=rng.integers(0, 9, N).astype(np.int64), node_cap_scale=np.zeros(N, np.int8)))
+    pn = many.cols["pod_node"].copy()
+    pn[pn == N] = 0xFFFFFFFF
+    cols = dict(many.cols)
+    cols["pod_node"] = pn
+    many = gpu.HostSnapshot.from_arrays({k: v for k, v in cols.items() if not k.startswith("pod_job") and k not in ("pod_role", "pod_created")})
+    cases = [gpu.HostSnapshot.synth(300_000, 3_000, seed=31), gpu.HostSnapshot.synth(1_000_000, 9_000, seed=5, skewed=True), many,
+             gpu.HostSnapshot.synth(5, 2, seed=1)]
+    st = torch.cuda.current_stream().cuda_stream
+    for h in cases:
+        tot, alloc, cl, _ = cref.top_node_columnar(h.cols)
+        dev = gpu.PackedDeviceSnapshot(h.pack())
+        assert 0 < dev.launch_bytes < h.algorithmic_bytes_top_node()
+        d_total = torch.full((h.n_nodes,), -1, dtype=torch.int64, device="cuda")
+        d_alloc = torch.full((h.n_nodes,), -1, dtype=torch.int64, device="cuda")
+        d_cluster = torch.full((2,), -1, dtype=torch.int64, device="cuda")
+        for _ in range(3):
+            gpu.top_node_packed_device(dev, d_total, d_alloc, d_cluster, st)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_total.cpu().numpy(), tot) and np.array_equal(d_alloc.cpu().numpy(), alloc)
+        assert d_cluster.cpu().numpy().tolist() == cl.tolist()
+        dev.close()
