@@ -35,10 +35,8 @@ struct Context {
     int device = -1;
     int sm_count = 0;
     int pods_ctas_per_sm = 0;
-    int pods_ctas_per_sm_min = 0;    // the smallest over the top-node instantiations
     int jobs_ctas_per_sm = 0;
     int packed_ctas_per_sm = 0;
-    bool cooperative = false;        // cudaLaunchCooperativeKernel available: the top-node launch zeroes node_alloc itself
     cudaStream_t stream = nullptr;
     // one-shot host calls: staging snapshot and packed staging block, kept between calls
     arena_snapshot *host_snap = nullptr;
@@ -132,23 +130,7 @@ static int init_current_slot(int device)
                     "code for other architectures", device, prop.major, prop.minor);
     ctx().device = device;
     ctx().sm_count = prop.multiProcessorCount;
-    {
-        int coop = 0;
-        CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
-        // Measured (profiles/r02_iterations.md): the barrier costs what the memset it replaces costs
-        // (1e8 pods: 456.3 + 2.6 us against 451.7 + 6.7; 1.25e7 pods: 68.4 + 2.6 against 64.7 + 6.6),
-        // so the memset stays the default and the self-zeroing launch is opt-in.
-        const char *on = getenv("ARENA_COOPERATIVE");
-        ctx().cooperative = coop != 0 && on && on[0] == '1';
-    }
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
-    {
-        int o1 = 0, o2 = 0, o3 = 0;
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, top_node_pods_kernel<true, false>, kThreads, 0));
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, top_node_pods_kernel<false, true>, kThreads, 0));
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, top_node_pods_kernel<true, true>, kThreads, 0));
-        ctx().pods_ctas_per_sm_min = std::min(std::min(o1, o2), std::min(o3, ctx().pods_ctas_per_sm));
-    }
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
     if (ctx().pods_ctas_per_sm < 1 || ctx().jobs_ctas_per_sm < 1 || ctx().packed_ctas_per_sm < 1)
@@ -291,14 +273,10 @@ int ensure_job_arrays(arena_snapshot *s)
 }
 
 template <typename K>
-cudaError_t launch_pods(K kernel, int grid, const PodsArgs &pa, bool cooperative, cudaStream_t st)
+cudaError_t launch_pods(K kernel, int grid, const PodsArgs &pa, cudaStream_t st)
 {
-    if (!cooperative) {
-        kernel<<<grid, kThreads, 0, st>>>(pa);
-        return cudaGetLastError();
-    }
-    void *args[] = {const_cast<PodsArgs *>(&pa)};
-    return cudaLaunchCooperativeKernel((const void *)kernel, dim3((unsigned)grid), dim3(kThreads), args, 0, st);
+    kernel<<<grid, kThreads, 0, st>>>(pa);
+    return cudaGetLastError();
 }
 
 // exchange: 0 none, 1 in-kernel totals exchange collected by the same launch, 2 collected one step late
@@ -309,15 +287,13 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
     const bool prof = g_prof.on && g_prof.used + 3 <= g_prof.ev.size() && (g_prof.seen++ % g_prof.every) == 0;
     cudaEvent_t *pe = prof ? &g_prof.ev[g_prof.used] : nullptr;
     if (prof) { g_prof.used += 3; CUDA_TRY(cudaEventRecord(pe[0], st)); }
-    // node_alloc is accumulated with atomics: it starts from zero.  A memset in front of the launch,
-    // or (ARENA_COOPERATIVE=1) the launch clears it itself: cooperative launch + one grid barrier.
-    bool self_zero = ctx().cooperative && v.n_nodes > 0 && (((uintptr_t)d_alloc) & 15) == 0;
+    // node_alloc is accumulated with atomics: it starts from zero.  (A launch that clears it itself --
+    // cooperative launch, every CTA zeroes a slice, one grid-wide barrier -- was measured and dropped:
+    // the barrier costs what the memset costs, profiles/r02_iterations.md.)
     int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm);
     const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, ctx().pods_ctas_per_sm);
     if (gn > gp) gp = gn;
-    // all CTAs must be resident for the barrier: the details / ungrouped instantiations may fit fewer per SM
-    if (self_zero && (d_pod_gpu || s->direct) && gp > ctx().sm_count * ctx().pods_ctas_per_sm_min) self_zero = false;
-    if (v.n_nodes && !self_zero) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
+    if (v.n_nodes) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
     if (prof) CUDA_TRY(cudaEventRecord(pe[1], st));
 
     PodsArgs pa{};
@@ -340,14 +316,13 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
         pa.px = ctx().px;
         pa.px_lag = exchange == 2 ? 1u : 0u;
     }
-    pa.zero_alloc = self_zero ? 1u : 0u;
     cudaError_t e;
     if (d_pod_gpu) {
-        if (s->direct) e = launch_pods(top_node_pods_kernel<true, true>, gp, pa, self_zero, st);
-        else e = launch_pods(top_node_pods_kernel<false, true>, gp, pa, self_zero, st);
+        if (s->direct) e = launch_pods(top_node_pods_kernel<true, true>, gp, pa, st);
+        else e = launch_pods(top_node_pods_kernel<false, true>, gp, pa, st);
     } else {
-        if (s->direct) e = launch_pods(top_node_pods_kernel<true, false>, gp, pa, self_zero, st);
-        else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, self_zero, st);
+        if (s->direct) e = launch_pods(top_node_pods_kernel<true, false>, gp, pa, st);
+        else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
     }
     if (e != cudaSuccess) return fail(ARENA_E_CUDA, "top-node kernel launch: %s", cudaGetErrorString(e));
     count_launch();

@@ -291,7 +291,6 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
             if (two) *out_b = (i64)tb;
         }
         sc->ticket[ticket_id] = 0;      // ready for the next launch
-        sc->ticket[0] = 0;              // the start-of-launch barrier (everybody is long past it)
         if (px) px->epoch += 1;         // this CTA is the only writer; the next launch is ordered behind it
     }
     if (!px) return;
@@ -368,9 +367,6 @@ struct PodsArgs {
     // multi-GPU: exchange the two totals with the peer GPUs inside this launch (or nullptr)
     PeerExchange *px;
     unsigned px_lag;                // 0: collect this step's totals; 1: the previous step's (deferred)
-    // key_alloc is zeroed by this launch itself (cooperative launch: every CTA clears a slice, one
-    // grid-wide barrier, then the tiles) instead of by a memset in front of it
-    unsigned zero_alloc;
 };
 
 // Rare path (a row that runs past the end of the container columns) kept out
@@ -746,24 +742,6 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     const int warp = threadIdx.x >> 5;
     const unsigned FULL = 0xffffffffu;
     unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
-
-    if (!kJob && a.zero_alloc) {
-        // node_alloc starts from zero: 128-bit stores, then everybody waits for everybody (the
-        // launch is cooperative, so all CTAs are resident and the spin cannot starve one of them)
-        ulonglong2 *z = reinterpret_cast<ulonglong2 *>(a.key_alloc);
-        const u64 n2 = a.K / 2;
-        for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (u64)gridDim.x * blockDim.x)
-            z[i] = make_ulonglong2(0ull, 0ull);
-        if ((a.K & 1) && blockIdx.x == 0 && threadIdx.x == 0) a.key_alloc[a.K - 1] = 0;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            atomicAdd(&a.scratch->ticket[0], 1u);
-            while (*((volatile unsigned *)&a.scratch->ticket[0]) < gridDim.x) __nanosleep(40);
-            __threadfence();
-        }
-        __syncthreads();
-    }
 
     u64 acc_alloc = 0;
     u64 job_req = 0, job_alloc = 0;             // kJob: every lane's own partial totals

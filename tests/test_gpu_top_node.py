@@ -275,9 +275,8 @@ def test_fused_totals_exchange_with_itself(gpu):
 
 
 def test_unaligned_and_dirty_output_buffers(gpu):
-    """node_alloc is accumulated with atomics, so the call must clear it first whatever it held; the
-    self-zeroing launch (ARENA_COOPERATIVE=1) needs 16-byte alignment and falls back to the memset
-    for a buffer that is 8 bytes off."""
+    """node_alloc is accumulated with atomics, so the call must clear it first whatever it held, and
+    only d_pod_gpu has an alignment requirement."""
     import torch
     host = gpu.HostSnapshot.synth(700_000, 9_001, seed=23)
     dev = gpu.DeviceSnapshot.upload(host)

@@ -160,16 +160,12 @@ def test_packed_snapshot_resident_on_the_device(gpu):
     P, N = 50_000, 300
     counts = rng.integers(0, 16, P)
     cb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+    pn = np.sort(rng.integers(0, N + 1, P)).astype(np.uint32)
+    pn[pn == N] = 0xFFFFFFFF                                   # the rows that name no node come last
     many = gpu.HostSnapshot.from_arrays(dict(
-        pod_node=np.sort(rng.integers(0, N + 1, P)).astype(np.uint32) % np.uint32(N + 1),
-        pod_phase=rng.choice([0, 1, 2, 3, 4, 5, 255], P).astype(np.uint8), pod_ctr_begin=cb,
+        pod_node=pn, pod_phase=rng.choice([0, 1, 2, 3, 4, 5, 255], P).astype(np.uint8), pod_ctr_begin=cb,
         ctr_val=rng.integers(0, 16, int(cb[-1])).astype(np.int64), ctr_scale=np.zeros(int(cb[-1]), np.int8),
         node_cap_val=rng.integers(0, 9, N).astype(np.int64), node_cap_scale=np.zeros(N, np.int8)))
-    pn = many.cols["pod_node"].copy()
-    pn[pn == N] = 0xFFFFFFFF
-    cols = dict(many.cols)
-    cols["pod_node"] = pn
-    many = gpu.HostSnapshot.from_arrays({k: v for k, v in cols.items() if not k.startswith("pod_job") and k not in ("pod_role", "pod_created")})
     cases = [gpu.HostSnapshot.synth(300_000, 3_000, seed=31), gpu.HostSnapshot.synth(1_000_000, 9_000, seed=5, skewed=True), many,
              gpu.HostSnapshot.synth(5, 2, seed=1)]
     st = torch.cuda.current_stream().cuda_stream
