@@ -95,6 +95,12 @@ struct arena_snapshot {
     u64 *sort_key = nullptr;
     unsigned *sort_idx = nullptr;
     u64 jpad = 0;
+    // radix sort of the job ordering (kernels.cuh): second key / id buffers, per-tile digit counts, the
+    // OR / AND accumulators, and the page-locked word the first query publishes the varying bits to
+    u64 *alt_key = nullptr;
+    unsigned *alt_idx = nullptr, *block_hist = nullptr;
+    SortPlan *sort_plan = nullptr;
+    SortHost *sort_host = nullptr;
     // device output staging for the host-output entry points
     i64 *d_out = nullptr;
     size_t d_out_bytes = 0;
@@ -258,16 +264,26 @@ int ensure_job_arrays(arena_snapshot *s)
     u64 J = s->v.n_jobs;
     u64 jpad = kSortTile;
     while (jpad < J) jpad <<= 1;
-    size_t bytes = pad16(J * 8) * 3 + pad16(J * 4) + pad16(jpad * 8) + pad16(jpad * 4);
+    const u64 n_tiles = (J + kRadixTile - 1) / kRadixTile;
+    size_t bytes = pad16(J * 8) * 3 + pad16(J * 4) + pad16(jpad * 8) + pad16(jpad * 4) + pad16(J * 8) + pad16(J * 4) +
+                   pad16(n_tiles * 256 * 4) + 16;
     char *base = nullptr;
     CUDA_TRY(cudaMalloc((void **)&base, bytes ? bytes : 16));
+    CUDA_TRY(cudaHostAlloc((void **)&s->sort_host, sizeof(SortHost), cudaHostAllocMapped));
+    *s->sort_host = SortHost{0, 0, 0};
     char *p = base;
     s->job_req = (u64 *)p; p += pad16(J * 8);
     s->job_alloc = (u64 *)p; p += pad16(J * 8);
     s->job_maxcreated = (i64 *)p; p += pad16(J * 8);
     s->sort_key = (u64 *)p; p += pad16(jpad * 8);
     s->job_latest = (unsigned *)p; p += pad16(J * 4);
-    s->sort_idx = (unsigned *)p;
+    s->sort_idx = (unsigned *)p; p += pad16(jpad * 4);
+    s->alt_key = (u64 *)p; p += pad16(J * 8);
+    s->alt_idx = (unsigned *)p; p += pad16(J * 4);
+    s->block_hist = (unsigned *)p; p += pad16(n_tiles * 256 * 4);
+    s->sort_plan = (SortPlan *)p;
+    const SortPlan fresh{0ull, ~0ull};
+    CUDA_TRY(cudaMemcpy(s->sort_plan, &fresh, sizeof fresh, cudaMemcpyHostToDevice));
     s->jpad = jpad;
     return ARENA_OK;
 }
@@ -402,8 +418,40 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     fa.sort_key = s->sort_key; fa.sort_idx = s->sort_idx;
     fa.totals = d_totals;
     fa.scratch = s->scratch;
+    // Which key bits vary is a property of the snapshot.  A snapshot the library uploaded cannot change,
+    // so once its first query has published them, later queries radix-sort on exactly those bits; columns
+    // the caller merely lent (arena_snapshot_wrap_device) may change under us and keep the bitonic network.
+    const bool radix = s->owns && *((volatile unsigned *)&s->sort_host->ready) != 0u;
+    fa.plan = (s->owns && !radix) ? s->sort_plan : nullptr;
     job_finish_kernel<<<grid_for(s->jpad, kThreads, 8), kThreads, 0, st>>>(fa);
     count_launch();
+
+    if (radix) {
+        u64 var = s->sort_host->varmask;
+        const u64 *k_in = s->sort_key;
+        const unsigned *i_in = s->sort_idx;
+        u64 *k_out = s->alt_key;
+        unsigned *i_out = s->alt_idx;
+        const unsigned tiles = (unsigned)((J + kRadixTile - 1) / kRadixTile);
+        while (var) {                                    // least significant eight varying bits first
+            u64 mask = 0;
+            for (int b = 0; b < 8 && var; b++) { mask |= var & (0 - var); var &= var - 1; }
+            const int shift = __builtin_ctzll(mask);
+            const int contiguous = ((mask >> shift) & ((mask >> shift) + 1)) == 0;
+            radix_hist_kernel<<<tiles, 256, 0, st>>>(k_in, J, mask, shift, contiguous, s->block_hist);
+            radix_scan_kernel<<<1, 1024, 0, st>>>(s->block_hist, tiles);
+            radix_scatter_kernel<<<tiles, 256, 0, st>>>(k_in, i_in, J, mask, shift, contiguous, s->block_hist, k_out, i_out);
+            g_launches.fetch_add(3, std::memory_order_relaxed);
+            std::swap(const_cast<u64 *&>(k_in), k_out);
+            std::swap(const_cast<unsigned *&>(i_in), i_out);
+        }
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaMemcpyAsync(d_req, s->job_req, J * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_alloc, s->job_alloc, J * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d_order, i_in, J * 4, cudaMemcpyDeviceToDevice, st));
+        if (d_latest) CUDA_TRY(cudaMemcpyAsync(d_latest, s->job_latest, J * 4, cudaMemcpyDeviceToDevice, st));
+        return ARENA_OK;
+    }
 
     // sort (requested desc, id asc)
     const u64 n = s->jpad;
@@ -423,6 +471,12 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
             count_launch();
         }
         tile_pass(k, 0);
+    }
+    if (fa.plan) {                                       // publish the varying bits for the next query on this handle
+        SortHost *mapped = nullptr;
+        CUDA_TRY(cudaHostGetDevicePointer((void **)&mapped, s->sort_host, 0));
+        sort_plan_kernel<<<1, 1, 0, st>>>(s->sort_plan, mapped);
+        count_launch();
     }
     CUDA_TRY(cudaGetLastError());
     if (J) {
@@ -732,6 +786,7 @@ void arena_snapshot_free(arena_snapshot *s)
     if (s->owns && s->block) arena_internal::device_release(s->block, s->block_bytes);
     if (s->scratch) arena_internal::device_release(s->scratch, sizeof(Scratch));
     if (s->job_req) cudaFree(s->job_req);
+    if (s->sort_host) cudaFreeHost(s->sort_host);
     if (s->d_out) cudaFree(s->d_out);
     delete s;
 }
@@ -1517,6 +1572,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
     fa.sort_key = w->sort_key; fa.sort_idx = w->sort_idx;
     fa.totals = (i64 *)d_totals;
     fa.scratch = &w->scratch;
+    fa.plan = nullptr;
     job_finish_kernel<<<grid_for(kNoAllocMaxJobs, kThreads, 8), kThreads, 0, st>>>(fa);
     count_launch();
 

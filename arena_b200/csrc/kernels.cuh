@@ -1004,10 +1004,13 @@ struct JobFinishArgs {
     unsigned *sort_idx;     // [Jpad]
     i64 *totals;            // {req, alloc}: in = sums of ROLE_COUNTS pods, out = full totals
     Scratch *scratch;
+    struct SortPlan *plan;  // or nullptr: OR / AND of all sort keys (which key bits vary at all)
 };
+struct SortPlan { u64 or_acc, and_acc; };
 __global__ void __launch_bounds__(kThreads) job_finish_kernel(JobFinishArgs a)
 {
     u64 add_req = 0, add_alloc = 0;
+    u64 key_or = 0, key_and = ~0ull;
     for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < a.Jpad; j += (u64)gridDim.x * blockDim.x) {
         if (j >= a.J) {                      // padding sorts last
             a.sort_key[j] = ~0ull;
@@ -1027,8 +1030,20 @@ __global__ void __launch_bounds__(kThreads) job_finish_kernel(JobFinishArgs a)
             a.job_alloc[j] = alc;
         }
         // requested DESC as an ascending unsigned key: flip sign bit, invert
-        a.sort_key[j] = ~(req ^ 0x8000000000000000ull);
+        const u64 key = ~(req ^ 0x8000000000000000ull);
+        a.sort_key[j] = key;
         a.sort_idx[j] = (unsigned)j;
+        key_or |= key;
+        key_and &= key;
+    }
+    if (a.plan) {                            // one pair of atomics per warp
+        const unsigned FULL = 0xffffffffu;
+        const unsigned olo = __reduce_or_sync(FULL, (unsigned)key_or), ohi = __reduce_or_sync(FULL, (unsigned)(key_or >> 32));
+        const unsigned alo = __reduce_and_sync(FULL, (unsigned)key_and), ahi = __reduce_and_sync(FULL, (unsigned)(key_and >> 32));
+        if ((threadIdx.x & 31) == 0) {
+            atomicOr(&a.plan->or_acc, ((u64)ohi << 32) | olo);
+            atomicAnd(&a.plan->and_acc, ((u64)ahi << 32) | alo);
+        }
     }
     __shared__ u64 s_a[kWarps], s_b[kWarps];
     add_req = warp_reduce_sum(add_req);
@@ -1102,6 +1117,142 @@ __global__ void bitonic_global_kernel(u64 *key, unsigned *idx, u64 n, u64 k, u64
         unsigned ia = idx[lo], ib = idx[hi];
         bool swap = up ? pair_less(kb, ib, ka, ia) : pair_less(ka, ia, kb, ib);
         if (swap) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
+    }
+}
+
+// ---- ordering of many jobs: LSD radix sort on the key bits that vary ----------------------------
+// The sort key is `requested` as an ascending unsigned number (sign flipped, inverted: requested desc).
+// Real clusters ask for a handful of GPUs per job, so of the key's 64 bits a few low ones vary and the
+// rest is the same in every job.  The first `top job` query on a snapshot sorts with the bitonic
+// network below and publishes WHICH bits vary (OR of all keys xor AND of all keys) to page-locked host
+// memory; later queries on the same (immutable) snapshot radix-sort on exactly those bits, eight per
+// pass -- one pass for any realistic snapshot.  LSD radix is stable, and the input is in id order, so
+// the documented tie-break (ascending job id) needs no id in the key.
+struct SortHost { u64 varmask; unsigned ready, pad; };
+
+__global__ void sort_plan_kernel(SortPlan *plan, SortHost *host)
+{
+    host->varmask = plan->or_acc ^ plan->and_acc;
+    __threadfence_system();
+    *((volatile unsigned *)&host->ready) = 1u;
+    plan->or_acc = 0;                        // ready for the next snapshot query
+    plan->and_acc = ~0ull;
+}
+
+constexpr int kRadixTile = 2048;           // keys per CTA of 256 threads: 8 per thread
+
+// this pass's digit: the key bits selected by `mask` (at most eight), packed together
+__device__ __forceinline__ unsigned radix_digit(u64 key, u64 mask, int shift, int contiguous)
+{
+    if (contiguous) return (unsigned)((key & mask) >> shift);
+    unsigned d = 0, i = 0;
+    while (mask) {
+        const int b = __ffsll((long long)mask) - 1;
+        d |= (unsigned)((key >> b) & 1ull) << i++;
+        mask &= mask - 1;
+    }
+    return d;
+}
+
+__global__ void __launch_bounds__(256) radix_hist_kernel(const u64 *__restrict__ key, u64 n, u64 mask, int shift, int contiguous,
+                                                         unsigned *__restrict__ block_hist)
+{
+    __shared__ unsigned hist[256];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const u64 base = (u64)blockIdx.x * kRadixTile;
+#pragma unroll
+    for (int k = 0; k < kRadixTile / 256; k++) {
+        const u64 i = base + (u64)k * 256 + threadIdx.x;
+        if (i < n) atomicAdd(&hist[radix_digit(key[i], mask, shift, contiguous)], 1u);
+    }
+    __syncthreads();
+    block_hist[(u64)blockIdx.x * 256 + threadIdx.x] = hist[threadIdx.x];
+}
+
+// block_hist[b][d] becomes where block b's keys of digit d start in the output.  One CTA of 1024
+// threads: four threads per digit walk a quarter of the blocks each, then the quarters and the digits
+// are chained.
+__global__ void __launch_bounds__(1024) radix_scan_kernel(unsigned *__restrict__ block_hist, unsigned n_blocks)
+{
+    __shared__ unsigned part[4][256];
+    __shared__ unsigned digit_base[256];
+    const unsigned d = threadIdx.x & 255, quarter = threadIdx.x >> 8;
+    const unsigned per = (n_blocks + 3) / 4, b0 = quarter * per, b1 = b0 + per < n_blocks ? b0 + per : n_blocks;
+    unsigned sum = 0;
+    for (unsigned b = b0; b < b1; b++) sum += block_hist[(u64)b * 256 + d];
+    part[quarter][d] = sum;
+    __syncthreads();
+    if (threadIdx.x < 256) {
+        unsigned total = part[0][d] + part[1][d] + part[2][d] + part[3][d];
+        digit_base[d] = total;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                  // 256 values: a serial exclusive scan is a microsecond
+        unsigned run = 0;
+        for (int i = 0; i < 256; i++) { const unsigned t = digit_base[i]; digit_base[i] = run; run += t; }
+    }
+    __syncthreads();
+    unsigned run = digit_base[d];
+    for (unsigned qd = 0; qd < quarter; qd++) run += part[qd][d];
+    for (unsigned b = b0; b < b1; b++) {
+        const unsigned t = block_hist[(u64)b * 256 + d];
+        block_hist[(u64)b * 256 + d] = run;
+        run += t;
+    }
+}
+
+// Stable scatter of one tile: warp w owns the tile's keys [256 w, 256 w + 256) and walks them 32 at a
+// time in order; inside a round, equal digits are ranked by lane (match_any + population count of the
+// lower lanes), across rounds by a per-warp running count, across warps by a prefix over the warps.
+__global__ void __launch_bounds__(256) radix_scatter_kernel(const u64 *__restrict__ key_in, const unsigned *__restrict__ idx_in, u64 n,
+                                                            u64 mask, int shift, int contiguous,
+                                                            const unsigned *__restrict__ block_off, u64 *__restrict__ key_out,
+                                                            unsigned *__restrict__ idx_out)
+{
+    __shared__ unsigned warp_cnt[8][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 8 * 256; i += 256) (&warp_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const u64 base = (u64)blockIdx.x * kRadixTile + (u64)warp * 256;
+    u64 k[8];
+    unsigned id[8], dg[8], rank[8];
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const u64 i = base + (u64)r * 32 + lane;
+        const bool in = i < n;
+        k[r] = in ? key_in[i] : 0ull;
+        id[r] = in ? idx_in[i] : 0u;
+        dg[r] = in ? radix_digit(k[r], mask, shift, contiguous) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const unsigned peers = __match_any_sync(0xffffffffu, dg[r]);
+        const unsigned below = __popc(peers & ((1u << lane) - 1u));
+        unsigned start = 0;
+        const int leader = __ffs(peers) - 1;
+        if (dg[r] != 0xffffffffu && lane == leader) {
+            start = warp_cnt[warp][dg[r]];
+            warp_cnt[warp][dg[r]] = start + __popc(peers);
+        }
+        start = __shfl_sync(0xffffffffu, start, leader);
+        rank[r] = start + below;
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // exclusive prefix over the warps, per digit, plus this block's start for the digit
+        const unsigned d = threadIdx.x;
+        unsigned run = block_off[(u64)blockIdx.x * 256 + d];
+#pragma unroll
+        for (int w = 0; w < 8; w++) { const unsigned t = warp_cnt[w][d]; warp_cnt[w][d] = run; run += t; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        if (dg[r] == 0xffffffffu) continue;
+        const unsigned pos = warp_cnt[warp][dg[r]] + rank[r];
+        key_out[pos] = k[r];
+        idx_out[pos] = id[r];
     }
 }
 

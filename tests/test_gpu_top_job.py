@@ -63,3 +63,30 @@ def test_top_job_without_any_job(gpu):
     res = gpu.top_job(dev)
     assert res.totals.tolist() == [0, 0] and len(res.job_req) == 0
     dev.close()
+
+
+def test_top_job_radix_ordering_on_wide_and_sparse_keys(gpu):
+    """From the second query on, an uploaded snapshot's jobs are radix-sorted on the key bits that vary.
+    Huge, negative and bit-sparse `requested` values make many / scattered bits vary (several passes,
+    non-contiguous digit masks); ties must stay in ascending id order."""
+    rng = np.random.default_rng(21)
+    P, J = 150_000, 9_000
+    for values in (rng.integers(-2**62, 2**62, P, dtype=np.int64),                       # ~all 64 bits vary
+                   (rng.integers(0, 4, P) << 40) | (rng.integers(0, 2, P) << 3),        # two separate groups of bits
+                   np.full(P, 2, np.int64),                                              # few distinct sums
+                   np.zeros(P, np.int64)):                                               # nothing varies: zero passes
+        cb = np.arange(P + 1, dtype=np.uint32)                                           # one container per pod
+        cols = dict(pod_node=np.zeros(P, np.uint32), pod_phase=rng.choice(np.array([2, 3, 1], np.uint8), P),
+                    pod_ctr_begin=cb, ctr_val=values.astype(np.int64), ctr_scale=np.zeros(P, np.int8),
+                    node_cap_val=np.array([8], np.int64), node_cap_scale=np.zeros(1, np.int8),
+                    pod_job=rng.integers(0, J, P).astype(np.uint32), pod_role=np.zeros(P, np.uint8),
+                    pod_created=np.zeros(P, np.int64))
+        host = gpu.HostSnapshot.from_arrays(cols, n_jobs=J)
+        dev = gpu.DeviceSnapshot.upload(host)
+        req, alloc, latest, totals = cref.top_job_columnar(host.cols, J)
+        want = np.array(sorted(range(J), key=lambda j: (-int(req[j]), j)), np.uint32)
+        for call in range(3):                      # bitonic first, radix afterwards
+            res = gpu.top_job(dev)
+            assert np.array_equal(res.job_req, req) and np.array_equal(res.job_alloc, alloc), call
+            assert np.array_equal(res.job_order, want), call
+        dev.close()
