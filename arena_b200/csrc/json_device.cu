@@ -369,6 +369,7 @@ struct ItemArgs {
     unsigned char *pod_phase, *pod_flag;
     u64 *pod_nctr;                 // u64: feeds the prefix sum
     long long *ctr_tmp;            // [kInlineCtrs][n_items]
+    signed char *scale_tmp;        // [kInlineCtrs][n_items]
     ScanResult *res;
 };
 
@@ -411,14 +412,18 @@ __global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const
     a.pod_phase[p] = out.phase;
     const u32 n = out.n_ctrs <= (u32)kInlineCtrs ? out.n_ctrs : 0u;
     a.pod_nctr[p] = n;
-    for (u32 k = 0; k < n; k++) a.ctr_tmp[(u64)k * a.n_items + p] = out.ctr_val[k];
+    for (u32 k = 0; k < n; k++) {
+        a.ctr_tmp[(u64)k * a.n_items + p] = out.ctr_val[k];
+        a.scale_tmp[(u64)k * a.n_items + p] = out.ctr_scale[k];
+    }
 }
 
 // ---- K7 ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCta) gather_columns_kernel(u64 n_items, const u64 *__restrict__ ctr_begin64,
                                                              const u64 *__restrict__ pod_nctr, const long long *__restrict__ ctr_tmp,
+                                                             const signed char *__restrict__ scale_tmp,
                                                              u64 n_containers, u32 *__restrict__ pod_ctr_begin,
-                                                             long long *__restrict__ ctr_val)
+                                                             long long *__restrict__ ctr_val, signed char *__restrict__ ctr_scale)
 {
     const u64 p = (u64)blockIdx.x * kCta + threadIdx.x;
     if (p == 0) pod_ctr_begin[n_items] = (u32)n_containers;
@@ -426,7 +431,10 @@ __global__ void __launch_bounds__(kCta) gather_columns_kernel(u64 n_items, const
     const u64 b = ctr_begin64[p];
     pod_ctr_begin[p] = (u32)b;
     const u32 n = (u32)pod_nctr[p];
-    for (u32 k = 0; k < n; k++) ctr_val[b + k] = ctr_tmp[(u64)k * n_items + p];
+    for (u32 k = 0; k < n; k++) {
+        ctr_val[b + k] = ctr_tmp[(u64)k * n_items + p];
+        ctr_scale[b + k] = scale_tmp[(u64)k * n_items + p];
+    }
 }
 
 // =================================== host side ====================================================
@@ -773,6 +781,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     unsigned char *d_pod_phase_tmp = nullptr, *d_pod_flag = nullptr;
     u64 *d_nctr = nullptr, *d_ctr_begin64 = nullptr, *d_tile_sums2 = nullptr;
     long long *d_ctr_tmp = nullptr;
+    signed char *d_scale_tmp = nullptr;
     u64 C = 0;
     if (P) {
         CUDA_TRY(bufs.alloc(&d_pod_node_tmp, P * 4));
@@ -782,6 +791,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         CUDA_TRY(bufs.alloc(&d_ctr_begin64, P * 8));
         CUDA_TRY(bufs.alloc(&d_tile_sums2, ((P + kScanTile - 1) / kScanTile) * 8));
         CUDA_TRY(bufs.alloc(&d_ctr_tmp, P * 8 * kInlineCtrs));
+        CUDA_TRY(bufs.alloc(&d_scale_tmp, P * kInlineCtrs));
         const u32 none = 0xFFFFFFFFu;
         CUDA_TRY(cudaMemcpyAsync(&d_res->first_flag_item, &none, 4, cudaMemcpyHostToDevice, st));
         ItemArgs ia;
@@ -789,7 +799,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         ia.n_items = P; ia.A = A; ia.B = B;
         ia.nodes = NodeTable{d_slots, (uint64_t)slots.size() - 1, d_blob};
         ia.pod_node = d_pod_node_tmp; ia.pod_phase = d_pod_phase_tmp; ia.pod_flag = d_pod_flag;
-        ia.pod_nctr = d_nctr; ia.ctr_tmp = d_ctr_tmp; ia.res = d_res;
+        ia.pod_nctr = d_nctr; ia.ctr_tmp = d_ctr_tmp; ia.scale_tmp = d_scale_tmp; ia.res = d_res;
         // aim at >= 4 warps per SM sub-partition before filling the warps up
         const u64 warps_wanted = (u64)sm_count * 16;
         unsigned lanes = 32;
@@ -831,12 +841,12 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
     step(cudaMemsetAsync(block + o_cb, 0, pad16((P + 1) * 4), st));
-    step(cudaMemsetAsync(block + o_scale, 0, pad16(C), st));               // digits-only GPU quantities: scale 0
     if (P) {
         step(cudaMemcpyAsync(block + o_node, d_pod_node_tmp, P * 4, cudaMemcpyDeviceToDevice, st));
         step(cudaMemcpyAsync(block + o_phase, d_pod_phase_tmp, P, cudaMemcpyDeviceToDevice, st));
-        gather_columns_kernel<<<(unsigned)((P + kCta - 1) / kCta), kCta, 0, st>>>(P, d_ctr_begin64, d_nctr, d_ctr_tmp, C,
-                                                                                 (u32 *)(block + o_cb), (long long *)(block + o_val));
+        gather_columns_kernel<<<(unsigned)((P + kCta - 1) / kCta), kCta, 0, st>>>(P, d_ctr_begin64, d_nctr, d_ctr_tmp, d_scale_tmp, C,
+                                                                                 (u32 *)(block + o_cb), (long long *)(block + o_val),
+                                                                                 (signed char *)(block + o_scale));
         arena_internal::add_launches(1);
         step(cudaGetLastError());
     }
@@ -925,7 +935,7 @@ int arena_load_json_device(const char *podlist_json, size_t podlist_len, const c
 
 int arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const arena_host_snapshot *nodes, uint64_t capacity,
                             uint64_t *n_items_out, uint32_t *pod_node, uint8_t *pod_phase, uint32_t *pod_n_ctrs,
-                            int64_t *ctr_val, uint8_t *pod_flag)
+                            int64_t *ctr_val, int8_t *ctr_scale, uint8_t *pod_flag)
 {
     if (!podlist_json || !nodes || !n_items_out) return fail(ARENA_E_INVALID, "NULL argument");
     std::vector<arena_json::Range> ranges;
@@ -954,6 +964,8 @@ int arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const 
         if (pod_n_ctrs) pod_n_ctrs[k] = out.n_ctrs;
         if (ctr_val)
             for (int c = 0; c < kInlineCtrs; c++) ctr_val[k * kInlineCtrs + c] = (uint32_t)c < out.n_ctrs ? out.ctr_val[c] : 0;
+        if (ctr_scale)
+            for (int c = 0; c < kInlineCtrs; c++) ctr_scale[k * kInlineCtrs + c] = (uint32_t)c < out.n_ctrs ? out.ctr_scale[c] : 0;
     }
     return ARENA_OK;
 }

@@ -39,7 +39,7 @@ enum Flag : uint32_t {
     kFlagShape = 2,           // a field has a type the host rejects or treats specially
     kFlagEscapedKey = 3,      // a key with a backslash in a place where key names matter
     kFlagDuplicateKey = 4,    // last-wins is left to the host
-    kFlagQuantity = 5,        // a quantity outside the plain grammar, or a GPU quantity that is not plain digits
+    kFlagQuantity = 5,        // a quantity outside the plain grammar, or a GPU quantity off the reference's fast path
     kFlagTime = 6,            // creationTimestamp not in the API server's canonical form
     kFlagTooDeep = 7,
     kFlagTooManyContainers = 8,
@@ -90,7 +90,8 @@ struct PodOut {
     uint32_t node;                    // node id or kNoNode
     uint32_t n_ctrs;
     uint8_t phase;                    // ARENA_PHASE_*
-    int64_t ctr_val[kInlineCtrs];     // column encoding with scale 0
+    int64_t ctr_val[kInlineCtrs];     // column encoding: int64Amount.value ...
+    int8_t ctr_scale[kInlineCtrs];    // ... and .scale (resource/amount.go:57-60)
 };
 
 namespace detail {
@@ -254,6 +255,97 @@ ARENA_HD inline bool quantity_plain(const unsigned char *p, size_t n)
     const size_t e0 = j;
     while (j < n && is_digit(p[j])) j++;
     return j == n && j > e0 && j - e0 <= 9;
+}
+
+// A GPU quantity on the reference's FAST path (resource/quantity.go:276-343: sign, digits, one
+// decimal point, a suffix from suffix.go:88-106 or an e/E exponent; at most 18 significant digits;
+// scale >= -9; mantissa product inside int64) -> int64Amount{value, scale}, the column encoding the
+// host loader produces (quantity.cc: parse_quantity + column_encoding).  Anything else -- the inf.Dec
+// slow path, scales beyond +-18, malformed text -- returns false and the item is handed to the host.
+ARENA_HD inline bool quantity_fast(const unsigned char *s, uint32_t n, int64_t &amount, int8_t &scale_out)
+{
+    amount = 0;
+    scale_out = 0;
+    if (n == 0 || n > 40) return false;
+    uint32_t pos = 0;
+    bool positive = true;
+    if (s[0] == '-') { positive = false; pos = 1; }
+    else if (s[0] == '+') pos = 1;
+    if (pos >= n) return false;                                // a bare sign: the host decides
+    const uint32_t zeros_from = pos;
+    while (pos < n && s[pos] == '0') pos++;                    // leading zeros
+    if (pos >= n) return true;                                 // "0", "000", "-0": zero
+    const bool stripped = pos > zeros_from;
+    uint64_t v = 0;
+    uint32_t num_len = 0, denom_len = 0;
+    while (pos < n && is_digit(s[pos])) { if (num_len < 19) v = v * 10 + (uint64_t)(s[pos] - '0'); num_len++; pos++; }
+    if (pos < n && s[pos] == '.') {
+        pos++;
+        while (pos < n && is_digit(s[pos])) { if (num_len + denom_len < 19) v = v * 10 + (uint64_t)(s[pos] - '0'); denom_len++; pos++; }
+    }
+    if (!stripped && num_len == 0 && denom_len == 0) return false;   // no digit at all ("m", "."): the host decides
+    const uint32_t digits = (num_len ? num_len : 1u) + denom_len;   // an empty numerator reads as "0"
+    // suffix
+    int32_t exponent = 0;
+    bool binary = false;
+    const uint32_t left = n - pos;
+    if (left == 1) {
+        switch (s[pos]) {
+        case 'n': exponent = -9; break;
+        case 'u': exponent = -6; break;
+        case 'm': exponent = -3; break;
+        case 'k': exponent = 3; break;
+        case 'M': exponent = 6; break;
+        case 'G': exponent = 9; break;
+        case 'T': exponent = 12; break;
+        case 'P': exponent = 15; break;
+        case 'E': exponent = 18; break;
+        default: return false;
+        }
+    } else if (left == 2 && s[pos + 1] == 'i') {
+        binary = true;
+        switch (s[pos]) {
+        case 'K': exponent = 10; break;
+        case 'M': exponent = 20; break;
+        case 'G': exponent = 30; break;
+        case 'T': exponent = 40; break;
+        case 'P': exponent = 50; break;
+        case 'E': exponent = 60; break;
+        default: return false;
+        }
+    } else if (left >= 2) {
+        if (s[pos] != 'e' && s[pos] != 'E') return false;
+        uint32_t j = pos + 1;
+        bool eneg = false;
+        if (s[j] == '+' || s[j] == '-') { eneg = s[j] == '-'; j++; }
+        if (j >= n || n - j > 3) return false;                // up to three exponent digits: enough for every fast-path scale
+        int32_t e = 0;
+        for (; j < n; j++) {
+            if (!is_digit(s[j])) return false;
+            e = e * 10 + (int32_t)(s[j] - '0');
+        }
+        exponent = eneg ? -e : e;
+    }
+    int64_t scale = 0;
+    uint64_t mantissa = 1;
+    int32_t precision;
+    if (binary) {
+        if (denom_len) return false;                           // fractional binary-SI: slow path
+        mantissa = 1ull << exponent;
+        precision = 15 - (int32_t)(num_len ? num_len : 1u) - (exponent * 3) / 10 - 1;
+    } else {
+        scale = exponent;
+        precision = 18 - (int32_t)digits;
+    }
+    if (precision < 0) return false;
+    scale -= (int64_t)denom_len;
+    if (scale < -9 || scale > 18) return false;
+    // int64Multiply(v, mantissa): v < 10^18 < 2^60
+    if (v != 0 && mantissa != 1 && v > 0x7fffffffffffffffull / mantissa) return false;
+    const uint64_t r = v * mantissa;
+    amount = positive ? (int64_t)r : -(int64_t)r;
+    scale_out = (int8_t)scale;
+    return true;
 }
 
 // The API server's creationTimestamp: "YYYY-MM-DDTHH:MM:SSZ" with the field ranges
@@ -536,7 +628,8 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
     // GPU quantities wait on the list; a container points at the one that counts for it
     constexpr int16_t kAbsent = -1, kNull = -2;                         // no GPU key / "key": null => 0
     int16_t ctr_ref[kInlineCtrs];
-    int64_t gpu_value[2 * kInlineCtrs + 2];                              // evaluated W_GPU entries
+    int64_t gpu_value[2 * kInlineCtrs + 2];                              // evaluated W_GPU entries: amount ...
+    int8_t gpu_scale[2 * kInlineCtrs + 2];                               // ... and scale
     int n_gpu = 0;
     int16_t cur_ref = kAbsent, gpu_ref = kAbsent, dep_ref = kAbsent;
     bool gpu_present = false, dep_present = false;
@@ -782,15 +875,12 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
             if (!quantity_plain(p, d.len)) flag = kFlagQuantity;
             break;
         case W_GPU: {
-            // plain digits only: every other spelling of a GPU count is the host's business
+            // the fast-path grammar ("2", "500m", "1.5", "1e3", "1Ki"); the rest is the host's business
             int64_t v = 0;
-            bool digits = d.len >= 1 && d.len <= 15;
-            for (uint32_t q = 0; digits && q < d.len; q++) {
-                if (!is_digit(p[q])) digits = false;
-                else v = v * 10 + (p[q] - '0');
-            }
-            if (!digits) flag = kFlagQuantity;
+            int8_t sc = 0;
+            if (!quantity_fast(p, d.len, v, sc)) flag = kFlagQuantity;
             gpu_value[d.arg] = v;
+            gpu_scale[d.arg] = sc;
             break;
         }
         case W_TIME:
@@ -803,7 +893,10 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
     }
     if (!flag)
         for (uint32_t k = 0; k < n_ctrs && k < (uint32_t)kInlineCtrs; k++)
+        {
             out.ctr_val[k] = ctr_ref[k] >= 0 ? gpu_value[ctr_ref[k]] : 0;
+            out.ctr_scale[k] = ctr_ref[k] >= 0 ? gpu_scale[ctr_ref[k]] : (int8_t)0;
+        }
     out.flag = flag;
     out.phase = phase;
     out.n_ctrs = n_ctrs;

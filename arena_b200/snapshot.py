@@ -183,11 +183,14 @@ class HostSnapshot:
         phase = np.zeros(capacity, np.uint8)
         nctr = np.zeros(capacity, np.uint32)
         vals = np.zeros((capacity, 8), np.int64)
+        scales = np.zeros((capacity, 8), np.int8)
         flag = np.zeros(capacity, np.uint8)
         check(lib().arena_scan_podlist_host(podlist, len(podlist), self._h, capacity, C.byref(n), node.ctypes.data,
-                                            phase.ctypes.data, nctr.ctypes.data, vals.ctypes.data, flag.ctypes.data))
+                                            phase.ctypes.data, nctr.ctypes.data, vals.ctypes.data, scales.ctypes.data,
+                                            flag.ctypes.data))
         k = int(n.value)
-        return {"n": k, "node": node[:k], "phase": phase[:k], "n_ctrs": nctr[:k], "ctr_val": vals[:k], "flag": flag[:k]}
+        return {"n": k, "node": node[:k], "phase": phase[:k], "n_ctrs": nctr[:k], "ctr_val": vals[:k], "ctr_scale": scales[:k],
+                "flag": flag[:k]}
 
     def close(self) -> None:
         if self._h:

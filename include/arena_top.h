@@ -74,7 +74,7 @@ int  arena_load_json(const char *podlist_json, size_t podlist_len,
  *                  for any order and pick the ungrouped variant when it is faster)
  *
  * Anything a pod item contains that the device scanner does not decide itself -- escaped or
- * duplicate keys, a GPU quantity that is not plain digits, a timestamp that is not in the API
+ * duplicate keys, a GPU quantity off the reference's fast path (resource/quantity.go:276-343), a timestamp that is not in the API
  * server's canonical form, more than 8 containers, any malformed text -- makes the whole
  * document go through arena_load_json + arena_snapshot_upload instead: the columns, the
  * results and the error messages are those of the host loader either way, and
@@ -108,13 +108,13 @@ int  arena_load_json_device(const char *podlist_json, size_t podlist_len,
 /*
  * Diagnostic: the per-item scanner of arena_load_json_device (csrc/pod_scan.cuh, the same
  * source compiled for the host) over every element of .items, in PodList order.  `nodes`
- * is a snapshot loaded from the NodeList.  Arrays hold `capacity` pods (ctr_val: 8 values
- * per pod); pod_flag[k] != 0 means item k would be handed to the host loader.  Used by the
+ * is a snapshot loaded from the NodeList.  Arrays hold `capacity` pods (ctr_val / ctr_scale:
+ * 8 entries per pod, the int64Amount{value, scale} of each container's selected GPU limit); pod_flag[k] != 0 means item k would be handed to the host loader.  Used by the
  * CPU test-suite to compare the device code with the host loader without a GPU.
  */
 int  arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const arena_host_snapshot *nodes,
                              uint64_t capacity, uint64_t *n_items_out, uint32_t *pod_node, uint8_t *pod_phase,
-                             uint32_t *pod_n_ctrs, int64_t *ctr_val, uint8_t *pod_flag);
+                             uint32_t *pod_n_ctrs, int64_t *ctr_val, int8_t *ctr_scale, uint8_t *pod_flag);
 
 /*
  * Packs a host snapshot (arena_snapshot_view with HOST pointers, rows grouped by node as the

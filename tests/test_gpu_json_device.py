@@ -164,3 +164,22 @@ def test_many_nodes_and_unmatched_names(gpu):
         pod["metadata"]["managedFields"] = []
         items.append(pod)
     check_device_load(gpu, json.dumps({"items": items}).encode(), nodes, expect_fallback=False)
+
+
+def test_fractional_gpu_limits_stay_on_the_device(gpu):
+    """GPU-sharing pods ask for "500m" / "250m" (BASELINE configs[4]); a few write "1.5", "1e1", "2k".  The device
+    scanner parses the reference's fast-path quantity grammar itself, so such a PodList is NOT handed to the host,
+    and its columns carry the same {value, scale} pairs as the host loader's."""
+    pods, nodes = LT.make_docs(20_000, 200, seed=11)
+    doc = json.loads(pods)
+    rnd = __import__("random").Random(3)
+    changed = 0
+    for it in doc["items"]:
+        for c in it["spec"]["containers"]:
+            lim = c.get("resources", {}).get("limits")
+            if lim and "nvidia.com/gpu" in lim and rnd.random() < 0.1:
+                lim["nvidia.com/gpu"] = rnd.choice(["500m", "250m", "500m", "1500m", "1.5", "1e1", "2k", "0.5"])
+                changed += 1
+    assert changed > 200
+    stats = check_device_load(gpu, json.dumps(doc).encode(), nodes, expect_fallback=False)
+    assert stats["n_items"] == 20_000

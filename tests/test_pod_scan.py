@@ -58,7 +58,8 @@ def check_against_host(pods: bytes, nodes: bytes, n_items: int):
     for k, (node, phase, ctrs) in enumerate(want):
         if r["flag"][k]:
             continue
-        got = (int(r["node"][k]), int(r["phase"][k]), [(int(v), 0) for v in r["ctr_val"][k][:int(r["n_ctrs"][k])]])
+        n_c = int(r["n_ctrs"][k])
+        got = (int(r["node"][k]), int(r["phase"][k]), [(int(v), int(sc)) for v, sc in zip(r["ctr_val"][k][:n_c], r["ctr_scale"][k][:n_c])])
         assert got == (node, phase, ctrs), (k, got, (node, phase, ctrs))
     return True, int((r["flag"] != 0).sum())
 
@@ -79,6 +80,49 @@ def test_edge_case_fixture(built):
     ok, flagged = check_against_host(rd("pods.json"), rd("nodes.json"), n)
     assert ok
     assert flagged < n, "the scanner should decide most of the fixture itself"
+
+
+def test_gpu_quantities_on_the_fast_path_are_decided_by_the_scanner(built):
+    """The scanner parses the reference's fast-path grammar (quantity.go:276-343) itself: "500m", "1k", "1.5", "2Ki",
+    "1e3" ... give the same int64Amount{value, scale} as the host loader and are NOT handed back; the inf.Dec slow
+    path, out-of-range scales and malformed text are flagged (and then match the host by delegation)."""
+    import random
+    from arena_b200 import HostSnapshot
+    rnd = random.Random(5)
+    fast = ["0", "1", "8", "0008", "500m", "1500m", "2000m", "250m", "0.5", "1.5", ".5", "3.", "1k", "2M", "1G", "1e3", "1E3", "1e0",
+            "12e-1", "1.5e1", "+3", "-3", "-500m", "1Ki", "2Ki", "1Mi", "3Gi", "100u", "5n", "123456789012345678", "0m", "00", "1T", "2P",
+            "1E", "7e+2", "0.000000001", "999999999999999999"]
+    slow_or_bad = ["1.5Gi", "0.0000000001", "1234567890123456789", "10E", "1e30", "1e19", "1x", "", "e", "1.2.3", " 4", "4 ", "-", "m",
+                   "1Ei", "9Ei", "0.5Ki", "1e-10", "12345678901234567890"]
+    extra = []
+    for _ in range(300):
+        body = rnd.choice(["", "-", "+"]) + str(rnd.randrange(0, 10 ** rnd.randrange(1, 19)))
+        if rnd.random() < 0.4:
+            body += "." + "".join(rnd.choice("0123456789") for _ in range(rnd.randrange(0, 6)))
+        body += rnd.choice(["", "", "m", "k", "M", "Ki", "Gi", "n", "u", "e3", "E-2", "e+5", "G", "T", "P", "E", "Ti"])
+        extra.append(body)
+    allq = fast + slow_or_bad + extra
+    nodes = json.dumps({"items": [{"metadata": {"name": "n0"}, "status": {"capacity": {"nvidia.com/gpu": "8"}}}]}).encode()
+    hn = HostSnapshot.from_json(b'{"items":[]}', nodes)
+    n_fast_unflagged = 0
+    for q in allq:
+        pod = {"metadata": {"name": "p"}, "spec": {"nodeName": "n0", "containers": [{"resources": {"limits": {"nvidia.com/gpu": q}}}]},
+               "status": {"phase": "Running"}}
+        doc = json.dumps({"items": [pod]}).encode()
+        r = hn.scan_podlist(doc, 4)
+        try:
+            h = HostSnapshot.from_json(doc, nodes)
+        except Exception:
+            assert r["flag"][0] != 0, f"{q!r}: the host rejects it but the scanner decided it"
+            continue
+        if r["flag"][0]:
+            assert q not in fast, f"{q!r} is on the fast path but was handed back"
+            continue
+        want = (int(h.cols["ctr_val"][0]), int(h.cols["ctr_scale"][0]))
+        got = (int(r["ctr_val"][0][0]), int(r["ctr_scale"][0][0]))
+        assert got == want, (q, got, want)
+        n_fast_unflagged += q in fast
+    assert n_fast_unflagged == len(fast)
 
 
 # ---- mutation fuzz ------------------------------------------------------------------------
