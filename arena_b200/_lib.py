@@ -48,6 +48,7 @@ class LoadDeviceStats(C.Structure):
     _fields_ = [
         ("n_items", C.c_uint64), ("flagged_item", C.c_uint64), ("flag_reason", C.c_uint32), ("fell_back", C.c_uint32),
         ("ms_h2d", C.c_double), ("ms_structure", C.c_double), ("ms_items", C.c_double), ("ms_device", C.c_double),
+        ("n_handed_back", C.c_uint64),
     ]
 
 

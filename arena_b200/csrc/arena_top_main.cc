@@ -112,9 +112,12 @@ int main(int argc, char **argv)
         arena_free_text(text);
         if (timing) {
             auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+            char how[96];
+            if (st.fell_back) snprintf(how, sizeof how, "host loader took over");
+            else if (st.n_handed_back) snprintf(how, sizeof how, "parsed on the GPU, %llu items handed back to the host", (unsigned long long)st.n_handed_back);
+            else snprintf(how, sizeof how, "parsed on the GPU");
             fprintf(stderr, "[arena-top] pods=%llu nodes=%llu  device load %.2f ms (%s; copy %.2f ms), query+format %.2f ms\n",
-                    (unsigned long long)counts[0], (unsigned long long)counts[2], ms(t0, t1),
-                    st.fell_back ? "host loader took over" : "parsed on the GPU", st.ms_h2d, ms(t1, t2));
+                    (unsigned long long)counts[0], (unsigned long long)counts[2], ms(t0, t1), how, st.ms_h2d, ms(t1, t2));
         }
         arena_snapshot_free(dev);
         arena_host_snapshot_free(node_names);

@@ -39,6 +39,18 @@ struct JobMeta {
     int64_t start_unix = 0;
 };
 
+// One PodList item through the HOST parser (json.cc + loader.cc extract_pod): what the GPU loader
+// calls for the few items its per-pod scanner hands back.  parse() returns false on ANY failure --
+// the caller then runs the whole document through the host loader, which owns every error message.
+struct PodItemParser {
+    explicit PodItemParser(const std::vector<std::string> &node_names);
+    ~PodItemParser();
+    bool parse(const char *text, size_t text_len, size_t begin, size_t end, uint32_t &node, uint8_t &phase,
+               std::vector<int64_t> &ctr_val, std::vector<int8_t> &ctr_scale);
+    struct Impl;
+    Impl *impl;
+};
+
 }  // namespace arena_host
 
 struct arena_host_snapshot {

@@ -431,10 +431,35 @@ __global__ void __launch_bounds__(kCta) gather_columns_kernel(u64 n_items, const
     const u64 b = ctr_begin64[p];
     pod_ctr_begin[p] = (u32)b;
     const u32 n = (u32)pod_nctr[p];
-    for (u32 k = 0; k < n; k++) {
+    // (an item the host parsed may hold more containers than the inline slots: those are patched in afterwards)
+    for (u32 k = 0; k < n && k < (u32)kInlineCtrs; k++) {
         ctr_val[b + k] = ctr_tmp[(u64)k * n_items + p];
         ctr_scale[b + k] = scale_tmp[(u64)k * n_items + p];
     }
+}
+
+// ---- items handed back to the host: their rows patched into the device arrays ----------------------
+struct PodPatch { u32 item, node, n_ctrs, phase; };
+__global__ void apply_pod_patches_kernel(const PodPatch *__restrict__ patch, u32 n, u32 *__restrict__ pod_node,
+                                         unsigned char *__restrict__ pod_phase, u64 *__restrict__ pod_nctr)
+{
+    const u32 k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const PodPatch p = patch[k];
+    pod_node[p.item] = p.node;
+    pod_phase[p.item] = (unsigned char)p.phase;
+    pod_nctr[p.item] = p.n_ctrs;
+}
+struct CtrPatch { u32 item, k; long long val; long long scale; };
+__global__ void apply_ctr_patches_kernel(const CtrPatch *__restrict__ patch, u32 n, const u32 *__restrict__ pod_ctr_begin,
+                                         long long *__restrict__ ctr_val, signed char *__restrict__ ctr_scale)
+{
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const CtrPatch p = patch[i];
+    const u64 at = (u64)pod_ctr_begin[p.item] + p.k;
+    ctr_val[at] = p.val;
+    ctr_scale[at] = (signed char)p.scale;
 }
 
 // =================================== host side ====================================================
@@ -782,6 +807,8 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     u64 *d_nctr = nullptr, *d_ctr_begin64 = nullptr, *d_tile_sums2 = nullptr;
     long long *d_ctr_tmp = nullptr;
     signed char *d_scale_tmp = nullptr;
+    CtrPatch *d_ctr_patches = nullptr;
+    u32 n_ctr_patches = 0;
     u64 C = 0;
     if (P) {
         CUDA_TRY(bufs.alloc(&d_pod_node_tmp, P * 4));
@@ -819,13 +846,51 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         CUDA_TRY(cudaStreamSynchronize(st));
         if (stats) { stats->n_items = P; stats->ms_items = ms_since(t_start); }
         if (res->any_flag) {
-            if (stats) {
-                stats->flagged_item = res->first_flag_item;
-                unsigned char reason = 0;
-                cudaMemcpy(&reason, d_pod_flag + res->first_flag_item, 1, cudaMemcpyDeviceToHost);
-                stats->flag_reason = reason;
+            // Only the flagged items go to the host: each is parsed by the host loader's own item code
+            // (json.cc parse_range + loader.cc extract_pod) and its row is patched into the device arrays.
+            // Should one of them fail there -- or should there be very many -- the whole document takes
+            // the host path, which then reports the error exactly as a sequential decode would.
+            std::vector<unsigned char> flags(P);
+            std::vector<u32> ib(P), ie(P);
+            CUDA_TRY(cudaMemcpyAsync(flags.data(), d_pod_flag, P, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(ib.data(), d_item_begin, P * 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(ie.data(), d_item_end, P * 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (stats) { stats->flagged_item = res->first_flag_item; stats->flag_reason = flags[res->first_flag_item]; }
+            std::vector<PodPatch> pod_patches;
+            std::vector<CtrPatch> ctr_patches;
+            arena_host::PodItemParser parser(nodes->node_names);
+            std::vector<int64_t> pv;
+            std::vector<int8_t> ps;
+            const u64 max_handed = std::max<u64>(64, P / 8);
+            bool give_up = false;
+            for (u64 k = 0; k < P && !give_up; k++) {
+                if (!flags[k]) continue;
+                if (flags[k] == kFlagSeparator || pod_patches.size() >= max_handed) { give_up = true; break; }
+                uint32_t node = 0;
+                uint8_t phase = 0;
+                if (!parser.parse(podlist, len, ib[k], ie[k], node, phase, pv, ps)) { give_up = true; break; }
+                pod_patches.push_back(PodPatch{(u32)k, node, (u32)pv.size(), phase});
+                for (size_t c = 0; c < pv.size(); c++) ctr_patches.push_back(CtrPatch{(u32)k, (u32)c, (long long)pv[c], (long long)ps[c]});
             }
-            return ARENA_OK;
+            if (give_up) return ARENA_OK;                        // handled stays false: host loader + upload
+            PodPatch *d_pp = nullptr;
+            CUDA_TRY(bufs.alloc(&d_pp, pod_patches.size() * sizeof(PodPatch)));
+            CUDA_TRY(cudaMemcpyAsync(d_pp, pod_patches.data(), pod_patches.size() * sizeof(PodPatch), cudaMemcpyHostToDevice, st));
+            apply_pod_patches_kernel<<<(unsigned)((pod_patches.size() + 255) / 256), 256, 0, st>>>(d_pp, (u32)pod_patches.size(), d_pod_node_tmp,
+                                                                                               d_pod_phase_tmp, d_nctr);
+            arena_internal::add_launches(1);
+            rc = exclusive_scan(d_nctr, P, d_ctr_begin64, d_tile_sums2, &d_res->n_containers, st);
+            if (rc) return rc;
+            CUDA_TRY(cudaMemcpyAsync(res, d_res, offsetof(ScanResult, root_open), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (!ctr_patches.empty()) {
+                CUDA_TRY(bufs.alloc(&d_ctr_patches, ctr_patches.size() * sizeof(CtrPatch)));
+                CUDA_TRY(cudaMemcpyAsync(d_ctr_patches, ctr_patches.data(), ctr_patches.size() * sizeof(CtrPatch), cudaMemcpyHostToDevice, st));
+                CUDA_TRY(cudaStreamSynchronize(st));             // the vector goes out of scope below
+                n_ctr_patches = (u32)ctr_patches.size();
+            }
+            if (stats) stats->n_handed_back = pod_patches.size();
         }
         C = res->n_containers;
     }
@@ -847,7 +912,10 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         gather_columns_kernel<<<(unsigned)((P + kCta - 1) / kCta), kCta, 0, st>>>(P, d_ctr_begin64, d_nctr, d_ctr_tmp, d_scale_tmp, C,
                                                                                  (u32 *)(block + o_cb), (long long *)(block + o_val),
                                                                                  (signed char *)(block + o_scale));
-        arena_internal::add_launches(1);
+        if (n_ctr_patches)
+            apply_ctr_patches_kernel<<<(n_ctr_patches + 255) / 256, 256, 0, st>>>(d_ctr_patches, n_ctr_patches, (const u32 *)(block + o_cb),
+                                                                               (long long *)(block + o_val), (signed char *)(block + o_scale));
+        arena_internal::add_launches(1 + (n_ctr_patches ? 1 : 0));
         step(cudaGetLastError());
     }
     if (N) {

@@ -755,6 +755,48 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
 
 }  // namespace
 
+namespace arena_host {
+
+struct PodItemParser::Impl {
+    std::unordered_map<std::string, uint32_t> node_id;
+    arena_json::Tree item;
+};
+
+PodItemParser::PodItemParser(const std::vector<std::string> &node_names) : impl(new Impl())
+{
+    impl->node_id.reserve(node_names.size() * 2);
+    for (size_t n = 0; n < node_names.size(); n++) impl->node_id.emplace(node_names[n], (uint32_t)n);   // first wins, as in load()
+}
+
+PodItemParser::~PodItemParser() { delete impl; }
+
+bool PodItemParser::parse(const char *text, size_t text_len, size_t begin, size_t end, uint32_t &node, uint8_t &phase,
+                          std::vector<int64_t> &ctr_val, std::vector<int8_t> &ctr_scale)
+{
+    try {
+        arena_json::ParseOptions opt;
+        opt.filter = keep_core;
+        arena_json::ParseError e;
+        arena_json::Range r;
+        r.begin = begin;
+        r.end = end;
+        if (!arena_json::parse_range(std::string_view(text, text_len), r, 2, "items", impl->item, e, opt)) return false;
+        PodRec rec;
+        extract_pod(impl->item.root(), rec, impl->node_id);
+        node = rec.node;
+        phase = rec.phase;
+        ctr_val = std::move(rec.ctr_val);
+        ctr_scale = std::move(rec.ctr_scale);
+        return true;
+    } catch (const LoadError &) {
+        return false;
+    } catch (const std::bad_alloc &) {
+        return false;
+    }
+}
+
+}  // namespace arena_host
+
 extern "C" {
 
 int arena_load_json(const char *podlist_json, size_t podlist_len, const char *nodelist_json, size_t nodelist_len,

@@ -73,12 +73,14 @@ int  arena_load_json(const char *podlist_json, size_t podlist_len,
  *   snapshot_out   device snapshot, rows in PodList order (the accounting kernels are exact
  *                  for any order and pick the ungrouped variant when it is faster)
  *
- * Anything a pod item contains that the device scanner does not decide itself -- escaped or
- * duplicate keys, a GPU quantity off the reference's fast path (resource/quantity.go:276-343), a timestamp that is not in the API
- * server's canonical form, more than 8 containers, any malformed text -- makes the whole
- * document go through arena_load_json + arena_snapshot_upload instead: the columns, the
- * results and the error messages are those of the host loader either way, and
- * stats->fell_back says which path ran.  Needs arena_acct_init(); there is no CPU stand-in
+ * A pod item that holds something the device scanner does not decide itself -- escaped or
+ * duplicate keys, a GPU quantity off the reference's fast path (resource/quantity.go:276-343),
+ * a timestamp that is not in the API server's canonical form, more than 8 containers -- is
+ * handed back ALONE: the host loader's item code parses it and its row is patched into the
+ * device columns (stats->n_handed_back).  Malformed text, an item the host rejects, or more
+ * than an eighth of the items flagged make the whole document go through arena_load_json +
+ * arena_snapshot_upload instead: the columns, the results and the error messages are those
+ * of the host loader either way, and stats->fell_back says which path ran.  Needs arena_acct_init(); there is no CPU stand-in
  * for the device (ARENA_E_NOT_INIT / ARENA_E_CUDA).  PodLists of 4 GiB and more take the
  * host path.
  */
@@ -92,6 +94,7 @@ typedef struct arena_load_device_stats {
     double   ms_structure;    /* + structural scan (3 kernels) */
     double   ms_items;        /* + envelope on the host, item ranges, one thread per pod, CSR offsets */
     double   ms_device;       /* + final columns: the whole device path */
+    uint64_t n_handed_back;   /* items the device scanner flagged and the host parsed one by one (device path kept) */
 } arena_load_device_stats;
 
 /* Page-locked host memory for documents: reading the API server's response straight into
