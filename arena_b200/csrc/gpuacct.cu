@@ -966,7 +966,15 @@ static int top_node_packed_native(const arena_packed_view *h, int64_t *node_tota
     }
     cudaStream_t up = ctx().stream, run = ctx().pipe_stream[0], down = ctx().pipe_stream[1];
     // chunk boundaries in nodes: equal shares of the rows (a node is never cut)
-    const int chunks = (P >= (4u << 20) && N >= (u64)kPackedChunks) ? kPackedChunks : 1;
+    // about 8 Mi rows per chunk, eight chunks at most: below that the per-copy overheads of a chunk
+    // (five uploads, a launch, three downloads) outweigh what the overlap hides
+    u64 chunk_rows = 8u << 20;
+    if (const char *env = getenv("ARENA_PACKED_CHUNK_PODS")) {           // tuning aid (and the tests' way to pipeline small inputs)
+        const long long v = atoll(env);
+        if (v > 0) chunk_rows = (u64)v;
+    }
+    int chunks = (int)std::min<u64>((u64)kPackedChunks, P / chunk_rows);
+    if (chunks < 1 || N < (u64)kPackedChunks) chunks = 1;
     u64 cut[kPackedChunks + 1];
     cut[0] = 0;
     for (int k = 1; k < chunks; k++) {

@@ -195,7 +195,7 @@ int  arena_peer_exchange_collect(int64_t *d_cluster, void *stream);
  * A snapshot with a pod of more than 15 containers, a container above 255 GPUs or pods that
  * are not grouped has no packed form: use the wide one (arena_host_snapshot_pack says so).
  * The summary (pod_gpu == NULL) is computed straight from the packed columns, one half-warp per
- * node, and pipelined: the node range is cut into eight chunks whose uploads, kernels and
+ * node, and pipelined: a large node range (from 16 Mi pods) is cut into up to eight chunks whose uploads, kernels and
  * downloads overlap (page-locked buffers, arena_pinned_alloc, make the copies asynchronous); with pod_gpu (per row, as in arena_top_node) the columns are first expanded into the
  * wide layout on the device and the ordinary kernels run on that.  No reference counterpart.
  */

@@ -136,10 +136,11 @@ def test_packed_path_on_the_json_fixture(gpu):
 
 
 @pytest.mark.gpu
-def test_packed_one_shot_call_is_pipelined_above_4m_pods(gpu):
-    """From 4 Mi pods up the one-shot call cuts the node range into eight chunks whose uploads, kernels and
-    downloads overlap; page-locked and ordinary buffers, uniform and skewed (giant nodes straddle nothing: a
-    node is never cut, its pieces go with its chunk)."""
+def test_packed_one_shot_call_is_pipelined(gpu, monkeypatch):
+    """Large snapshots (8 Mi pods per chunk; here the threshold is lowered) are cut into up to eight node-range
+    chunks whose uploads, kernels and downloads overlap; page-locked and ordinary buffers, uniform and skewed
+    (giant nodes straddle nothing: a node is never cut, its pieces go with its chunk)."""
+    monkeypatch.setenv("ARENA_PACKED_CHUNK_PODS", "700000")
     for skewed, seed in ((False, 17), (True, 5)):
         h = gpu.HostSnapshot.synth(6_000_000, 60_000, seed=seed, skewed=skewed)
         tot, alloc, cl, _ = cref.top_node_columnar(h.cols)
