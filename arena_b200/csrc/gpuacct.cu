@@ -35,6 +35,7 @@ struct Context {
     int device = -1;
     int sm_count = 0;
     int pods_ctas_per_sm = 0;
+    int staged_ctas_per_sm = 0;      // > 0: the bulk-copy staged top-node kernel is used for grouped summaries
     int jobs_ctas_per_sm = 0;
     int packed_ctas_per_sm = 0;
     cudaStream_t stream = nullptr;
@@ -137,6 +138,11 @@ static int init_current_slot(int device)
     ctx().device = device;
     ctx().sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
+    {
+        const char *env = getenv("ARENA_STAGED");                    // A/B switch while the variant is evaluated
+        if (env && env[0] == '1')
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().staged_ctas_per_sm, top_node_pods_staged_kernel, kThreads, 0));
+    }
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().jobs_ctas_per_sm, job_pods_kernel, kThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().packed_ctas_per_sm, top_node_packed_kernel<4>, kThreads, 0));
     if (ctx().pods_ctas_per_sm < 1 || ctx().jobs_ctas_per_sm < 1 || ctx().packed_ctas_per_sm < 1)
@@ -338,7 +344,12 @@ int launch_top_node(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i64 *d_
         else e = launch_pods(top_node_pods_kernel<false, true>, gp, pa, st);
     } else {
         if (s->direct) e = launch_pods(top_node_pods_kernel<true, false>, gp, pa, st);
-        else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
+        else if (ctx().staged_ctas_per_sm > 0) {
+            // the pod columns staged one iteration ahead by the bulk-copy engine (kernels.cuh)
+            int gs = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().staged_ctas_per_sm);
+            if (gn > gs) gs = std::min(gn, ctx().sm_count * ctx().staged_ctas_per_sm);
+            e = launch_pods(top_node_pods_staged_kernel, gs, pa, st);
+        } else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
     }
     if (e != cudaSuccess) return fail(ARENA_E_CUDA, "top-node kernel launch: %s", cudaGetErrorString(e));
     count_launch();

@@ -929,6 +929,212 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.px_lag);
 }
 
+// ---------------------------------------------------------------------------
+// The same summary kernel with the three POD columns staged by the bulk-copy engine (TMA), one
+// iteration ahead.  The eight tiles a CTA works on in one iteration are 1024 consecutive pods, so
+// their offsets, node ids and phases are three contiguous spans (4 KB + 4 KB + 1 KB): one thread
+// requests the NEXT iteration's spans with three cp.async.bulk copies (no LSU request, no register)
+// while the warps work on the current ones out of shared memory.  What remains per tile is ONE
+// dependent global phase, the container rows.  Two stages, an mbarrier pair per stage: `full`
+// (transaction bytes of the copies) and `empty` (one arrival per warp when it has read its tile).
+// Grouped input, summary only (no pod_gpu, no per-pod adds): the launcher picks it for that case.
+// ---------------------------------------------------------------------------
+constexpr int kStagePods = kWarps * kWarpPods;                 // 1024 pods per CTA iteration
+constexpr int kStageBytes = kStagePods * 9;                    // offsets + node ids + phases
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(u64 *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+// bounded: a copy that never lands must not hang the GPU (a trap fails the launch instead)
+__device__ __forceinline__ void mbar_wait(u64 *bar, unsigned parity)
+{
+    const unsigned addr = smem_u32(bar);
+    for (unsigned spins = 0;; spins++) {
+        unsigned done;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+        if (spins > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, unsigned bytes, u64 *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_staged_kernel(const __grid_constant__ PodsArgs a)
+{
+    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
+    __shared__ __align__(128) unsigned char s_stage[2][kStageBytes];
+    __shared__ __align__(8) u64 s_full[2], s_empty[2];
+    __shared__ u64 s_wa[kWarps];
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const unsigned FULL = 0xffffffffu;
+    unsigned *pre32 = reinterpret_cast<unsigned *>(s_prefix[warp]);
+
+    const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
+    const unsigned n_full = (unsigned)(a.P / kWarpPods);
+    const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
+    const unsigned n_blocks = (n_tiles + kWarps - 1) / kWarps;     // CTA iterations in the whole launch
+
+    if (threadIdx.x == 0) {
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1);
+        mbar_init(&s_empty[0], kWarps); mbar_init(&s_empty[1], kWarps);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    // the full tiles of block `blk`, as bytes of each column, into stage `st`
+    auto request = [&](unsigned blk, int st) {
+        const u64 first = (u64)blk * kStagePods;
+        const u64 lim = (u64)n_full * kWarpPods;
+        if (first >= lim) return;                                  // no full tile in this block: nobody will wait
+        const unsigned pods = (unsigned)(lim - first < (u64)kStagePods ? lim - first : (u64)kStagePods);
+        unsigned char *dst = s_stage[st];
+        mbar_expect_tx(&s_full[st], pods * 9u);
+        bulk_load(dst, a.pod_ctr_begin + first, pods * 4u, &s_full[st]);
+        bulk_load(dst + kStagePods * 4, a.pod_key + first, pods * 4u, &s_full[st]);
+        bulk_load(dst + kStagePods * 8, a.pod_phase + first, pods, &s_full[st]);
+    };
+    if (threadIdx.x == 0 && blockIdx.x < n_blocks) request(blockIdx.x, 0);
+
+    u64 acc_alloc = 0;
+    unsigned it = 0;
+    for (unsigned blk = blockIdx.x; blk < n_blocks; blk += gridDim.x, it++) {
+        const int st = (int)(it & 1u);
+        if (threadIdx.x == 0 && blk + gridDim.x < n_blocks) {      // the next iteration's spans
+            if (it >= 1) mbar_wait(&s_empty[st ^ 1], ((it - 1) >> 1) & 1u);
+            request(blk + gridDim.x, st ^ 1);
+        }
+        const unsigned tile = blk * kWarps + warp;
+        u64 tile_alloc = 0;
+        if (tile < n_tiles) {
+            bool fast = tile < n_full;
+            if (fast) {
+                const u64 q = (u64)tile * kWarpPods + (u64)lane * kPodsPerLane;
+                unsigned cb4 = 0;
+                if (lane == 31) cb4 = __ldg(a.pod_ctr_begin + q + kPodsPerLane);
+                mbar_wait(&s_full[st], (it >> 1) & 1u);
+                const unsigned char *sg = s_stage[st];
+                const uint4 c4 = *reinterpret_cast<const uint4 *>(sg + (warp * kWarpPods + lane * kPodsPerLane) * 4);
+                {
+                    const unsigned nxt = __shfl_down_sync(FULL, c4.x, 1);
+                    if (lane != 31) cb4 = nxt;
+                }
+                const unsigned wc0 = __shfl_sync(FULL, c4.x, 0);
+                const unsigned wc1 = __shfl_sync(FULL, cb4, 31);
+                const unsigned base = wc0 & ~15u;
+                const unsigned span = wc1 - base;
+                fast = span <= (unsigned)kChunkCtrs && (u64)base + kChunkCtrs <= a.C;
+                if (fast) {
+                    const unsigned i0 = base + 2u * lane;
+                    const bool two = span > (unsigned)kFastRow;
+                    const ulonglong2 vA0 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0));
+                    const ulonglong2 vB0 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kHalf));
+                    unsigned s0 = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0));
+                    s0 |= (unsigned)__ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kHalf)) << 16;
+                    ulonglong2 vA1, vB1;
+                    unsigned s1 = 0;
+                    vA1.x = vA1.y = vB1.x = vB1.y = 0;
+                    if (two) {
+                        vA1 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow));
+                        vB1 = ldg_stream(reinterpret_cast<const ulonglong2 *>(a.ctr_val + i0 + kFastRow + kHalf));
+                        s1 = __ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow));
+                        s1 |= (unsigned)__ldg(reinterpret_cast<const unsigned short *>(a.ctr_scale + i0 + kFastRow + kHalf)) << 16;
+                    }
+                    bool bad = ((vA0.x | vA0.y | vB0.x | vB0.y | vA1.x | vA1.y | vB1.x | vB1.y) >> kSmallBits) != 0ull;
+                    bad |= (c4.x > c4.y) | (c4.y > c4.z) | (c4.z > c4.w) | (c4.w > cb4);
+                    fast = !__any_sync(FULL, bad);
+                    if (fast) {
+                        unsigned total = fast_row((unsigned)vA0.x, (unsigned)vA0.y, (unsigned)vB0.x, (unsigned)vB0.y, s0,
+                                                  0u, pre32, lane, bad);
+                        if (two)
+                            total = fast_row((unsigned)vA1.x, (unsigned)vA1.y, (unsigned)vB1.x, (unsigned)vB1.y, s1,
+                                             total, pre32 + kFastRow, lane, bad);
+                        fast = !__any_sync(FULL, bad);
+                    }
+                    if (fast) {
+                        __syncwarp();
+                        const unsigned b0 = pre32[c4.x - base], b1 = pre32[c4.y - base], b2 = pre32[c4.z - base],
+                                       b3 = pre32[c4.w - base], b4 = pre32[cb4 - base];
+                        __syncwarp();
+                        const unsigned g0 = b1 - b0, g1 = b2 - b1, g2 = b3 - b2, g3 = b4 - b3;
+                        const uint4 k4 = *reinterpret_cast<const uint4 *>(sg + kStagePods * 4 + (warp * kWarpPods + lane * kPodsPerLane) * 4);
+                        const unsigned ph4 = *reinterpret_cast<const unsigned *>(sg + kStagePods * 8 + warp * kWarpPods + lane * kPodsPerLane);
+                        const unsigned a0 = (k4.x < K32 && phase_active(ph4 & 0xffu)) ? g0 : 0u;
+                        const unsigned a1 = (k4.y < K32 && phase_active((ph4 >> 8) & 0xffu)) ? g1 : 0u;
+                        const unsigned a2 = (k4.z < K32 && phase_active((ph4 >> 16) & 0xffu)) ? g2 : 0u;
+                        const unsigned a3 = (k4.w < K32 && phase_active(ph4 >> 24)) ? g3 : 0u;
+                        const unsigned S0 = a0, S1 = S0 + a1, S2 = S1 + a2, S3 = S2 + a3;
+                        const unsigned inc = warp_inclusive_scan_u32(S3);
+                        const unsigned off = inc - S3;
+                        tile_alloc = inc;
+                        unsigned key_next = __shfl_down_sync(FULL, k4.x, 1);
+                        if (lane == 31) key_next = kNone;
+                        const bool e0 = k4.x != k4.y, e1 = k4.y != k4.z, e2 = k4.z != k4.w;
+                        const bool e3 = (k4.w != key_next) & (lane != 31);
+                        if (lane == 31 && k4.w < K32) red_add_u64(a.key_alloc + k4.w, (u64)(off + S3));
+                        if (e0 | e1 | e2 | e3) {
+                            if (e0) {
+                                const u64 v = off + S0;
+                                if (k4.x < K32) red_add_u64(a.key_alloc + k4.x, v);
+                                if (k4.y < K32) red_add_u64(a.key_alloc + k4.y, 0ull - v);
+                            }
+                            if (e1) {
+                                const u64 v = off + S1;
+                                if (k4.y < K32) red_add_u64(a.key_alloc + k4.y, v);
+                                if (k4.z < K32) red_add_u64(a.key_alloc + k4.z, 0ull - v);
+                            }
+                            if (e2) {
+                                const u64 v = off + S2;
+                                if (k4.z < K32) red_add_u64(a.key_alloc + k4.z, v);
+                                if (k4.w < K32) red_add_u64(a.key_alloc + k4.w, 0ull - v);
+                            }
+                            if (e3) {
+                                const u64 v = off + S3;
+                                if (k4.w < K32) red_add_u64(a.key_alloc + k4.w, v);
+                                if (key_next < K32) red_add_u64(a.key_alloc + key_next, 0ull - v);
+                            }
+                        }
+                    }
+                }
+            }
+            if (!fast) tile_alloc = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+            if (lane == 31) acc_alloc += tile_alloc;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[st]);                  // this warp is done with the stage
+    }
+
+    u64 cap_sum = 0;
+    for (u64 n = (u64)blockIdx.x * blockDim.x + threadIdx.x; n < a.n_nodes; n += (u64)gridDim.x * blockDim.x) {
+        const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
+        a.node_total[n] = t;
+        cap_sum += (u64)t;
+    }
+    cap_sum = warp_reduce_sum(cap_sum);
+    __shared__ u64 s_wc[kWarps];
+    if (lane == 31) s_wa[warp] = acc_alloc;
+    if (lane == 0) s_wc[warp] = cap_sum;
+    __syncthreads();
+    u64 block_a = 0, block_c = 0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
+    finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.px_lag);
+}
+
 // The totals of the most recent step (posted by the launches of every rank) summed into out = {total capacity,
 // allocated} (the mailbox carries them in the kernel's order: allocated first): the end of a
 // sequence of deferred-collection steps.  One CTA of 32 threads.
