@@ -381,7 +381,8 @@ oracle_aos *oracle_aos_from_columnar(uint64_t P, uint64_t N,
     a->pods = (oracle_pod *)calloc(P ? P : 1, sizeof(oracle_pod));
     a->nodes = (oracle_node *)calloc(N ? N : 1, sizeof(oracle_node));
     a->containers = (oracle_container *)calloc(C ? C : 1, sizeof(oracle_container));
-    a->limits = (oracle_limit *)calloc((C + N) ? (C + N) : 1, sizeof(oracle_limit));
+    /* up to two limits per container (see below), one per node */
+    a->limits = (oracle_limit *)calloc((2 * C + N) ? (2 * C + N) : 1, sizeof(oracle_limit));
     a->names = (char *)malloc((N + 2) * 16);
     for (uint64_t n = 0; n < N; n++) {
         char *nm = a->names + n * 16;
@@ -392,19 +393,40 @@ oracle_aos *oracle_aos_from_columnar(uint64_t P, uint64_t N,
         nm[12] = 0;
         a->nodes[n].name = nm;
         a->nodes[n].n_capacity = 1;
-        a->limits[C + n].key = KEY_PRIMARY;
-        a->limits[C + n].value = node_cap_val[n];
-        a->limits[C + n].scale = node_cap_scale[n];
-        a->nodes[n].capacity = &a->limits[C + n];
+        /* every third node advertises its GPUs under the deprecated key only (gpu.go:28-37) */
+        a->limits[2 * C + n].key = n % 3 == 2 ? KEY_DEPRECATED : KEY_PRIMARY;
+        a->limits[2 * C + n].value = node_cap_val[n];
+        a->limits[2 * C + n].scale = node_cap_scale[n];
+        a->nodes[n].capacity = &a->limits[2 * C + n];
     }
     char *empty = a->names + N * 16; empty[0] = 0;
     char *ghost = a->names + (N + 1) * 16; memcpy(ghost, "ghost-node", 11);
+    /* The columnar form carries the limit of the SELECTED key.  The structs spread it over the spellings
+     * the selection rule has to see through (gpu.go:61-79: presence of the primary key decides):
+     *   c % 8 == 5   only the deprecated key carries the limit
+     *   c % 8 == 6   both keys: the primary one carries the limit, the deprecated one a decoy (value + 1)
+     *   c % 8 == 7   an unrelated key ("cpu") in front of the primary one
+     *   otherwise    the primary key alone */
+    static const char KEY_CPU[] = "cpu";
     for (uint64_t c = 0; c < C; c++) {
-        a->limits[c].key = KEY_PRIMARY;
-        a->limits[c].value = ctr_val[c];
-        a->limits[c].scale = ctr_scale[c];
+        oracle_limit *l = &a->limits[2 * c];
+        const unsigned shape = (unsigned)(c % 8);
+        l[0].value = ctr_val[c]; l[0].scale = ctr_scale[c];
+        a->containers[c].limits = l;
         a->containers[c].n_limits = 1;
-        a->containers[c].limits = &a->limits[c];
+        if (shape == 5) {
+            l[0].key = KEY_DEPRECATED;
+        } else if (shape == 6) {
+            l[0].key = KEY_DEPRECATED; l[0].value = ctr_val[c] + 1;
+            l[1].key = KEY_PRIMARY; l[1].value = ctr_val[c]; l[1].scale = ctr_scale[c];
+            a->containers[c].n_limits = 2;
+        } else if (shape == 7) {
+            l[0].key = KEY_CPU; l[0].value = 64; l[0].scale = 0;
+            l[1].key = KEY_PRIMARY; l[1].value = ctr_val[c]; l[1].scale = ctr_scale[c];
+            a->containers[c].n_limits = 2;
+        } else {
+            l[0].key = KEY_PRIMARY;
+        }
     }
     for (uint64_t p = 0; p < P; p++) {
         uint32_t n = pod_node[p];

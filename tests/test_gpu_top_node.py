@@ -305,3 +305,28 @@ def test_pageable_columns_take_the_staged_upload(gpu):
     assert np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
     res = gpu.top_node_packed(host.pack(pinned=False))
     assert np.array_equal(res.node_alloc, alloc) and np.array_equal(res.cluster, cl)
+
+
+def test_bulk_copy_staged_variant_is_exact(gpu):
+    """ARENA_STAGED=1 selects top_node_pods_staged_kernel (pod columns staged one iteration ahead by
+    cp.async.bulk into an mbarrier ring; slower than the shipped kernel, kept with its evidence in
+    profiles/r02_iterations.md).  The switch is read at arena_acct_init, so the check runs in a child."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np, arena_b200 as ab\n"
+        "from oracle import cref\n"
+        "ab.init(0)\n"
+        "for P, N, seed, kw in [(1_000_000, 10_000, 1, {}), (129, 3, 2, {}), (2_000_000, 20_000, 5, dict(skewed=True)), (100_003, 977, 7, {})]:\n"
+        "    h = ab.HostSnapshot.synth(P, N, seed=seed, **kw)\n"
+        "    d = ab.DeviceSnapshot.upload(h)\n"
+        "    tot, alloc, cl, _ = cref.top_node_columnar(h.cols)\n"
+        "    for _ in range(2):\n"
+        "        r = ab.top_node(d)\n"
+        "        assert np.array_equal(r.node_total, tot) and np.array_equal(r.node_alloc, alloc) and np.array_equal(r.cluster, cl), (P, N)\n"
+        "print('staged ok')\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=root,
+                       env=dict(os.environ, ARENA_STAGED="1", PYTHONPATH=root))
+    assert p.returncode == 0 and "staged ok" in p.stdout, (p.stdout[-1000:], p.stderr[-2000:])
