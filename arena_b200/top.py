@@ -140,10 +140,11 @@ def top_node_device(snap: DeviceSnapshot, d_node_total, d_node_alloc, d_cluster,
         _stream_arg(stream)))
 
 
-def top_node_multi(snap, details: bool = False) -> TopNodeResult:
-    """arena_top_node_multi: every device of the process computes its node range; one table comes back."""
+def top_node_multi(snap, details: bool = False, out: Optional[TopNodeResult] = None) -> TopNodeResult:
+    """arena_top_node_multi: every device of the process computes its node range; one table comes back
+    (`out`: page-locked arrays make the per-device downloads asynchronous and concurrent)."""
     N, P = snap.n_nodes, snap.n_pods
-    total, alloc, cluster, pod_gpu = _outputs(N, P, details, None)
+    total, alloc, cluster, pod_gpu = _outputs(N, P, details, out)
     check(lib().arena_top_node_multi(snap.handle, _ptr(total), _ptr(alloc), cluster.ctypes.data,
                                      pod_gpu.ctypes.data if details and P else None))
     return TopNodeResult(total, alloc, cluster, pod_gpu)

@@ -28,10 +28,19 @@ for skewed, seed in ((False, 1), (True, 5)):
         r = ab.top_node_multi(ms)
         best = min(best, time.perf_counter() - t0)
     ok = np.array_equal(r.node_total, tot) and np.array_equal(r.node_alloc, alloc) and np.array_equal(r.cluster, cl)
+    pin = lambda n: torch.zeros(max(n, 1), dtype=torch.int64).pin_memory().numpy()[:n]
+    out = ab.TopNodeResult(pin(host.n_nodes), pin(host.n_nodes), pin(2), None)
+    best_pinned = 1e9
+    for _ in range(5):
+        t0 = time.perf_counter()
+        r2 = ab.top_node_multi(ms, out=out)
+        best_pinned = min(best_pinned, time.perf_counter() - t0)
+    ok = ok and np.array_equal(r2.node_alloc, alloc) and np.array_equal(r2.cluster, cl)
     ok_all &= ok
     sizes = np.diff(ms.pod_cut.astype(np.int64))
     print(f"top node x{G} one process, {'skewed' if skewed else 'uniform'} P={P}: upload {t_up*1e3:.0f} ms, query (kernels + download of the "
-          f"{host.n_nodes}-row table) {best*1e3:.2f} ms = {P/best:.3g} pods/s, largest shard {sizes.max()*G/P:.4f} of the mean, "
+          f"{host.n_nodes}-row table) {best*1e3:.2f} ms = {P/best:.3g} pods/s into pageable arrays, {best_pinned*1e3:.2f} ms = {P/best_pinned:.3g} pods/s into "
+          f"page-locked ones, largest shard {sizes.max()*G/P:.4f} of the mean, "
           f"parity={'OK' if ok else 'FAIL'}", flush=True)
     ms.close()
 J = P // 20
