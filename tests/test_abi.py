@@ -79,3 +79,34 @@ def test_newer_entry_points_also_fail_loudly_without_a_gpu(built):
     assert L.arena_peer_exchange_timed_out() == 0
     L.arena_peer_exchange_destroy()                      # harmless without a mailbox
     assert b"arena_acct_init" in L.arena_last_error()
+
+
+def test_round2_entry_points_fail_loudly_without_a_gpu(built):
+    """Multi-device, packed-resident, deferred-exchange entry points: no host stand-in either.  The
+    host-only ones (regroup, age ordering, the list printer) work without a device."""
+    import numpy as np
+    import torch
+    from arena_b200 import HostSnapshot, _lib
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the -m gpu tests")
+    L = _lib.lib()
+    cluster = (C.c_int64 * 2)()
+    ids = (C.c_int * 2)(0, 1)
+    assert L.arena_acct_init_devices(2, ids) != 0 and L.arena_acct_device_count() == 0
+    assert L.arena_acct_init_devices(2, (C.c_int * 2)(0, 0)) == -1           # a device listed twice
+    h = HostSnapshot.synth(1000, 10, seed=1, n_jobs=5)
+    ms = C.c_void_p()
+    assert L.arena_multi_snapshot_upload(C.byref(h.view), 0, C.byref(ms)) == -3 and ms.value is None
+    assert L.arena_top_node_multi(None, None, None, cluster, None) == -1
+    assert L.arena_top_job_multi(None, None, None, None, None, cluster) == -1
+    pd = C.c_void_p()
+    p = h.pack()
+    assert L.arena_snapshot_upload_packed(C.byref(p.view), C.byref(pd)) == -3 and pd.value is None
+    assert L.arena_top_node_packed_device(None, None, None, cluster, None) == -3
+    assert L.arena_top_node_device_posted(None, None, None, cluster, None) == -3
+    assert L.arena_peer_exchange_collect(cluster, None) == -3
+    # host-only helpers
+    byjob = h.regroup(by_job=True)
+    pj = byjob.cols["pod_job"].astype(np.int64)
+    pj[pj == 0xFFFFFFFF] = 5
+    assert np.all(pj[:-1] <= pj[1:]) and byjob.n_pods == 1000
