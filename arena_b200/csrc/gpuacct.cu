@@ -174,9 +174,15 @@ void arena_acct_shutdown(void)
             arena_internal::device_pool_clear();
             arena_internal::free_loader_workspace();
         }
+        if (ctx().pipe_ready) {
+            cudaStreamDestroy(ctx().pipe_stream[0]);
+            cudaStreamDestroy(ctx().pipe_stream[1]);
+            for (cudaEvent_t e : ctx().pipe_event) if (e) cudaEventDestroy(e);
+        }
         cudaStreamDestroy(ctx().stream);
         ctx() = Context{};
     }
+    arena_internal::multi_reset();
 }
 
 int arena_acct_device(void) { return g_ctxs[0].ready ? g_ctxs[0].device : (int)ARENA_E_NOT_INIT; }

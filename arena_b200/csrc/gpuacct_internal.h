@@ -23,6 +23,8 @@ struct UseSlot {
 int init_slot(int device);
 // In-process totals exchange between the first n slots (peer access instead of CUDA IPC).
 int peer_exchange_in_process(int n);
+// arena_acct_shutdown() tells the multi-device driver (multi.cu) that its slots are gone.
+void multi_reset();
 
 // arena_acct_init() done?  Selects the device and returns the library stream.
 int ready(cudaStream_t *stream, int *sm_count);

@@ -72,6 +72,15 @@ int ensure_out(arena_multi_snapshot *m, int i, size_t bytes)
 
 }  // namespace
 
+namespace arena_internal {
+void multi_reset()
+{
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    g_n_dev = 0;
+    g_peer_totals = false;
+}
+}  // namespace arena_internal
+
 extern "C" {
 
 int arena_acct_init_devices(int n_dev, const int *dev_ids)

@@ -91,3 +91,28 @@ def test_cli_gpus_flag_prints_the_golden_text(gpu):
                            capture_output=True, text=True, timeout=120)
         assert p.returncode == 0, p.stdout + p.stderr
         assert p.stdout == open(os.path.join(g, want)).read(), args
+
+
+def test_shutdown_and_reinit_in_a_fresh_process(gpu):
+    """arena_acct_shutdown drops every device context (and the multi-device driver's memory of them);
+    a later arena_acct_init_devices starts from scratch.  In a child process: the session's own
+    library state must stay as it is."""
+    code = (
+        "import numpy as np, arena_b200 as ab\n"
+        "from oracle import cref\n"
+        "h = ab.HostSnapshot.synth(400_000, 4_000, seed=3)\n"
+        "tot, alloc, cl, _ = cref.top_node_columnar(h.cols)\n"
+        "for round in range(2):\n"
+        "    ab.init_devices([0])\n"
+        "    ms = ab.MultiSnapshot(h)\n"
+        "    r = ab.top_node_multi(ms)\n"
+        "    assert np.array_equal(r.node_alloc, alloc) and np.array_equal(r.cluster, cl)\n"
+        "    r = ab.top_node_packed(h.pack())\n"
+        "    assert np.array_equal(r.node_alloc, alloc)\n"
+        "    ms.close()\n"
+        "    ab.lib().arena_acct_shutdown()\n"
+        "    assert ab.lib().arena_acct_device_count() == 0\n"
+        "print('reinit ok')\n")
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=ROOT,
+                       env=dict(os.environ, PYTHONPATH=ROOT))
+    assert p.returncode == 0 and "reinit ok" in p.stdout, (p.stdout[-1000:], p.stderr[-2000:])
