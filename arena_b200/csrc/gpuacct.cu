@@ -161,6 +161,7 @@ int arena_acct_init(int device)
 
 void arena_acct_shutdown(void)
 {
+    {
     std::lock_guard<std::mutex> lk(g_mu);
     for (int slot = kMaxSlots - 1; slot >= 0; slot--) {
         arena_internal::UseSlot use(slot);
@@ -182,7 +183,8 @@ void arena_acct_shutdown(void)
         cudaStreamDestroy(ctx().stream);
         ctx() = Context{};
     }
-    arena_internal::multi_reset();
+    }
+    arena_internal::multi_reset();           // (after g_mu is released: arena_acct_init_devices takes the two locks the other way round)
 }
 
 int arena_acct_device(void) { return g_ctxs[0].ready ? g_ctxs[0].device : (int)ARENA_E_NOT_INIT; }
