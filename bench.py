@@ -453,7 +453,9 @@ def main():
     d_total = torch.empty(N, dtype=torch.int64, device="cuda")
     d_alloc = torch.empty(N, dtype=torch.int64, device="cuda")
     d_cluster = torch.empty(2, dtype=torch.int64, device="cuda")
-    stream = torch.cuda.current_stream()
+    # a stream of its own: the library replays the step from a CUDA graph, which the legacy default stream cannot do
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
 
     fused = False
     if world > 1 and args.collective in ("fused", "posted"):
