@@ -1,5 +1,6 @@
 """GPU box: what a `top node` STEP costs beyond its kernel at a small shard (1.25e7 pods, the 8-GPU share of
-BASELINE configs[3]): per-call event profiling on / off, and the step replayed from a CUDA graph."""
+BASELINE configs[3]): per-call event profiling on / off, and the step replayed from a CUDA graph.  Since the
+library replays the step from a graph of its own, run with ARENA_NO_GRAPH=1 to see plain launches in the first line."""
 import ctypes as C
 import os
 import sys
@@ -36,9 +37,9 @@ def loop(fn, label):
 
 
 step = lambda: ab.top_node_device(dev, d_total, d_alloc, d_cluster, None, st.cuda_stream)
-loop(step, "plain launches, no profiling")
+loop(step, "library calls, no profiling (graph replay inside the library unless ARENA_NO_GRAPH=1)")
 ab._lib.check(ab.lib().arena_profile_begin(K + 10))
-loop(step, "plain launches, per-call events (arena_profile_begin)")
+loop(step, "library calls, per-call events (arena_profile_begin: plain launches)")
 a, b, c = C.c_double(), C.c_double(), C.c_uint64()
 ab._lib.check(ab.lib().arena_profile_end(C.byref(a), C.byref(b), C.byref(c)))
 print(f"   events: memset {a.value / c.value * 1e3:.1f} us, kernel {b.value / c.value * 1e3:.1f} us", flush=True)
