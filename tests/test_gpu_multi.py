@@ -116,3 +116,35 @@ def test_shutdown_and_reinit_in_a_fresh_process(gpu):
     p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=ROOT,
                        env=dict(os.environ, PYTHONPATH=ROOT))
     assert p.returncode == 0 and "reinit ok" in p.stdout, (p.stdout[-1000:], p.stderr[-2000:])
+
+
+def test_multi_device_edge_shapes(gpu):
+    """No pods at all, fewer nodes than devices, every pod on one node, pods that name no node: the cut may
+    leave devices with empty ranges; the table and the totals must not notice."""
+    import numpy as np
+    from oracle import cref
+    gpu.init_devices(list(range(_n_devices())))
+    z = lambda dt, n=0: np.zeros(n, dt)
+    rng = np.random.default_rng(4)
+
+    def snap(pod_node, n_nodes):
+        P = len(pod_node)
+        counts = rng.integers(0, 4, P)
+        cb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+        C = int(cb[-1])
+        return gpu.HostSnapshot.from_arrays(dict(
+            pod_node=np.asarray(pod_node, np.uint32), pod_phase=rng.choice(np.array([1, 2, 3, 4], np.uint8), P) if P else z(np.uint8),
+            pod_ctr_begin=cb, ctr_val=rng.integers(0, 9, C).astype(np.int64), ctr_scale=z(np.int8, C),
+            node_cap_val=rng.integers(0, 9, n_nodes).astype(np.int64), node_cap_scale=z(np.int8, n_nodes)))
+
+    cases = [snap([], 3), snap([], 0), snap([0] * 700, 1), snap([0] * 5 + [0xFFFFFFFF] * 9, 2),
+             snap(np.sort(rng.integers(0, 3, 4000)), 3), snap([0xFFFFFFFF] * 50, 4)]
+    for h in cases:
+        tot, alloc, cl, pg = cref.top_node_columnar(h.cols, True)
+        ms = gpu.MultiSnapshot(h)
+        for details in (False, True):
+            r = gpu.top_node_multi(ms, details=details)
+            assert np.array_equal(r.node_total, tot) and np.array_equal(r.node_alloc, alloc) and np.array_equal(r.cluster, cl)
+            if details:
+                assert np.array_equal(r.pod_gpu, pg)
+        ms.close()
