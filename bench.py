@@ -701,7 +701,9 @@ def main():
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
         "vs_baseline": None, "dtype": "int64", "data": "synthetic",
         "parity_ok": parity_ok,
-        "config": dict(workload_config(n_gpus, args.scaling, args.skewed, args.collective), pods_per_gpu=P, nodes_per_gpu=N,
+        "config": dict(workload_config(n_gpus, args.scaling, args.skewed, args.collective),
+                       l2=f"inputs ({step_bytes / 1e9:.2f} GB on this rank) exceed the 126 MB L2; no flush between steps",
+                       pods_per_gpu=P, nodes_per_gpu=N,
                        containers_per_gpu=C, total_pods=total_pods, shard_imbalance_max_over_mean=imbalance),
         "clocks": clocks,
         "e2e": {"value": total_pods * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
