@@ -750,6 +750,14 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
     const unsigned tile_step = gridDim.x * kWarps;
 
+    // Tiles the 32-bit fast path cannot take (huge or negative values, positive scales, pods with hundreds of
+    // containers, the ragged last tile) are not summed where they are met: the call into the generic 64-bit
+    // tile would sit inside the hot loop and its live registers would be spilled around it on every trip.
+    // A warp notes up to kDeferred such tiles and sums them after its loop; a warp that meets more leaves the
+    // hot loop for good and takes ALL its remaining tiles generically (an input like that has no fast tiles).
+    constexpr int kDeferred = 8;
+    __shared__ unsigned s_deferred[kWarps][kDeferred];
+    unsigned n_deferred = 0, resume = 0xFFFFFFFFu;
     for (unsigned tile = blockIdx.x * kWarps + warp; tile < n_tiles; tile += tile_step) {
         bool fast = tile < n_full;
         u64 tile_alloc = 0;
@@ -885,15 +893,32 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
                 }
             }
         }
-        if (kJob) {
-            if (!fast) {
-                const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
-                if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
-            }
-            continue;
+        if (!fast) {                                   // warp-uniform
+            if (n_deferred == (unsigned)kDeferred) { resume = tile; break; }
+            if (lane == 0) s_deferred[warp][n_deferred] = tile;
+            n_deferred++;
         }
-        if (!fast) tile_alloc = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
-        if (lane == 31) acc_alloc += tile_alloc;
+        if (!kJob && lane == 31) acc_alloc += tile_alloc;
+    }
+    __syncwarp();
+    for (unsigned k = 0; k < n_deferred; k++) {
+        const unsigned tile = s_deferred[warp][k];
+        if (kJob) {
+            const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
+            if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
+        } else {
+            const u64 t = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+            if (lane == 31) acc_alloc += t;
+        }
+    }
+    for (unsigned tile = resume; tile < n_tiles; tile += tile_step) {      // (resume is past n_tiles unless the list overflowed)
+        if (kJob) {
+            const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
+            if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
+        } else {
+            const u64 t = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+            if (lane == 31) acc_alloc += t;
+        }
     }
     if (kJob) {
         __shared__ u64 s_wr[kWarps];
