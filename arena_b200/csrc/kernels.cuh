@@ -1737,6 +1737,62 @@ __device__ __forceinline__ unsigned packed_values_sum(const unsigned char *gpu, 
     return s;
 }
 
+// ---- the 4-bit fast lane: eight pods, at most sixteen values, no per-pod loop -----------------------
+// The pods of a lane own consecutive runs of the value column, so "which values count" is a run-length
+// code: a TOGGLE bit at the value index where the activity changes (pod j toggles at its first value
+// when its activity differs from pod j-1's; pods without containers toggle on the same index and
+// cancel), and the mask is the running parity of the toggles.  One shift per pod builds the toggle
+// word, a 256-entry table in shared memory turns eight toggle bits into eight mask nibbles, and the
+// sixteen values are added up inside two registers.
+__device__ __forceinline__ unsigned shl_clamp(unsigned x, unsigned n)      // 0 when n >= 32 (PTX shl), not n mod 32
+{
+    unsigned r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(n));
+    return r;
+}
+// 1 in every byte whose phase nibble is counted (not Succeeded = 3, not Failed = 4)
+__device__ __forceinline__ unsigned packed_active_bytes(unsigned meta4)
+{
+    const unsigned x = (meta4 & 0x0f0f0f0fu) + 0x05050505u;              // 3, 4 -> 8, 9: the only ones with (x & 0x1e) == 8
+    const unsigned y = (x & 0x1e1e1e1eu) ^ 0x08080808u;                  // zero byte <=> not counted
+    return ((y + 0x7f7f7f7fu) >> 7) & 0x01010101u;
+}
+// table entry b: nibble i = 0xF when an odd number of bits 0..i of b are set
+__device__ __forceinline__ unsigned packed_parity_nibbles(unsigned b)
+{
+    unsigned m = 0, par = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        par ^= (b >> i) & 1u;
+        m |= (0u - par) & (0xFu << (4 * i));
+    }
+    return m;
+}
+// cl / ch: container counts of pods 0..3 / 4..7, one per byte; al / ah: their activity bytes; the
+// values start at nibble index `start`, and there are at most 16 of them
+__device__ __forceinline__ unsigned packed_lane_sum16(const unsigned *words, const unsigned *lut, unsigned cl, unsigned ch,
+                                                      unsigned al, unsigned ah, unsigned start)
+{
+    const unsigned pre_lo = cl * 0x01010101u;
+    const unsigned pre_hi = ch * 0x01010101u + (pre_lo >> 24) * 0x01010101u;
+    const unsigned ex_lo = pre_lo - cl, ex_hi = pre_hi - ch;             // byte j = first value of pod j (0..16)
+    const unsigned t_lo = al ^ (al << 8), t_hi = ah ^ __funnelshift_l(al, ah, 8);     // byte j = activity changes at pod j
+    // shift counts: the pod's first value, or 32 + that (= no bit at all) when it does not toggle
+    const unsigned sh_lo = ex_lo | ((t_lo ^ 0x01010101u) << 5), sh_hi = ex_hi | ((t_hi ^ 0x01010101u) << 5);
+    unsigned d = shl_clamp(ah >> 24, pre_hi >> 24);                      // the last pod's run ends here
+    d ^= shl_clamp(1u, __byte_perm(sh_lo, 0u, 0x4440u)) ^ shl_clamp(1u, __byte_perm(sh_lo, 0u, 0x4441u));
+    d ^= shl_clamp(1u, __byte_perm(sh_lo, 0u, 0x4442u)) ^ shl_clamp(1u, __byte_perm(sh_lo, 0u, 0x4443u));
+    d ^= shl_clamp(1u, __byte_perm(sh_hi, 0u, 0x4440u)) ^ shl_clamp(1u, __byte_perm(sh_hi, 0u, 0x4441u));
+    d ^= shl_clamp(1u, __byte_perm(sh_hi, 0u, 0x4442u)) ^ shl_clamp(1u, __byte_perm(sh_hi, 0u, 0x4443u));
+    const unsigned m_lo = lut[d & 0xffu];
+    const unsigned m_hi = lut[(d >> 8) & 0xffu] ^ (0u - (__popc(d & 0xffu) & 1u));
+    const unsigned *w = words + (start >> 3);
+    const unsigned x0 = __ldg(w), x1 = __ldg(w + 1), x2 = __ldg(w + 2), sh = (start & 7u) * 4u;
+    const unsigned v_lo = __funnelshift_r(x0, x1, sh) & m_lo, v_hi = __funnelshift_r(x1, x2, sh) & m_hi;
+    const unsigned y = (v_lo & 0x0f0f0f0fu) + ((v_lo >> 4) & 0x0f0f0f0fu) + (v_hi & 0x0f0f0f0fu) + ((v_hi >> 4) & 0x0f0f0f0fu);
+    return (y * 0x01010101u) >> 24;                                      // bytes <= 60, total <= 240
+}
+
 // Masked GPU sum of the rows [lo, hi) whose containers start at value index c0, by one HALF-WARP
 // (16 lanes, `hmask` = its lanes): the same value in every lane of the half.  A lane owns EIGHT
 // consecutive pods per trip, so a half-warp covers 128 rows at once and an ordinary node (about a
@@ -1749,7 +1805,7 @@ __device__ __forceinline__ unsigned packed_values_sum(const unsigned char *gpu, 
 //   values       each pod's few nibbles (bytes): packed_values_sum, skipped for pods without containers
 template <int kBits>
 __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const unsigned char *gpu, unsigned lo, unsigned hi,
-                                               unsigned c0, int l16, unsigned hmask)
+                                               unsigned c0, int l16, unsigned hmask, const unsigned *lut)
 {
     const unsigned *mw = reinterpret_cast<const unsigned *>(meta);
     unsigned acc = 0;
@@ -1776,6 +1832,24 @@ __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const 
             if (l16 >= d) inc += up;
         }
         const unsigned start = c0 + inc - total;
+        c0 += __shfl_sync(hmask, inc, 15, 16);
+        if (kBits == 4) {
+            // whole lane at once when its values fit sixteen nibbles; two rounds of four pods when only the
+            // halves do; the per-pod loop below for the rest (a pod with more than a dozen containers)
+            const unsigned tot_lo = pre_lo >> 24;
+            unsigned rounds = 1;
+            if (total > 16u) rounds = (tot_lo <= 16u && total - tot_lo <= 16u) ? 2u : 0u;
+            if (rounds) {
+                const unsigned a_lo = packed_active_bytes(m_lo), a_hi = packed_active_bytes(m_hi);
+                const unsigned *words = reinterpret_cast<const unsigned *>(gpu);
+                if (rounds == 1) acc += packed_lane_sum16(words, lut, cnt_lo, cnt_hi, a_lo, a_hi, start);
+                else {
+                    acc += packed_lane_sum16(words, lut, cnt_lo, 0u, a_lo, 0u, start);
+                    acc += packed_lane_sum16(words, lut, cnt_hi, 0u, a_hi, 0u, start + tot_lo);
+                }
+                continue;
+            }
+        }
         const unsigned ex_lo = pre_lo - cnt_lo, ex_hi = pre_hi - cnt_hi;   // byte k = counts before pod k
 #pragma unroll
         for (int j = 0; j < 8; j++) {
@@ -1787,7 +1861,6 @@ __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const 
             const unsigned v = packed_values_sum<kBits>(gpu, start + off, cnt);
             if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += v;
         }
-        c0 += __shfl_sync(hmask, inc, 15, 16);
     }
     u64 sum = acc;
 #pragma unroll
@@ -1801,6 +1874,11 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l16 = lane & 15;
     const unsigned hmask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
+    __shared__ unsigned s_lut[256];
+    if (kBits == 4) {
+        s_lut[threadIdx.x] = packed_parity_nibbles(threadIdx.x);       // kThreads == 256
+        __syncthreads();
+    }
     // one unit of work per HALF-warp
     const u64 n_units = (u64)gridDim.x * kWarps * 2, u0 = ((u64)blockIdx.x * kWarps + warp) * 2 + (lane >> 4);
     u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every half
@@ -1815,7 +1893,7 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
             c_n = __ldg(a.node_ctr_begin + n + n_units);
         }
         if (hi - lo <= kBigNodePods) {
-            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, hmask);
+            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, hmask, s_lut);
             if (l16 == 0) { a.node_alloc[n] = s; alloc_sum += s; }
         }
         if (l16 == 0) {
@@ -1826,7 +1904,7 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
     }
     for (u64 k = a.piece_lo + u0; k < a.n_pieces; k += n_units) {
         const uint4 pc = __ldg(a.pieces + k);
-        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, hmask);
+        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, hmask, s_lut);
         if (l16 == 0 && s) { red_add_u64(a.node_alloc + pc.x, s); }
         if (l16 == 0) alloc_sum += s;
     }

@@ -31,7 +31,7 @@ for (p, n, seed, kw) in [] if os.environ.get("KBENCH_NOPARITY") else [(1_000_000
         sys.exit(1)
     d.close()
 
-host = ab.HostSnapshot.synth(P, N, seed=1)
+host = ab.HostSnapshot.synth(P, N, seed=1, skewed=bool(os.environ.get("KBENCH_SKEWED")))
 dev = ab.DeviceSnapshot.upload(host)
 d_total = torch.empty(N, dtype=torch.int64, device="cuda")
 d_alloc = torch.empty(N, dtype=torch.int64, device="cuda")
