@@ -1794,7 +1794,9 @@ __device__ __forceinline__ unsigned packed_lane_sum16(const unsigned *words, con
 }
 
 // Masked GPU sum of the rows [lo, hi) whose containers start at value index c0, by one HALF-WARP
-// (16 lanes, `hmask` = its lanes): the same value in every lane of the half.  A lane owns EIGHT
+// (16 lanes): the same value in every lane of the half.  Both halves of the warp are in here together
+// and stay together (the trip count is the larger of the two; a half without rows left works on
+// nothing), so every shuffle is a full-warp instruction of width 16.  At most kBigNodePods rows.  A lane owns EIGHT
 // consecutive pods per trip, so a half-warp covers 128 rows at once and an ordinary node (about a
 // hundred pods) is one trip; the two halves of a warp work on two different nodes, which doubles
 // the number of independent load chains in flight (the kernel is a chain of dependent loads per
@@ -1804,13 +1806,15 @@ __device__ __forceinline__ unsigned packed_lane_sum16(const unsigned *words, con
 //   placement    a 16-lane scan of the lane totals places every lane in the value column
 //   values       each pod's few nibbles (bytes): packed_values_sum, skipped for pods without containers
 template <int kBits>
-__device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const unsigned char *gpu, unsigned lo, unsigned hi,
-                                               unsigned c0, int l16, unsigned hmask, const unsigned *lut)
+__device__ __forceinline__ unsigned packed_rows_sum(const unsigned char *meta, const unsigned char *gpu, unsigned lo, unsigned hi,
+                                                    unsigned c0, int l16, const unsigned *lut)
 {
+    const unsigned hmask = 0xffffffffu;
     const unsigned *mw = reinterpret_cast<const unsigned *>(meta);
     unsigned acc = 0;
-    for (unsigned p0 = lo; p0 < hi; p0 += 128) {
-        const unsigned q = p0 + 8u * (unsigned)l16;
+    const unsigned rows = hi - lo;
+    for (unsigned done = 0; __any_sync(hmask, done < rows); done += 128) {
+        const unsigned q = lo + done + 8u * (unsigned)l16;
         unsigned m_lo = 0, m_hi = 0;
         if (q < hi) {
             const unsigned *w = mw + (q >> 2);
@@ -1862,10 +1866,9 @@ __device__ __forceinline__ u64 packed_rows_sum(const unsigned char *meta, const 
             if (ph != kPhaseSucceeded && ph != kPhaseFailed) acc += v;
         }
     }
-    u64 sum = acc;
 #pragma unroll
-    for (int d = 8; d > 0; d >>= 1) sum += __shfl_xor_sync(hmask, sum, d, 16);
-    return sum;
+    for (int d = 8; d > 0; d >>= 1) acc += __shfl_xor_sync(hmask, acc, d, 16);      // at most 2048 * 15 * 255
+    return acc;
 }
 
 template <int kBits>
@@ -1873,44 +1876,52 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l16 = lane & 15;
-    const unsigned hmask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
+    const unsigned half = (unsigned)lane >> 4;
     __shared__ unsigned s_lut[256];
     if (kBits == 4) {
         s_lut[threadIdx.x] = packed_parity_nibbles(threadIdx.x);       // kThreads == 256
         __syncthreads();
     }
-    // one unit of work per HALF-warp
-    const u64 n_units = (u64)gridDim.x * kWarps * 2, u0 = ((u64)blockIdx.x * kWarps + warp) * 2 + (lane >> 4);
-    u64 alloc_sum = 0, cap_sum = 0;                     // lane 0 of every half
+    // One unit of work per HALF-warp; the loops run on the warp's pair of units so that both halves make
+    // the same trips (the odd one out at the end of the range gets an empty node).
+    const u64 n_units = (u64)gridDim.x * kWarps * 2, w0 = ((u64)blockIdx.x * kWarps + warp) * 2;
+    u64 alloc_sum = 0;                                  // lane 0 of every half
     unsigned lo_n = 0, hi_n = 0, c_n = 0;               // the next node's offsets, fetched one node ahead
-    const u64 first = a.n_lo + u0;
-    if (first < a.N) { lo_n = __ldg(a.node_pod_begin + first); hi_n = __ldg(a.node_pod_begin + first + 1); c_n = __ldg(a.node_ctr_begin + first); }
-    for (u64 n = first; n < a.N; n += n_units) {
-        const unsigned lo = lo_n, hi = hi_n, c0 = c_n;
+    {
+        const u64 first = a.n_lo + w0 + half;
+        if (first < a.N) { lo_n = __ldg(a.node_pod_begin + first); hi_n = __ldg(a.node_pod_begin + first + 1); c_n = __ldg(a.node_ctr_begin + first); }
+    }
+    for (u64 nb = a.n_lo + w0; nb < a.N; nb += n_units) {
+        const u64 n = nb + half;
+        const unsigned lo = lo_n, c0 = c_n;
+        unsigned hi = hi_n;
+        lo_n = hi_n = c_n = 0;
         if (n + n_units < a.N) {
             lo_n = __ldg(a.node_pod_begin + n + n_units);
             hi_n = __ldg(a.node_pod_begin + n + n_units + 1);
             c_n = __ldg(a.node_ctr_begin + n + n_units);
         }
-        if (hi - lo <= kBigNodePods) {
-            const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, hmask, s_lut);
-            if (l16 == 0) { a.node_alloc[n] = s; alloc_sum += s; }
-        }
-        if (l16 == 0) {
-            const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
-            a.node_total[n] = t;
-            cap_sum += (u64)t;
-        }
+        const bool own = n < a.N && hi - lo <= kBigNodePods;            // larger nodes come as pieces, below
+        if (!own) hi = lo;
+        const unsigned s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, s_lut);
+        if (l16 == 0 && own) { a.node_alloc[n] = (u64)s; alloc_sum += s; }
     }
-    for (u64 k = a.piece_lo + u0; k < a.n_pieces; k += n_units) {
-        const uint4 pc = __ldg(a.pieces + k);
-        const u64 s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, hmask, s_lut);
-        if (l16 == 0 && s) { red_add_u64(a.node_alloc + pc.x, s); }
-        if (l16 == 0) alloc_sum += s;
+    for (u64 kb = a.piece_lo + w0; kb < a.n_pieces; kb += n_units) {
+        const u64 k = kb + half;
+        uint4 pc = make_uint4(0u, 0u, 0u, 0u);
+        if (k < a.n_pieces) pc = __ldg(a.pieces + k);
+        const unsigned s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, s_lut);
+        if (l16 == 0 && s) { red_add_u64(a.node_alloc + pc.x, (u64)s); alloc_sum += s; }
     }
-    __syncwarp();
+    // node capacities (gpuInNode): one thread per node, after the rows
+    u64 cap_sum = 0;
+    for (u64 n = a.n_lo + (u64)blockIdx.x * blockDim.x + threadIdx.x; n < a.N; n += (u64)gridDim.x * blockDim.x) {
+        const i64 t = quantity_value(__ldg(a.cap_val + n), (int)__ldg(a.cap_scale + n));
+        a.node_total[n] = t;
+        cap_sum += (u64)t;
+    }
+    cap_sum = warp_reduce_sum(cap_sum);
     alloc_sum += __shfl_down_sync(0xffffffffu, alloc_sum, 16);
-    cap_sum += __shfl_down_sync(0xffffffffu, cap_sum, 16);
     __shared__ u64 s_a[kWarps], s_c[kWarps];
     if (lane == 0) { s_a[warp] = alloc_sum; s_c[warp] = cap_sum; }
     __syncthreads();
