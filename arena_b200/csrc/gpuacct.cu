@@ -1016,7 +1016,9 @@ static int check_packed(const arena_packed_view *h)
 {
     if (!h) return fail(ARENA_E_INVALID, "packed view is NULL");
     const u64 P = h->n_pods, C = h->n_containers, N = h->n_nodes;
-    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFFFFFFFull) return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
+    // (the kernel counts nodes and pieces in 32 bits and steps past the end by one grid stride)
+    if (P >= 0xFFFFFFFFull || C > 0xFFFFFFFFull || N >= 0xFFF00000ull || h->n_pieces >= 0xFFF00000ull)
+        return fail(ARENA_E_TOO_LARGE, "snapshot exceeds 32-bit offsets");
     if (!h->node_pod_begin || (P && !h->pod_meta) || (C && !h->ctr_gpu) || (N && (!h->node_cap_val || !h->node_cap_scale)))
         return fail(ARENA_E_INVALID, "packed columns are NULL");
     if (h->ctr_bits != 4 && h->ctr_bits != 8) return fail(ARENA_E_INVALID, "ctr_bits must be 4 or 8, not %u", h->ctr_bits);

@@ -1769,9 +1769,10 @@ __device__ __forceinline__ unsigned packed_parity_nibbles(unsigned b)
     return m;
 }
 // cl / ch: container counts of pods 0..3 / 4..7, one per byte; al / ah: their activity bytes; the
-// values start at nibble index `start`, and there are at most 16 of them
-__device__ __forceinline__ unsigned packed_lane_sum16(const unsigned *words, const unsigned *lut, unsigned cl, unsigned ch,
-                                                      unsigned al, unsigned ah, unsigned start)
+// values start at nibble index `start`, and there are `total` <= 24 of them (the third word is only
+// touched by the lanes that have more than 16)
+__device__ __forceinline__ unsigned packed_lane_sum24(const unsigned *words, const unsigned *lut, unsigned cl, unsigned ch,
+                                                      unsigned al, unsigned ah, unsigned start, unsigned total)
 {
     const unsigned pre_lo = cl * 0x01010101u;
     const unsigned pre_hi = ch * 0x01010101u + (pre_lo >> 24) * 0x01010101u;
@@ -1789,8 +1790,14 @@ __device__ __forceinline__ unsigned packed_lane_sum16(const unsigned *words, con
     const unsigned *w = words + (start >> 3);
     const unsigned x0 = __ldg(w), x1 = __ldg(w + 1), x2 = __ldg(w + 2), sh = (start & 7u) * 4u;
     const unsigned v_lo = __funnelshift_r(x0, x1, sh) & m_lo, v_hi = __funnelshift_r(x1, x2, sh) & m_hi;
-    const unsigned y = (v_lo & 0x0f0f0f0fu) + ((v_lo >> 4) & 0x0f0f0f0fu) + (v_hi & 0x0f0f0f0fu) + ((v_hi >> 4) & 0x0f0f0f0fu);
-    return (y * 0x01010101u) >> 24;                                      // bytes <= 60, total <= 240
+    unsigned y = (v_lo & 0x0f0f0f0fu) + ((v_lo >> 4) & 0x0f0f0f0fu) + (v_hi & 0x0f0f0f0fu) + ((v_hi >> 4) & 0x0f0f0f0fu);
+    if (total > 16u) {
+        const unsigned m_3 = lut[(d >> 16) & 0xffu] ^ (0u - (__popc(d & 0xffffu) & 1u));
+        const unsigned v_3 = __funnelshift_r(x2, __ldg(w + 3), sh) & m_3;
+        y += (v_3 & 0x0f0f0f0fu) + ((v_3 >> 4) & 0x0f0f0f0fu);          // bytes <= 90
+    }
+    y = (y & 0x00ff00ffu) + ((y >> 8) & 0x00ff00ffu);
+    return (y * 0x00010001u) >> 16;                                      // <= 360
 }
 
 // Masked GPU sum of the rows [lo, hi) whose containers start at value index c0, by one HALF-WARP
@@ -1821,9 +1828,11 @@ __device__ __forceinline__ unsigned packed_rows_sum(const unsigned char *meta, c
             const unsigned w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2), sh = (q & 3u) * 8u;
             m_lo = __funnelshift_r(w0, w1, sh);
             m_hi = __funnelshift_r(w1, w2, sh);
-            const unsigned n = hi - q;                               // rows of this lane inside the range
-            if (n < 4) { m_lo &= (1u << (8 * n)) - 1u; m_hi = 0; }
-            else if (n < 8) m_hi &= n == 4 ? 0u : (1u << (8 * (n - 4))) - 1u;
+        }
+        {   // keep the rows of this lane that are inside the range: min(hi - q, 8) bytes (none when q >= hi)
+            const int nv = max((int)(hi - q), 0), n4 = min(nv, 4), n8 = min(nv, 8);
+            m_lo &= shl_clamp(1u, 8u * (unsigned)n4) - 1u;
+            m_hi &= shl_clamp(1u, 8u * (unsigned)(n8 - n4)) - 1u;
         }
         const unsigned cnt_lo = (m_lo >> 4) & 0x0f0f0f0fu, cnt_hi = (m_hi >> 4) & 0x0f0f0f0fu;
         const unsigned pre_lo = cnt_lo * 0x01010101u;               // byte k = counts 0..k (at most 60: no carry)
@@ -1838,18 +1847,19 @@ __device__ __forceinline__ unsigned packed_rows_sum(const unsigned char *meta, c
         const unsigned start = c0 + inc - total;
         c0 += __shfl_sync(hmask, inc, 15, 16);
         if (kBits == 4) {
-            // whole lane at once when its values fit sixteen nibbles; two rounds of four pods when only the
-            // halves do; the per-pod loop below for the rest (a pod with more than a dozen containers)
+            // whole lane at once when it has at most 24 values (three pods out of four have one or two
+            // containers); two rounds of four pods when only the halves fit; the per-pod loop below for the
+            // rest (a pod with more than a dozen containers)
             const unsigned tot_lo = pre_lo >> 24;
             unsigned rounds = 1;
-            if (total > 16u) rounds = (tot_lo <= 16u && total - tot_lo <= 16u) ? 2u : 0u;
+            if (total > 24u) rounds = (tot_lo <= 24u && total - tot_lo <= 24u) ? 2u : 0u;
             if (rounds) {
                 const unsigned a_lo = packed_active_bytes(m_lo), a_hi = packed_active_bytes(m_hi);
                 const unsigned *words = reinterpret_cast<const unsigned *>(gpu);
-                if (rounds == 1) acc += packed_lane_sum16(words, lut, cnt_lo, cnt_hi, a_lo, a_hi, start);
+                if (rounds == 1) acc += packed_lane_sum24(words, lut, cnt_lo, cnt_hi, a_lo, a_hi, start, total);
                 else {
-                    acc += packed_lane_sum16(words, lut, cnt_lo, 0u, a_lo, 0u, start);
-                    acc += packed_lane_sum16(words, lut, cnt_hi, 0u, a_hi, 0u, start + tot_lo);
+                    acc += packed_lane_sum24(words, lut, cnt_lo, 0u, a_lo, 0u, start, tot_lo);
+                    acc += packed_lane_sum24(words, lut, cnt_hi, 0u, a_hi, 0u, start + tot_lo, total - tot_lo);
                 }
                 continue;
             }
@@ -1884,32 +1894,34 @@ __global__ void __launch_bounds__(kThreads) top_node_packed_kernel(const __grid_
     }
     // One unit of work per HALF-warp; the loops run on the warp's pair of units so that both halves make
     // the same trips (the odd one out at the end of the range gets an empty node).
-    const u64 n_units = (u64)gridDim.x * kWarps * 2, w0 = ((u64)blockIdx.x * kWarps + warp) * 2;
+    // (node and piece numbers fit 32 bits with room for one stride: check_packed)
+    const unsigned n_units = gridDim.x * kWarps * 2, w0 = (blockIdx.x * kWarps + warp) * 2;
+    const unsigned N = (unsigned)a.N, n_pieces = (unsigned)a.n_pieces;
     u64 alloc_sum = 0;                                  // lane 0 of every half
     unsigned lo_n = 0, hi_n = 0, c_n = 0;               // the next node's offsets, fetched one node ahead
     {
-        const u64 first = a.n_lo + w0 + half;
-        if (first < a.N) { lo_n = __ldg(a.node_pod_begin + first); hi_n = __ldg(a.node_pod_begin + first + 1); c_n = __ldg(a.node_ctr_begin + first); }
+        const unsigned first = (unsigned)a.n_lo + w0 + half;
+        if (first < N) { lo_n = __ldg(a.node_pod_begin + first); hi_n = __ldg(a.node_pod_begin + first + 1); c_n = __ldg(a.node_ctr_begin + first); }
     }
-    for (u64 nb = a.n_lo + w0; nb < a.N; nb += n_units) {
-        const u64 n = nb + half;
+    for (unsigned nb = (unsigned)a.n_lo + w0; nb < N; nb += n_units) {
+        const unsigned n = nb + half, nn = n + n_units;
         const unsigned lo = lo_n, c0 = c_n;
         unsigned hi = hi_n;
         lo_n = hi_n = c_n = 0;
-        if (n + n_units < a.N) {
-            lo_n = __ldg(a.node_pod_begin + n + n_units);
-            hi_n = __ldg(a.node_pod_begin + n + n_units + 1);
-            c_n = __ldg(a.node_ctr_begin + n + n_units);
+        if (nn < N) {
+            lo_n = __ldg(a.node_pod_begin + nn);
+            hi_n = __ldg(a.node_pod_begin + nn + 1);
+            c_n = __ldg(a.node_ctr_begin + nn);
         }
-        const bool own = n < a.N && hi - lo <= kBigNodePods;            // larger nodes come as pieces, below
+        const bool own = n < N && hi - lo <= kBigNodePods;              // larger nodes come as pieces, below
         if (!own) hi = lo;
         const unsigned s = packed_rows_sum<kBits>(a.meta, a.gpu, lo, hi, c0, l16, s_lut);
         if (l16 == 0 && own) { a.node_alloc[n] = (u64)s; alloc_sum += s; }
     }
-    for (u64 kb = a.piece_lo + w0; kb < a.n_pieces; kb += n_units) {
-        const u64 k = kb + half;
+    for (unsigned kb = (unsigned)a.piece_lo + w0; kb < n_pieces; kb += n_units) {
+        const unsigned k = kb + half;
         uint4 pc = make_uint4(0u, 0u, 0u, 0u);
-        if (k < a.n_pieces) pc = __ldg(a.pieces + k);
+        if (k < n_pieces) pc = __ldg(a.pieces + k);
         const unsigned s = packed_rows_sum<kBits>(a.meta, a.gpu, pc.y, pc.z, pc.w, l16, s_lut);
         if (l16 == 0 && s) { red_add_u64(a.node_alloc + pc.x, (u64)s); alloc_sum += s; }
     }
