@@ -1685,10 +1685,11 @@ __global__ void __launch_bounds__(256) packed_expand_nodes_kernel(const unsigned
 }  // namespace arena
 
 // ---- `top node` summary straight from the packed columns (no expansion) ---------------------------
-// One warp per node: its pods are the rows [b[n], b[n+1]) and their containers the values from
-// node_ctr_begin[n] on, so the join is a pair of offsets and nothing is shared between warps: no
-// atomics, no pod_node column.  32 pods per trip: one meta byte per lane, a warp scan of the container
-// counts places every lane in the value column, each lane adds up its own pod's few values.  Nodes
+// One HALF-warp per node: its pods are the rows [b[n], b[n+1]) and their containers the values from
+// node_ctr_begin[n] on, so the join is a pair of offsets and nothing is shared between half-warps: no
+// atomics, no pod_node column.  128 pods per trip: eight meta bytes per lane, a 16-lane scan of the
+// container counts places every lane in the value column, each lane adds up its own pods' values in one
+// pass (4-bit values) or pod by pod (8-bit values, lanes with dozens of containers).  Nodes
 // above kBigNodePods rows (power-law snapshots) are cut by the host into pieces of at most that many
 // rows, each with its own container offset; pieces are spread over the grid and meet in node_alloc
 // with one atomic each.
