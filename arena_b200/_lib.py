@@ -116,6 +116,12 @@ _SIGS = [
     ("arena_pinned_free", None, [_VP]),
     ("arena_load_json_device", C.c_int, [_VP, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(_VP), C.POINTER(_VP),
                                          C.POINTER(LoadDeviceStats)]),
+    ("arena_load_json_gpu", C.c_int, [_VP, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
+                                      C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_VP),
+                                      C.POINTER(LoadDeviceStats)]),
+    ("arena_load_json_hostscan", C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
+                                           C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_int, C.POINTER(_VP),
+                                           C.POINTER(C.c_uint64)]),
     ("arena_scan_podlist_host", C.c_int, [C.c_char_p, C.c_size_t, _VP, C.c_uint64, C.POINTER(C.c_uint64), _VP, _VP, _VP,
                                           _VP, _VP, _VP]),
     ("arena_host_snapshot_pack", C.c_int, [C.POINTER(SnapshotView), C.c_int, C.POINTER(_VP)]),

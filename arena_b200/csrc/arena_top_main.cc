@@ -9,10 +9,10 @@
 //                  user of the job printer: ordered by age, no GPU columns
 // Common: [--device N] [--gpus N] [--time] [--loader host|device]
 //   --gpus N (N > 1): this one process drives devices 0..N-1 (arena_acct_init_devices): node ranges for
-//   `node`, job-id ranges for `job`; the host loader is used.  Same output for any N.
-//   --loader device (the default for `node` without -d): the PodList is parsed on the GPU
-//   (arena_load_json_device); host: the C++ loader + upload (always used for -d and for `job`,
-//   which need pod names and labels on the host).
+//   `node`, job-id ranges for `job`.  Same output for any N.
+//   --loader device (the default): the PodList is parsed on the GPU -- `node` without -d keeps the columns
+//   there (arena_load_json_device); -d, `job`, `list` and --gpus N get the whole host snapshot with pod
+//   names, labels and the job table from arena_load_json_gpu.  --loader host: the C++ loader + upload.
 // Errors are printed to stdout and the exit status is 1, as in the reference
 // (`fmt.Println(err); os.Exit(1)`, top_node.go:34-48).
 #include "../../include/arena_top.h"
@@ -90,7 +90,7 @@ int main(int argc, char **argv)
 
     if (loader && strcmp(loader, "host") != 0 && strcmp(loader, "device") != 0) return die("--loader must be host or device");
     const bool device_loader = is_node && !details && gpus == 1 && !(loader && strcmp(loader, "host") == 0);
-    if (loader && strcmp(loader, "device") == 0 && !device_loader) return die("--loader device serves `top node` without -d only");
+    const bool gpu_decode = !(loader && strcmp(loader, "host") == 0);      // every command decodes the PodList on the GPU by default
     if (device_loader) {
         if (arena_acct_init(device)) return die_arena();
         auto t0 = std::chrono::steady_clock::now();
@@ -125,20 +125,34 @@ int main(int argc, char **argv)
         return 0;
     }
 
+    // `-d`, `top job`, `list` (and --gpus N): the whole host snapshot -- names, job table -- with the PodList
+    // decoded on the GPU (arena_load_json_gpu) unless --loader host
+    if (gpus > 1) {
+        std::vector<int> ids(gpus);
+        for (int i = 0; i < gpus; i++) ids[i] = i;
+        if (arena_acct_init_devices(gpus, ids.data())) return die_arena();
+    } else if (arena_acct_init(device)) return die_arena();
     auto t0 = std::chrono::steady_clock::now();
     arena_host_snapshot *host = nullptr;
-    if (arena_load_json(pods.data(), pods.size(), nodes.data(), nodes.size(), jobs_path ? jobs.data() : nullptr, jobs.size(),
-                        tfjobs_path ? tfjobs.data() : nullptr, tfjobs.size(),
-                        (!is_node && releases_path) ? releases.data() : nullptr, releases.size(), is_node ? 0 : 1, &host))
+    arena_load_device_stats lst;
+    memset(&lst, 0, sizeof lst);
+    lst.fell_back = 1;
+    const char *jobs_p = jobs_path ? jobs.data() : nullptr, *tf_p = tfjobs_path ? tfjobs.data() : nullptr,
+               *rel_p = (!is_node && releases_path) ? releases.data() : nullptr;
+    if (gpu_decode ? arena_load_json_gpu(pods.data(), pods.size(), nodes.data(), nodes.size(), jobs_p, jobs.size(), tf_p, tfjobs.size(),
+                                         rel_p, releases.size(), is_node ? 0 : 1, &host, &lst)
+                   : arena_load_json(pods.data(), pods.size(), nodes.data(), nodes.size(), jobs_p, jobs.size(), tf_p, tfjobs.size(),
+                                     rel_p, releases.size(), is_node ? 0 : 1, &host))
         return die_arena();
     auto t1 = std::chrono::steady_clock::now();
+    char how[96];
+    if (lst.fell_back) snprintf(how, sizeof how, "host loader");
+    else if (lst.n_handed_back) snprintf(how, sizeof how, "PodList parsed on the GPU, %llu items handed back to the host", (unsigned long long)lst.n_handed_back);
+    else snprintf(how, sizeof how, "PodList parsed on the GPU");
     arena_snapshot_view view;
     arena_host_snapshot_view(host, &view);
     if (gpus > 1) {
         // one process, several GPUs: the loops of top_node.go:109-118 / top_job.go:53-66 split by key range
-        std::vector<int> ids(gpus);
-        for (int i = 0; i < gpus; i++) ids[i] = i;
-        if (arena_acct_init_devices(gpus, ids.data())) return die_arena();
         arena_multi_snapshot *ms = nullptr;
         if (arena_multi_snapshot_upload(&view, is_node ? 0 : 1, &ms)) return die_arena();
         auto t2 = std::chrono::steady_clock::now();
@@ -164,16 +178,15 @@ int main(int argc, char **argv)
         arena_free_text(text);
         if (timing) {
             auto ms_ = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-            fprintf(stderr, "[arena-top] gpus=%d pods=%llu nodes=%llu jobs=%llu  load %.2f ms, init+upload %.2f ms, query+format %.2f ms\n",
+            fprintf(stderr, "[arena-top] gpus=%d pods=%llu nodes=%llu jobs=%llu  load %.2f ms (%s), upload %.2f ms, query+format %.2f ms\n",
                     gpus, (unsigned long long)view.n_pods, (unsigned long long)view.n_nodes, (unsigned long long)view.n_jobs,
-                    ms_(t0, t1), ms_(t1, t2), ms_(t2, t3));
+                    ms_(t0, t1), how, ms_(t1, t2), ms_(t2, t3));
         }
         arena_multi_snapshot_free(ms);
         arena_host_snapshot_free(host);
         arena_acct_shutdown();
         return 0;
     }
-    if (arena_acct_init(device)) return die_arena();
     arena_snapshot *dev = nullptr;
     if (arena_snapshot_upload(&view, &dev)) return die_arena();
     auto t2 = std::chrono::steady_clock::now();
@@ -200,9 +213,9 @@ int main(int argc, char **argv)
     arena_free_text(text);
     if (timing) {
         auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-        fprintf(stderr, "[arena-top] pods=%llu nodes=%llu jobs=%llu  load %.2f ms, init+upload %.2f ms, query+format %.2f ms\n",
+        fprintf(stderr, "[arena-top] pods=%llu nodes=%llu jobs=%llu  load %.2f ms (%s), upload %.2f ms, query+format %.2f ms\n",
                 (unsigned long long)view.n_pods, (unsigned long long)view.n_nodes, (unsigned long long)view.n_jobs,
-                ms(t0, t1), ms(t1, t2), ms(t2, t3));
+                ms(t0, t1), how, ms(t1, t2), ms(t2, t3));
     }
     arena_snapshot_free(dev);
     arena_host_snapshot_free(host);

@@ -371,8 +371,10 @@ struct ItemArgs {
     long long *ctr_tmp;            // [kInlineCtrs][n_items]
     signed char *scale_tmp;        // [kInlineCtrs][n_items]
     ScanResult *res;
+    PodMeta *meta;                 // [n_items], kMeta launches only
 };
 
+template <bool kMeta>
 __global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const uint4 *__restrict__ fused_table)
 {
     // every lane indexes the table with its own state: shared memory, not constant
@@ -399,7 +401,8 @@ __global__ void __launch_bounds__(128) scan_items_kernel(const ItemArgs a, const
     const u64 prev_end = p == 0 ? a.A + 1 : (u64)a.item_end[p - 1];
     if (end <= begin || prev_end > begin || !gap_ok(a.text, prev_end, begin, p == 0)) out.flag = kFlagSeparator;
     else if (p + 1 == a.n_items && !gap_ok(a.text, end, a.B - 1, true)) out.flag = kFlagSeparator;
-    else scan_pod_item(a.text, begin, end, a.nodes, SharedLex{fused_base}, RingFeed(a.text, s_ring + threadIdx.x * 64), out);
+    else scan_pod_item<SharedLex, RingFeed, kMeta>(a.text, begin, end, a.nodes, SharedLex{fused_base},
+                                                   RingFeed(a.text, s_ring + threadIdx.x * 64), out, kMeta ? a.meta + p : nullptr);
     if (out.flag) {
         atomicOr(&a.res->any_flag, 1u);
         const u32 old = atomicMin(&a.res->first_flag_item, (u32)p);
@@ -668,9 +671,37 @@ double ms_since(std::chrono::steady_clock::time_point t0)
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
+// One pod record from what the scanner reported: the fields loader.cc extract_pod reads from its tree.
+void rec_from_scan(const char *text, uint32_t node, uint8_t phase, uint32_t n_ctrs, const int64_t *ctr_val, size_t val_stride,
+                   const int8_t *ctr_scale, const PodMeta &m, arena_host::PodRec &r)
+{
+    auto str = [&](int f) { return std::string(text + m.off[f], m.len[f]); };
+    auto has = [&](int f) { return (m.present >> f) & 1u; };
+    r.name = str(kMetaName);
+    r.ns = str(kMetaNamespace);
+    r.host_ip = str(kMetaHostIP);
+    r.created = has(kMetaCreated) ? arena_host::canonical_time_unix(text + m.off[kMetaCreated]) : arena_host::kZeroTimeUnix;
+    r.owner_is_job = m.owner_is_job != 0;
+    r.labels.has = 0;
+    if (has(kMetaRelease)) { r.labels.has |= arena_host::kHasRelease; r.labels.release = str(kMetaRelease); }
+    if (has(kMetaApp)) { r.labels.has |= arena_host::kHasApp; r.labels.app = str(kMetaApp); }
+    if (has(kMetaGroup)) { r.labels.has |= arena_host::kHasGroup; r.labels.group_name = str(kMetaGroup); }
+    if (has(kMetaReplicaType)) { r.labels.has |= arena_host::kHasReplicaType; r.labels.replica_type = str(kMetaReplicaType); }
+    if (has(kMetaReplicaIndex)) { r.labels.has |= arena_host::kHasReplicaIndex; r.labels.replica_index = str(kMetaReplicaIndex); }
+    r.node = node;
+    r.phase = phase;
+    r.ctr_val.resize(n_ctrs);
+    r.ctr_scale.resize(n_ctrs);
+    for (uint32_t k = 0; k < n_ctrs; k++) { r.ctr_val[k] = ctr_val[k * val_stride]; r.ctr_scale[k] = ctr_scale[k * val_stride]; }
+}
+
 // Returns ARENA_OK with *handled == false when the document must go through the host loader.
-int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *nodes, arena_snapshot **snap_out,
-                   arena_load_device_stats *stats, bool *handled)
+// pods_out == nullptr: the `top node` columns are left on the device (*snap_out; `nodes` holds the capacities).
+// pods_out != nullptr: every pod comes back as a host record with the job / printer fields too (nothing stays
+// on the device; `nodes` and snap_out are not used).
+int load_on_device(const char *podlist, size_t len, const std::vector<std::string> &node_names, const arena_host_snapshot *nodes,
+                   arena_snapshot **snap_out, arena_load_device_stats *stats, bool *handled,
+                   std::vector<arena_host::PodRec> *pods_out)
 {
     *handled = false;
     cudaStream_t st;
@@ -788,7 +819,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     // ---- node table ---------------------------------------------------------------------------------
     std::vector<NodeSlot> slots;
     std::vector<unsigned char> blob;
-    arena_scan_host::build_node_table(nodes->node_names, slots, blob);
+    arena_scan_host::build_node_table(node_names, slots, blob);
     NodeSlot *d_slots;
     unsigned char *d_blob;
     uint32_t *d_fused;
@@ -810,6 +841,8 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
     CtrPatch *d_ctr_patches = nullptr;
     u32 n_ctr_patches = 0;
     u64 C = 0;
+    PodMeta *d_meta = nullptr;
+    if (P && pods_out) CUDA_TRY(bufs.alloc(&d_meta, P * sizeof(PodMeta)));
     if (P) {
         CUDA_TRY(bufs.alloc(&d_pod_node_tmp, P * 4));
         CUDA_TRY(bufs.alloc(&d_pod_phase_tmp, P));
@@ -827,6 +860,7 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         ia.nodes = NodeTable{d_slots, (uint64_t)slots.size() - 1, d_blob};
         ia.pod_node = d_pod_node_tmp; ia.pod_phase = d_pod_phase_tmp; ia.pod_flag = d_pod_flag;
         ia.pod_nctr = d_nctr; ia.ctr_tmp = d_ctr_tmp; ia.scale_tmp = d_scale_tmp; ia.res = d_res;
+        ia.meta = d_meta;
         // aim at >= 4 warps per SM sub-partition before filling the warps up
         const u64 warps_wanted = (u64)sm_count * 16;
         unsigned lanes = 32;
@@ -837,9 +871,53 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
         }
         ia.lanes = lanes;
         const u64 n_warps = (P + lanes - 1) / lanes;
-        scan_items_kernel<<<(unsigned)((n_warps + 3) / 4), 128, 0, st>>>(ia, (const uint4 *)d_fused);
+        if (pods_out) scan_items_kernel<true><<<(unsigned)((n_warps + 3) / 4), 128, 0, st>>>(ia, (const uint4 *)d_fused);
+        else scan_items_kernel<false><<<(unsigned)((n_warps + 3) / 4), 128, 0, st>>>(ia, (const uint4 *)d_fused);
         arena_internal::add_launches(1);
         CUDA_TRY(cudaGetLastError());
+        if (pods_out) {
+            // ---- everything comes home: one record per pod, flagged items through the host's item code ----
+            std::vector<unsigned char> flags(P), phase(P);
+            std::vector<u32> node(P), ib, ie;
+            std::vector<u64> nctr(P);
+            std::vector<long long> vals(P * kInlineCtrs);
+            std::vector<signed char> scales(P * kInlineCtrs);
+            std::vector<PodMeta> meta(P);
+            CUDA_TRY(cudaMemcpyAsync(res, d_res, offsetof(ScanResult, root_open), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(flags.data(), d_pod_flag, P, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(phase.data(), d_pod_phase_tmp, P, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(node.data(), d_pod_node_tmp, P * 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(nctr.data(), d_nctr, P * 8, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(vals.data(), d_ctr_tmp, P * 8 * kInlineCtrs, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(scales.data(), d_scale_tmp, P * kInlineCtrs, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(meta.data(), d_meta, P * sizeof(PodMeta), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (stats) { stats->n_items = P; stats->ms_items = ms_since(t_start); }
+            if (res->any_flag) {
+                ib.resize(P); ie.resize(P);
+                CUDA_TRY(cudaMemcpyAsync(ib.data(), d_item_begin, P * 4, cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(cudaMemcpyAsync(ie.data(), d_item_end, P * 4, cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(cudaStreamSynchronize(st));
+                if (stats) { stats->flagged_item = res->first_flag_item; stats->flag_reason = flags[res->first_flag_item]; }
+            }
+            arena_host::PodItemParser parser(node_names);
+            const u64 max_handed = std::max<u64>(64, P / 8);
+            u64 handed = 0;
+            pods_out->assign(P, arena_host::PodRec());
+            for (u64 k = 0; k < P; k++) {
+                arena_host::PodRec &r = (*pods_out)[k];
+                if (flags[k]) {
+                    if (flags[k] == kFlagSeparator || ++handed > max_handed) return ARENA_OK;      // not handled
+                    if (!parser.parse_full(podlist, len, ib[k], ie[k], r)) return ARENA_OK;
+                    continue;
+                }
+                rec_from_scan(podlist, node[k], phase[k], (uint32_t)nctr[k], (const int64_t *)vals.data() + k, P,
+                              (const int8_t *)scales.data() + k, meta[k], r);
+            }
+            if (stats) { stats->n_handed_back = handed; stats->ms_device = ms_since(t_start); }
+            *handled = true;
+            return ARENA_OK;
+        }
         rc = exclusive_scan(d_nctr, P, d_ctr_begin64, d_tile_sums2, &d_res->n_containers, st);
         if (rc) return rc;
         CUDA_TRY(cudaMemcpyAsync(res, d_res, offsetof(ScanResult, root_open), cudaMemcpyDeviceToHost, st));
@@ -893,6 +971,13 @@ int load_on_device(const char *podlist, size_t len, const arena_host_snapshot *n
             if (stats) stats->n_handed_back = pod_patches.size();
         }
         C = res->n_containers;
+    }
+
+    if (pods_out) {                                                // (no pods at all)
+        pods_out->clear();
+        if (stats) stats->ms_device = ms_since(t_start);
+        *handled = true;
+        return ARENA_OK;
     }
 
     // ---- final block: the layout arena_snapshot_upload() uses -----------------------------------------
@@ -983,7 +1068,7 @@ int arena_load_json_device(const char *podlist_json, size_t podlist_len, const c
         return rc2;
     }
     bool handled = false;
-    rc = load_on_device(podlist_json, podlist_len, nodes, snapshot_out, stats, &handled);
+    rc = load_on_device(podlist_json, podlist_len, nodes->node_names, nodes, snapshot_out, stats, &handled, nullptr);
     if (rc) { arena_host_snapshot_free(nodes); return rc; }
     if (handled) { *nodes_out = nodes; return ARENA_OK; }
 
@@ -999,6 +1084,93 @@ int arena_load_json_device(const char *podlist_json, size_t podlist_len, const c
     if (stats) stats->fell_back = 1;
     *nodes_out = full;
     return ARENA_OK;
+}
+
+int arena_load_json_gpu(const char *podlist_json, size_t podlist_len, const char *nodelist_json, size_t nodelist_len,
+                        const char *joblist_json, size_t joblist_len, const char *tfjoblist_json, size_t tfjoblist_len,
+                        const char *helm_list_text, size_t helm_len, int group_by_job, arena_host_snapshot **out,
+                        arena_load_device_stats *stats)
+{
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    if (!podlist_json || !nodelist_json) return fail(ARENA_E_INVALID, "PodList and NodeList are required");
+    int rc = arena_internal::ready(nullptr, nullptr);
+    if (rc) return rc;                                                     // no CUDA, no loader: there is no CPU stand-in here
+    struct DeviceSource : arena_host::PodSource {
+        const char *text; size_t len; arena_load_device_stats *stats; int err = ARENA_OK;
+        bool pods(const std::vector<std::string> &node_names, std::vector<arena_host::PodRec> &pods_out) override
+        {
+            bool handled = false;
+            err = load_on_device(text, len, node_names, nullptr, nullptr, stats, &handled, &pods_out);
+            return !err && handled;
+        }
+    } src;
+    src.text = podlist_json; src.len = podlist_len; src.stats = stats;
+    bool handled = false;
+    rc = arena_host::load_with_pods(src, nodelist_json, nodelist_len, joblist_json, joblist_len, tfjoblist_json, tfjoblist_len,
+                                    helm_list_text, helm_len, group_by_job != 0, out, &handled);
+    if (src.err) return src.err;
+    if (rc) return rc;
+    if (handled) return ARENA_OK;
+    if (stats) stats->fell_back = 1;
+    return arena_load_json(podlist_json, podlist_len, nodelist_json, nodelist_len, joblist_json, joblist_len, tfjoblist_json,
+                           tfjoblist_len, helm_list_text, helm_len, group_by_job, out);
+}
+
+// Diagnostic twin of arena_load_json_gpu: the same scanner source compiled for the host walks the items
+// (no CUDA call), so the CPU test-suite can compare whole snapshots with arena_load_json.
+int arena_load_json_hostscan(const char *podlist_json, size_t podlist_len, const char *nodelist_json, size_t nodelist_len,
+                             const char *joblist_json, size_t joblist_len, const char *tfjoblist_json, size_t tfjoblist_len,
+                             const char *helm_list_text, size_t helm_len, int group_by_job, arena_host_snapshot **out,
+                             uint64_t *n_handed_back)
+{
+    if (!out) return fail(ARENA_E_INVALID, "out is NULL");
+    *out = nullptr;
+    if (n_handed_back) *n_handed_back = 0;
+    if (!podlist_json || !nodelist_json) return fail(ARENA_E_INVALID, "PodList and NodeList are required");
+    struct HostScanSource : arena_host::PodSource {
+        const char *text; size_t len; uint64_t handed = 0;
+        bool pods(const std::vector<std::string> &node_names, std::vector<arena_host::PodRec> &pods_out) override
+        {
+            std::vector<arena_json::Range> ranges;
+            const std::string_view doc(text, len);
+            size_t open = doc.find("\"items\"");
+            if (open == std::string_view::npos) return false;
+            open = doc.find('[', open);
+            size_t end = 0;
+            if (open == std::string_view::npos || !arena_json::split_array(doc, open, ranges, end)) return false;
+            std::vector<NodeSlot> slots;
+            std::vector<unsigned char> blob;
+            arena_scan_host::build_node_table(node_names, slots, blob);
+            const NodeTable nt{slots.data(), (uint64_t)slots.size() - 1, blob.data()};
+            std::vector<uint32_t> fused(kFusedEntries);
+            build_fused(fused.data());
+            arena_host::PodItemParser parser(node_names);
+            pods_out.assign(ranges.size(), arena_host::PodRec());
+            for (size_t k = 0; k < ranges.size(); k++) {
+                PodOut o = PodOut();
+                PodMeta m;
+                scan_pod_item<DirectLex, DirectFeed, true>((const unsigned char *)text, ranges[k].begin, ranges[k].end, nt,
+                                                           DirectLex{fused.data()}, DirectFeed{(const unsigned char *)text}, o, &m);
+                if (o.flag) {
+                    handed++;
+                    if (!parser.parse_full(text, len, ranges[k].begin, ranges[k].end, pods_out[k])) return false;
+                    continue;
+                }
+                rec_from_scan(text, o.node, o.phase, o.n_ctrs, o.ctr_val, 1, o.ctr_scale, m, pods_out[k]);
+            }
+            return true;
+        }
+    } src;
+    src.text = podlist_json; src.len = podlist_len;
+    bool handled = false;
+    int rc = arena_host::load_with_pods(src, nodelist_json, nodelist_len, joblist_json, joblist_len, tfjoblist_json, tfjoblist_len,
+                                        helm_list_text, helm_len, group_by_job != 0, out, &handled);
+    if (rc) return rc;
+    if (n_handed_back) *n_handed_back = src.handed;
+    if (handled) return ARENA_OK;
+    return fail(ARENA_E_PARSE, "the scanner path did not take this document (arena_load_json reports why)");
 }
 
 int arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const arena_host_snapshot *nodes, uint64_t capacity,
@@ -1023,7 +1195,7 @@ int arena_scan_podlist_host(const char *podlist_json, size_t podlist_len, const 
     std::vector<uint32_t> fused(kFusedEntries);
     build_fused(fused.data());
     for (size_t k = 0; k < ranges.size(); k++) {
-        PodOut out;
+        PodOut out = PodOut();
         scan_pod_item((const unsigned char *)podlist_json, ranges[k].begin, ranges[k].end, nt, DirectLex{fused.data()},
                       DirectFeed{(const unsigned char *)podlist_json}, out);
         if (pod_flag) pod_flag[k] = (uint8_t)out.flag;

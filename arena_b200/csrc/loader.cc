@@ -118,7 +118,7 @@ int64_t days_from_civil(int64_t y, unsigned m, unsigned d)
     return era * 146097 + (int64_t)doe - 719468;
 }
 
-const int64_t kZeroTimeUnix = -62135596800ll;      // Go's time.Time{} (0001-01-01T00:00:00Z)
+using arena_host::kZeroTimeUnix;                   // Go's time.Time{} (0001-01-01T00:00:00Z)
 
 // metav1.Time.UnmarshalJSON: null -> zero time, else time.Parse(RFC3339)
 // (vendor/k8s.io/apimachinery/pkg/apis/meta/v1/time.go:105-121).  Sub-second
@@ -171,26 +171,16 @@ uint8_t phase_code(const std::string &p)
     return ARENA_PHASE_OTHER;
 }
 
-// The labels the job-membership rules read, copied out so a pod record does not
-// point into its (per-item, short-lived) JSON tree.
-enum : uint8_t { kHasRelease = 1, kHasApp = 2, kHasGroup = 4, kHasReplicaType = 8, kHasReplicaIndex = 16 };
-struct PodLabels {
-    uint8_t has = 0;
-    std::string release, app, group_name, replica_type, replica_index;
-    bool is(uint8_t bit, const std::string &field, const char *want) const { return (has & bit) && field == want; }
-};
-
-struct PodRec {
-    std::string name, ns, node_name, host_ip;
-    uint8_t phase = 0;
-    std::vector<int64_t> ctr_val;
-    std::vector<int8_t> ctr_scale;
-    int64_t created = kZeroTimeUnix;
-    bool owner_is_job = false;
-    PodLabels labels;
-    uint32_t node = ARENA_NONE, job = ARENA_NONE;
-    uint8_t role = ARENA_ROLE_COUNTS;
-};
+// (PodRec / PodLabels: host_snapshot.h.  The labels are copied out so a pod record does not point
+// into its per-item, short-lived JSON tree.)
+using arena_host::PodLabels;
+using arena_host::PodRec;
+using arena_host::kHasRelease;
+using arena_host::kHasApp;
+using arena_host::kHasGroup;
+using arena_host::kHasReplicaType;
+using arena_host::kHasReplicaIndex;
+static_assert(ARENA_NONE == 0xFFFFFFFFu && ARENA_ROLE_COUNTS == 0, "PodRec defaults");
 
 struct NodeRec {
     std::string name, internal_ip, first_addr;
@@ -495,14 +485,17 @@ bool tf_condition(const Value *status, const char *type)
     return false;
 }
 
+struct PodsNotDelivered {};     // thrown by load() when its PodSource gives up: nothing was produced
+
+// `src` != nullptr: the pods come from there (the GPU loader) and `podlist` is not looked at.
 int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodelen, const char *joblist, size_t joblen,
          const char *tfjoblist, size_t tflen, const char *helm, size_t helmlen, bool group_by_job,
-         arena_host_snapshot *h)
+         arena_host_snapshot *h, arena_host::PodSource *src = nullptr)
 {
     PhaseTrace trace;
     Doc pod_doc, node_doc, job_doc, tf_doc;
     parse_doc(nodelist, nodelen, "NodeList", node_doc, keep_core, true);
-    parse_doc(podlist, podlen, "PodList", pod_doc, keep_core, true);
+    if (!src) parse_doc(podlist, podlen, "PodList", pod_doc, keep_core, true);
     trace.mark("envelopes + item scan");
 
     // ---- nodes -------------------------------------------------------------------
@@ -512,6 +505,7 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
     } catch (const LoadError &e) {
         // a sequential decode reads BOTH documents before looking at any field, so a syntax
         // error inside a pod outranks a bad field in a node
+        if (src) throw PodsNotDelivered{};          // the plain path sorts out which document's error comes first
         if (pod_doc.split && e.msg.find("JSON syntax error") == std::string::npos) {
             Doc whole;
             parse_doc(podlist, podlen, "PodList", whole, [](std::string_view, std::string_view) { return false; }, false);
@@ -537,15 +531,21 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
         cap_val[n] = r.cap_val;
         cap_scale[n] = r.cap_scale;
     }
-    if (!dup_node.empty())
+    if (!dup_node.empty()) {
+        if (src) throw PodsNotDelivered{};
         bad("duplicate node name \"" + dup_node + "\" (the API server guarantees unique node names)");
+    }
 
     trace.mark("nodes");
 
     // ---- pods --------------------------------------------------------------------
     std::vector<PodRec> pods;
-    for_each_item(podlist, podlen, "PodList", pod_doc, keep_core, pods,
-                  [&](const Value &item, PodRec &r) { extract_pod(item, r, node_id); });
+    if (src) {
+        if (!src->pods(h->node_names, pods)) throw PodsNotDelivered{};
+    } else {
+        for_each_item(podlist, podlen, "PodList", pod_doc, keep_core, pods,
+                      [&](const Value &item, PodRec &r) { extract_pod(item, r, node_id); });
+    }
     const size_t P = pods.size();
     trace.mark("pods");
 
@@ -770,8 +770,7 @@ PodItemParser::PodItemParser(const std::vector<std::string> &node_names) : impl(
 
 PodItemParser::~PodItemParser() { delete impl; }
 
-bool PodItemParser::parse(const char *text, size_t text_len, size_t begin, size_t end, uint32_t &node, uint8_t &phase,
-                          std::vector<int64_t> &ctr_val, std::vector<int8_t> &ctr_scale)
+bool PodItemParser::parse_full(const char *text, size_t text_len, size_t begin, size_t end, PodRec &rec)
 {
     try {
         arena_json::ParseOptions opt;
@@ -781,18 +780,55 @@ bool PodItemParser::parse(const char *text, size_t text_len, size_t begin, size_
         r.begin = begin;
         r.end = end;
         if (!arena_json::parse_range(std::string_view(text, text_len), r, 2, "items", impl->item, e, opt)) return false;
-        PodRec rec;
+        rec = PodRec();
         extract_pod(impl->item.root(), rec, impl->node_id);
-        node = rec.node;
-        phase = rec.phase;
-        ctr_val = std::move(rec.ctr_val);
-        ctr_scale = std::move(rec.ctr_scale);
         return true;
     } catch (const LoadError &) {
         return false;
     } catch (const std::bad_alloc &) {
         return false;
     }
+}
+
+bool PodItemParser::parse(const char *text, size_t text_len, size_t begin, size_t end, uint32_t &node, uint8_t &phase,
+                          std::vector<int64_t> &ctr_val, std::vector<int8_t> &ctr_scale)
+{
+    PodRec rec;
+    if (!parse_full(text, text_len, begin, end, rec)) return false;
+    node = rec.node;
+    phase = rec.phase;
+    ctr_val = std::move(rec.ctr_val);
+    ctr_scale = std::move(rec.ctr_scale);
+    return true;
+}
+
+int64_t canonical_time_unix(const char *p)
+{
+    auto two = [&](int at) { return (p[at] - '0') * 10 + (p[at + 1] - '0'); };
+    const int64_t Y = two(0) * 100 + two(2);
+    return days_from_civil(Y, (unsigned)two(5), (unsigned)two(8)) * 86400 + two(11) * 3600 + two(14) * 60 + two(17);
+}
+
+int load_with_pods(PodSource &src, const char *nodelist, size_t nodelen, const char *joblist, size_t joblen,
+                   const char *tfjoblist, size_t tflen, const char *helm, size_t helmlen, bool group_by_job,
+                   arena_host_snapshot **out, bool *handled)
+{
+    *out = nullptr;
+    *handled = false;
+    arena_host_snapshot *h = new arena_host_snapshot();
+    int rc = ARENA_OK;
+    try {
+        rc = load(nullptr, 0, nodelist, nodelen, joblist, joblen, tfjoblist, tflen, helm, helmlen, group_by_job, h, &src);
+        if (!rc) { *out = h; *handled = true; return ARENA_OK; }
+    } catch (const PodsNotDelivered &) {
+        rc = ARENA_OK;                                  // not handled: the caller runs the plain path
+    } catch (const LoadError &) {
+        rc = ARENA_OK;                                  // the plain path owns every error message (and their order)
+    } catch (const std::bad_alloc &) {
+        rc = fail(ARENA_E_NOMEM, "out of host memory while loading");
+    }
+    delete h;
+    return rc;
 }
 
 }  // namespace arena_host

@@ -94,6 +94,20 @@ struct PodOut {
     int8_t ctr_scale[kInlineCtrs];    // ... and .scale (resource/amount.go:57-60)
 };
 
+// What `top job`, `top node -d` and `arena list` read besides the accounting columns, as places in
+// the document: the host copies the bytes out (loader.cc extract_pod reads the same fields from its
+// tree).  Filled only when the caller asks for it (scan_pod_item<..., true>).
+enum MetaField : int {
+    kMetaName, kMetaNamespace, kMetaHostIP, kMetaCreated,
+    kMetaRelease, kMetaApp, kMetaGroup, kMetaReplicaType, kMetaReplicaIndex, kMetaFields
+};
+struct PodMeta {
+    uint32_t off[kMetaFields];        // absolute byte offset of the string body
+    uint16_t len[kMetaFields];
+    uint16_t present;                 // bit f: the key is there (a label whose value is null counts: it reads as "")
+    uint8_t owner_is_job;             // some ownerReference has kind "Job" (trainer_mpi.go:247-279)
+};
+
 namespace detail {
 
 enum Role : uint8_t {
@@ -600,12 +614,18 @@ constexpr int kMaxTodo = 96;
 constexpr int kRoleLevels = 8;           // ITEM > SPEC > CTRS > CTR > RES > LIMITS is the deepest path with a role
 constexpr int kMaxBitDepth = 62;         // container types live in a 64-bit stack
 
-template <class Lex, class Feed>
+template <class Lex, class Feed, bool kMeta = false>
 ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t end_, const NodeTable &nodes,
-                                   const Lex lex, Feed feed, PodOut &out)
+                                   const Lex lex, Feed feed, PodOut &out, PodMeta *meta_out = nullptr)
 {
     using namespace detail;
-    enum What : uint8_t { W_KEY, W_QUANTITY, W_GPU, W_TIME, W_PHASE };
+    enum What : uint8_t { W_KEY, W_QUANTITY, W_GPU, W_TIME, W_PHASE, W_KIND };
+    PodMeta meta;
+    if (kMeta) {
+        for (int f = 0; f < kMetaFields; f++) { meta.off[f] = 0; meta.len[f] = 0; }
+        meta.present = 0;
+        meta.owner_is_job = 0;
+    }
     struct Todo {
         uint32_t pos;                    // relative to `begin`
         uint16_t len;
@@ -650,6 +670,14 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
         return n_todo++;
     };
 
+    // a string (or null) field the job rules and the printers read: remember where it is
+    auto remember = [&](int field, bool is_string, uint32_t body, uint32_t len) {
+        if (is_string && (escaped || len > 0xFFFFu)) { flag = escaped ? kFlagEscapedValue : kFlagTooManyFields; return; }
+        meta.off[field] = is_string ? body : 0u;
+        meta.len[field] = (uint16_t)(is_string ? len : 0u);
+        meta.present |= (uint16_t)(1u << field);
+    };
+
     // one finished scalar in context (parent role, key): the host loader's field rules
     auto scalar = [&](bool is_string, bool is_number, bool is_null, uint32_t body, uint32_t len) {
         if (depth == 0) { flag = kFlagShape; return; }                 // "PodList item is not an object"
@@ -670,13 +698,33 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
         case K_LIMITS: if (!is_null) flag = kFlagShape; cur_ref = kAbsent; break;
         case K_NAME: case K_NAMESPACE: case K_HOSTIP: case K_KIND:
         case K_L_RELEASE: case K_L_APP: case K_L_GROUP: case K_L_RTYPE: case K_L_RINDEX:
-            if (!is_string && !is_null) flag = kFlagShape;
+            if (!is_string && !is_null) { flag = kFlagShape; break; }
+            if (!kMeta) break;
+            switch (key) {
+            case K_NAME: remember(kMetaName, is_string, body, len); break;
+            case K_NAMESPACE: remember(kMetaNamespace, is_string, body, len); break;
+            case K_HOSTIP: remember(kMetaHostIP, is_string, body, len); break;
+            case K_L_RELEASE: remember(kMetaRelease, is_string, body, len); break;
+            case K_L_APP: remember(kMetaApp, is_string, body, len); break;
+            case K_L_GROUP: remember(kMetaGroup, is_string, body, len); break;
+            case K_L_RTYPE: remember(kMetaReplicaType, is_string, body, len); break;
+            case K_L_RINDEX: remember(kMetaReplicaIndex, is_string, body, len); break;
+            default:                                                     // K_KIND: compared with "Job" after the walk
+                if (is_string) {
+                    if (escaped) flag = kFlagEscapedValue;
+                    else defer(W_KIND, 0, body, len);
+                }
+                break;
+            }
             break;
         case K_CREATED:
             if (is_null) break;
             if (!is_string) flag = kFlagShape;
             else if (escaped) flag = kFlagTime;
-            else defer(W_TIME, 0, body, len);
+            else {
+                defer(W_TIME, 0, body, len);
+                if (kMeta) remember(kMetaCreated, true, body, len);
+            }
             break;
         case K_NODENAME:
             node_len = 0;
@@ -886,6 +934,9 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
         case W_TIME:
             if (!time_canonical(p, d.len)) flag = kFlagTime;
             break;
+        case W_KIND:
+            if (kMeta && bytes_are(p, d.len, "Job")) meta.owner_is_job = 1;
+            break;
         default:                                                       // W_PHASE
             if (k == phase_todo) phase = phase_code(p, d.len);
             break;
@@ -901,6 +952,7 @@ ARENA_HD inline void scan_pod_item(const unsigned char *t, size_t begin_, size_t
     out.phase = phase;
     out.n_ctrs = n_ctrs;
     out.node = (!flag && node_len) ? find_node(nodes, t + node_off, node_len) : kNoNode;     // loader.cc: "" joins nothing
+    if (kMeta && meta_out) *meta_out = meta;
 }
 
 // What must sit between two items (or between '[' and the first one): whitespace and,

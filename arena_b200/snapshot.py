@@ -104,6 +104,37 @@ class HostSnapshot:
                                     C.byref(h)))
         return cls.from_handle(h.value)
 
+    @classmethod
+    def from_json_gpu(cls, podlist, nodelist: bytes, joblist: Optional[bytes] = None,
+                      tfjoblist: Optional[bytes] = None, helm_list: Optional[bytes] = None,
+                      group_by_job: bool = False):
+        """arena_load_json_gpu: the same snapshot as from_json, the PodList (bytes or a PinnedBuffer)
+        decoded on the GPU.  Returns (snapshot, stats dict)."""
+        h = C.c_void_p()
+        st = LoadDeviceStats()
+        n = lambda b: len(b) if b is not None else 0
+        if isinstance(podlist, PinnedBuffer):
+            ptr, plen = C.c_void_p(podlist.ptr), podlist.nbytes
+        else:
+            ptr, plen = podlist, len(podlist)
+        check(lib().arena_load_json_gpu(ptr, plen, nodelist, len(nodelist), joblist, n(joblist), tfjoblist, n(tfjoblist),
+                                        helm_list, n(helm_list), int(group_by_job), C.byref(h), C.byref(st)))
+        return cls.from_handle(h.value), {k: getattr(st, k) for k, _ in LoadDeviceStats._fields_}
+
+    @classmethod
+    def from_json_hostscan(cls, podlist: bytes, nodelist: bytes, joblist: Optional[bytes] = None,
+                           tfjoblist: Optional[bytes] = None, helm_list: Optional[bytes] = None,
+                           group_by_job: bool = False):
+        """arena_load_json_hostscan (diagnostic): the device scanner's source run on the host.
+        Returns (snapshot, items handed to the host's item code)."""
+        h = C.c_void_p()
+        handed = C.c_uint64(0)
+        n = lambda b: len(b) if b is not None else 0
+        check(lib().arena_load_json_hostscan(podlist, len(podlist), nodelist, len(nodelist), joblist, n(joblist),
+                                             tfjoblist, n(tfjoblist), helm_list, n(helm_list), int(group_by_job),
+                                             C.byref(h), C.byref(handed)))
+        return cls.from_handle(h.value), int(handed.value)
+
     # -- properties -----------------------------------------------------------
     @property
     def handle(self) -> Optional[int]:

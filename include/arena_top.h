@@ -109,6 +109,37 @@ int  arena_load_json_device(const char *podlist_json, size_t podlist_len,
                             arena_load_device_stats *stats /* may be NULL */);
 
 /*
+ * arena_load_json with the PodList decoded on the GPU: the SAME host snapshot (columns, names, jobs,
+ * row order) as arena_load_json gives for the same five inputs, so `top job`, `top node -d` and
+ * `arena list` can use the device loader too.  The device scanner reports, per pod, the accounting
+ * columns and the PLACES of metadata.name / namespace / creationTimestamp, the five labels the trainers
+ * read (trainer_mpi.go:315-332, trainer_standalone.go:257-273, trainer_tensorflow.go:394-418),
+ * ownerReferences[].kind == "Job" and status.hostIP; the host copies those bytes out and runs the job
+ * membership rules and the grouping as arena_load_json does.  Replaces pod_helper.go:15-43 +
+ * json.go:171 for all three commands.  Items the scanner does not decide (escaped strings, exotic
+ * quantities ...) are parsed one by one by the host's item code; a document it cannot take at all goes
+ * through arena_load_json as a whole (stats->fell_back), which also owns every error message.
+ */
+int  arena_load_json_gpu(const char *podlist_json, size_t podlist_len,
+                         const char *nodelist_json, size_t nodelist_len,
+                         const char *joblist_json, size_t joblist_len,       /* may be NULL */
+                         const char *tfjoblist_json, size_t tfjoblist_len,   /* may be NULL */
+                         const char *helm_list_text, size_t helm_len,        /* may be NULL */
+                         int group_by_job, arena_host_snapshot **out,
+                         arena_load_device_stats *stats /* may be NULL */);
+
+/* Diagnostic twin: the same scanner source compiled for the HOST walks the items (no CUDA call), then
+ * the same record building and job rules run.  For the CPU test-suite (whole snapshots against
+ * arena_load_json without a GPU); not a fallback of anything.  n_handed_back: items that went through
+ * the host's item code.  A document the scanner path does not take is an error here. */
+int  arena_load_json_hostscan(const char *podlist_json, size_t podlist_len,
+                              const char *nodelist_json, size_t nodelist_len,
+                              const char *joblist_json, size_t joblist_len,
+                              const char *tfjoblist_json, size_t tfjoblist_len,
+                              const char *helm_list_text, size_t helm_len,
+                              int group_by_job, arena_host_snapshot **out, uint64_t *n_handed_back);
+
+/*
  * Diagnostic: the per-item scanner of arena_load_json_device (csrc/pod_scan.cuh, the same
  * source compiled for the host) over every element of .items, in PodList order.  `nodes`
  * is a snapshot loaded from the NodeList.  Arrays hold `capacity` pods (ctr_val / ctr_scale:

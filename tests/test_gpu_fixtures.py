@@ -119,9 +119,32 @@ def test_cli_parses_an_api_server_shaped_list_on_the_gpu(gpu, tmp_path):
                                "--loader", loader, "--time")
         assert rc == 0 and out == want, loader
         assert ("parsed on the GPU" in err) == (loader == "device")
-    rc, out, _ = run_cli("node", "-d", "--pods", str(tmp_path / "pods.json"), "--nodes", str(tmp_path / "nodes.json"),
-                         "--loader", "device")
-    assert rc == 1 and "without -d" in out
+    # -d needs pod names and namespaces: the whole host snapshot, the PodList still decoded on the GPU
+    want_d, _ = top_ref.top_node(pods, nodes, details=True)
+    for loader in ("device", "host"):
+        rc, out, err = run_cli("node", "-d", "--pods", str(tmp_path / "pods.json"), "--nodes", str(tmp_path / "nodes.json"),
+                               "--loader", loader, "--time")
+        assert rc == 0 and out == want_d, loader
+        assert ("parsed on the GPU" in err) == (loader == "device")
+
+
+def test_cli_top_job_decodes_the_podlist_on_the_gpu(gpu, tmp_path):
+    podlist, nodelist, joblist, tfjoblist, helm = MF.config2(n_pods_target=3000, n_nodes=300)
+    docs = {"pods.json": podlist, "nodes.json": nodelist, "jobs.json": joblist, "tfjobs.json": tfjoblist}
+    for name, doc in docs.items():
+        (tmp_path / name).write_text(json.dumps(doc))
+    (tmp_path / "helm.txt").write_text(helm)
+    P, Jl, T = (json.dumps(x).encode() for x in (podlist, joblist, tfjoblist))
+    want_job, _ = top_ref.top_job(P, Jl, T, helm, MF.NOW)
+    want_list, _ = top_ref.job_list(P, Jl, T, helm, MF.NOW)
+    flags = ["--pods", str(tmp_path / "pods.json"), "--nodes", str(tmp_path / "nodes.json"), "--jobs", str(tmp_path / "jobs.json"),
+             "--tfjobs", str(tmp_path / "tfjobs.json"), "--releases", str(tmp_path / "helm.txt"), "--now", str(MF.NOW), "--time"]
+    for loader in ("device", "host"):
+        rc, out, err = run_cli("job", *flags, "--loader", loader)
+        assert rc == 0 and out == want_job, loader
+        assert ("parsed on the GPU" in err) == (loader == "device"), err
+        rc, out, err = run_cli("list", *flags, "--loader", loader)
+        assert rc == 0 and out == want_list, loader
 
 
 def test_cli_error_behaviour(gpu, tmp_path):

@@ -209,3 +209,81 @@ def test_fractional_gpu_limits_stay_on_the_device(gpu):
     assert changed > 200
     stats = check_device_load(gpu, json.dumps(doc).encode(), nodes, expect_fallback=False)
     assert stats["n_items"] == 20_000
+
+
+# ---- arena_load_json_gpu: the whole host snapshot (names, labels, job table) with the PodList decoded on the GPU ----
+
+def test_full_snapshot_from_the_gpu_equals_the_host_loader_on_the_fixture(gpu):
+    from test_loader_full_scan import same_snapshot
+    docs = (rd("pods.json"), rd("nodes.json"), rd("jobs.json"), rd("tfjobs.json"), rd("helm_list.txt"))
+    for by_job in (False, True):
+        want = gpu.HostSnapshot.from_json(*docs, group_by_job=by_job)
+        got, st = gpu.HostSnapshot.from_json_gpu(*docs, group_by_job=by_job)
+        assert not st["fell_back"] and st["n_items"] == want.n_pods and 0 < st["n_handed_back"] < want.n_pods // 2
+        same_snapshot(got, want)
+    # and the texts the user sees, computed on the GPU from that snapshot
+    import make_fixtures as MF
+    got, _ = gpu.HostSnapshot.from_json_gpu(*docs, group_by_job=True)
+    res = gpu.top_job(gpu.DeviceSnapshot.upload(got))
+    assert gpu.format_top_job(got, res, MF.NOW) == rd("expected_top_job.txt", "r")
+    assert gpu.format_job_list(got, res, MF.NOW) == rd("expected_list.txt", "r")
+    got, _ = gpu.HostSnapshot.from_json_gpu(docs[0], docs[1])
+    assert gpu.format_top_node(got, gpu.top_node(gpu.DeviceSnapshot.upload(got), details=True), details=True) == rd("expected_top_node_details.txt", "r")
+
+
+def test_full_snapshot_config2_from_pinned_memory(gpu):
+    """BASELINE configs[2] shape (jobs of all three trainers) at 3000 pods, the document in page-locked memory."""
+    from test_loader_full_scan import same_snapshot
+    import make_fixtures as MF
+    podlist, nodelist, joblist, tfjoblist, helm = MF.config2(n_pods_target=3000, n_nodes=300)
+    P, N, Jl, T = (json.dumps(x).encode() for x in (podlist, nodelist, joblist, tfjoblist))
+    want = gpu.HostSnapshot.from_json(P, N, Jl, T, helm.encode(), group_by_job=True)
+    buf = gpu.PinnedBuffer(len(P)).fill(P)
+    got, st = gpu.HostSnapshot.from_json_gpu(buf, N, Jl, T, helm.encode(), group_by_job=True)
+    assert not st["fell_back"] and st["n_handed_back"] == 0 and st["n_items"] == want.n_pods
+    same_snapshot(got, want)
+    text, _ = top_ref.top_job(P, Jl, T, helm, MF.NOW)
+    assert gpu.format_top_job(got, gpu.top_job(gpu.DeviceSnapshot.upload(got)), MF.NOW) == text
+
+
+def test_full_snapshot_fuzz_and_errors(gpu):
+    """The job-field fuzz of tests/test_loader_full_scan.py through the device; errors are the host loader's."""
+    import test_loader_full_scan as F
+    rng = random.Random(99)
+    nodes = json.dumps({"items": [LT.make_node(n) for n in range(5)]}).encode()
+    helm = b"NAME\tNAMESPACE\nr0\t1\tdefault\nr1\t1\tdefault\njob-00000\t1\tdefault\n"
+    jobs = json.dumps({"items": [
+        {"metadata": {"namespace": "default", "labels": {"release": "r0", "app": "tf-horovod"}}, "status": {"active": 2}},
+        {"metadata": {"namespace": "default", "labels": {"release": "r1", "app": "training"}}, "status": {"succeeded": 1}},
+        {"metadata": {"namespace": "default", "labels": {"release": "job-00000", "app": "tf-horovod"}}, "status": {}}]}).encode()
+    seen = {"device": 0, "handed": 0, "fallback": 0, "error": 0}
+    for trial in range(120):
+        items = []
+        for i in range(rng.randrange(1, 40)):
+            pod = LT.make_pod(rng.randrange(8), rng, 6)
+            pod["metadata"]["managedFields"] = []
+            if rng.random() < 0.3:
+                F.mutate_meta(pod, rng)
+            items.append(pod)
+        case = json.dumps({"kind": "PodList", "items": items}, ensure_ascii=rng.random() < 0.5).replace("\\\\u00", "\\u00").encode()
+        by_job = rng.random() < 0.5
+        try:
+            want = gpu.HostSnapshot.from_json(case, nodes, jobs, None, helm, group_by_job=by_job)
+        except gpu.ArenaError as e1:
+            with pytest.raises(gpu.ArenaError) as e2:
+                gpu.HostSnapshot.from_json_gpu(case, nodes, jobs, None, helm, group_by_job=by_job)
+            assert str(e1) == str(e2.value)
+            seen["error"] += 1
+            continue
+        got, st = gpu.HostSnapshot.from_json_gpu(case, nodes, jobs, None, helm, group_by_job=by_job)
+        F.same_snapshot(got, want)
+        seen["fallback" if st["fell_back"] else "handed" if st["n_handed_back"] else "device"] += 1
+    assert seen["device"] > 10 and seen["handed"] > 10 and seen["error"] > 3, seen
+    # a bad JobList: the PodList was fine, the message is still arena_load_json's
+    pods, _ = LT.make_docs(50, 5, seed=1)
+    for bad in (b'{"items": 5}', b'{"items": [', b'{"items":[{"status":{"active":"x"}, "metadata":{"labels":{"release":"r0","app":"tf-horovod"},"namespace":"default"}}]}'):
+        with pytest.raises(gpu.ArenaError) as e1:
+            gpu.HostSnapshot.from_json(pods, nodes, bad, None, helm)
+        with pytest.raises(gpu.ArenaError) as e2:
+            gpu.HostSnapshot.from_json_gpu(pods, nodes, bad, None, helm)
+        assert str(e1.value) == str(e2.value)
