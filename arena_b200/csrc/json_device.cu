@@ -904,15 +904,26 @@ int load_on_device(const char *podlist, size_t len, const std::vector<std::strin
             const u64 max_handed = std::max<u64>(64, P / 8);
             u64 handed = 0;
             pods_out->assign(P, arena_host::PodRec());
-            for (u64 k = 0; k < P; k++) {
-                arena_host::PodRec &r = (*pods_out)[k];
-                if (flags[k]) {
-                    if (flags[k] == kFlagSeparator || ++handed > max_handed) return ARENA_OK;      // not handled
-                    if (!parser.parse_full(podlist, len, ib[k], ie[k], r)) return ARENA_OK;
-                    continue;
-                }
-                rec_from_scan(podlist, node[k], phase[k], (uint32_t)nctr[k], (const int64_t *)vals.data() + k, P,
-                              (const int8_t *)scales.data() + k, meta[k], r);
+            for (u64 k = 0; k < P; k++) {                       // the few flagged items first: any of them may end the attempt
+                if (!flags[k]) continue;
+                if (flags[k] == kFlagSeparator || ++handed > max_handed) return ARENA_OK;          // not handled
+                if (!parser.parse_full(podlist, len, ib[k], ie[k], (*pods_out)[k])) return ARENA_OK;
+            }
+            // the rest is copying a dozen short strings per pod: spread over a few threads when there are many
+            auto build = [&](u64 lo, u64 hi) {
+                for (u64 k = lo; k < hi; k++)
+                    if (!flags[k])
+                        rec_from_scan(podlist, node[k], phase[k], (uint32_t)nctr[k], (const int64_t *)vals.data() + k, P,
+                                      (const int8_t *)scales.data() + k, meta[k], (*pods_out)[k]);
+            };
+            const unsigned hw = std::thread::hardware_concurrency();
+            const u64 n_thr = P < 4096 ? 1 : std::min<u64>(hw ? hw : 1, 8);
+            if (n_thr <= 1) build(0, P);
+            else {
+                std::vector<std::thread> pool;
+                const u64 per = (P + n_thr - 1) / n_thr;
+                for (u64 t = 0; t < n_thr; t++) pool.emplace_back(build, std::min(P, t * per), std::min(P, (t + 1) * per));
+                for (auto &th : pool) th.join();
             }
             if (stats) { stats->n_handed_back = handed; stats->ms_device = ms_since(t_start); }
             *handled = true;

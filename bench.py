@@ -221,16 +221,23 @@ def wire_format_leg(ab, n_pods=10_000, n_nodes=1000, reps=5):
         dev, st = ab.DeviceSnapshot.from_json_device(src, nodes)
         return ab.top_node(dev).cluster.tolist(), st
 
+    def full_path(src):
+        # the whole host snapshot (names, labels: what -d / top job / list need), PodList decoded on the GPU
+        h, st = ab.HostSnapshot.from_json_gpu(src, nodes)
+        return ab.top_node(ab.DeviceSnapshot.upload(h)).cluster.tolist(), st
+
     host_ms, host_cluster = best(host_path)
     dev_ms, (dev_cluster, st) = best(lambda: device_path(pods))
     pin_ms, (pin_cluster, st_pin) = best(lambda: device_path(pinned))
-    assert host_cluster == dev_cluster == pin_cluster, "loaders disagree"
+    full_ms, (full_cluster, st_full) = best(lambda: full_path(pinned))
+    assert host_cluster == dev_cluster == pin_cluster == full_cluster, "loaders disagree"
     return {
         "workload": f"API-server-shaped PodList, {n_pods} pods / {n_nodes} nodes (BASELINE configs[1] scale), "
                     f"{len(pods)} bytes of JSON, then one `top node`",
         "host_loader_ms": host_ms, "host_threads": os.cpu_count(),
         "gpu_loader_ms": dev_ms, "gpu_loader_pinned_input_ms": pin_ms,
-        "gpu_loader_h2d_ms": st_pin["ms_h2d"], "fell_back": int(st["fell_back"] or st_pin["fell_back"]),
+        "gpu_loader_h2d_ms": st_pin["ms_h2d"], "fell_back": int(st["fell_back"] or st_pin["fell_back"] or st_full["fell_back"]),
+        "gpu_loader_full_snapshot_ms": full_ms,
         "pods_per_s_host": n_pods / host_ms * 1e3, "pods_per_s_gpu_pinned": n_pods / pin_ms * 1e3,
         "json_gb_per_s_gpu_pinned": len(pods) / pin_ms / 1e6,
     }

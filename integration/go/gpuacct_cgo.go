@@ -185,9 +185,11 @@ func listJobsGPU(podList, nodeList, jobList, tfjobList, helmList []byte, nowUnix
 		return (*C.char)(unsafe.Pointer(&b[0]))
 	}
 	var host *C.arena_host_snapshot
-	if err := gpuacctErr(C.arena_load_json(ptr(podList), C.size_t(len(podList)), ptr(nodeList), C.size_t(len(nodeList)),
+	// the PodList is decoded on the GPU (names, labels, owners, timestamps come back as places in the
+	// document); the snapshot is the one arena_load_json builds, and so are the errors
+	if err := gpuacctErr(C.arena_load_json_gpu(ptr(podList), C.size_t(len(podList)), ptr(nodeList), C.size_t(len(nodeList)),
 		ptr(jobList), C.size_t(len(jobList)), ptr(tfjobList), C.size_t(len(tfjobList)),
-		ptr(helmList), C.size_t(len(helmList)), 1, &host)); err != nil {
+		ptr(helmList), C.size_t(len(helmList)), 1, &host, nil)); err != nil {
 		return "", err
 	}
 	defer C.arena_host_snapshot_free(host)
