@@ -147,7 +147,7 @@ static int init_current_slot(int device)
                     "code for other architectures", device, prop.major, prop.minor);
     ctx().device = device;
     ctx().sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kPodThreads, 0));
     {
         const char *env = getenv("ARENA_STAGED");                    // A/B switch while the variant is evaluated
         if (env && env[0] == '1')
@@ -312,10 +312,27 @@ int ensure_job_arrays(arena_snapshot *s)
     return ARENA_OK;
 }
 
-template <typename K>
-cudaError_t launch_pods(K kernel, int grid, const PodsArgs &pa, cudaStream_t st)
+// PodsArgs::n_static: how many tiles a launch shares out grid-stride before its CTAs turn to the pool: all but
+// the last four rounds when the launch has at least 32 of them.  Shorter launches keep everything grid-stride: a
+// pool round is a third slower than a fixed one (a barrier per run), which costs a 14-round launch more than the
+// shorter tail gives back (1.27e7 pods: 67.8 -> 69.8 us; 1e8 pods: 431.6 -> 424.1 us; profiles/r02_iterations.md).
+// ARENA_DYN_ROUNDS=r forces the last r rounds into the pool (0: none).
+unsigned static_tiles(u64 n_pods, int grid)
 {
-    kernel<<<grid, kThreads, 0, st>>>(pa);
+    const u64 W = (u64)grid * kPodWarps, n_tiles = (n_pods + kWarpPods - 1) / kWarpPods;
+    const u64 rounds = n_tiles / W;
+    static const long forced = [] { const char *e = getenv("ARENA_DYN_ROUNDS"); return e ? std::strtol(e, nullptr, 10) : -1L; }();
+    const u64 pool_rounds = forced >= 0 ? (u64)forced : (rounds >= 32 ? 4 : 0);
+    if (pool_rounds == 0) return 0xFFFFFFFFu;
+    const u64 static_rounds = rounds > pool_rounds ? rounds - pool_rounds : 1;
+    return (unsigned)std::min<u64>(static_rounds * W, 0xFFFFFFFFull);
+}
+
+template <typename K>
+cudaError_t launch_pods(K kernel, int grid, PodsArgs pa, cudaStream_t st, int threads = kPodThreads)
+{
+    pa.n_static = static_tiles(pa.P, grid);
+    kernel<<<grid, threads, 0, st>>>(pa);
     return cudaGetLastError();
 }
 
@@ -383,8 +400,8 @@ int launch_top_node_plain(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i
     // node_alloc is accumulated with atomics: it starts from zero.  (A launch that clears it itself --
     // cooperative launch, every CTA zeroes a slice, one grid-wide barrier -- was measured and dropped:
     // the barrier costs what the memset costs, profiles/r02_iterations.md.)
-    int gp = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm);
-    const int gn = grid_for(v.n_nodes, (u64)kThreads * 4, ctx().pods_ctas_per_sm);
+    int gp = grid_for(v.n_pods, (u64)kPodWarps * kWarpPods, ctx().pods_ctas_per_sm);
+    const int gn = grid_for(v.n_nodes, (u64)kPodThreads * 4, ctx().pods_ctas_per_sm);
     if (gn > gp) gp = gn;
     if (v.n_nodes) CUDA_TRY(cudaMemsetAsync(d_alloc, 0, v.n_nodes * 8, st));
     if (prof) CUDA_TRY(cudaEventRecord(pe[1], st));
@@ -419,7 +436,7 @@ int launch_top_node_plain(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i
             // the pod columns staged one iteration ahead by the bulk-copy engine (kernels.cuh)
             int gs = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().staged_ctas_per_sm);
             if (gn > gs) gs = std::min(gn, ctx().sm_count * ctx().staged_ctas_per_sm);
-            e = launch_pods(top_node_pods_staged_kernel, gs, pa, st);
+            e = launch_pods(top_node_pods_staged_kernel, gs, pa, st, kThreads);
         } else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
     }
     if (e != cudaSuccess) return fail(ARENA_E_CUDA, "top-node kernel launch: %s", cudaGetErrorString(e));
@@ -479,7 +496,8 @@ int launch_top_job(arena_snapshot *s, i64 *d_req, i64 *d_alloc, unsigned *d_orde
     pa.total_alloc = d_totals + 1;
     pa.scratch = s->scratch;
     // the top-node kernel's 32-bit fast tiles, keyed by job (generic tiles where a tile does not qualify)
-    top_node_pods_kernel<true, false, true><<<grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().pods_ctas_per_sm), kThreads, 0, st>>>(pa);
+    if (launch_pods(top_node_pods_kernel<true, false, true>, grid_for(v.n_pods, (u64)kPodWarps * kWarpPods, ctx().pods_ctas_per_sm), pa, st) != cudaSuccess)
+        return fail(ARENA_E_CUDA, "top-job pods kernel launch failed");
     count_launch();
 
     if (v.n_pods) {
@@ -1623,7 +1641,7 @@ int arena_top_job_device_noalloc(const arena_snapshot_view *dev, int64_t *d_job_
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx().stream;
 
     // leftovers of an earlier (possibly interrupted) call must not leak into this one
-    CUDA_TRY(cudaMemsetAsync(w->scratch.ticket, 0, sizeof(w->scratch.ticket), st));
+    CUDA_TRY(cudaMemsetAsync(w->scratch.ticket, 0, sizeof(w->scratch.ticket) + sizeof(w->scratch.next_round), st));   // (adjacent)
 
     // the per-job accumulators are the caller's output buffers themselves
     JobInitArgs ia{J, (u64 *)d_job_req, (u64 *)d_job_alloc, w->maxcreated, d_job_latest};
@@ -1703,3 +1721,12 @@ int arena_quantity_values(const int64_t *val, const int8_t *scale, uint64_t n, i
 }
 
 }  // extern "C"
+
+#ifdef ARENA_TIMELINE
+extern "C" int arena_debug_timeline(unsigned long long *out, int n)
+{
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpyFromSymbol(out, arena::g_timeline, sizeof(unsigned long long) * (size_t)n));
+    return ARENA_OK;
+}
+#endif

@@ -189,6 +189,7 @@ struct Scratch {
     u64 partial_a[kMaxPartials];   // per-CTA partial of the first total
     u64 partial_b[kMaxPartials];   // per-CTA partial of the second total
     unsigned ticket[4];
+    unsigned next_round[4];        // per ticket id: CTA-rounds handed out from the pool of the running launch
 };
 
 // ---- totals across GPUs without a collective launch -------------------------------------------
@@ -276,7 +277,7 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
         a += *((volatile u64 *)&part_a[i]);
         if (two) b += *((volatile u64 *)&part_b[i]);
     }
-    __shared__ u64 s_a[kWarps], s_b[kWarps];
+    __shared__ u64 s_a[32], s_b[32];            // (any CTA size)
     a = warp_reduce_sum(a);
     b = warp_reduce_sum(b);
     if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
@@ -291,6 +292,7 @@ __device__ __forceinline__ void finish_totals(u64 block_a, u64 block_b, bool two
             if (two) *out_b = (i64)tb;
         }
         sc->ticket[ticket_id] = 0;      // ready for the next launch
+        sc->next_round[ticket_id] = 0;
         if (px) px->epoch += 1;         // this CTA is the only writer; the next launch is ordered behind it
     }
     if (!px) return;
@@ -367,6 +369,9 @@ struct PodsArgs {
     // multi-GPU: exchange the two totals with the peer GPUs inside this launch (or nullptr)
     PeerExchange *px;
     unsigned px_lag;                // 0: collect this step's totals; 1: the previous step's (deferred)
+    // Tiles below n_static (a multiple of the grid's warp count) are taken grid-stride; the rest form a pool
+    // that CTAs draw from, one run of kPodWarps consecutive tiles at a time (top_node_pods_kernel).
+    unsigned n_static;
 };
 
 // Rare path (a row that runs past the end of the container columns) kept out
@@ -721,8 +726,15 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
     return total;
 }
 
+// 16 warps x 3 CTAs per SM rather than 8 x 6: the same 48 warps, fewer CTAs for the SM to play favourites with
+// (1e8 pods: 437 -> 432 us, tools/variants.sh)
+#ifndef ARENA_POD_WARPS
+#define ARENA_POD_WARPS 16
+#endif
+constexpr int kPodWarps = ARENA_POD_WARPS;      // warps per CTA of top_node_pods_kernel
+constexpr int kPodThreads = kPodWarps * 32;
 #ifndef ARENA_MINB
-#define ARENA_MINB 6
+#define ARENA_MINB 3
 #endif
 // kDirect: pods are NOT grouped by node (almost every position would be an edge and telescoping
 // would cost two atomics per pod): each pod's own value is added to its node instead, one atomic
@@ -732,11 +744,34 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
 // kJob: the same tiles keyed by pod_job for `top job` (job_info.go:51-70): requested = every pod,
 // allocated = active pods, ARENA_ROLE_LATEST pods only bid with their creation time; per-pod adds
 // (pods of one job are scattered over the node-grouped rows), two totals.
-template <bool kDirect, bool kDetails, bool kJob = false>
-__global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
+#ifdef ARENA_TIMELINE
+// Debug builds only (tools/variants.sh timeline "-DARENA_TIMELINE"): thread 0 of every CTA notes the global
+// timer at six points of a launch; arena_debug_timeline() copies the table out (tools/timeline.py).
+__device__ unsigned long long g_timeline[2048 * 6];
+__device__ __forceinline__ void timeline_mark(int k)
 {
-    __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
-    __shared__ u64 s_wa[kWarps];
+    if (threadIdx.x == 0 && blockIdx.x < 2048) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_timeline[blockIdx.x * 6 + k] = t;
+        if (k == 0) {                                   // where the CTA runs: the SM id rides in the top bits of mark 0
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_timeline[blockIdx.x * 6] = (t & 0x0000FFFFFFFFFFFFull) | ((unsigned long long)smid << 48);
+        }
+    }
+}
+#define ARENA_MARK(k) timeline_mark(k)
+#else
+#define ARENA_MARK(k)
+#endif
+
+template <bool kDirect, bool kDetails, bool kJob = false>
+__global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
+{
+    ARENA_MARK(0);
+    __shared__ __align__(16) u64 s_prefix[kPodWarps][kChunkCtrs + 2];
+    __shared__ u64 s_wa[kPodWarps];
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -748,17 +783,32 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
     const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
     const unsigned n_full = (unsigned)(a.P / kWarpPods);
     const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
-    const unsigned tile_step = gridDim.x * kWarps;
+    const unsigned tile_step = gridDim.x * kPodWarps;
 
     // Tiles the 32-bit fast path cannot take (huge or negative values, positive scales, pods with hundreds of
     // containers, the ragged last tile) are not summed where they are met: the call into the generic 64-bit
     // tile would sit inside the hot loop and its live registers would be spilled around it on every trip.
     // A warp notes up to kDeferred such tiles and sums them after its loop; a warp that meets more leaves the
     // hot loop for good and takes ALL its remaining tiles generically (an input like that has no fast tiles).
+    //
+    // Who takes which tile.  The warps of an SM do not advance at one pace: its CTAs finish equal shares up to
+    // 10 us apart (the scheduler favours some of them for the whole launch: profiles/r02_iterations.md), and a
+    // launch is over when the slowest is.  So only the first n_static tiles are shared out in advance, grid-stride;
+    // the last few rounds are a pool from which a CTA draws one run of kPodWarps consecutive tiles at a time (one
+    // atomic per CTA and run, asked for a run ahead; one barrier per run).  CTAs that are ahead take more of them.
     constexpr int kDeferred = 8;
-    __shared__ unsigned s_deferred[kWarps][kDeferred];
-    unsigned n_deferred = 0, resume = 0xFFFFFFFFu;
-    for (unsigned tile = blockIdx.x * kWarps + warp; tile < n_tiles; tile += tile_step) {
+    __shared__ unsigned s_deferred[kPodWarps][kDeferred];
+    __shared__ unsigned s_claim[2];
+    unsigned n_deferred = 0;
+    bool generic = false;                                  // this warp has left the fast code for good
+    unsigned *const pool = &a.scratch->next_round[kJob ? 2 : 1];
+    const unsigned n_static = a.n_static < n_tiles ? a.n_static : n_tiles;
+    unsigned pending = 0, parity = 0;
+    if (threadIdx.x == 0) pending = atomicAdd(pool, 1u);   // this CTA's first run from the pool: asked for now, read after its share
+    unsigned tile = blockIdx.x * kPodWarps + warp, limit = n_static;
+    for (;;) {
+    if (!generic)
+    for (; tile < limit; tile += tile_step) {
         bool fast = tile < n_full;
         u64 tile_alloc = 0;
         if (fast) {
@@ -894,13 +944,35 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
             }
         }
         if (!fast) {                                   // warp-uniform
-            if (n_deferred == (unsigned)kDeferred) { resume = tile; break; }
+            if (n_deferred == (unsigned)kDeferred) { generic = true; break; }      // (`tile` is still to be done)
             if (lane == 0) s_deferred[warp][n_deferred] = tile;
             n_deferred++;
         }
         if (!kJob && lane == 31) acc_alloc += tile_alloc;
+        ARENA_MARK(1);
+    }
+    if (generic)
+        for (; tile < limit; tile += tile_step) {
+            if (kJob) {
+                const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
+                if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
+            } else {
+                const u64 t = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
+                if (lane == 31) acc_alloc += t;
+            }
+        }
+    // ---- the CTA's next run from the pool -----------------------------------------------------
+    if (threadIdx.x == 0) s_claim[parity] = pending;
+    __syncthreads();
+    const unsigned run0 = n_static + s_claim[parity] * (unsigned)kPodWarps;
+    parity ^= 1u;
+    if (run0 >= n_tiles) break;                            // the same for the whole CTA
+    if (threadIdx.x == 0) pending = atomicAdd(pool, 1u);   // the run after this one
+    tile = run0 + warp;
+    limit = tile + 1 < n_tiles ? tile + 1 : n_tiles;       // exactly this tile (none when the last run is short)
     }
     __syncwarp();
+    ARENA_MARK(2);
     for (unsigned k = 0; k < n_deferred; k++) {
         const unsigned tile = s_deferred[warp][k];
         if (kJob) {
@@ -911,24 +983,15 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
             if (lane == 31) acc_alloc += t;
         }
     }
-    for (unsigned tile = resume; tile < n_tiles; tile += tile_step) {      // (resume is past n_tiles unless the list overflowed)
-        if (kJob) {
-            const TileSums ts = process_tile_fallback_job(&a, tile, tile < n_full, lane, s_prefix[warp]);
-            if (lane == 31) { job_req += ts.req; job_alloc += ts.alloc; }
-        } else {
-            const u64 t = process_tile_fallback(&a, tile, tile < n_full, lane, s_prefix[warp]).alloc;
-            if (lane == 31) acc_alloc += t;
-        }
-    }
     if (kJob) {
-        __shared__ u64 s_wr[kWarps];
+        __shared__ u64 s_wr[kPodWarps];
         job_req = warp_reduce_sum(job_req);
         job_alloc = warp_reduce_sum(job_alloc);
         if (lane == 0) { s_wr[warp] = job_req; s_wa[warp] = job_alloc; }
         __syncthreads();
         u64 block_r = 0, block_al = 0;
         if (threadIdx.x == 0)
-            for (int w = 0; w < kWarps; w++) { block_r += s_wr[w]; block_al += s_wa[w]; }
+            for (int w = 0; w < kPodWarps; w++) { block_r += s_wr[w]; block_al += s_wa[w]; }
         finish_totals(block_al, block_r, true, a.scratch, 2, a.total_alloc, a.total_req);
         return;
     }
@@ -943,15 +1006,18 @@ __global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_kernel(con
         cap_sum += (u64)t;
     }
     cap_sum = warp_reduce_sum(cap_sum);
+    ARENA_MARK(3);
 
-    __shared__ u64 s_wc[kWarps];
+    __shared__ u64 s_wc[kPodWarps];
     if (lane == 31) s_wa[warp] = acc_alloc;
     if (lane == 0) s_wc[warp] = cap_sum;
     __syncthreads();
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
-        for (int w = 0; w < kWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
+        for (int w = 0; w < kPodWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
+    ARENA_MARK(4);
     finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.px_lag);
+    ARENA_MARK(5);
 }
 
 // ---------------------------------------------------------------------------
@@ -998,7 +1064,7 @@ __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, 
                  :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-__global__ void __launch_bounds__(kThreads, ARENA_MINB) top_node_pods_staged_kernel(const __grid_constant__ PodsArgs a)
+__global__ void __launch_bounds__(kThreads, 6) top_node_pods_staged_kernel(const __grid_constant__ PodsArgs a)
 {
     __shared__ __align__(16) u64 s_prefix[kWarps][kChunkCtrs + 2];
     __shared__ __align__(128) unsigned char s_stage[2][kStageBytes];

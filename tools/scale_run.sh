@@ -19,6 +19,11 @@ PY
 }
 LAST=1
 for N in $NS; do run strong $N; LAST=$N; done
-run skewed $LAST --skewed
-run weak $LAST --scaling weak
-run job $LAST --command job
+# SCALE_EXTRA: the other arms at the largest rank count (default all three; "" = strong only)
+for arm in ${SCALE_EXTRA-skewed weak job}; do
+  case $arm in
+    skewed) run skewed $LAST --skewed ;;
+    weak) run weak $LAST --scaling weak ;;
+    job) run job $LAST --command job ;;
+  esac
+done
