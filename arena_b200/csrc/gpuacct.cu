@@ -34,7 +34,7 @@ struct Context {
     bool ready = false;
     int device = -1;
     int sm_count = 0;
-    int pods_ctas_per_sm = 0;
+    int pods_ctas_per_sm = 0, pods_long_ctas_per_sm = 0;
     int staged_ctas_per_sm = 0;      // > 0: the bulk-copy staged top-node kernel is used for grouped summaries
     int jobs_ctas_per_sm = 0;
     int packed_ctas_per_sm = 0;
@@ -148,6 +148,8 @@ static int init_current_slot(int device)
     ctx().device = device;
     ctx().sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_ctas_per_sm, top_node_pods_kernel<false, false>, kPodThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx().pods_long_ctas_per_sm,
+                                                           top_node_pods_kernel<false, false, false, kPodWarpsLong>, kPodThreadsLong, 0));
     {
         const char *env = getenv("ARENA_STAGED");                    // A/B switch while the variant is evaluated
         if (env && env[0] == '1')
@@ -317,12 +319,13 @@ int ensure_job_arrays(arena_snapshot *s)
 // pool round is a third slower than a fixed one (a barrier per run), which costs a 14-round launch more than the
 // shorter tail gives back (1.27e7 pods: 67.8 -> 69.8 us; 1e8 pods: 431.6 -> 424.1 us; profiles/r02_iterations.md).
 // ARENA_DYN_ROUNDS=r forces the last r rounds into the pool (0: none).
-unsigned static_tiles(u64 n_pods, int grid)
+constexpr u64 kLongLaunchRounds = 32;
+unsigned static_tiles(u64 n_pods, int grid, int warps_per_cta)
 {
-    const u64 W = (u64)grid * kPodWarps, n_tiles = (n_pods + kWarpPods - 1) / kWarpPods;
+    const u64 W = (u64)grid * (u64)warps_per_cta, n_tiles = (n_pods + kWarpPods - 1) / kWarpPods;
     const u64 rounds = n_tiles / W;
     static const long forced = [] { const char *e = getenv("ARENA_DYN_ROUNDS"); return e ? std::strtol(e, nullptr, 10) : -1L; }();
-    const u64 pool_rounds = forced >= 0 ? (u64)forced : (rounds >= 32 ? 4 : 0);
+    const u64 pool_rounds = forced >= 0 ? (u64)forced : (rounds >= kLongLaunchRounds ? 4 : 0);
     if (pool_rounds == 0) return 0xFFFFFFFFu;
     const u64 static_rounds = rounds > pool_rounds ? rounds - pool_rounds : 1;
     return (unsigned)std::min<u64>(static_rounds * W, 0xFFFFFFFFull);
@@ -331,7 +334,7 @@ unsigned static_tiles(u64 n_pods, int grid)
 template <typename K>
 cudaError_t launch_pods(K kernel, int grid, PodsArgs pa, cudaStream_t st, int threads = kPodThreads)
 {
-    pa.n_static = static_tiles(pa.P, grid);
+    pa.n_static = static_tiles(pa.P, grid, threads / 32);
     kernel<<<grid, threads, 0, st>>>(pa);
     return cudaGetLastError();
 }
@@ -437,7 +440,15 @@ int launch_top_node_plain(const arena_snapshot *s, i64 *d_total, i64 *d_alloc, i
             int gs = grid_for(v.n_pods, (u64)kWarps * kWarpPods, ctx().staged_ctas_per_sm);
             if (gn > gs) gs = std::min(gn, ctx().sm_count * ctx().staged_ctas_per_sm);
             e = launch_pods(top_node_pods_staged_kernel, gs, pa, st, kThreads);
-        } else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
+        } else {
+            // a long launch (32 rounds and more: 3e7 pods on a B200) takes the 16-warp shape and the pool
+            const u64 n_tiles = (v.n_pods + kWarpPods - 1) / kWarpPods;
+            const u64 warps = (u64)ctx().sm_count * (u64)ctx().pods_long_ctas_per_sm * kPodWarpsLong;
+            if (ctx().pods_long_ctas_per_sm > 0 && n_tiles / warps >= kLongLaunchRounds) {
+                int gl = grid_for(v.n_pods, (u64)kPodWarpsLong * kWarpPods, ctx().pods_long_ctas_per_sm);
+                e = launch_pods(top_node_pods_kernel<false, false, false, kPodWarpsLong>, gl, pa, st, kPodThreadsLong);
+            } else e = launch_pods(top_node_pods_kernel<false, false>, gp, pa, st);
+        }
     }
     if (e != cudaSuccess) return fail(ARENA_E_CUDA, "top-node kernel launch: %s", cudaGetErrorString(e));
     count_launch();

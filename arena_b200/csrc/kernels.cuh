@@ -726,16 +726,12 @@ __device__ __forceinline__ unsigned fast_row(unsigned xa0, unsigned xa1, unsigne
     return total;
 }
 
-// 16 warps x 3 CTAs per SM rather than 8 x 6: the same 48 warps, fewer CTAs for the SM to play favourites with
-// (1e8 pods: 437 -> 432 us, tools/variants.sh)
-#ifndef ARENA_POD_WARPS
-#define ARENA_POD_WARPS 16
-#endif
-constexpr int kPodWarps = ARENA_POD_WARPS;      // warps per CTA of top_node_pods_kernel
-constexpr int kPodThreads = kPodWarps * 32;
-#ifndef ARENA_MINB
-#define ARENA_MINB 3
-#endif
+// top_node_pods_kernel comes in two CTA shapes with the same 48 warps per SM: 8 warps x 6 CTAs, and 16 x 3 for
+// the summary kernel on long launches -- fewer CTAs for the SM to play favourites with (1e8 pods: 437 -> 432 us;
+// at 1.25e7 pods per GPU with the peer exchange the small shape is the quicker one by 1.5 us: tools/ab_shard2.sh).
+constexpr int kPodWarps = 8, kPodThreads = kPodWarps * 32;
+constexpr int kPodWarpsLong = 16, kPodThreadsLong = kPodWarpsLong * 32;
+
 // kDirect: pods are NOT grouped by node (almost every position would be an edge and telescoping
 // would cost two atomics per pod): each pod's own value is added to its node instead, one atomic
 // per pod that contributes anything.  Both instantiations are exact for any order; the host picks
@@ -766,12 +762,12 @@ __device__ __forceinline__ void timeline_mark(int k)
 #define ARENA_MARK(k)
 #endif
 
-template <bool kDirect, bool kDetails, bool kJob = false>
-__global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
+template <bool kDirect, bool kDetails, bool kJob = false, int kPW = kPodWarps>
+__global__ void __launch_bounds__(kPW * 32, 48 / kPW) top_node_pods_kernel(const __grid_constant__ PodsArgs a)
 {
     ARENA_MARK(0);
-    __shared__ __align__(16) u64 s_prefix[kPodWarps][kChunkCtrs + 2];
-    __shared__ u64 s_wa[kPodWarps];
+    __shared__ __align__(16) u64 s_prefix[kPW][kChunkCtrs + 2];
+    __shared__ u64 s_wa[kPW];
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -783,7 +779,7 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
     const unsigned n_tiles = (unsigned)((a.P + kWarpPods - 1) / kWarpPods);
     const unsigned n_full = (unsigned)(a.P / kWarpPods);
     const unsigned K32 = (unsigned)(a.K < 0xFFFFFFFFull ? a.K : 0xFFFFFFFFull);
-    const unsigned tile_step = gridDim.x * kPodWarps;
+    const unsigned tile_step = gridDim.x * kPW;
 
     // Tiles the 32-bit fast path cannot take (huge or negative values, positive scales, pods with hundreds of
     // containers, the ragged last tile) are not summed where they are met: the call into the generic 64-bit
@@ -794,10 +790,10 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
     // Who takes which tile.  The warps of an SM do not advance at one pace: its CTAs finish equal shares up to
     // 10 us apart (the scheduler favours some of them for the whole launch: profiles/r02_iterations.md), and a
     // launch is over when the slowest is.  So only the first n_static tiles are shared out in advance, grid-stride;
-    // the last few rounds are a pool from which a CTA draws one run of kPodWarps consecutive tiles at a time (one
+    // the last few rounds are a pool from which a CTA draws one run of kPW consecutive tiles at a time (one
     // atomic per CTA and run, asked for a run ahead; one barrier per run).  CTAs that are ahead take more of them.
     constexpr int kDeferred = 8;
-    __shared__ unsigned s_deferred[kPodWarps][kDeferred];
+    __shared__ unsigned s_deferred[kPW][kDeferred];
     __shared__ unsigned s_claim[2];
     unsigned n_deferred = 0;
     bool generic = false;                                  // this warp has left the fast code for good
@@ -805,7 +801,7 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
     const unsigned n_static = a.n_static < n_tiles ? a.n_static : n_tiles;
     unsigned pending = 0, parity = 0;
     if (threadIdx.x == 0) pending = atomicAdd(pool, 1u);   // this CTA's first run from the pool: asked for now, read after its share
-    unsigned tile = blockIdx.x * kPodWarps + warp, limit = n_static;
+    unsigned tile = blockIdx.x * kPW + warp, limit = n_static;
     for (;;) {
     if (!generic)
     for (; tile < limit; tile += tile_step) {
@@ -964,7 +960,7 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
     // ---- the CTA's next run from the pool -----------------------------------------------------
     if (threadIdx.x == 0) s_claim[parity] = pending;
     __syncthreads();
-    const unsigned run0 = n_static + s_claim[parity] * (unsigned)kPodWarps;
+    const unsigned run0 = n_static + s_claim[parity] * (unsigned)kPW;
     parity ^= 1u;
     if (run0 >= n_tiles) break;                            // the same for the whole CTA
     if (threadIdx.x == 0) pending = atomicAdd(pool, 1u);   // the run after this one
@@ -984,14 +980,14 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
         }
     }
     if (kJob) {
-        __shared__ u64 s_wr[kPodWarps];
+        __shared__ u64 s_wr[kPW];
         job_req = warp_reduce_sum(job_req);
         job_alloc = warp_reduce_sum(job_alloc);
         if (lane == 0) { s_wr[warp] = job_req; s_wa[warp] = job_alloc; }
         __syncthreads();
         u64 block_r = 0, block_al = 0;
         if (threadIdx.x == 0)
-            for (int w = 0; w < kPodWarps; w++) { block_r += s_wr[w]; block_al += s_wa[w]; }
+            for (int w = 0; w < kPW; w++) { block_r += s_wr[w]; block_al += s_wa[w]; }
         finish_totals(block_al, block_r, true, a.scratch, 2, a.total_alloc, a.total_req);
         return;
     }
@@ -1008,13 +1004,13 @@ __global__ void __launch_bounds__(kPodThreads, ARENA_MINB) top_node_pods_kernel(
     cap_sum = warp_reduce_sum(cap_sum);
     ARENA_MARK(3);
 
-    __shared__ u64 s_wc[kPodWarps];
+    __shared__ u64 s_wc[kPW];
     if (lane == 31) s_wa[warp] = acc_alloc;
     if (lane == 0) s_wc[warp] = cap_sum;
     __syncthreads();
     u64 block_a = 0, block_c = 0;
     if (threadIdx.x == 0)
-        for (int w = 0; w < kPodWarps; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
+        for (int w = 0; w < kPW; w++) { block_a += s_wa[w]; block_c += s_wc[w]; }
     ARENA_MARK(4);
     finish_totals(block_a, block_c, true, a.scratch, 1, a.total_alloc, a.total_capacity, a.px, a.px_lag);
     ARENA_MARK(5);
