@@ -18,7 +18,8 @@ def test_parser_fuzz_tests_are_clean_under_asan_and_ubsan(built):
         pytest.skip("no libasan in this toolchain")
     if "ARENA_GPUACCT_LIB" in os.environ:
         pytest.skip("already running against an alternate build")
-    p = subprocess.run(["bash", os.path.join(ROOT, "tools", "asan_tests.sh"), "tests/test_pod_scan.py", "tests/test_loader_scan.py"],
+    p = subprocess.run(["bash", os.path.join(ROOT, "tools", "asan_tests.sh"), "tests/test_pod_scan.py", "tests/test_loader_scan.py",
+                        "tests/test_loader_full_scan.py"],
                        capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert p.returncode == 0, (p.stdout[-2000:], p.stderr[-2000:])
     assert "passed" in p.stdout and "runtime error" not in p.stderr and "AddressSanitizer" not in p.stderr
