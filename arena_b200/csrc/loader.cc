@@ -826,6 +826,8 @@ int load_with_pods(PodSource &src, const char *nodelist, size_t nodelen, const c
         rc = ARENA_OK;                                  // the plain path owns every error message (and their order)
     } catch (const std::bad_alloc &) {
         rc = fail(ARENA_E_NOMEM, "out of host memory while loading");
+    } catch (const std::exception &) {
+        rc = ARENA_OK;                                  // (a helper thread that could not start, ...): the plain path
     }
     delete h;
     return rc;
