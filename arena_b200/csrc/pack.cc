@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 #include <new>
 #include <thread>
 #include <vector>
@@ -33,20 +34,20 @@ int arena_host_snapshot_pack(const arena_snapshot_view *h, int pinned, arena_pac
     if (!p) return fail(ARENA_E_NOMEM, "out of host memory");
     int rc;
     // sizes are rounded up so that the device can read whole 32-bit words past the end
+    // (the value column is allocated once the widest value is known: a nibble or a byte each)
     if ((rc = p->c_node_pod_begin.alloc((N + 1) * 4, pinned != 0)) || (rc = p->c_pod_meta.alloc(P + 4, pinned != 0)) ||
-        (rc = p->c_ctr_gpu.alloc(C + 4, pinned != 0)) || (rc = p->c_node_cap_val.alloc(N * 8, pinned != 0)) ||
-        (rc = p->c_node_cap_scale.alloc(N, pinned != 0))) {
+        (rc = p->c_node_cap_val.alloc(N * 8, pinned != 0)) || (rc = p->c_node_cap_scale.alloc(N, pinned != 0))) {
         delete p;
         return rc;
     }
     uint32_t *begin = p->c_node_pod_begin.as<uint32_t>();
     uint8_t *meta = p->c_pod_meta.as<uint8_t>();
-    uint8_t *gpu = p->c_ctr_gpu.as<uint8_t>();
-    for (uint64_t k = 0; k < 4; k++) { meta[P + k] = 0; gpu[C + k] = 0; }
+    for (uint64_t k = 0; k < 4; k++) meta[P + k] = 0;
 
-    // Two passes over the rows and two over the containers, each cut into one contiguous range per
-    // host thread (the packing is a memory-bound transform of 2.3 GB into 0.2 GB per 1e8 pods).  A
-    // failure is reported for the LOWEST offending row / container, as a sequential pass would.
+    // One pass over the rows and one over the containers (the wide columns are read ONCE: the packing
+    // is a memory-bound transform of 2.3 GB into 0.2 GB per 1e8 pods), each cut into one contiguous
+    // range per host thread; a short second pass folds the container bytes into nibbles when every value
+    // fits one.  A failure is reported for the LOWEST offending row / container, as a sequential pass would.
     struct Err { uint64_t at = ~0ull; int code = 0; char text[160] = ""; };
     unsigned T = std::thread::hardware_concurrency();
     if (T == 0) T = 1;
@@ -104,14 +105,20 @@ int arena_host_snapshot_pack(const arena_snapshot_view *h, int pinned, arena_pac
     }
     if (P && h->pod_ctr_begin[0] != 0) { delete p; return fail(ARENA_E_INVALID, "pod_ctr_begin[0] != 0"); }
     if (h->pod_ctr_begin[P] != C) { delete p; return fail(ARENA_E_INVALID, "pod_ctr_begin[P] != n_containers"); }
-    // containers: the widest value decides between a byte and a nibble each
+    // containers: Quantity.Value() of each, one byte each into a scratch column; the widest value then
+    // decides between a byte and a nibble each
+    Column bytes;                                        // (plain memory, freed on return)
+    if ((rc = bytes.alloc(C + 8, false))) { delete p; return rc; }
+    uint8_t *wide = bytes.as<uint8_t>();
     std::vector<uint8_t> tops(T, 0);
     run([&](unsigned t) {
         const uint64_t c0 = C * t / T, c1 = C * (t + 1) / T;
         uint8_t top = 0;
         for (uint64_t c = c0; c < c1; c++) {
-            const int64_t v = amount_value(h->ctr_val[c], h->ctr_scale[c]);        // Quantity.Value()
+            const int8_t sc = h->ctr_scale[c];
+            const int64_t v = sc == 0 ? h->ctr_val[c] : amount_value(h->ctr_val[c], sc);       // Quantity.Value()
             if (v < 0 || v > 255) PACK_FAIL(t, c, "no packed form: container %llu holds %lld GPUs (0..255)", (unsigned long long)c, (long long)v);
+            wide[c] = (uint8_t)v;
             top |= (uint8_t)v;
         }
         tops[t] = top;
@@ -120,21 +127,21 @@ int arena_host_snapshot_pack(const arena_snapshot_view *h, int pinned, arena_pac
     uint8_t top = 0;
     for (uint8_t x : tops) top |= x;
     p->v.ctr_bits = top < 16 ? 4 : 8;
+    // sizes are rounded up so that the device can read whole 32-bit words past the end
+    const uint64_t pairs = (C + 1) / 2, gpu_bytes = top < 16 ? pairs : C;
+    if ((rc = p->c_ctr_gpu.alloc(gpu_bytes + 8, pinned != 0))) { delete p; return rc; }
+    uint8_t *gpu = p->c_ctr_gpu.as<uint8_t>();
+    for (uint64_t k = gpu_bytes; k < gpu_bytes + 8; k++) gpu[k] = 0;
+    if (C & 1) wide[C] = 0;                               // the odd container's partner
     if (top < 16) {                          // every container fits a nibble: two per byte, container 2k in the low nibble
-        const uint64_t pairs = (C + 1) / 2;
         run([&](unsigned t) {
             const uint64_t k0 = pairs * t / T, k1 = pairs * (t + 1) / T;
-            for (uint64_t k = k0; k < k1; k++) {
-                const uint8_t lo = (uint8_t)amount_value(h->ctr_val[2 * k], h->ctr_scale[2 * k]);
-                const uint8_t hi = 2 * k + 1 < C ? (uint8_t)amount_value(h->ctr_val[2 * k + 1], h->ctr_scale[2 * k + 1]) : 0;
-                gpu[k] = (uint8_t)(lo | (hi << 4));
-            }
+            for (uint64_t k = k0; k < k1; k++) gpu[k] = (uint8_t)(wide[2 * k] | (wide[2 * k + 1] << 4));
         });
-        for (uint64_t k = pairs; k < pairs + 4 && k < C + 4; k++) gpu[k] = 0;
     } else {
         run([&](unsigned t) {
             const uint64_t c0 = C * t / T, c1 = C * (t + 1) / T;
-            for (uint64_t c = c0; c < c1; c++) gpu[c] = (uint8_t)amount_value(h->ctr_val[c], h->ctr_scale[c]);
+            if (c1 > c0) std::memcpy(gpu + c0, wide + c0, c1 - c0);
         });
     }
 #undef PACK_FAIL
