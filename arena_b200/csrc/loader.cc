@@ -717,22 +717,36 @@ int load(const char *podlist, size_t podlen, const char *nodelist, size_t nodele
     }
     h->pod_names.resize(P); h->pod_namespaces.resize(P); h->pod_host_ip.resize(P);
     std::vector<uint32_t> row_of(P);
-    size_t c = 0;
-    for (size_t row = 0; row < P; row++) {
-        PodRec &r = pods[order[row]];
-        row_of[order[row]] = (uint32_t)row;
-        pod_node[row] = r.node;
-        pod_phase[row] = r.phase;
-        cb[row] = (uint32_t)c;
-        for (size_t k = 0; k < r.ctr_val.size(); k++, c++) { ctr_val[c] = r.ctr_val[k]; ctr_scale[c] = r.ctr_scale[k]; }
-        pod_job[row] = r.job;
-        pod_role[row] = r.role;
-        pod_created[row] = r.created;
-        h->pod_names[row] = std::move(r.name);
-        h->pod_namespaces[row] = std::move(r.ns);
-        h->pod_host_ip[row] = std::move(r.host_ip);
+    {   // CSR offsets first (a running sum in row order), then the rows themselves, which no longer depend on
+        // each other, on a few threads: a row is a dozen scattered reads of its pod record
+        size_t c = 0;
+        for (size_t row = 0; row < P; row++) { cb[row] = (uint32_t)c; c += pods[order[row]].ctr_val.size(); }
+        cb[P] = (uint32_t)c;
     }
-    cb[P] = (uint32_t)c;
+    auto fill = [&](size_t lo, size_t hi) {
+        for (size_t row = lo; row < hi; row++) {
+            PodRec &r = pods[order[row]];
+            row_of[order[row]] = (uint32_t)row;
+            pod_node[row] = r.node;
+            pod_phase[row] = r.phase;
+            size_t c = cb[row];
+            for (size_t k = 0; k < r.ctr_val.size(); k++, c++) { ctr_val[c] = r.ctr_val[k]; ctr_scale[c] = r.ctr_scale[k]; }
+            pod_job[row] = r.job;
+            pod_role[row] = r.role;
+            pod_created[row] = r.created;
+            h->pod_names[row] = std::move(r.name);
+            h->pod_namespaces[row] = std::move(r.ns);
+            h->pod_host_ip[row] = std::move(r.host_ip);
+        }
+    };
+    const unsigned fill_threads = std::min(loader_threads(P / 8), 8u);     // (from ~4000 rows up)
+    if (fill_threads <= 1) fill(0, P);
+    else {
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < fill_threads; t++) pool.emplace_back(fill, P * t / fill_threads, P * (t + 1) / fill_threads);
+        fill(0, P / fill_threads);
+        for (std::thread &th : pool) th.join();
+    }
 
     // chief pod of a tfjob: worker index 0; the LAST match in list order is kept
     // (trainer_tensorflow.go:336-338, 357-372)
