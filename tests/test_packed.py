@@ -183,3 +183,87 @@ def test_packed_snapshot_resident_on_the_device(gpu):
         assert np.array_equal(d_total.cpu().numpy(), tot) and np.array_equal(d_alloc.cpu().numpy(), alloc)
         assert d_cluster.cpu().numpy().tolist() == cl.tolist()
         dev.close()
+
+
+# ---- the arithmetic of the packed kernel's one-pass lane sum -------------------------------------------
+# kernels.cuh packed_lane_sum24 adds up a lane's eight pods in one pass: each pod sets a TOGGLE bit at its first
+# value when its activity differs from the pod before it, a 256-entry table turns eight toggle bits into eight
+# mask nibbles (running parity), and the masked words are summed with byte arithmetic.  This is that arithmetic
+# restated in Python (32-bit wrap-around included) against a plain per-pod loop -- a check of the METHOD on the
+# CPU; the kernel itself is checked against the oracle by the GPU tests above.
+M32 = 0xFFFFFFFF
+
+
+def _shl_clamp(x, n):
+    return 0 if n >= 32 else (x << n) & M32
+
+
+def _active_bytes(m):
+    x = ((m & 0x0F0F0F0F) + 0x05050505) & M32
+    y = (x & 0x1E1E1E1E) ^ 0x08080808
+    return (((y + 0x7F7F7F7F) & M32) >> 7) & 0x01010101
+
+
+def _parity_nibbles(b):
+    m = par = 0
+    for i in range(8):
+        par ^= (b >> i) & 1
+        if par:
+            m |= 0xF << (4 * i)
+    return m
+
+
+_LUT = [_parity_nibbles(b) for b in range(256)]
+
+
+def _lane_sum24(words, cl, ch, al, ah, start, total):
+    funnel_r = lambda lo, hi, sh: ((hi << 32 | lo) >> sh) & M32
+    pre_lo = (cl * 0x01010101) & M32
+    pre_hi = (ch * 0x01010101 + (pre_lo >> 24) * 0x01010101) & M32
+    ex_lo, ex_hi = (pre_lo - cl) & M32, (pre_hi - ch) & M32
+    t_lo = al ^ ((al << 8) & M32)
+    t_hi = ah ^ ((((ah << 32 | al) << 8) >> 32) & M32)
+    sh_lo = ex_lo | (((t_lo ^ 0x01010101) << 5) & M32)
+    sh_hi = ex_hi | (((t_hi ^ 0x01010101) << 5) & M32)
+    d = _shl_clamp(ah >> 24, pre_hi >> 24)
+    for w in (sh_lo, sh_hi):
+        for j in range(4):
+            d ^= _shl_clamp(1, (w >> (8 * j)) & 0xFF)
+    par = lambda x: bin(x).count("1") & 1
+    m = [_LUT[d & 0xFF], _LUT[(d >> 8) & 0xFF] ^ (M32 if par(d & 0xFF) else 0), _LUT[(d >> 16) & 0xFF] ^ (M32 if par(d & 0xFFFF) else 0)]
+    w, sh = start >> 3, (start & 7) * 4
+    y = 0
+    for k in range(3 if total > 16 else 2):
+        v = funnel_r(words[w + k], words[w + k + 1], sh) & m[k]
+        y += (v & 0x0F0F0F0F) + ((v >> 4) & 0x0F0F0F0F)
+    y = (y & 0x00FF00FF) + ((y >> 8) & 0x00FF00FF)
+    return ((y * 0x00010001) & M32) >> 16
+
+
+def test_one_pass_lane_sum_arithmetic():
+    import random
+    rng = random.Random(2)
+    for _ in range(20000):
+        n = rng.randint(0, 8)
+        cnts, tot = [], 0
+        for j in range(8):
+            c = rng.choice([0, 1, 1, 2, 2, 3, 4, 7, 15]) if j < n else 0
+            if tot + c > 24:
+                c = 0
+            cnts.append(c)
+            tot += c
+        phases = [rng.choice([0, 1, 2, 3, 4, 5, 15, 2, 2, 3]) if j < n else 0 for j in range(8)]
+        start = rng.randint(0, 40)
+        nib = [rng.randint(0, 15) for _ in range(start + tot + 48)]
+        words = [sum(nib[8 * k + i] << (4 * i) for i in range(8)) for k in range(len(nib) // 8)]
+        meta = [(cnts[j] << 4) | phases[j] for j in range(8)]
+        m_lo = sum(meta[j] << (8 * j) for j in range(4))
+        m_hi = sum(meta[4 + j] << (8 * j) for j in range(4))
+        got = _lane_sum24(words, (m_lo >> 4) & 0x0F0F0F0F, (m_hi >> 4) & 0x0F0F0F0F, _active_bytes(m_lo), _active_bytes(m_hi), start, tot)
+        want, pos = 0, start
+        for j in range(8):
+            v = sum(nib[pos:pos + cnts[j]])
+            pos += cnts[j]
+            if phases[j] not in (3, 4):
+                want += v
+        assert got == want, (cnts, phases, start)
