@@ -32,7 +32,9 @@
  *
  * Parity status: the reference has no tests or golden vectors for this path
  * and cannot be compiled here (Go, no toolchain): "parity unpinned" by the
- * reference; pinned by the hand-derived vectors under tests/golden/.
+ * reference; pinned by the hand-derived vectors under tests/golden/ and, for
+ * quantity_value, by the worked examples of the reference's own doc comments
+ * (tests/test_reference_examples.py).
  *
  * All int64 accumulation wraps like Go's `+=`: done in uint64_t here because
  * signed overflow is undefined in C.

@@ -25,7 +25,11 @@ Parity status: the reference holds NO test or golden vector for this code
 (vendored tests are pruned, Gopkg.toml:56-58) and no Go toolchain exists in the
 build container, so the known-answer table in tests/golden/quantity_kat.json
 was derived by hand from the lines cited above ("parity unpinned" by the
-reference's own tests; pinned by hand-derived vectors).
+reference's own tests; pinned by hand-derived vectors).  The only answers the
+reference itself states are the worked examples in its doc comments
+(quantity.go:52, 55-58, 69-74, 524-526; amount.go:90-94; math.go:170-172;
+suffix.go:88-106): tests/test_reference_examples.py holds this module, the C
+oracle and the product's parser to them.
 """
 
 from __future__ import annotations
