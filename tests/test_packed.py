@@ -43,6 +43,10 @@ def test_pack_is_the_wide_snapshot_in_fewer_bytes(built, skewed, P, N):
     assert np.array_equal(meta >> 4, np.diff(h.cols["pod_ctr_begin"]).astype(np.uint8))
     want = np.array([cref.quantity_value(int(v), int(s)) for v, s in zip(h.cols["ctr_val"][:2000], h.cols["ctr_scale"][:2000])])
     assert np.array_equal(gpu[:2000].astype(np.int64), want)
+    # every container, vectorised: the generator only writes scale 0 and scale -3 ("500m": rounded up)
+    v, sc = h.cols["ctr_val"], h.cols["ctr_scale"]
+    assert set(np.unique(sc).tolist()) <= {0, -3}
+    assert np.array_equal(gpu.astype(np.int64), np.where(sc == 0, v, -((-v) // 1000)))
     assert p.nbytes < h.algorithmic_bytes_top_node() / 5
 
 
